@@ -1,0 +1,100 @@
+"""ctypes binding of libb200llm.so (the C-ABI declared in include/b200llm.h).
+
+There is deliberately no fallback: if the shared library is missing or a call returns a
+non-zero status this module raises. The signatures below are the single Python-side copy of
+the header; tests/test_abi.py checks that every symbol the header declares is exported.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200llm.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200llm.h")
+
+_lib = None
+
+P = C.c_void_p
+I64 = C.c_int64
+I = C.c_int
+F = C.c_float
+SZ = C.c_size_t
+
+# name -> (restype, argtypes)
+SIGNATURES = {
+    "b200_version": (I, []),
+    "b200_init": (I, [I]),
+    "b200_last_error": (C.c_char_p, []),
+    "b200_launch_count": (C.c_uint64, []),
+    "b200_gemm_nt_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, I, P]),
+    "b200_gemm_ex": (I, [P, I64, I, P, I64, I, I64, P, I64, I, P, I64, I, I64, P, P, I64, P, I64,
+                         I64, I64, I, I, I, I, F, I, P]),
+    "b200_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I, I, F, I64, I64, I64, P]),
+    "b200_rmsnorm_fwd_bf16": (I, [P, P, P, P, P, I64, I64, F, I, P]),
+    "b200_rmsnorm_bwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),
+    "b200_rmsnorm_fwd_f32": (I, [P, P, P, I64, I64, F, P]),
+    "b200_rmsnorm_bwd_f32": (I, [P, P, P, P, P, I64, I64, F, P]),
+    "b200_layernorm_fwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),
+    "b200_layernorm_bwd_bf16": (I, [P, P, P, P, P, P, P, P, I64, I64, P]),
+    "b200_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, I, P]),
+    "b200_swiglu_bwd_bf16": (I, [P, I64, P, P, I64, I64, I64, P]),
+    "b200_gelu_fwd_bf16": (I, [P, P, I64, P]),
+    "b200_gelu_bwd_bf16": (I, [P, P, P, I64, P]),
+    "b200_rope_bf16": (I, [P, I64, P, P, I64, I64, I64, I64, I, I, P]),
+    "b200_embedding_fwd_bf16": (I, [P, P, P, P, I64, I64, I64, I64, P]),
+    "b200_embedding_bwd_f32acc": (I, [P, P, P, P, I64, I64, I64, I64, P]),
+    "b200_cross_entropy_workspace_bytes": (SZ, [I64]),
+    "b200_cross_entropy_bf16": (I, [P, I64, P, P, I64, I64, I, P, SZ, P]),
+    "b200_grad_norm_workspace_bytes": (SZ, [I64]),
+    "b200_grad_norm_bf16": (I, [P, I64, F, P, P, SZ, P]),
+    "b200_adamw_bf16": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P]),
+    "b200_adamw_f32": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P]),
+    "b200_cast_f32_to_bf16": (I, [P, P, I64, P]),
+    "b200_cast_bf16_to_f32": (I, [P, P, I64, P]),
+    "b200_transpose_bf16": (I, [P, I64, P, I64, I64, I64, F, P]),
+    "b200_add_bf16": (I, [P, P, P, I64, P]),
+    "b200_attention_fwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, I64, I64, F, P]),
+    "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, P, I64, P, I64, P,
+                                    I64, I64, I64, I64, I64, I64, F, P]),
+}
+
+
+def header_symbols(path: str = HEADER_PATH) -> list[str]:
+    """All function names declared in include/b200llm.h."""
+    text = open(path).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def load() -> C.CDLL:
+    """Load libb200llm.so, binding every signature. Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU or library fallback for the b200llm ops)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def check(status: int, what: str = "") -> None:
+    if status != 0:
+        msg = load().b200_last_error().decode(errors="replace")
+        raise B200Error(f"b200llm {what} failed with status {status}: {msg}")
+
+
+def launch_count() -> int:
+    return int(load().b200_launch_count())

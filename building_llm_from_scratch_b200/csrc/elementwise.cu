@@ -1,0 +1,397 @@
+// K5/K5'/K6/K7/K9 — SwiGLU, GELU, RoPE, embedding gather/scatter, casts, transpose, add.
+// All HBM-bound: 128-bit loads/stores, grid sized as a multiple of the SM count, grid-stride.
+#include "common.cuh"
+
+namespace {
+
+inline int ew_grid(long long nvec, int threads) {
+  long long blocks = (nvec + threads - 1) / threads;
+  const long long cap = (long long)b200_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+
+// ---------------- SwiGLU ----------------
+// Reference (common_components.py:87,123): silu(a) = a * sigmoid(a) -> bf16 each op, then * b.
+// Algorithmic bytes: fwd 6 B per output element (read a, b; write h), bwd 10 B.
+__global__ void __launch_bounds__(256)
+swiglu_fwd_kernel(const bf16* __restrict__ ab, long long ldab, bf16* __restrict__ h, long long M,
+                  int F, int bf16_steps) {
+  const int fv = F >> 3;
+  const long long total = M * fv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / fv;
+    const int c = (int)(i % fv) * 8;
+    float a[8], b[8], o[8];
+    unpack8(ld_nc_v4(ab + row * ldab + c), a);
+    unpack8(ld_nc_v4(ab + row * ldab + F + c), b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = sigmoidf_(a[j]);
+      if (bf16_steps) {
+        s = bf16_round(s);
+        o[j] = bf16_round(a[j] * s) * b[j];
+      } else {
+        o[j] = a[j] * s * b[j];
+      }
+    }
+    st_v4(h + row * F + c, pack8(o));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+swiglu_bwd_kernel(const bf16* __restrict__ ab, long long ldab, const bf16* __restrict__ dh,
+                  bf16* __restrict__ dab, long long lddab, long long M, int F) {
+  const int fv = F >> 3;
+  const long long total = M * fv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / fv;
+    const int c = (int)(i % fv) * 8;
+    float a[8], b[8], g[8], da[8], db[8];
+    unpack8(ld_nc_v4(ab + row * ldab + c), a);
+    unpack8(ld_nc_v4(ab + row * ldab + F + c), b);
+    unpack8(ld_nc_v4(dh + row * F + c), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float s = sigmoidf_(a[j]);
+      const float silu = a[j] * s;
+      da[j] = g[j] * b[j] * (s * (1.f + a[j] * (1.f - s)));
+      db[j] = g[j] * silu;
+    }
+    st_v4(dab + row * lddab + c, pack8(da));
+    st_v4(dab + row * lddab + F + c, pack8(db));
+  }
+}
+
+// ---------------- GELU (erf) ----------------
+__global__ void __launch_bounds__(256)
+gelu_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long n) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld_nc_v4(x + i * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = 0.5f * f[j] * (1.f + erff(f[j] * 0.70710678118654752440f));
+    st_v4(y + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) {
+      const float f = __bfloat162float(x[k]);
+      y[k] = __float2bfloat16_rn(0.5f * f * (1.f + erff(f * 0.70710678118654752440f)));
+    }
+}
+
+__device__ __forceinline__ float gelu_grad(float x) {
+  const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+__global__ void __launch_bounds__(256)
+gelu_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                long long n) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8], g[8];
+    unpack8(ld_nc_v4(x + i * 8), f);
+    unpack8(ld_nc_v4(dy + i * 8), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = g[j] * gelu_grad(f[j]);
+    st_v4(dx + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k)
+      dx[k] = __float2bfloat16_rn(__bfloat162float(dy[k]) * gelu_grad(__bfloat162float(x[k])));
+}
+
+// ---------------- RoPE (rotate-half, in place) ----------------
+// Reference (common_components.py:24-35): x*cos + cat(-x2, x1)*sin, bf16 tables, every op
+// rounds to bf16. Each thread owns 8 columns of the first half and the matching 8 of the second.
+__global__ void __launch_bounds__(256)
+rope_kernel(bf16* __restrict__ x, long long ld, const bf16* __restrict__ cosT,
+            const bf16* __restrict__ sinT, long long B, int T, int nheads, int hd, int inverse,
+            int bf16_steps) {
+  const int half = hd >> 1;
+  const int vh = half >> 3;  // vectors per half head
+  const long long total = B * T * (long long)nheads * vh;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vh);
+    const long long rest = i / vh;
+    const int head = (int)(rest % nheads);
+    const long long tok = rest / nheads;
+    const int t = (int)(tok % T);
+    bf16* p1 = x + tok * ld + (long long)head * hd + v * 8;
+    bf16* p2 = p1 + half;
+    float x1[8], x2[8], c1[8], c2[8], s1[8], s2[8], o1[8], o2[8];
+    unpack8(ld_v4(p1), x1);
+    unpack8(ld_v4(p2), x2);
+    unpack8(ld_nc_v4(cosT + (long long)t * hd + v * 8), c1);
+    unpack8(ld_nc_v4(cosT + (long long)t * hd + half + v * 8), c2);
+    unpack8(ld_nc_v4(sinT + (long long)t * hd + v * 8), s1);
+    unpack8(ld_nc_v4(sinT + (long long)t * hd + half + v * 8), s2);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (!inverse) {
+        if (bf16_steps) {
+          o1[j] = bf16_round(x1[j] * c1[j]) + bf16_round(-x2[j] * s1[j]);
+          o2[j] = bf16_round(x2[j] * c2[j]) + bf16_round(x1[j] * s2[j]);
+        } else {
+          o1[j] = x1[j] * c1[j] - x2[j] * s1[j];
+          o2[j] = x2[j] * c2[j] + x1[j] * s2[j];
+        }
+      } else {
+        // transpose of the map above: dx1 = dy1*c1 + dy2*s2, dx2 = dy2*c2 - dy1*s1
+        o1[j] = x1[j] * c1[j] + x2[j] * s2[j];
+        o2[j] = x2[j] * c2[j] - x1[j] * s1[j];
+      }
+    }
+    st_v4(p1, pack8(o1));
+    st_v4(p2, pack8(o2));
+  }
+}
+
+// ---------------- embedding ----------------
+__global__ void __launch_bounds__(256)
+embedding_fwd_kernel(const long long* __restrict__ idx, const bf16* __restrict__ tok_w,
+                     const bf16* __restrict__ pos_w, bf16* __restrict__ out, long long M, int T,
+                     int d, long long vocab) {
+  const int dv = d >> 3;
+  const long long total = M * dv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / dv;
+    const int c = (int)(i % dv) * 8;
+    long long id = idx[row];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    uint4 v = ld_nc_v4(tok_w + id * d + c);
+    if (pos_w != nullptr) {
+      float a[8], b[8];
+      unpack8(v, a);
+      unpack8(ld_nc_v4(pos_w + (row % T) * d + c), b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] += b[j];
+      v = pack8(a);
+    }
+    st_v4(out + row * d + c, v);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+embedding_bwd_kernel(const long long* __restrict__ idx, const bf16* __restrict__ dout,
+                     float* __restrict__ dtok, float* __restrict__ dpos, long long M, int T, int d,
+                     long long vocab) {
+  const int dv = d >> 3;
+  const long long total = M * dv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / dv;
+    const int c = (int)(i % dv) * 8;
+    const long long id = idx[row];
+    if (id < 0 || id >= vocab) continue;
+    float g[8];
+    unpack8(ld_nc_v4(dout + row * d + c), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&dtok[id * d + c + j], g[j]);
+      if (dpos != nullptr) atomicAdd(&dpos[(row % T) * d + c + j], g[j]);
+    }
+  }
+}
+
+// ---------------- casts ----------------
+__global__ void __launch_bounds__(256)
+cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float4 a = *reinterpret_cast<const float4*>(in + i * 8);
+    const float4 b = *reinterpret_cast<const float4*>(in + i * 8 + 4);
+    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    st_v4(out + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) out[k] = __float2bfloat16_rn(in[k]);
+}
+
+__global__ void __launch_bounds__(256)
+cast_bf16_f32_kernel(const bf16* __restrict__ in, float* __restrict__ out, long long n) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld_nc_v4(in + i * 8), f);
+    *reinterpret_cast<float4*>(out + i * 8) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(out + i * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) out[k] = __bfloat162float(in[k]);
+}
+
+// ---------------- add ----------------
+__global__ void __launch_bounds__(256)
+add_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ out,
+           long long n) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8], g[8];
+    unpack8(ld_nc_v4(a + i * 8), f);
+    unpack8(ld_nc_v4(b + i * 8), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] += g[j];
+    st_v4(out + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k)
+      out[k] = __float2bfloat16_rn(__bfloat162float(a[k]) + __bfloat162float(b[k]));
+}
+
+// ---------------- transpose (out[c][r] = alpha * in[r][c]) ----------------
+__global__ void __launch_bounds__(256)
+transpose_kernel(const bf16* __restrict__ in, long long ldi, bf16* __restrict__ out, long long ldo,
+                 int rows, int cols, float alpha) {
+  __shared__ bf16 tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = r0 + ty + k * 8, c = c0 + tx;
+    if (r < rows && c < cols) tile[ty + k * 8][tx] = in[(long long)r * ldi + c];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int c = c0 + ty + k * 8, r = r0 + tx;
+    if (r < rows && c < cols)
+      out[(long long)c * ldo + r] = __float2bfloat16_rn(alpha * __bfloat162float(tile[tx][ty + k * 8]));
+  }
+}
+
+}  // namespace
+
+extern "C" int b200_swiglu_fwd_bf16(const void* ab, int64_t ldab, void* h, int64_t M, int64_t F,
+                                    int bf16_steps, void* stream) {
+  B200_CHECK_ARG(ab && h && M > 0 && F > 0, "swiglu_fwd: null pointer or empty");
+  B200_CHECK_ARG(F % 8 == 0 && ldab % 8 == 0 && ldab >= 2 * F, "swiglu_fwd: F and ldab must be multiples of 8, ldab >= 2F");
+  B200_CHECK_ARG(b200_aligned16(ab) && b200_aligned16(h), "swiglu_fwd: pointers must be 16-B aligned");
+  swiglu_fwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)ab, ldab, (bf16*)h, M, (int)F, bf16_steps);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_swiglu_bwd_bf16(const void* ab, int64_t ldab, const void* dh, void* dab,
+                                    int64_t lddab, int64_t M, int64_t F, void* stream) {
+  B200_CHECK_ARG(ab && dh && dab && M > 0 && F > 0, "swiglu_bwd: null pointer or empty");
+  B200_CHECK_ARG(F % 8 == 0 && ldab % 8 == 0 && lddab % 8 == 0 && ldab >= 2 * F && lddab >= 2 * F,
+                 "swiglu_bwd: F, ldab, lddab must be multiples of 8 and pitches >= 2F");
+  swiglu_bwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)ab, ldab, (const bf16*)dh, (bf16*)dab, lddab, M, (int)F);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_gelu_fwd_bf16(const void* x, void* y, int64_t n, void* stream) {
+  B200_CHECK_ARG(x && y && n > 0, "gelu_fwd: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y), "gelu_fwd: pointers must be 16-B aligned");
+  gelu_fwd_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, n);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_gelu_bwd_bf16(const void* x, const void* dy, void* dx, int64_t n, void* stream) {
+  B200_CHECK_ARG(x && dy && dx && n > 0, "gelu_bwd: null pointer or empty");
+  gelu_bwd_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, (const bf16*)dy, (bf16*)dx, n);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_rope_bf16(void* x, int64_t ld, const void* cos, const void* sin, int64_t B,
+                              int64_t T, int64_t nheads, int64_t hd, int inverse, int bf16_steps,
+                              void* stream) {
+  B200_CHECK_ARG(x && cos && sin && B > 0 && T > 0 && nheads > 0, "rope: null pointer or empty");
+  B200_CHECK_ARG(hd % 16 == 0 && ld % 8 == 0 && ld >= nheads * hd, "rope: hd must be a multiple of 16, ld a multiple of 8 and >= nheads*hd");
+  B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(cos) && b200_aligned16(sin), "rope: pointers must be 16-B aligned");
+  const long long total = B * T * nheads * (hd / 16);
+  rope_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (bf16*)x, ld, (const bf16*)cos, (const bf16*)sin, B, (int)T, (int)nheads, (int)hd, inverse, bf16_steps);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_embedding_fwd_bf16(const int64_t* idx, const void* tok_w, const void* pos_w,
+                                       void* out, int64_t M, int64_t T, int64_t d, int64_t vocab,
+                                       void* stream) {
+  B200_CHECK_ARG(idx && tok_w && out && M > 0 && T > 0 && vocab > 0, "embedding_fwd: null pointer or empty");
+  B200_CHECK_ARG(d % 8 == 0 && d > 0, "embedding_fwd: d must be a multiple of 8");
+  embedding_fwd_kernel<<<ew_grid(M * (d / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)idx, (const bf16*)tok_w, (const bf16*)pos_w, (bf16*)out, M, (int)T, (int)d, vocab);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_embedding_bwd_f32acc(const int64_t* idx, const void* dout, float* dtok_w,
+                                         float* dpos_w, int64_t M, int64_t T, int64_t d,
+                                         int64_t vocab, void* stream) {
+  B200_CHECK_ARG(idx && dout && dtok_w && M > 0 && T > 0 && vocab > 0, "embedding_bwd: null pointer or empty");
+  B200_CHECK_ARG(d % 8 == 0 && d > 0, "embedding_bwd: d must be a multiple of 8");
+  embedding_bwd_kernel<<<ew_grid(M * (d / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)idx, (const bf16*)dout, dtok_w, dpos_w, M, (int)T, (int)d, vocab);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream) {
+  B200_CHECK_ARG(in && out && n > 0, "cast: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(in) && b200_aligned16(out), "cast: pointers must be 16-B aligned");
+  cast_f32_bf16_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(in, (bf16*)out, n);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream) {
+  B200_CHECK_ARG(in && out && n > 0, "cast: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(in) && b200_aligned16(out), "cast: pointers must be 16-B aligned");
+  cast_bf16_f32_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)in, out, n);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream) {
+  B200_CHECK_ARG(a && b && out && n > 0, "add: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(a) && b200_aligned16(b) && b200_aligned16(out), "add: pointers must be 16-B aligned");
+  add_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)a, (const bf16*)b, (bf16*)out, n);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_transpose_bf16(const void* in, int64_t ldi, void* out, int64_t ldo, int64_t rows,
+                                   int64_t cols, float alpha, void* stream) {
+  B200_CHECK_ARG(in && out && rows > 0 && cols > 0, "transpose: null pointer or empty");
+  B200_CHECK_ARG(ldi >= cols && ldo >= rows, "transpose: pitches too small");
+  dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
+  B200_CHECK_ARG(grid.y <= 65535, "transpose: too many rows for one launch");
+  transpose_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)in, ldi, (bf16*)out, ldo, (int)rows, (int)cols, alpha);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}

@@ -1,0 +1,415 @@
+// K1 — bf16 GEMM on tcgen05 / TMEM fed by TMA (sm_100a).
+//
+//   C[M,N] = alpha * ( opA1·opB1^T + opA2·opB2^T ) (+ bias) (gelu) (+ R)
+//
+// One persistent CTA per SM, 256 threads, warp-specialised:
+//   warp 0   : TMA producer (one lane)  — global -> 128B-swizzled smem ring (192 KB)
+//   warp 1   : MMA issuer  (one lane)   — tcgen05.mma 128 x BN x 16, fp32 accumulators in TMEM
+//   warp 2   : TMEM allocator / deallocator
+//   warps 4-7: epilogue — tcgen05.ld TMEM -> registers -> bias/GELU/residual -> global
+// The accumulator is double buffered in TMEM (2 x BN columns) so the epilogue of tile i
+// overlaps the main loop of tile i+1. The second operand pair is the rank-r LoRA update
+// (lora.py:26): extra K blocks accumulated into the same TMEM tile. Either operand of either
+// pair may be K-major ([rows, K], K contiguous) or MN-major ([K, rows], rows contiguous);
+// MN-major tiles are fetched as 64-wide panels and described to the MMA with the MN-major
+// shared-memory descriptor, so backward GEMMs (dX = dY·W, dW = dY^T·X) need no transposes.
+//
+// Roofline: tensor pipe. Algorithmic FLOPs per launch = 2·M·N·(K1+K2).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int A_BYTES = BM * BK * 2;  // 16 KB
+constexpr int RING_BYTES = 192 * 1024;
+
+enum : int {
+  EP_BIAS = 1,
+  EP_GELU = 2,
+  EP_RESIDUAL = 4,
+  EP_OUT_F32 = 8,
+  EP_ATOMIC = 16,
+  EP_TRANS_OUT = 32,
+};
+
+struct GemmParams {
+  int M, N;
+  int kb1, kb2;  // 64-wide K blocks of the main / LoRA product
+  int a1_mn, b1_mn, a2_mn, b2_mn;
+  int splits;
+  int m_tiles, n_tiles;
+  int flags;
+  float alpha;
+  const bf16* bias;
+  const bf16* R;
+  long long ldr;
+  void* C;
+  long long ldc;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+template <int BN>
+__global__ void __launch_bounds__(256, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                    const GemmParams p) {
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGES = RING_BYTES / STAGE_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BN;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB1);
+    if (p.kb2 > 0) {
+      tma_prefetch_desc(&tmA2);
+      tma_prefetch_desc(&tmB2);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_kb = p.kb1 + p.kb2;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+  const int num_work = num_tiles * p.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer ----------------
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int split = w / num_tiles, tile = w % num_tiles;
+        const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+        const int kb_begin = (int)((long long)split * total_kb / p.splits);
+        const int kb_end = (int)((long long)(split + 1) * total_kb / p.splits);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], STAGE_BYTES);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const bool ext = kb >= p.kb1;
+          const int kk = (ext ? kb - p.kb1 : kb) * BK;
+          const CUtensorMap* ma = ext ? &tmA2 : &tmA1;
+          const CUtensorMap* mb = ext ? &tmB2 : &tmB1;
+          const int a_mn = ext ? p.a2_mn : p.a1_mn;
+          const int b_mn = ext ? p.b2_mn : p.b1_mn;
+          if (!a_mn) {
+            tma_load_2d(sa, ma, &full[stage], kk, m_blk * BM);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)
+              tma_load_2d(sa + i * 8192, ma, &full[stage], m_blk * BM + i * 64, kk);
+          }
+          if (!b_mn) {
+            tma_load_2d(sb, mb, &full[stage], kk, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tma_load_2d(sb + i * 8192, mb, &full[stage], n_blk * BN + i * 64, kk);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++it) {
+        const int split = w / num_tiles;
+        const int kb_begin = (int)((long long)split * total_kb / p.splits);
+        const int kb_end = (int)((long long)(split + 1) * total_kb / p.splits);
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tempty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+          const bool ext = kb >= p.kb1;
+          const int a_mn = ext ? p.a2_mn : p.a1_mn;
+          const int b_mn = ext ? p.b2_mn : p.b1_mn;
+          const uint32_t idesc = umma_idesc_bf16(BM, BN, (uint32_t)a_mn, (uint32_t)b_mn);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = a_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
+            const uint64_t bd = b_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
+            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull[as]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ---------------- epilogue ----------------
+    const int ew = warp - 4;  // == warp % 4: the TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++it) {
+      const int tile = w % num_tiles;
+      const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(&tfull[as], aph);
+      tc_fence_after();
+      const long long row = (long long)m_blk * BM + ew * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BN + c * 32);
+        tmem_ld_32x32(taddr, r);
+        tmem_ld_wait();
+        const long long col0 = (long long)n_blk * BN + c * 32;
+        if (col0 >= p.N) continue;
+        const bool full_cols = col0 + 32 <= p.N;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+        if (p.flags & EP_BIAS) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+        }
+        if (p.flags & EP_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        }
+        if (p.flags & EP_TRANS_OUT) {
+          // C is [N, M]-shaped in memory: element (row, col) goes to C[col * ldc + row]
+          if (row_ok) {
+            if (p.flags & EP_OUT_F32) {
+              float* C = (float*)p.C;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.N) {
+                  if (p.flags & EP_ATOMIC) atomicAdd(&C[(col0 + j) * p.ldc + row], v[j]);
+                  else C[(col0 + j) * p.ldc + row] = v[j];
+                }
+            } else {
+              bf16* C = (bf16*)p.C;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.N) C[(col0 + j) * p.ldc + row] = __float2bfloat16_rn(v[j]);
+            }
+          }
+          continue;
+        }
+        if (!row_ok) continue;
+        if (p.flags & EP_RESIDUAL) {
+          const bf16* R = p.R + row * p.ldr + col0;
+          if (full_cols && (p.ldr & 7) == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float f[8];
+              unpack8(ld_v4(R + q * 8), f);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[q * 8 + j] += f[j];
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) v[j] += __bfloat162float(R[j]);
+          }
+        }
+        if (p.flags & EP_OUT_F32) {
+          float* C = (float*)p.C + row * p.ldc + col0;
+          if (p.flags & EP_ATOMIC) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) atomicAdd(&C[j], v[j]);
+          } else if (full_cols && (p.ldc & 3) == 0) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              *reinterpret_cast<float4*>(C + q * 4) =
+                  make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) C[j] = v[j];
+          }
+        } else {
+          bf16* C = (bf16*)p.C + row * p.ldc + col0;
+          if (full_cols && (p.ldc & 7) == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) st_v4(C + q * 8, pack8(&v[q * 8]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) C[j] = __float2bfloat16_rn(v[j]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int BN>
+int launch_bn(const CUtensorMap* maps, const GemmParams& p, int grid, cudaStream_t st) {
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGES = RING_BYTES / STAGE_BYTES;
+  constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + (2 * STAGES + 4) * 8 + 16;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_set[dev] = true;
+  }
+  gemm_tcgen05_kernel<BN><<<grid, 256, SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], p);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+struct Operand {
+  const void* ptr;
+  int64_t ld;
+  int mn_major;  // 0: [rows, K] K contiguous, 1: [K, rows] rows contiguous
+};
+
+int make_operand_map(CUtensorMap* map, const Operand& o, int64_t rows, int64_t K, int box_rows) {
+  if (!o.mn_major) return b200_make_tmap_2d_bf16(map, o.ptr, (uint64_t)rows, (uint64_t)K, (uint64_t)o.ld, (uint32_t)box_rows, BK);
+  // stored [K, rows]: box = 64 K-rows x 64 contiguous MN elements
+  return b200_make_tmap_2d_bf16(map, o.ptr, (uint64_t)K, (uint64_t)rows, (uint64_t)o.ld, BK, 64);
+}
+
+}  // namespace
+
+extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_t ldb1,
+                            int b1_mn, int64_t K1, const void* A2, int64_t lda2, int a2_mn,
+                            const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
+                            const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
+                            int flags, int out_f32, int accumulate, int trans_out, float alpha,
+                            int splitk, void* stream) {
+  B200_CHECK_ARG(M > 0 && N > 0 && K1 > 0 && K2 >= 0, "gemm: bad sizes M=%lld N=%lld K1=%lld K2=%lld",
+                 (long long)M, (long long)N, (long long)K1, (long long)K2);
+  B200_CHECK_ARG(A1 && B1 && C, "gemm: null operand");
+  B200_CHECK_ARG(K2 == 0 || (A2 && B2), "gemm: K2 > 0 needs A2 and B2");
+  B200_CHECK_ARG(!(flags & B200_GEMM_BIAS) || bias, "gemm: bias flag without bias pointer");
+  B200_CHECK_ARG(!(flags & B200_GEMM_RESIDUAL) || R, "gemm: residual flag without R pointer");
+  B200_CHECK_ARG(!(accumulate && !out_f32), "gemm: accumulate needs fp32 output");
+  B200_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31) && K1 < (1ll << 31), "gemm: sizes exceed int32");
+
+  const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  GemmParams p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.kb1 = (int)((K1 + BK - 1) / BK);
+  p.kb2 = (int)((K2 + BK - 1) / BK);
+  p.a1_mn = a1_mn; p.b1_mn = b1_mn; p.a2_mn = a2_mn; p.b2_mn = b2_mn;
+  p.m_tiles = (int)((M + BM - 1) / BM);
+  p.n_tiles = (int)((N + BN - 1) / BN);
+  p.alpha = alpha;
+  p.bias = (const bf16*)bias;
+  p.R = (const bf16*)R;
+  p.ldr = ldr;
+  p.C = C;
+  p.ldc = ldc;
+  p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0);
+
+  const int sms = b200_num_sms();
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int total_kb = p.kb1 + p.kb2;
+  int splits = 1;
+  if (accumulate) {
+    if (splitk > 0) splits = splitk;
+    else if (tiles * 2 <= sms) splits = sms / tiles;
+    if (splits > total_kb) splits = total_kb;
+    if (splits < 1) splits = 1;
+    p.flags |= EP_ATOMIC;
+  }
+  p.splits = splits;
+
+  CUtensorMap maps[4];
+  int rc;
+  Operand oa1{A1, lda1, a1_mn}, ob1{B1, ldb1, b1_mn};
+  if ((rc = make_operand_map(&maps[0], oa1, M, K1, BM))) return rc;
+  if ((rc = make_operand_map(&maps[1], ob1, N, K1, BN))) return rc;
+  if (K2 > 0) {
+    Operand oa2{A2, lda2, a2_mn}, ob2{B2, ldb2, b2_mn};
+    if ((rc = make_operand_map(&maps[2], oa2, M, K2, BM))) return rc;
+    if ((rc = make_operand_map(&maps[3], ob2, N, K2, BN))) return rc;
+  } else {
+    maps[2] = maps[0];
+    maps[3] = maps[1];
+  }
+  const int work = tiles * splits;
+  const int grid = work < sms ? work : sms;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (BN) {
+    case 64: return launch_bn<64>(maps, p, grid, st);
+    case 128: return launch_bn<128>(maps, p, grid, st);
+    default: return launch_bn<256>(maps, p, grid, st);
+  }
+}
+
+extern "C" int b200_gemm_nt_bf16(const void* A1, int64_t lda1, const void* B1, int64_t ldb1,
+                                 int64_t K1, const void* A2, int64_t lda2, const void* B2,
+                                 int64_t ldb2, int64_t K2, const void* bias, const void* R,
+                                 int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N, int flags,
+                                 void* stream) {
+  return b200_gemm_ex(A1, lda1, 0, B1, ldb1, 0, K1, A2, lda2, 0, B2, ldb2, 0, K2, bias, R, ldr, C,
+                      ldc, M, N, flags, 0, 0, 0, 1.0f, 0, stream);
+}
+
+extern "C" int b200_gemm_bf16(const void* A, int64_t lda, int transa, const void* B, int64_t ldb,
+                              int transb, void* C, int64_t ldc, int out_f32, int accumulate,
+                              float alpha, int64_t M, int64_t N, int64_t K, void* stream) {
+  return b200_gemm_ex(A, lda, transa, B, ldb, transb, K, nullptr, 0, 0, nullptr, 0, 0, 0, nullptr,
+                      nullptr, 0, C, ldc, M, N, 0, out_f32, accumulate, 0, alpha, 0, stream);
+}

@@ -1,0 +1,289 @@
+// K3 (materialised-logits form), K8a, K8b — cross-entropy fwd+bwd, gradient norm, AdamW.
+// All HBM-bound. Algorithmic bytes: CE 6 B per logit for a non-ignored row (read twice from
+// L2/HBM, write grad) and 2 B for an ignored row (write zeros); grad-norm 2 B/param;
+// AdamW 14 B/param (bf16) or 28 B/param (fp32).
+#include "common.cuh"
+
+namespace {
+
+constexpr int CE_THREADS = 512;
+
+// ws layout (floats): [0] valid count, [1] 1/valid, [2..2+M) per-row loss
+__global__ void __launch_bounds__(256)
+ce_count_kernel(const long long* __restrict__ targets, long long M, float* __restrict__ ws) {
+  __shared__ float red[33];
+  float c = 0.f;
+  for (long long i = threadIdx.x; i < M; i += blockDim.x) c += (targets[i] != -100) ? 1.f : 0.f;
+  c = block_sum(c, red);
+  if (threadIdx.x == 0) {
+    ws[0] = c;
+    ws[1] = 1.f / c;  // inf when everything is ignored -> loss = 0 * inf = NaN like the reference
+  }
+}
+
+// One CTA per row. Pass 1: online max / sum-exp over the row; pass 2 (row now L2 resident):
+// grad = (softmax - onehot) / n_valid written in place. Ignored rows just get zeros.
+__global__ void __launch_bounds__(CE_THREADS)
+ce_row_kernel(bf16* __restrict__ logits, long long ld, const long long* __restrict__ targets,
+              float* __restrict__ ws, long long M, int V, int write_grad) {
+  __shared__ float red[33];
+  const int nvec = (V + 7) >> 3;
+  for (long long row = blockIdx.x; row < M; row += gridDim.x) {
+    bf16* lrow = logits + row * ld;
+    const long long tgt = targets[row];
+    if (tgt == -100) {
+      if (threadIdx.x == 0) ws[2 + row] = 0.f;
+      if (write_grad) {
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int i = threadIdx.x; i < nvec; i += CE_THREADS) {
+          if (i * 8 + 8 <= V) st_v4(lrow + i * 8, z);
+          else
+            for (int j = i * 8; j < V; ++j) lrow[j] = __float2bfloat16_rn(0.f);
+        }
+      }
+      continue;
+    }
+    float m = -INFINITY, s = 0.f;
+    for (int i = threadIdx.x; i < nvec; i += CE_THREADS) {
+      float f[8];
+      unpack8(ld_v4(lrow + i * 8), f);
+      if (i * 8 + 8 > V) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (i * 8 + j >= V) f[j] = -INFINITY;
+      }
+      float vm = f[0];
+#pragma unroll
+      for (int j = 1; j < 8; ++j) vm = fmaxf(vm, f[j]);
+      if (vm > m) {
+        s *= __expf(m - vm);
+        m = vm;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += __expf(f[j] - m);
+    }
+    const float gm = block_max(m, red);
+    s *= (m == -INFINITY) ? 0.f : __expf(m - gm);
+    const float gs = block_sum(s, red);
+    const float lse = gm + logf(gs);
+    if (threadIdx.x == 0) {
+      const float lt = (tgt >= 0 && tgt < V) ? __bfloat162float(lrow[tgt]) : 0.f;
+      ws[2 + row] = lse - lt;
+    }
+    if (write_grad) {
+      const float inv = ws[1];
+      __syncthreads();  // lrow[tgt] was read above before anyone overwrites it
+      for (int i = threadIdx.x; i < nvec; i += CE_THREADS) {
+        float f[8];
+        unpack8(ld_v4(lrow + i * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float p = __expf(f[j] - lse);
+          if ((long long)(i * 8 + j) == tgt) p -= 1.f;
+          f[j] = p * inv;
+        }
+        if (i * 8 + 8 <= V) st_v4(lrow + i * 8, pack8(f));
+        else
+          for (int j = i * 8; j < V; ++j) lrow[j] = __float2bfloat16_rn(f[j - i * 8]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+ce_finish_kernel(const float* __restrict__ ws, long long M, float* __restrict__ loss) {
+  __shared__ float red[33];
+  float acc = 0.f;
+  for (long long i = threadIdx.x; i < M; i += blockDim.x) acc += ws[2 + i];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) loss[0] = acc * ws[1];
+}
+
+// ---------------- grad norm ----------------
+constexpr int GN_MAX_BLOCKS = 1024;
+
+__global__ void __launch_bounds__(256)
+sumsq_partial_kernel(const bf16* __restrict__ g, long long n, float* __restrict__ partial) {
+  __shared__ float red[33];
+  const long long nv = n >> 3;
+  float acc = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld_nc_v4(g + i * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) {
+      const float f = __bfloat162float(g[k]);
+      acc += f * f;
+    }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partial[blockIdx.x] = acc;
+}
+
+__global__ void __launch_bounds__(1024)
+norm_finish_kernel(const float* __restrict__ partial, int nblocks, float max_norm,
+                   float* __restrict__ out) {
+  __shared__ float red[33];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < nblocks; i += blockDim.x) acc += partial[i];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) {
+    const float nrm = sqrtf(acc);
+    out[0] = nrm;
+    // torch.nn.utils.clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1
+    out[1] = fminf(1.f, max_norm / (nrm + 1e-6f));
+  }
+}
+
+// ---------------- AdamW ----------------
+// torch.optim.AdamW single step (decoupled weight decay, no amsgrad):
+//   p *= 1 - lr*wd;  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;
+//   p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
+struct AdamConsts {
+  float lr, b1, b2, eps, wd, step_size, inv_sqrt_bc2;
+};
+
+__device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v,
+                                            const AdamConsts& c) {
+  p *= 1.f - c.lr * c.wd;
+  m = c.b1 * m + (1.f - c.b1) * g;
+  v = c.b2 * v + (1.f - c.b2) * g * g;
+  const float denom = sqrtf(v) * c.inv_sqrt_bc2 + c.eps;
+  p -= c.step_size * (m / denom);
+}
+
+__global__ void __launch_bounds__(256)
+adamw_bf16_kernel(bf16* __restrict__ p, const bf16* __restrict__ g, bf16* __restrict__ m,
+                  bf16* __restrict__ v, long long n, AdamConsts c,
+                  const float* __restrict__ grad_scale) {
+  const float gs = grad_scale ? grad_scale[0] : 1.f;
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float fp[8], fg[8], fm[8], fv[8];
+    unpack8(ld_v4(p + i * 8), fp);
+    unpack8(ld_nc_v4(g + i * 8), fg);
+    unpack8(ld_v4(m + i * 8), fm);
+    unpack8(ld_v4(v + i * 8), fv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) adam_update(fp[j], bf16_round(fg[j] * gs), fm[j], fv[j], c);
+    st_v4(p + i * 8, pack8(fp));
+    st_v4(m + i * 8, pack8(fm));
+    st_v4(v + i * 8, pack8(fv));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) {
+      float fp = __bfloat162float(p[k]), fm = __bfloat162float(m[k]), fv = __bfloat162float(v[k]);
+      adam_update(fp, bf16_round(__bfloat162float(g[k]) * gs), fm, fv, c);
+      p[k] = __float2bfloat16_rn(fp);
+      m[k] = __float2bfloat16_rn(fm);
+      v[k] = __float2bfloat16_rn(fv);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+adamw_f32_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                 float* __restrict__ v, long long n, AdamConsts c,
+                 const float* __restrict__ grad_scale) {
+  const float gs = grad_scale ? grad_scale[0] : 1.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    float fp = p[i], fm = m[i], fv = v[i];
+    adam_update(fp, g[i] * gs, fm, fv, c);
+    p[i] = fp;
+    m[i] = fm;
+    v[i] = fv;
+  }
+}
+
+AdamConsts make_consts(float lr, float b1, float b2, float eps, float wd, long long step) {
+  AdamConsts c;
+  c.lr = lr; c.b1 = b1; c.b2 = b2; c.eps = eps; c.wd = wd;
+  const double bc1 = 1.0 - pow((double)b1, (double)step);
+  const double bc2 = 1.0 - pow((double)b2, (double)step);
+  c.step_size = (float)((double)lr / bc1);
+  c.inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  return c;
+}
+
+inline int ew_grid(long long nvec, int threads) {
+  long long blocks = (nvec + threads - 1) / threads;
+  const long long cap = (long long)b200_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace
+
+extern "C" size_t b200_cross_entropy_workspace_bytes(int64_t M) {
+  return (size_t)(M + 2) * sizeof(float);
+}
+
+extern "C" int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets,
+                                       float* loss_out, int64_t M, int64_t V, int write_grad,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  B200_CHECK_ARG(logits && targets && loss_out && workspace && M > 0 && V > 0, "cross_entropy: null pointer or empty");
+  B200_CHECK_ARG(ld % 8 == 0 && ld >= V, "cross_entropy: ld=%lld must be a multiple of 8 and >= V", (long long)ld);
+  B200_CHECK_ARG(b200_aligned16(logits), "cross_entropy: logits must be 16-B aligned");
+  B200_CHECK_ARG(workspace_bytes >= b200_cross_entropy_workspace_bytes(M), "cross_entropy: workspace too small");
+  B200_CHECK_ARG(V < (1ll << 31), "cross_entropy: V too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* ws = (float*)workspace;
+  ce_count_kernel<<<1, 256, 0, st>>>((const long long*)targets, M, ws);
+  B200_CHECK_LAUNCH();
+  const long long cap = (long long)b200_num_sms() * 4;
+  ce_row_kernel<<<(int)(M < cap ? M : cap), CE_THREADS, 0, st>>>((bf16*)logits, ld, (const long long*)targets, ws, M, (int)V, write_grad);
+  B200_CHECK_LAUNCH();
+  ce_finish_kernel<<<1, 1024, 0, st>>>(ws, M, loss_out);
+  B200_CHECK_LAUNCH();
+  b200_count_launch(3);
+  return 0;
+}
+
+extern "C" size_t b200_grad_norm_workspace_bytes(int64_t n) {
+  (void)n;
+  return (size_t)GN_MAX_BLOCKS * sizeof(float);
+}
+
+extern "C" int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, float* out,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+  B200_CHECK_ARG(g && out && workspace && n > 0, "grad_norm: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(g), "grad_norm: gradient buffer must be 16-B aligned");
+  B200_CHECK_ARG(workspace_bytes >= b200_grad_norm_workspace_bytes(n), "grad_norm: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  int blocks = ew_grid(n / 8 + 1, 256);
+  if (blocks > GN_MAX_BLOCKS) blocks = GN_MAX_BLOCKS;
+  sumsq_partial_kernel<<<blocks, 256, 0, st>>>((const bf16*)g, n, (float*)workspace);
+  B200_CHECK_LAUNCH();
+  norm_finish_kernel<<<1, 1024, 0, st>>>((const float*)workspace, blocks, max_norm, out);
+  B200_CHECK_LAUNCH();
+  b200_count_launch(2);
+  return 0;
+}
+
+extern "C" int b200_adamw_bf16(void* p, const void* g, void* m, void* v, int64_t n, float lr,
+                               float beta1, float beta2, float eps, float weight_decay,
+                               int64_t step, const float* grad_scale, void* stream) {
+  B200_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw: null pointer, empty, or step < 1");
+  B200_CHECK_ARG(b200_aligned16(p) && b200_aligned16(g) && b200_aligned16(m) && b200_aligned16(v), "adamw: buffers must be 16-B aligned");
+  adamw_bf16_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+      (bf16*)p, (const bf16*)g, (bf16*)m, (bf16*)v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step), grad_scale);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_adamw_f32(float* p, const float* g, float* m, float* v, int64_t n, float lr,
+                              float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                              const float* grad_scale, void* stream) {
+  B200_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw: null pointer, empty, or step < 1");
+  adamw_f32_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(
+      p, g, m, v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step), grad_scale);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}

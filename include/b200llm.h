@@ -1,0 +1,193 @@
+/* b200llm.h — C-ABI of the B200-native decoder training-step library (libb200llm.so).
+ *
+ * This is the lower face of the drop-in boundary: plain pointers and sizes,
+ * no torch types. Every entry point enqueues hand-written sm_100a kernels on the CUDA stream
+ * it is given and returns immediately (no hidden synchronisation, no per-call cudaMalloc;
+ * the caller owns all device memory including workspaces).
+ *
+ * The reference (chemphenoms/Building_LLM_from_scratch) is pure PyTorch, so "the interface
+ * each entry replaces" is an ATen call site in the reference's Python; each declaration cites
+ * it as file:line relative to the reference root.
+ *
+ * Return value: 0 = OK; < 0 = argument / shape / alignment error (text in b200_last_error());
+ * > 0 = a cudaError_t / CUresult passed through.
+ *
+ * Conventions: all matrices are row-major; "ld*" is the row pitch in ELEMENTS; bf16 data is
+ * the raw 16-bit brain-float; device pointers must be 16-byte aligned unless stated otherwise;
+ * `stream` is a cudaStream_t passed as void*.
+ */
+#ifndef B200LLM_H_
+#define B200LLM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_ARG (-1)
+#define B200_ERR_UNSUPPORTED (-2)
+#define B200_ERR_INTERNAL (-3)
+
+#define B200LLM_VERSION 100
+
+/* ---- library plumbing ------------------------------------------------------------------ */
+int b200_version(void);
+/* Binds driver entry points and caches device properties; optional (done lazily otherwise). */
+int b200_init(int device);
+/* Thread-local text of the last error returned on this thread. */
+const char* b200_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+uint64_t b200_launch_count(void);
+
+/* ---- K1: dense contraction on tcgen05/TMEM fed by TMA ------------------------------------
+ * C[M,N] = A1[M,K1]·B1[N,K1]^T  (+ A2[M,K2]·B2[N,K2]^T)  (+ bias[N])  (gelu)  (+ R[M,N])
+ * bf16 in, fp32 accumulate in tensor memory, bf16 out. The second product is the rank-r
+ * LoRA update accumulated into the same TMEM tile (A2 = s·(x·A), B2 = B^T), pass K2 = 0 to
+ * skip it. Replaces nn.Linear / LinearWithLoRA forward:  lora.py:26,46;
+ * Models/Llama/Llama3.py:135-137,155,203; Models/Llama/common_components.py:121-124;
+ * Models/GPT2/GPT2.py:33-35,49,58-62,121.
+ * flags: B200_GEMM_BIAS | B200_GEMM_GELU | B200_GEMM_RESIDUAL.
+ * K1, K2, lda*, ldb* must be multiples of 8; A/B bases 16-B aligned. */
+#define B200_GEMM_BIAS 1
+#define B200_GEMM_GELU 2
+#define B200_GEMM_RESIDUAL 4
+int b200_gemm_nt_bf16(const void* A1, int64_t lda1, const void* B1, int64_t ldb1, int64_t K1,
+                      const void* A2, int64_t lda2, const void* B2, int64_t ldb2, int64_t K2,
+                      const void* bias, const void* R, int64_t ldr, void* C, int64_t ldc,
+                      int64_t M, int64_t N, int flags, void* stream);
+
+/* Fully general form behind the two wrappers below and above: each operand of each product is
+ * K-major (x_mn = 0: [rows, K]) or MN-major (x_mn = 1: stored [K, rows]); out_f32 writes fp32;
+ * accumulate adds into C with fp32 atomics and allows split-K (splitk = 0: automatic);
+ * trans_out stores element (i, j) at C[j*ldc + i]. Used for the LoRA backward
+ * (dX = dY·W + s·u·A^T, dA = x^T·u, dB = t^T·dY; lora.py:26,46). */
+int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_t ldb1, int b1_mn,
+                 int64_t K1, const void* A2, int64_t lda2, int a2_mn, const void* B2, int64_t ldb2,
+                 int b2_mn, int64_t K2, const void* bias, const void* R, int64_t ldr, void* C,
+                 int64_t ldc, int64_t M, int64_t N, int flags, int out_f32, int accumulate,
+                 int trans_out, float alpha, int splitk, void* stream);
+
+/* General bf16 GEMM with operand layouts, C[M,N] (+)= op(A)·op(B):
+ *   transa = 0: A is [M,K] (K contiguous);  1: A is stored [K,M] (M contiguous)
+ *   transb = 0: B is [N,K] (K contiguous);  1: B is stored [K,N] (N contiguous)
+ * out_f32 != 0 writes fp32 C (used for gradient accumulation), `accumulate` adds to C.
+ * Replaces the autograd MmBackward of the call sites above (dX = dY·W, dW = dY^T·X,
+ * LoRA dA / dB: lora.py:26). */
+int b200_gemm_bf16(const void* A, int64_t lda, int transa, const void* B, int64_t ldb, int transb,
+                   void* C, int64_t ldc, int out_f32, int accumulate, float alpha, int64_t M,
+                   int64_t N, int64_t K, void* stream);
+
+/* ---- K4: RMSNorm (Models/Llama/common_components.py:54-70) ------------------------------
+ * y = (x * rsqrt(mean(x^2) + eps)) * w, x,y bf16 [M,d], w fp32 [d]. With bf16_steps != 0 the
+ * intermediate roundings of the reference's bf16 eager evaluation (x^2, mean, +eps, rsqrt,
+ * x*r rounded to bf16 before the fp32 weight multiply) are reproduced. If `res` is non-NULL
+ * the kernel first forms s = x + res (bf16), writes it to `sum_out` and normalises s
+ * (fuses the residual add of Llama3.py:178,180). d % 8 == 0, d <= 16384. */
+int b200_rmsnorm_fwd_bf16(const void* x, const void* res, const float* w, void* sum_out, void* y,
+                          int64_t M, int64_t d, float eps, int bf16_steps, void* stream);
+/* dx = r*(g - xn*mean(g*xn)), g = dy*w; dw[d] (fp32, may be NULL) += sum_m dy*xn. If dres_in
+ * is non-NULL it is added to dx (gradient arriving through the residual branch). */
+int b200_rmsnorm_bwd_bf16(const void* x, const float* w, const void* dy, const void* dres_in,
+                          void* dx, float* dw, int64_t M, int64_t d, float eps, void* stream);
+/* fp32 instantiation for the 1e-4 parity mode (no intermediate roundings). */
+int b200_rmsnorm_fwd_f32(const float* x, const float* w, float* y, int64_t M, int64_t d, float eps,
+                         void* stream);
+int b200_rmsnorm_bwd_f32(const float* x, const float* w, const float* dy, float* dx, float* dw,
+                         int64_t M, int64_t d, float eps, void* stream);
+
+/* ---- K4': LayerNorm (nn.LayerNorm, Models/GPT2/GPT2.py:79-80,85,87,105,120), eps 1e-5 ---- */
+int b200_layernorm_fwd_bf16(const void* x, const void* w, const void* b, void* y, float* mean,
+                            float* rstd, int64_t M, int64_t d, float eps, void* stream);
+int b200_layernorm_bwd_bf16(const void* x, const void* w, const void* dy, const float* mean,
+                            const float* rstd, void* dx, float* dw, float* db, int64_t M,
+                            int64_t d, void* stream);
+
+/* ---- K5: SwiGLU gate (Models/Llama/common_components.py:78-88,121-123) --------------------
+ * h = silu(a) * b with a = ab[:, 0:F], b = ab[:, F:2F] (row pitch ldab), h [M,F] contiguous.
+ * bf16_steps reproduces the bf16 roundings of sigmoid, a*sig and the product. F % 8 == 0. */
+int b200_swiglu_fwd_bf16(const void* ab, int64_t ldab, void* h, int64_t M, int64_t F,
+                         int bf16_steps, void* stream);
+/* dab[:, 0:F] = dh*b*silu'(a), dab[:, F:2F] = dh*silu(a). */
+int b200_swiglu_bwd_bf16(const void* ab, int64_t ldab, const void* dh, void* dab, int64_t lddab,
+                         int64_t M, int64_t F, void* stream);
+
+/* ---- K5': GELU (erf form, nn.GELU(), Models/GPT2/GPT2.py:60) ------------------------------ */
+int b200_gelu_fwd_bf16(const void* x, void* y, int64_t n, void* stream);
+int b200_gelu_bwd_bf16(const void* x, const void* dy, void* dx, int64_t n, void* stream);
+
+/* ---- K6: rotary embedding (Models/Llama/common_components.py:6-35) -------------------------
+ * In-place rotate-half RoPE on `nheads` heads of width hd inside a [B*T, ld] activation whose
+ * heads are laid out consecutively starting at column 0 (token row = b*T + t, position = t).
+ * cos/sin are the module's [ctx, hd] tables (bf16). inverse != 0 applies the transpose
+ * (the backward of the rotation). bf16_steps reproduces x*cos, rot*sin roundings. */
+int b200_rope_bf16(void* x, int64_t ld, const void* cos, const void* sin, int64_t B, int64_t T,
+                   int64_t nheads, int64_t hd, int inverse, int bf16_steps, void* stream);
+
+/* ---- K7: embedding gather (Models/Llama/Llama3.py:197; GPT2.py:110-112) --------------------
+ * out[m,:] = tok_w[idx[m],:] (+ pos_w[m % T,:] when pos_w != NULL). idx int64. */
+int b200_embedding_fwd_bf16(const int64_t* idx, const void* tok_w, const void* pos_w, void* out,
+                            int64_t M, int64_t T, int64_t d, int64_t vocab, void* stream);
+/* dW[idx[m],:] += dout[m,:] in fp32 (full pre-training only). */
+int b200_embedding_bwd_f32acc(const int64_t* idx, const void* dout, float* dtok_w, float* dpos_w,
+                              int64_t M, int64_t T, int64_t d, int64_t vocab, void* stream);
+
+/* ---- K3: cross-entropy over materialised logits (train.py:91) ------------------------------
+ * F.cross_entropy(logits, targets) with ignore_index = -100, reduction = mean over the
+ * non-ignored rows; all rows ignored -> NaN like the reference. Overwrites `logits` in place
+ * with dloss/dlogits (already divided by the valid count) when write_grad != 0.
+ * loss_out: 1 fp32. workspace: b200_cross_entropy_workspace_bytes(M) bytes. */
+size_t b200_cross_entropy_workspace_bytes(int64_t M);
+int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets, float* loss_out,
+                            int64_t M, int64_t V, int write_grad, void* workspace,
+                            size_t workspace_bytes, void* stream);
+
+/* ---- K8a: global gradient norm + clip coefficient (train.py:115-120) ----------------------
+ * out[0] = ||g||_2 over n bf16 elements; out[1] = min(1, max_norm / (out[0] + 1e-6)), the
+ * factor clip_grad_norm_ multiplies every gradient by. workspace:
+ * b200_grad_norm_workspace_bytes(n). */
+size_t b200_grad_norm_workspace_bytes(int64_t n);
+int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, float* out, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* ---- K8b: AdamW over a flat buffer (torch.optim.AdamW, build_components.py:258) ------------
+ * decoupled weight decay, bias correction from `step` (1-based); grad_scale (device pointer,
+ * may be NULL) is the clip coefficient from b200_grad_norm_bf16 (out + 1). p,g,m,v bf16. */
+int b200_adamw_bf16(void* p, const void* g, void* m, void* v, int64_t n, float lr, float beta1,
+                    float beta2, float eps, float weight_decay, int64_t step,
+                    const float* grad_scale, void* stream);
+int b200_adamw_f32(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int64_t step,
+                   const float* grad_scale, void* stream);
+
+/* ---- K9: dtype casts (datautils/mixed_precision.py:10-35) ---------------------------------- */
+int b200_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
+int b200_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
+
+/* ---- helpers: transposed copy and residual add ------------------------------------------- */
+/* out[c, r] = alpha * in[r, c]; in [rows, cols] pitch ldi, out [cols, rows] pitch ldo. */
+int b200_transpose_bf16(const void* in, int64_t ldi, void* out, int64_t ldo, int64_t rows,
+                        int64_t cols, float alpha, void* stream);
+int b200_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream);
+
+/* ---- K2: fused causal attention (Models/Llama/Llama3.py:131-153; GPT2.py:29-47) ------------
+ * q [B*T, ldq] with h heads of width hd starting at q, k/v likewise with hkv heads; head j
+ * of q attends kv head j / (h / hkv). o [B*T, ldo]. lse [B, h, T] fp32 (natural-log
+ * logsumexp of the scaled scores) is saved for backward. scale = 1/sqrt(hd). hd in {64,128}. */
+int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                            int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
+                            int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
+/* delta [B, h, T] fp32 scratch (rowsum(dO*O)), written by the call. dq/dk/dv have the layouts
+ * of q/k/v. */
+int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                            int64_t ldv, const void* o, int64_t ldo, const void* dout,
+                            int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq,
+                            void* dk, int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T,
+                            int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LLM_H_ */
