@@ -38,11 +38,11 @@ SIGNATURES = {
     "b200_rmsnorm_bwd_f32": (I, [P, P, P, P, P, I64, I64, F, P]),
     "b200_layernorm_fwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),
     "b200_layernorm_bwd_bf16": (I, [P, P, P, P, P, P, P, P, I64, I64, P]),
-    "b200_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, I, P]),
-    "b200_swiglu_bwd_bf16": (I, [P, I64, P, P, I64, I64, I64, P]),
+    "b200_swiglu_fwd_bf16": (I, [P, I64, P, I64, P, I64, I64, I, P]),
+    "b200_swiglu_bwd_bf16": (I, [P, I64, P, I64, P, P, I64, P, I64, I64, I64, P]),
     "b200_gelu_fwd_bf16": (I, [P, P, I64, P]),
     "b200_gelu_bwd_bf16": (I, [P, P, P, I64, P]),
-    "b200_rope_bf16": (I, [P, I64, P, P, I64, I64, I64, I64, I, I, P]),
+    "b200_rope_bf16": (I, [P, I64, P, I64, P, P, I64, I64, I64, I64, I, I, P]),
     "b200_embedding_fwd_bf16": (I, [P, P, P, P, I64, I64, I64, I64, P]),
     "b200_embedding_bwd_f32acc": (I, [P, P, P, P, I64, I64, I64, I64, P]),
     "b200_cross_entropy_workspace_bytes": (SZ, [I64]),

@@ -18,8 +18,8 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf
 // Reference (common_components.py:87,123): silu(a) = a * sigmoid(a) -> bf16 each op, then * b.
 // Algorithmic bytes: fwd 6 B per output element (read a, b; write h), bwd 10 B.
 __global__ void __launch_bounds__(256)
-swiglu_fwd_kernel(const bf16* __restrict__ ab, long long ldab, bf16* __restrict__ h, long long M,
-                  int F, int bf16_steps) {
+swiglu_fwd_kernel(const bf16* __restrict__ pa, long long lda, const bf16* __restrict__ pb,
+                  long long ldb, bf16* __restrict__ h, long long M, int F, int bf16_steps) {
   const int fv = F >> 3;
   const long long total = M * fv;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -27,8 +27,8 @@ swiglu_fwd_kernel(const bf16* __restrict__ ab, long long ldab, bf16* __restrict_
     const long long row = i / fv;
     const int c = (int)(i % fv) * 8;
     float a[8], b[8], o[8];
-    unpack8(ld_nc_v4(ab + row * ldab + c), a);
-    unpack8(ld_nc_v4(ab + row * ldab + F + c), b);
+    unpack8(ld_nc_v4(pa + row * lda + c), a);
+    unpack8(ld_nc_v4(pb + row * ldb + c), b);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float s = sigmoidf_(a[j]);
@@ -44,8 +44,9 @@ swiglu_fwd_kernel(const bf16* __restrict__ ab, long long ldab, bf16* __restrict_
 }
 
 __global__ void __launch_bounds__(256)
-swiglu_bwd_kernel(const bf16* __restrict__ ab, long long ldab, const bf16* __restrict__ dh,
-                  bf16* __restrict__ dab, long long lddab, long long M, int F) {
+swiglu_bwd_kernel(const bf16* __restrict__ pa, long long lda, const bf16* __restrict__ pb,
+                  long long ldb, const bf16* __restrict__ dh, bf16* __restrict__ pda, long long ldda,
+                  bf16* __restrict__ pdb, long long lddb, long long M, int F) {
   const int fv = F >> 3;
   const long long total = M * fv;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -53,8 +54,8 @@ swiglu_bwd_kernel(const bf16* __restrict__ ab, long long ldab, const bf16* __res
     const long long row = i / fv;
     const int c = (int)(i % fv) * 8;
     float a[8], b[8], g[8], da[8], db[8];
-    unpack8(ld_nc_v4(ab + row * ldab + c), a);
-    unpack8(ld_nc_v4(ab + row * ldab + F + c), b);
+    unpack8(ld_nc_v4(pa + row * lda + c), a);
+    unpack8(ld_nc_v4(pb + row * ldb + c), b);
     unpack8(ld_nc_v4(dh + row * F + c), g);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -63,8 +64,8 @@ swiglu_bwd_kernel(const bf16* __restrict__ ab, long long ldab, const bf16* __res
       da[j] = g[j] * b[j] * (s * (1.f + a[j] * (1.f - s)));
       db[j] = g[j] * silu;
     }
-    st_v4(dab + row * lddab + c, pack8(da));
-    st_v4(dab + row * lddab + F + c, pack8(db));
+    st_v4(pda + row * ldda + c, pack8(da));
+    st_v4(pdb + row * lddb + c, pack8(db));
   }
 }
 
@@ -115,7 +116,7 @@ gelu_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* _
 // Reference (common_components.py:24-35): x*cos + cat(-x2, x1)*sin, bf16 tables, every op
 // rounds to bf16. Each thread owns 8 columns of the first half and the matching 8 of the second.
 __global__ void __launch_bounds__(256)
-rope_kernel(bf16* __restrict__ x, long long ld, const bf16* __restrict__ cosT,
+rope_kernel(const bf16* x, long long ld, bf16* y, long long ldy, const bf16* __restrict__ cosT,
             const bf16* __restrict__ sinT, long long B, int T, int nheads, int hd, int inverse,
             int bf16_steps) {
   const int half = hd >> 1;
@@ -128,8 +129,10 @@ rope_kernel(bf16* __restrict__ x, long long ld, const bf16* __restrict__ cosT,
     const int head = (int)(rest % nheads);
     const long long tok = rest / nheads;
     const int t = (int)(tok % T);
-    bf16* p1 = x + tok * ld + (long long)head * hd + v * 8;
-    bf16* p2 = p1 + half;
+    const bf16* p1 = x + tok * ld + (long long)head * hd + v * 8;
+    const bf16* p2 = p1 + half;
+    bf16* q1 = y + tok * ldy + (long long)head * hd + v * 8;
+    bf16* q2 = q1 + half;
     float x1[8], x2[8], c1[8], c2[8], s1[8], s2[8], o1[8], o2[8];
     unpack8(ld_v4(p1), x1);
     unpack8(ld_v4(p2), x2);
@@ -153,8 +156,8 @@ rope_kernel(bf16* __restrict__ x, long long ld, const bf16* __restrict__ cosT,
         o2[j] = x2[j] * c2[j] - x1[j] * s1[j];
       }
     }
-    st_v4(p1, pack8(o1));
-    st_v4(p2, pack8(o2));
+    st_v4(q1, pack8(o1));
+    st_v4(q2, pack8(o2));
   }
 }
 
@@ -277,25 +280,27 @@ transpose_kernel(const bf16* __restrict__ in, long long ldi, bf16* __restrict__ 
 
 }  // namespace
 
-extern "C" int b200_swiglu_fwd_bf16(const void* ab, int64_t ldab, void* h, int64_t M, int64_t F,
-                                    int bf16_steps, void* stream) {
-  B200_CHECK_ARG(ab && h && M > 0 && F > 0, "swiglu_fwd: null pointer or empty");
-  B200_CHECK_ARG(F % 8 == 0 && ldab % 8 == 0 && ldab >= 2 * F, "swiglu_fwd: F and ldab must be multiples of 8, ldab >= 2F");
-  B200_CHECK_ARG(b200_aligned16(ab) && b200_aligned16(h), "swiglu_fwd: pointers must be 16-B aligned");
+extern "C" int b200_swiglu_fwd_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, void* h,
+                                    int64_t M, int64_t F, int bf16_steps, void* stream) {
+  B200_CHECK_ARG(a && b && h && M > 0 && F > 0, "swiglu_fwd: null pointer or empty");
+  B200_CHECK_ARG(F % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && lda >= F && ldb >= F, "swiglu_fwd: F, lda, ldb must be multiples of 8 and pitches >= F");
+  B200_CHECK_ARG(b200_aligned16(a) && b200_aligned16(b) && b200_aligned16(h), "swiglu_fwd: pointers must be 16-B aligned");
   swiglu_fwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
-      (const bf16*)ab, ldab, (bf16*)h, M, (int)F, bf16_steps);
+      (const bf16*)a, lda, (const bf16*)b, ldb, (bf16*)h, M, (int)F, bf16_steps);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
 }
 
-extern "C" int b200_swiglu_bwd_bf16(const void* ab, int64_t ldab, const void* dh, void* dab,
-                                    int64_t lddab, int64_t M, int64_t F, void* stream) {
-  B200_CHECK_ARG(ab && dh && dab && M > 0 && F > 0, "swiglu_bwd: null pointer or empty");
-  B200_CHECK_ARG(F % 8 == 0 && ldab % 8 == 0 && lddab % 8 == 0 && ldab >= 2 * F && lddab >= 2 * F,
-                 "swiglu_bwd: F, ldab, lddab must be multiples of 8 and pitches >= 2F");
+extern "C" int b200_swiglu_bwd_bf16(const void* a, int64_t lda, const void* b, int64_t ldb,
+                                    const void* dh, void* da, int64_t ldda, void* db, int64_t lddb,
+                                    int64_t M, int64_t F, void* stream) {
+  B200_CHECK_ARG(a && b && dh && da && db && M > 0 && F > 0, "swiglu_bwd: null pointer or empty");
+  B200_CHECK_ARG(F % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldda % 8 == 0 && lddb % 8 == 0,
+                 "swiglu_bwd: F and all pitches must be multiples of 8");
+  B200_CHECK_ARG(b200_aligned16(a) && b200_aligned16(b) && b200_aligned16(dh) && b200_aligned16(da) && b200_aligned16(db), "swiglu_bwd: pointers must be 16-B aligned");
   swiglu_bwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
-      (const bf16*)ab, ldab, (const bf16*)dh, (bf16*)dab, lddab, M, (int)F);
+      (const bf16*)a, lda, (const bf16*)b, ldb, (const bf16*)dh, (bf16*)da, ldda, (bf16*)db, lddb, M, (int)F);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -319,15 +324,16 @@ extern "C" int b200_gelu_bwd_bf16(const void* x, const void* dy, void* dx, int64
   return 0;
 }
 
-extern "C" int b200_rope_bf16(void* x, int64_t ld, const void* cos, const void* sin, int64_t B,
-                              int64_t T, int64_t nheads, int64_t hd, int inverse, int bf16_steps,
-                              void* stream) {
-  B200_CHECK_ARG(x && cos && sin && B > 0 && T > 0 && nheads > 0, "rope: null pointer or empty");
-  B200_CHECK_ARG(hd % 16 == 0 && ld % 8 == 0 && ld >= nheads * hd, "rope: hd must be a multiple of 16, ld a multiple of 8 and >= nheads*hd");
-  B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(cos) && b200_aligned16(sin), "rope: pointers must be 16-B aligned");
+extern "C" int b200_rope_bf16(const void* x, int64_t ldx, void* y, int64_t ldy, const void* cos,
+                              const void* sin, int64_t B, int64_t T, int64_t nheads, int64_t hd,
+                              int inverse, int bf16_steps, void* stream) {
+  B200_CHECK_ARG(x && y && cos && sin && B > 0 && T > 0 && nheads > 0, "rope: null pointer or empty");
+  B200_CHECK_ARG(hd % 16 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && ldx >= nheads * hd && ldy >= nheads * hd,
+                 "rope: hd must be a multiple of 16, pitches multiples of 8 and >= nheads*hd");
+  B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y) && b200_aligned16(cos) && b200_aligned16(sin), "rope: pointers must be 16-B aligned");
   const long long total = B * T * nheads * (hd / 16);
   rope_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      (bf16*)x, ld, (const bf16*)cos, (const bf16*)sin, B, (int)T, (int)nheads, (int)hd, inverse, bf16_steps);
+      (const bf16*)x, ldx, (bf16*)y, ldy, (const bf16*)cos, (const bf16*)sin, B, (int)T, (int)nheads, (int)hd, inverse, bf16_steps);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;

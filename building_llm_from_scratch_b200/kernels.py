@@ -1,0 +1,319 @@
+"""Tensor-level wrappers over the C-ABI (one Python function per extern "C" entry point).
+
+These take CUDA torch tensors, pass raw pointers / sizes / the current stream to libb200llm.so
+and return tensors allocated by the PyTorch caching allocator (the library itself never
+allocates). CPU tensors are rejected: there is no fallback path.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _lib
+
+BF16 = torch.bfloat16
+GEMM_BIAS, GEMM_GELU, GEMM_RESIDUAL = 1, 2, 4
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("b200llm ops need CUDA tensors on an sm_100a device (no CPU fallback)")
+
+
+def _rowmajor2d(t):
+    """(tensor, ld) for a 2-D view whose last dim is contiguous."""
+    assert t.dim() == 2 and t.stride(1) == 1, f"need a row-major 2-D view, got {t.shape} {t.stride()}"
+    return t, t.stride(0)
+
+
+def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, b2_mn=False, bias=None,
+            residual=None, gelu=False, out=None, out_dtype=BF16, accumulate=False, trans_out=False,
+            alpha=1.0, splitk=0, M=None, N=None):
+    """C[M,N] = alpha*(op(a1)·op(b1)^T + op(a2)·op(b2)^T) (+bias)(gelu)(+residual).
+
+    K-major operands are [rows, K]; MN-major (x_mn=True) are stored [K, rows]."""
+    _need_cuda(a1, b1, a2, b2, bias, residual, out)
+    lib = _lib.load()
+    a1, lda1 = _rowmajor2d(a1)
+    b1, ldb1 = _rowmajor2d(b1)
+    m1, k1 = (a1.shape[1], a1.shape[0]) if a1_mn else a1.shape
+    n1, kb = (b1.shape[1], b1.shape[0]) if b1_mn else b1.shape
+    assert k1 == kb, (a1.shape, b1.shape)
+    M = m1 if M is None else M
+    N = n1 if N is None else N
+    K2 = 0
+    lda2 = ldb2 = 0
+    if a2 is not None:
+        a2, lda2 = _rowmajor2d(a2)
+        b2, ldb2 = _rowmajor2d(b2)
+        K2 = a2.shape[0] if a2_mn else a2.shape[1]
+        assert K2 == (b2.shape[0] if b2_mn else b2.shape[1])
+    if out is None:
+        shape = (N, M) if trans_out else (M, N)
+        out = (torch.zeros if accumulate else torch.empty)(shape, device=a1.device, dtype=out_dtype)
+    out2, ldc = _rowmajor2d(out)
+    flags = (GEMM_BIAS if bias is not None else 0) | (GEMM_GELU if gelu else 0) | (
+        GEMM_RESIDUAL if residual is not None else 0)
+    ldr = 0
+    if residual is not None:
+        residual, ldr = _rowmajor2d(residual)
+    rc = lib.b200_gemm_ex(_p(a1), lda1, int(a1_mn), _p(b1), ldb1, int(b1_mn), k1, _p(a2), lda2, int(a2_mn),
+                          _p(b2), ldb2, int(b2_mn), K2, _p(bias), _p(residual), ldr, _p(out2), ldc, M, N, flags,
+                          int(out.dtype == torch.float32), int(accumulate), int(trans_out), float(alpha),
+                          int(splitk), _stream())
+    _lib.check(rc, "gemm_ex")
+    return out
+
+
+def rmsnorm_fwd(x, w, eps=1e-5, res=None, bf16_steps=True):
+    """-> y (and the residual sum when res is given). x [M, d] bf16 (or fp32), w fp32 [d]."""
+    _need_cuda(x, w, res)
+    lib = _lib.load()
+    x2 = x.reshape(-1, x.shape[-1])
+    M, d = x2.shape
+    y = torch.empty_like(x2)
+    if x.dtype == torch.float32:
+        assert res is None
+        _lib.check(lib.b200_rmsnorm_fwd_f32(_p(x2), _p(w), _p(y), M, d, eps, _stream()), "rmsnorm_fwd_f32")
+        return y.view_as(x)
+    s = None
+    if res is not None:
+        res = res.reshape(-1, d)
+        s = torch.empty_like(x2)
+    _lib.check(lib.b200_rmsnorm_fwd_bf16(_p(x2), _p(res), _p(w), _p(s), _p(y), M, d, eps, int(bf16_steps), _stream()),
+               "rmsnorm_fwd")
+    return (y.view_as(x), s.view_as(x)) if res is not None else y.view_as(x)
+
+
+def rmsnorm_bwd(x, w, dy, eps=1e-5, dres=None, need_dw=False):
+    _need_cuda(x, w, dy, dres)
+    lib = _lib.load()
+    x2 = x.reshape(-1, x.shape[-1])
+    M, d = x2.shape
+    dx = torch.empty_like(x2)
+    dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+    dy2 = dy.reshape(-1, d)
+    if x.dtype == torch.float32:
+        _lib.check(lib.b200_rmsnorm_bwd_f32(_p(x2), _p(w), _p(dy2), _p(dx), _p(dw), M, d, eps, _stream()), "rmsnorm_bwd_f32")
+    else:
+        _lib.check(lib.b200_rmsnorm_bwd_bf16(_p(x2), _p(w), _p(dy2), _p(dres), _p(dx), _p(dw), M, d, eps, _stream()),
+                   "rmsnorm_bwd")
+    return dx.view_as(x), dw
+
+
+def layernorm_fwd(x, w, b, eps=1e-5):
+    _need_cuda(x, w, b)
+    lib = _lib.load()
+    x2 = x.reshape(-1, x.shape[-1])
+    M, d = x2.shape
+    y = torch.empty_like(x2)
+    mean = torch.empty(M, device=x.device, dtype=torch.float32)
+    rstd = torch.empty(M, device=x.device, dtype=torch.float32)
+    _lib.check(lib.b200_layernorm_fwd_bf16(_p(x2), _p(w), _p(b), _p(y), _p(mean), _p(rstd), M, d, eps, _stream()),
+               "layernorm_fwd")
+    return y.view_as(x), mean, rstd
+
+
+def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True):
+    _need_cuda(x, w, dy)
+    lib = _lib.load()
+    x2 = x.reshape(-1, x.shape[-1])
+    M, d = x2.shape
+    dx = torch.empty_like(x2)
+    dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+    db = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+    _lib.check(lib.b200_layernorm_bwd_bf16(_p(x2), _p(w), _p(dy.reshape(-1, d)), _p(mean), _p(rstd), _p(dx), _p(dw),
+                                           _p(db), M, d, _stream()), "layernorm_bwd")
+    return dx.view_as(x), dw, db
+
+
+def swiglu_fwd(a, b, bf16_steps=True):
+    """a, b: row-major 2-D views [M, F] (possibly the halves of one buffer) -> h [M, F]."""
+    _need_cuda(a, b)
+    a, lda = _rowmajor2d(a)
+    b, ldb = _rowmajor2d(b)
+    M, F = a.shape
+    h = torch.empty((M, F), device=a.device, dtype=BF16)
+    _lib.check(_lib.load().b200_swiglu_fwd_bf16(_p(a), lda, _p(b), ldb, _p(h), M, F, int(bf16_steps), _stream()),
+               "swiglu_fwd")
+    return h
+
+
+def swiglu_bwd(a, b, dh, da=None, db=None):
+    _need_cuda(a, b, dh)
+    a, lda = _rowmajor2d(a)
+    b, ldb = _rowmajor2d(b)
+    M, F = a.shape
+    da = torch.empty((M, F), device=a.device, dtype=BF16) if da is None else da
+    db = torch.empty((M, F), device=a.device, dtype=BF16) if db is None else db
+    dh = dh.reshape(M, F)
+    assert dh.is_contiguous()
+    _lib.check(_lib.load().b200_swiglu_bwd_bf16(_p(a), lda, _p(b), ldb, _p(dh), _p(da), da.stride(0), _p(db),
+                                                db.stride(0), M, F, _stream()), "swiglu_bwd")
+    return da, db
+
+
+def gelu_fwd(x):
+    _need_cuda(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.load().b200_gelu_fwd_bf16(_p(x), _p(y), x.numel(), _stream()), "gelu_fwd")
+    return y
+
+
+def gelu_bwd(x, dy):
+    _need_cuda(x, dy)
+    dx = torch.empty_like(x)
+    _lib.check(_lib.load().b200_gelu_bwd_bf16(_p(x), _p(dy), _p(dx), x.numel(), _stream()), "gelu_bwd")
+    return dx
+
+
+def rope(x2d, cos, sin, B, T, nheads, hd, inverse=False, bf16_steps=True, out=None):
+    """RoPE on the first nheads*hd columns of the [B*T, ld] view x2d; out=None -> new tensor,
+    out=x2d -> in place."""
+    _need_cuda(x2d, cos, sin)
+    x2d, ld = _rowmajor2d(x2d)
+    if out is None:
+        out = torch.empty((x2d.shape[0], nheads * hd), device=x2d.device, dtype=BF16)
+    out, ldo = _rowmajor2d(out)
+    assert cos.dtype == BF16 and sin.dtype == BF16 and cos.shape[1] == hd and cos.shape[0] >= T
+    _lib.check(_lib.load().b200_rope_bf16(_p(x2d), ld, _p(out), ldo, _p(cos), _p(sin), B, T, nheads, hd, int(inverse),
+                                          int(bf16_steps), _stream()), "rope")
+    return out
+
+
+def rope_(x2d, cos, sin, B, T, nheads, hd, inverse=False, bf16_steps=True):
+    return rope(x2d, cos, sin, B, T, nheads, hd, inverse, bf16_steps, out=x2d)
+
+
+def embedding_fwd(idx, tok_w, pos_w=None):
+    _need_cuda(idx, tok_w, pos_w)
+    B, T = idx.shape
+    d = tok_w.shape[1]
+    out = torch.empty((B, T, d), device=tok_w.device, dtype=BF16)
+    _lib.check(_lib.load().b200_embedding_fwd_bf16(_p(idx.contiguous()), _p(tok_w), _p(pos_w), _p(out), B * T, T, d,
+                                                   tok_w.shape[0], _stream()), "embedding_fwd")
+    return out
+
+
+def embedding_bwd(idx, dout, vocab, ctx=None):
+    _need_cuda(idx, dout)
+    B, T = idx.shape
+    d = dout.shape[-1]
+    dtok = torch.zeros((vocab, d), device=dout.device, dtype=torch.float32)
+    dpos = torch.zeros((ctx, d), device=dout.device, dtype=torch.float32) if ctx else None
+    _lib.check(_lib.load().b200_embedding_bwd_f32acc(_p(idx.contiguous()), _p(dout.contiguous()), _p(dtok), _p(dpos),
+                                                     B * T, T, d, vocab, _stream()), "embedding_bwd")
+    return dtok, dpos
+
+
+def cross_entropy_(logits2d, targets, write_grad=True):
+    """Loss (fp32 scalar tensor); logits2d [M, V(+pad)] is overwritten with dloss/dlogits."""
+    _need_cuda(logits2d, targets)
+    lib = _lib.load()
+    logits2d, ld = _rowmajor2d(logits2d)
+    M = logits2d.shape[0]
+    V = logits2d.shape[1]
+    tg = targets.reshape(-1).contiguous()
+    assert tg.numel() == M and tg.dtype == torch.int64
+    nbytes = lib.b200_cross_entropy_workspace_bytes(M)
+    ws = torch.empty(nbytes, device=logits2d.device, dtype=torch.uint8)
+    loss = torch.empty(1, device=logits2d.device, dtype=torch.float32)
+    _lib.check(lib.b200_cross_entropy_bf16(_p(logits2d), ld, _p(tg), _p(loss), M, V, int(write_grad), _p(ws), nbytes,
+                                           _stream()), "cross_entropy")
+    return loss
+
+
+def grad_norm(g_flat, max_norm=1.0, out=None, ws=None):
+    """-> fp32 tensor [norm, clip_coef]."""
+    _need_cuda(g_flat)
+    lib = _lib.load()
+    n = g_flat.numel()
+    nbytes = lib.b200_grad_norm_workspace_bytes(n)
+    if ws is None:
+        ws = torch.empty(nbytes, device=g_flat.device, dtype=torch.uint8)
+    if out is None:
+        out = torch.empty(2, device=g_flat.device, dtype=torch.float32)
+    _lib.check(lib.b200_grad_norm_bf16(_p(g_flat), n, float(max_norm), _p(out), _p(ws), nbytes, _stream()), "grad_norm")
+    return out
+
+
+def adamw_(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.1, grad_scale=None):
+    _need_cuda(p, g, m, v, grad_scale)
+    lib = _lib.load()
+    fn = lib.b200_adamw_f32 if p.dtype == torch.float32 else lib.b200_adamw_bf16
+    _lib.check(fn(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, weight_decay, int(step),
+                  _p(grad_scale), _stream()), "adamw")
+
+
+def cast(x, dtype):
+    _need_cuda(x)
+    lib = _lib.load()
+    out = torch.empty(x.shape, device=x.device, dtype=dtype)
+    xc = x.contiguous()
+    if x.dtype == torch.float32 and dtype == BF16:
+        _lib.check(lib.b200_cast_f32_to_bf16(_p(xc), _p(out), x.numel(), _stream()), "cast")
+    elif x.dtype == BF16 and dtype == torch.float32:
+        _lib.check(lib.b200_cast_bf16_to_f32(_p(xc), _p(out), x.numel(), _stream()), "cast")
+    else:
+        raise RuntimeError(f"unsupported cast {x.dtype} -> {dtype}")
+    return out
+
+
+def transpose(x, alpha=1.0, out=None):
+    _need_cuda(x)
+    x, ldi = _rowmajor2d(x)
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty((cols, rows), device=x.device, dtype=BF16)
+    _lib.check(_lib.load().b200_transpose_bf16(_p(x), ldi, _p(out), out.stride(0), rows, cols, float(alpha), _stream()),
+               "transpose")
+    return out
+
+
+def add(a, b):
+    _need_cuda(a, b)
+    out = torch.empty_like(a)
+    _lib.check(_lib.load().b200_add_bf16(_p(a), _p(b), _p(out), a.numel(), _stream()), "add")
+    return out
+
+
+def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None):
+    """q/k/v: 2-D row-major views [B*T, *] whose first h*hd (hkv*hd) columns are the heads."""
+    _need_cuda(q, k, v)
+    q, ldq = _rowmajor2d(q)
+    k, ldk = _rowmajor2d(k)
+    v, ldv = _rowmajor2d(v)
+    o = torch.empty((B * T, h * hd), device=q.device, dtype=BF16) if out is None else out
+    lse = torch.empty((B, h, T), device=q.device, dtype=torch.float32)
+    _lib.check(_lib.load().b200_attention_fwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), o.stride(0), _p(lse), B, T,
+                                                   h, hkv, hd, 1.0 / math.sqrt(hd), _stream()), "attention_fwd")
+    return o, lse
+
+
+def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None):
+    _need_cuda(q, k, v, o, do, lse)
+    q, ldq = _rowmajor2d(q)
+    k, ldk = _rowmajor2d(k)
+    v, ldv = _rowmajor2d(v)
+    o, ldo = _rowmajor2d(o)
+    do, lddo = _rowmajor2d(do)
+    dev = q.device
+    dq = torch.empty((B * T, h * hd), device=dev, dtype=BF16) if dq is None else dq
+    dk = torch.empty((B * T, hkv * hd), device=dev, dtype=BF16) if dk is None else dk
+    dv = torch.empty((B * T, hkv * hd), device=dev, dtype=BF16) if dv is None else dv
+    delta = torch.empty((B, h, T), device=dev, dtype=torch.float32)
+    _lib.check(_lib.load().b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
+                                                   _p(delta), _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
+                                                   dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _stream()),
+               "attention_bwd")
+    return dq, dk, dv

@@ -106,25 +106,29 @@ int b200_layernorm_bwd_bf16(const void* x, const void* w, const void* dy, const 
                             int64_t d, void* stream);
 
 /* ---- K5: SwiGLU gate (Models/Llama/common_components.py:78-88,121-123) --------------------
- * h = silu(a) * b with a = ab[:, 0:F], b = ab[:, F:2F] (row pitch ldab), h [M,F] contiguous.
- * bf16_steps reproduces the bf16 roundings of sigmoid, a*sig and the product. F % 8 == 0. */
-int b200_swiglu_fwd_bf16(const void* ab, int64_t ldab, void* h, int64_t M, int64_t F,
-                         int bf16_steps, void* stream);
-/* dab[:, 0:F] = dh*b*silu'(a), dab[:, F:2F] = dh*silu(a). */
-int b200_swiglu_bwd_bf16(const void* ab, int64_t ldab, const void* dh, void* dab, int64_t lddab,
-                         int64_t M, int64_t F, void* stream);
+ * h = silu(a) * b; a, b [M,F] with row pitches lda, ldb (they may be the two halves of one
+ * fused fc1|fc2 GEMM output), h [M,F] contiguous. bf16_steps reproduces the bf16 roundings of
+ * sigmoid, a*sig and the product. F % 8 == 0. */
+int b200_swiglu_fwd_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, void* h, int64_t M,
+                         int64_t F, int bf16_steps, void* stream);
+/* da = dh*b*silu'(a), db = dh*silu(a); dh [M,F] contiguous. */
+int b200_swiglu_bwd_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, const void* dh,
+                         void* da, int64_t ldda, void* db, int64_t lddb, int64_t M, int64_t F,
+                         void* stream);
 
 /* ---- K5': GELU (erf form, nn.GELU(), Models/GPT2/GPT2.py:60) ------------------------------ */
 int b200_gelu_fwd_bf16(const void* x, void* y, int64_t n, void* stream);
 int b200_gelu_bwd_bf16(const void* x, const void* dy, void* dx, int64_t n, void* stream);
 
 /* ---- K6: rotary embedding (Models/Llama/common_components.py:6-35) -------------------------
- * In-place rotate-half RoPE on `nheads` heads of width hd inside a [B*T, ld] activation whose
- * heads are laid out consecutively starting at column 0 (token row = b*T + t, position = t).
- * cos/sin are the module's [ctx, hd] tables (bf16). inverse != 0 applies the transpose
- * (the backward of the rotation). bf16_steps reproduces x*cos, rot*sin roundings. */
-int b200_rope_bf16(void* x, int64_t ld, const void* cos, const void* sin, int64_t B, int64_t T,
-                   int64_t nheads, int64_t hd, int inverse, int bf16_steps, void* stream);
+ * Rotate-half RoPE on `nheads` heads of width hd laid out consecutively from column 0 of a
+ * [B*T, ldx] activation (token row = b*T + t, position = t); result written to y (pitch ldy;
+ * y may alias x for in-place use). cos/sin are the module's [ctx, hd] tables (bf16).
+ * inverse != 0 applies the transpose (the backward of the rotation). bf16_steps reproduces
+ * the x*cos, rot*sin roundings of the reference's bf16 evaluation. */
+int b200_rope_bf16(const void* x, int64_t ldx, void* y, int64_t ldy, const void* cos, const void* sin,
+                   int64_t B, int64_t T, int64_t nheads, int64_t hd, int inverse, int bf16_steps,
+                   void* stream);
 
 /* ---- K7: embedding gather (Models/Llama/Llama3.py:197; GPT2.py:110-112) --------------------
  * out[m,:] = tok_w[idx[m],:] (+ pos_w[m % T,:] when pos_w != NULL). idx int64. */

@@ -1,0 +1,98 @@
+"""GPU: the tcgen05 GEMM through the C-ABI against the oracle's linear / LoRA-linear
+(oracle/reference_ops.py) evaluated in fp32 on the same bf16 inputs. bf16 tolerance 2e-2
+relative (north star); in practice the fp32-accumulating kernel is ~3e-3 from the fp32 result."""
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+BF16_TOL = 2e-2
+
+
+@pytest.fixture(scope="module")
+def K():
+    from building_llm_from_scratch_b200 import kernels
+    return kernels
+
+
+def rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, generator=g, device="cuda") * scale).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,N,K_", [(128, 256, 64), (128, 64, 64), (128, 128, 128), (256, 512, 256),
+                                   (8192, 2048, 2048), (300, 200, 136), (1000, 50257 // 16, 192), (64, 3072, 2048)])
+def test_gemm_nt(K, M, N, K_):
+    from oracle import reference_ops as R
+    a, w = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2)
+    c = K.gemm_ex(a, w)
+    ref = R.linear(a.float(), w.float())
+    assert c.shape == (M, N) and c.dtype == torch.bfloat16
+    assert rel_err(c.float(), ref) < BF16_TOL
+
+
+def test_gemm_nt_exact_small_integers(K):
+    # integer-valued inputs: every product and partial sum is exact in fp32 -> bit-exact result
+    g = torch.Generator(device="cuda").manual_seed(5)
+    a = torch.randint(-3, 4, (256, 320), generator=g, device="cuda").to(torch.bfloat16)
+    w = torch.randint(-3, 4, (384, 320), generator=g, device="cuda").to(torch.bfloat16)
+    c = K.gemm_ex(a, w, out_dtype=torch.float32)
+    assert torch.equal(c, a.float() @ w.float().t())
+
+
+def test_gemm_lora_dual_k(K):
+    """LinearWithLoRA forward (lora.py:46): x W^T + s (x A) B in one TMEM accumulation."""
+    from oracle import reference_ops as R
+    M, d_in, d_out, r, s = 512, 256, 384, 8, 2.0
+    x, W = rnd(M, d_in, seed=1), rnd(d_out, d_in, scale=0.05, seed=2)
+    A, B = rnd(d_in, r, scale=0.3, seed=3), rnd(r, d_out, scale=0.05, seed=4)
+    sd = {"l.linear.weight": W.float(), "l.lora.A": A.float(), "l.lora.B": B.float()}
+    ref = R.lora_linear(x.float(), sd, "l", s)
+    At = K.transpose(A)                       # [r, in]  (K-major "B operand" of t = x A)
+    t = K.gemm_ex(x, At, alpha=s)             # s * (x A)   [M, r]
+    Bt = K.transpose(B)                       # [out, r]
+    y = K.gemm_ex(x, W, a2=t, b2=Bt)
+    assert rel_err(y.float(), ref) < BF16_TOL
+    # and with r = 64 plus residual + bias + gelu epilogues
+    r = 64
+    A, B = rnd(d_in, r, scale=0.1, seed=5), rnd(r, d_out, scale=0.05, seed=6)
+    bias, res = rnd(d_out, seed=7), rnd(M, d_out, seed=8)
+    t = K.gemm_ex(x, K.transpose(A), alpha=s)
+    y = K.gemm_ex(x, W, a2=t, b2=K.transpose(B), bias=bias, residual=res, gelu=True)
+    lin = x.float() @ W.float().t() + t.float() @ B.float() + bias.float()
+    ref = R.gelu_erf(lin) + res.float()
+    assert rel_err(y.float(), ref) < BF16_TOL
+
+
+@pytest.mark.parametrize("M,N,K_", [(256, 256, 128), (1024, 2048, 512), (200, 264, 72)])
+def test_gemm_mn_major_operands(K, M, N, K_):
+    a, b = rnd(M, K_, seed=1), rnd(N, K_, scale=0.1, seed=2)
+    ref = a.float() @ b.float().t()
+    at, bt = a.t().contiguous(), b.t().contiguous()   # stored [K, M], [K, N]
+    assert rel_err(K.gemm_ex(a, bt, b1_mn=True, M=M, N=N).float(), ref) < BF16_TOL      # NN (dX = dY W)
+    assert rel_err(K.gemm_ex(at, bt, a1_mn=True, b1_mn=True).float(), ref) < BF16_TOL   # TN (dW = dY^T X)
+    assert rel_err(K.gemm_ex(at, b, a1_mn=True).float(), ref) < BF16_TOL
+
+
+def test_gemm_splitk_accumulate_and_transposed_store(K):
+    """LoRA weight gradients: dA = x^T u [in, r], dB^T = dY^T t stored as dB [r, out]; fp32
+    atomics across split-K, accumulating on top of existing contents."""
+    Mtok, d_in, d_out, r = 4096, 512, 768, 64
+    x, u = rnd(Mtok, d_in, seed=1), rnd(Mtok, r, scale=0.1, seed=2)
+    dY, t = rnd(Mtok, d_out, scale=0.1, seed=3), rnd(Mtok, r, seed=4)
+    dA = torch.ones(d_in, r, device="cuda", dtype=torch.float32)
+    K.gemm_ex(x, u, a1_mn=True, b1_mn=True, out=dA, accumulate=True)
+    assert rel_err(dA, 1 + x.float().t() @ u.float()) < 1e-3
+    dB = torch.zeros(r, d_out, device="cuda", dtype=torch.float32)
+    K.gemm_ex(dY, t, a1_mn=True, b1_mn=True, out=dB, accumulate=True, trans_out=True, alpha=0.5)
+    assert rel_err(dB, 0.5 * t.float().t() @ dY.float()) < 1e-3
+
+
+def test_gemm_rejects_cpu_and_bad_args(K):
+    with pytest.raises(RuntimeError):
+        K.gemm_ex(torch.zeros(8, 8, dtype=torch.bfloat16), torch.zeros(8, 8, dtype=torch.bfloat16))
+    from building_llm_from_scratch_b200 import _lib
+    with pytest.raises(_lib.B200Error):
+        K.gemm_ex(rnd(16, 12), rnd(16, 12))   # K = 12 breaks the 16-byte row pitch TMA needs
