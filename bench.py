@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py — train tokens/sec of the decoder training step (Llama-3.2-1B LoRA bf16, BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one Trainer.train_batch over one synthetic Alpaca-shaped batch (per-GPU micro-batch
+B=4 x T=2048, the reference default, args.py:53): zero_grad, LR schedule, forward + fused vocab
+projection/cross-entropy, backward, [data-parallel gradient mean], clip 1.0, AdamW.
+
+Prints ONE JSON line (rank 0): `value` = whole-job tokens/s with inputs resident in HBM,
+device-timed (CUDA events, max over ranks); `e2e` = the same metric through the public API
+(engine.TrainStep.run) with pinned HOST batches (H2D of tokens+targets and D2H of the loss inside the
+timed region); `roofline` for the dominant kernel (the tcgen05 GEMM) from a separately instrumented
+pass; `cpu_baseline` = the oracle (CPU port of the reference modules) timed on this box's host cores
+on a bounded sample. `--impl reference` times that CPU path alone.
+"""
+from __future__ import annotations
+
+import argparse
+import copy
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "train tokens/sec (Llama-3.2-1B LoRA bf16)"
+UNIT = "tokens/s"
+SEQ_LEN = 2048
+MICRO_BATCH = 4
+LORA_RANK, LORA_ALPHA = 64, 32          # args.py:89-90 defaults
+PEAK_LR, WEIGHT_DECAY = 5e-4, 0.1       # args.py lr default / build_components.py:258
+
+
+def llama32_1b_cfg(seq_len=SEQ_LEN, n_layers=None):
+    from building_llm_from_scratch_b200.Models.Llama.config import get_config_llama
+    cfg = get_config_llama("1B", "llama3_2", target_context_length=seq_len)   # SURVEY.md R4 override
+    if n_layers is not None:
+        cfg["n_layers"] = n_layers
+    return cfg
+
+
+def flops_per_token(cfg, rank, seq_len):
+    """LoRA with frozen base = 4*P_lin + 6*P_lora + causal attention."""
+    d, f, L, V = cfg["emb_dim"], cfg["hidden_dim"], cfg["n_layers"], cfg["vocab_size"]
+    hd = d // cfg["n_heads"]
+    kv = cfg["n_kv_groups"] * hd
+    lin = [(d, d), (d, kv), (d, kv), (d, d), (d, f), (d, f), (f, d)]
+    p_lin = L * sum(i * o for i, o in lin) + d * V
+    p_lora = L * sum(rank * (i + o) for i, o in lin) + rank * (d + V)
+    attn = 0.5 * (4 + 8) * seq_len * d * L
+    return 4 * p_lin + 6 * p_lora + attn
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(tf_burst=p["bf16_tflops"], tf_sustained=p["bf16_tflops_sustained"], hbm=p["hbm_gbs"], src="measured")
+    return dict(tf_burst=1590.0, tf_sustained=1400.0, hbm=6650.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks / throttle reasons with nvidia-smi during the timed region."""
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._halt = threading.Event()
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.gpu)], capture_output=True, text=True, timeout=5).stdout.strip()
+                parts = [x.strip() for x in out.split(",")]
+                self.samples.append(float(parts[0]))
+                self.max_mhz = float(parts[1])
+                for n, v in zip(names, parts[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=3)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# --------------------------------------------------------------------------------------
+# CPU baseline: the oracle (port of the reference modules) on the host cores
+# --------------------------------------------------------------------------------------
+def cpu_reference_sample(seq_len=256, budget_s=25.0):
+    """One bounded sample of the same workload on CPU: Llama-3.2-1B dims, LoRA r=64, bf16,
+    B=1 x T=seq_len, forward + CE + backward through the oracle with 1 and 2 blocks; the per-block
+    and head+embedding costs are separated and extrapolated to the 16-block model."""
+    from oracle import reference_ops as R
+    torch.manual_seed(123)
+    times = {}
+    cfg = None
+    for nl in (1, 2):
+        cfg = llama32_1b_cfg(seq_len, n_layers=nl)
+        sd = oracle_state(cfg, LORA_RANK)
+        x = torch.randint(0, cfg["vocab_size"], (1, seq_len))
+        y = torch.roll(x, -1, 1)
+        y[:, : seq_len // 2] = -100
+        t0 = time.perf_counter()
+        logits = R.llama3_forward(x, sd, cfg, LORA_ALPHA / LORA_RANK)
+        loss = R.cross_entropy(logits, y)
+        loss.backward()
+        times[nl] = time.perf_counter() - t0
+        del sd, logits, loss
+        if times[nl] > budget_s:
+            break
+    if 2 in times:
+        per_block = max(times[2] - times[1], 1e-6)
+        rest = max(times[1] - per_block, 0.0)
+    else:  # very slow host: scale the single-block run by FLOPs
+        per_block = times[1] * 0.3
+        rest = times[1] * 0.7
+    full = rest + 16 * per_block
+    return dict(tokens_per_s=seq_len / full, seconds=sum(times.values()),
+                sample=f"oracle Llama-3.2-1B dims LoRA r={LORA_RANK} bf16 CPU, B=1xT={seq_len}, fwd+CE+bwd with 1 and 2 "
+                       f"blocks ({times.get(1, 0):.1f}s, {times.get(2, 0):.1f}s), extrapolated to 16 blocks + head")
+
+
+def oracle_state(cfg, rank):
+    """Random-init state_dict with the reference's key names (bf16, fp32 norm weights)."""
+    d, f, V, L = cfg["emb_dim"], cfg["hidden_dim"], cfg["vocab_size"], cfg["n_layers"]
+    hd = d // cfg["n_heads"]
+    kv = cfg["n_kv_groups"] * hd
+    from oracle import reference_ops as R
+    cos, sin = R.precompute_rope_params(hd, cfg["rope_base"], cfg["context_length"], cfg["rope_freq"])
+    sd = {"tok_emb.weight": (torch.randn(V, d) * 0.02).bfloat16(), "final_norm.weight": torch.ones(d)}
+
+    def lin(prefix, i, o):
+        sd[prefix + ".linear.weight"] = (torch.randn(o, i) * 0.02).bfloat16()
+        sd[prefix + ".lora.A"] = ((torch.rand(i, rank) * 2 - 1) / rank ** 0.5).bfloat16().requires_grad_(True)
+        sd[prefix + ".lora.B"] = (torch.randn(rank, o) * 0.01).bfloat16().requires_grad_(True)
+
+    for l in range(L):
+        p = f"trf_blocks.{l}"
+        for name, (i, o) in {"att.W_query": (d, d), "att.W_key": (d, kv), "att.W_value": (d, kv), "att.out_proj": (d, d),
+                             "ff.fc1": (d, f), "ff.fc2": (d, f), "ff.fc3": (f, d)}.items():
+            lin(f"{p}.{name}", i, o)
+        sd[f"{p}.norm1.weight"] = torch.ones(d)
+        sd[f"{p}.norm2.weight"] = torch.ones(d)
+        sd[f"{p}.att.cos"] = cos.bfloat16()
+        sd[f"{p}.att.sin"] = sin.bfloat16()
+    lin("out_head", d, V)
+    return sd
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    vals = []
+    sample = None
+    for i in range(args.warmup + args.steps):
+        r = cpu_reference_sample(seq_len=128 if i < args.warmup else 512)
+        if i >= args.warmup:
+            vals.append(r["tokens_per_s"])
+            sample = r["sample"]
+    v = sum(vals) / len(vals)
+    cfg = llama32_1b_cfg()
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * MICRO_BATCH * SEQ_LEN / v, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(cfg, 1),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(cfg, n_gpus):
+    return {"workload": f"Llama-3.2-1B LoRA r={LORA_RANK} alpha={LORA_ALPHA} instruction finetune, bf16, Alpaca-shaped "
+                        f"synthetic batches, micro-batch {MICRO_BATCH} x seq {SEQ_LEN} per GPU (BASELINE.json configs[2])",
+            "global_batch": MICRO_BATCH * n_gpus, "seq_len": SEQ_LEN, "parallelism": f"dp{n_gpus}",
+            "l2_policy": "per-step working set (2.5 GB frozen weights + activations) far exceeds the 126 MB L2",
+            "n_layers": cfg["n_layers"], "vocab_size": cfg["vocab_size"]}
+
+
+# --------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------
+def build_trainer(cfg, device, world_size):
+    from building_llm_from_scratch_b200.Models.Llama import Llama3 as L
+    from building_llm_from_scratch_b200.ddp import B200DDP
+    from building_llm_from_scratch_b200.lora import replace_linear_with_lora
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    from building_llm_from_scratch_b200.train import Trainer
+    torch.manual_seed(123)                                       # utils.set_seed(123), main.py:58
+    with torch.device(device):
+        model = L.Llama3Model(copy.deepcopy(cfg))
+    for p in model.parameters():                                 # activate_lora, build_components.py:117-135
+        p.requires_grad = False
+    with torch.device(device):
+        replace_linear_with_lora(model, rank=LORA_RANK, alpha=LORA_ALPHA, dtype=cfg["dtype"])
+    model.train()
+    if world_size > 1:
+        model = B200DDP(model)
+    opt = B200AdamW(model.parameters(), lr=PEAK_LR, weight_decay=WEIGHT_DECAY)
+    tr = Trainer(model, opt, cfg, [], None, "/tmp", device=device)
+    tr.set_schedule(total_training_steps=100_000)
+    return tr
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--layers", type=int, default=None, help="debug: fewer blocks (result is then not a bench value)")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    from building_llm_from_scratch_b200 import _lib, kernels
+    from building_llm_from_scratch_b200.datautils.synthetic import alpaca_batch
+    from building_llm_from_scratch_b200.engine import TrainStep
+    _lib.check(_lib.load().b200_init(local_rank), "init")
+
+    cfg = llama32_1b_cfg(SEQ_LEN, n_layers=args.layers)
+    tr = build_trainer(cfg, device, world)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    n_batches = 4
+    host = [alpaca_batch(gen, MICRO_BATCH, SEQ_LEN, cfg["vocab_size"]) for _ in range(n_batches)]
+    host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
+    dev = [(x.to(device), y.to(device)) for x, y in host]
+    ignored = float(sum((y == -100).float().mean() for _, y in host) / n_batches)
+
+    step = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=not args.no_graph)
+    step.capture(warmup=2)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(batches, read_loss):
+        for i in range(args.warmup):
+            step.run(*batches[i % n_batches])
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _lib.launch_count()
+        e0.record()
+        for i in range(args.steps):
+            loss = step.run(*batches[i % n_batches])
+            if read_loss:
+                last = float(loss)          # D2H read of the step's result, every step
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        n = _lib.launch_count() - l0
+        if step.graphs is not None:   # replayed launches are not host calls: count what the graph holds
+            n += step.launches_per_step * args.steps
+        return ms, n
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms_dev, launches = timed(dev, read_loss=False)
+    clocks = sampler.stop() if sampler else None
+    ms_e2e, _ = timed(host, read_loss=True)
+    final_loss = float(step.loss)
+
+    tokens_step = MICRO_BATCH * SEQ_LEN * world
+    value = tokens_step * args.steps / (ms_dev / 1e3)
+    e2e = tokens_step * args.steps / (ms_e2e / 1e3)
+
+    # ---- roofline of the dominant kernel: instrumented eager pass (not part of the timed runs)
+    roof = None
+    if rank == 0:
+        peaks = load_peaks()
+        prof = kernels.GemmProfile()
+        kernels.set_gemm_profile(prof)
+        eager = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=False)
+        eager.x.copy_(dev[0][0]); eager.y.copy_(dev[0][1])
+        eager._refresh_hyper(peek=True)
+        eager._eager_step()                       # warm
+        prof.reset()
+        eager._eager_step()
+        torch.cuda.synchronize()
+        kernels.set_gemm_profile(None)
+        flops, ms_gemm, n_gemm = prof.totals()
+        fpt = flops_per_token(cfg, LORA_RANK, SEQ_LEN)
+        roof = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (all launches of one step)",
+                "achieved": flops / (ms_gemm * 1e-3) / 1e12, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": flops / (ms_gemm * 1e-3) / 1e12 / peaks["tf_sustained"], "traffic": None,
+                "peak_source": f"{peaks['src']} (sustained; burst {peaks['tf_burst']})",
+                "gemm_launches_per_step": n_gemm, "gemm_ms_per_step": ms_gemm,
+                "gemm_share_of_step": ms_gemm / (ms_dev / args.steps),
+                "step_frac_of_burst_peak": value / world * fpt / 1e12 / peaks["tf_burst"],
+                "algorithmic_gflops_per_token": fpt / 1e9}
+    if world > 1:
+        dist.barrier()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        r = cpu_reference_sample(seq_len=1024)
+        cpu = {"value": r["tokens_per_s"], "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+               "sample": r["sample"]}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(cfg, world),
+                "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 2 * MICRO_BATCH * SEQ_LEN * 8 + 28,
+                        "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+                "cuda_graph": step.graphs is not None, "final_loss": final_loss,
+                "ignored_target_fraction": ignored}
+        if args.layers is not None:
+            line["debug_layers"] = args.layers
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

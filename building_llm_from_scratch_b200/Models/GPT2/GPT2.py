@@ -1,0 +1,127 @@
+"""Drop-in for Models/GPT2/GPT2.py: same class names, constructor signatures and state_dict keys.
+
+Deviations (documented in DESIGN.md): the per-forward debug print (GPT2.py:123) is dropped; the
+modules compute in bf16 (the GPU configs of BASELINE.json; the reference's GPT-2 ignores
+cfg["dtype"]); dropout sites keep their nn.Dropout modules (identity at
+drop_rate 0, which is what parity runs use — SURVEY.md H5)."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+from torch.utils.checkpoint import checkpoint_sequential
+
+from ... import ops
+from ...lora import B200Linear, head_operands
+
+
+class B200LayerNorm(nn.LayerNorm):
+    def forward(self, x):
+        return ops.layernorm(x, self.weight, self.bias, self.eps)[0]
+
+
+class GELU(nn.GELU):
+    def forward(self, x):
+        return ops.gelu(x)
+
+
+class MultiHeadAttention(nn.Module):
+    """GPT2.py:6-49."""
+
+    def __init__(self, d_in, d_out, context_length, dropout, num_heads, qkv_bias=False):
+        super().__init__()
+        assert d_out % num_heads == 0, "Output dimension must be divisible by number of heads"
+        self.d_out = d_out
+        self.num_heads = num_heads
+        self.head_dim = d_out // num_heads
+        self.context_length = context_length
+        self.W_query = B200Linear(d_in, d_out, bias=qkv_bias)
+        self.W_key = B200Linear(d_in, d_out, bias=qkv_bias)
+        self.W_value = B200Linear(d_in, d_out, bias=qkv_bias)
+        self.out_proj = B200Linear(d_out, d_out)
+        self.dropout = nn.Dropout(dropout)
+        self.register_buffer("mask", torch.empty(0), persistent=False)  # see Llama3.GroupedQueryAttention
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        super()._save_to_state_dict(destination, prefix, keep_vars)
+        n = self.context_length
+        destination[prefix + "mask"] = torch.triu(torch.ones(n, n, device=self.out_proj.weight.device), diagonal=1)
+
+    def _load_from_state_dict(self, state_dict, prefix, *args):
+        state_dict.pop(prefix + "mask", None)
+        super()._load_from_state_dict(state_dict, prefix, *args)
+
+    def forward(self, x, residual=None):
+        if self.training and self.dropout.p > 0:
+            raise NotImplementedError("attention-weight dropout (GPT2.py:43) is not fused yet: use drop_rate=0.0")
+        b, num_tokens, _ = x.shape
+        q = self.W_query(x).view(b * num_tokens, -1)
+        k = self.W_key(x).view(b * num_tokens, -1)
+        v = self.W_value(x).view(b * num_tokens, -1)
+        ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)[0]
+        return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
+
+
+class FeedForward(nn.Module):
+    """GPT2.py:52-65."""
+
+    def __init__(self, cfg):
+        super().__init__()
+        self.layers = nn.Sequential(B200Linear(cfg["emb_dim"], 4 * cfg["emb_dim"]), GELU(),
+                                    B200Linear(4 * cfg["emb_dim"], cfg["emb_dim"]))
+
+    def forward(self, x, residual=None):
+        h = self.layers[1](self.layers[0](x))
+        return self.layers[2](h, residual)
+
+
+class TransformerBlock(nn.Module):
+    """GPT2.py:68-88."""
+
+    def __init__(self, cfg):
+        super().__init__()
+        self.att = MultiHeadAttention(d_in=cfg["emb_dim"], d_out=cfg["emb_dim"], context_length=cfg["context_length"],
+                                      num_heads=cfg["n_heads"], dropout=cfg["drop_rate"], qkv_bias=cfg["qkv_bias"])
+        self.ff = FeedForward(cfg)
+        self.norm1 = B200LayerNorm(cfg["emb_dim"])
+        self.norm2 = B200LayerNorm(cfg["emb_dim"])
+        self.dropout = nn.Dropout(cfg["drop_rate"])
+
+    def forward(self, x):
+        if self.training and self.dropout.p > 0:
+            x = x + self.dropout(self.att(self.norm1(x)))
+            return x + self.dropout(self.ff(self.norm2(x)))
+        x = self.att(self.norm1(x), residual=x)
+        return self.ff(self.norm2(x), residual=x)
+
+
+class GPTModel(nn.Module):
+    """GPT2.py:91-124."""
+
+    def __init__(self, cfg, use_actv_ckpt=False):
+        super().__init__()
+        self.cfg = cfg
+        self.use_actv_ckpt = use_actv_ckpt
+        self.tok_emb = nn.Embedding(cfg["vocab_size"], cfg["emb_dim"])
+        self.pos_emb = nn.Embedding(cfg["context_length"], cfg["emb_dim"])
+        self.drop_emb = nn.Dropout(cfg["drop_rate"])
+        self.blocks = nn.Sequential(*[TransformerBlock(cfg) for _ in range(cfg["n_layers"])])
+        self.norm = B200LayerNorm(cfg["emb_dim"])
+        self.output_head = B200Linear(cfg["emb_dim"], cfg["vocab_size"], bias=False)
+
+    def hidden_states(self, x):
+        x = ops.embedding(x, self.tok_emb.weight, self.pos_emb.weight)
+        x = self.drop_emb(x)
+        if self.use_actv_ckpt:
+            if not x.requires_grad:
+                x.requires_grad_(True)
+            x = checkpoint_sequential(self.blocks, segments=self.cfg["n_layers"], input=x, use_reentrant=False)
+        else:
+            x = self.blocks(x)
+        return self.norm(x)
+
+    def forward(self, x):
+        return self.output_head(self.hidden_states(x))
+
+    def forward_loss(self, x, targets):
+        w, A, B, s = head_operands(self.output_head)
+        return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets)[0]

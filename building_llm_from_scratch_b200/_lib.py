@@ -49,12 +49,15 @@ SIGNATURES = {
     "b200_cross_entropy_bf16": (I, [P, I64, P, P, I64, I64, I, P, SZ, P]),
     "b200_grad_norm_workspace_bytes": (SZ, [I64]),
     "b200_grad_norm_bf16": (I, [P, I64, F, P, P, SZ, P]),
-    "b200_adamw_bf16": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P]),
-    "b200_adamw_f32": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P]),
+    "b200_grad_norm_f32": (I, [P, I64, F, P, P, SZ, P]),
+    "b200_adam_hyper": (I, [P, F, F, F, F, F, I64]),
+    "b200_adamw_bf16": (I, [P, P, I, P, P, I64, F, F, F, F, F, I64, P, P, P]),
+    "b200_adamw_f32": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P, P]),
     "b200_cast_f32_to_bf16": (I, [P, P, I64, P]),
     "b200_cast_bf16_to_f32": (I, [P, P, I64, P]),
     "b200_transpose_bf16": (I, [P, I64, P, I64, I64, I64, F, P]),
     "b200_add_bf16": (I, [P, P, P, I64, P]),
+    "b200_colsum_bf16": (I, [P, I64, P, I64, I64, P]),
     "b200_attention_fwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, I64, I64, F, P]),
     "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, P, I64, P, I64, P,
                                     I64, I64, I64, I64, I64, I64, F, P]),

@@ -278,7 +278,42 @@ transpose_kernel(const bf16* __restrict__ in, long long ldi, bf16* __restrict__ 
   }
 }
 
+// ---------------- column sum (bias gradient): out[n] += sum_m x[m, n] ----------------
+__global__ void __launch_bounds__(256)
+colsum_kernel(const bf16* __restrict__ x, long long ld, float* __restrict__ out, long long M, int N,
+              int rows_per_block) {
+  const int c = (blockIdx.x * 256 + threadIdx.x) * 8;
+  if (c >= N) return;
+  const long long r0 = (long long)blockIdx.y * rows_per_block;
+  const long long r1 = r0 + rows_per_block < M ? r0 + rows_per_block : M;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c + 8 <= N && (ld & 7) == 0) {
+    for (long long r = r0; r < r1; ++r) {
+      float f[8];
+      unpack8(ld_nc_v4(x + r * ld + c), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+  } else {
+    for (long long r = r0; r < r1; ++r)
+      for (int j = 0; j < 8 && c + j < N; ++j) acc[j] += __bfloat162float(x[r * ld + c + j]);
+  }
+  for (int j = 0; j < 8 && c + j < N; ++j) atomicAdd(&out[c + j], acc[j]);
+}
+
 }  // namespace
+
+extern "C" int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N,
+                                void* stream) {
+  B200_CHECK_ARG(x && out && M > 0 && N > 0 && ld >= N, "colsum: null pointer, empty or bad pitch");
+  const int rows_per_block = 128;
+  dim3 grid((unsigned)((N + 2047) / 2048), (unsigned)((M + rows_per_block - 1) / rows_per_block));
+  B200_CHECK_ARG(grid.y <= 65535, "colsum: too many rows for one launch");
+  colsum_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, ld, out, M, (int)N, rows_per_block);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
 
 extern "C" int b200_swiglu_fwd_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, void* h,
                                     int64_t M, int64_t F, int bf16_steps, void* stream) {

@@ -123,6 +123,24 @@ sumsq_partial_kernel(const bf16* __restrict__ g, long long n, float* __restrict_
   if (threadIdx.x == 0) partial[blockIdx.x] = acc;
 }
 
+__global__ void __launch_bounds__(256)
+sumsq_partial_f32_kernel(const float* __restrict__ g, long long n, float* __restrict__ partial) {
+  __shared__ float red[33];
+  const long long nv = n >> 2;
+  float acc = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    const uint4 u = ld_nc_v4(g + i * 4);
+    const float a = __uint_as_float(u.x), b = __uint_as_float(u.y), c = __uint_as_float(u.z),
+                d = __uint_as_float(u.w);
+    acc += a * a + b * b + c * c + d * d;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 4; k < n; ++k) acc += g[k] * g[k];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partial[blockIdx.x] = acc;
+}
+
 __global__ void __launch_bounds__(1024)
 norm_finish_kernel(const float* __restrict__ partial, int nblocks, float max_norm,
                    float* __restrict__ out) {
@@ -155,17 +173,37 @@ __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& 
   p -= c.step_size * (m / denom);
 }
 
+// Hyper-parameters may come from device memory (7 floats: lr, beta1, beta2, eps, weight_decay,
+// step_size = lr / bias_correction1, 1/sqrt(bias_correction2)) so that a captured CUDA graph
+// can be replayed with a new learning rate / step count.
+__device__ __forceinline__ AdamConsts load_consts(const AdamConsts& c, const float* __restrict__ dev) {
+  if (dev == nullptr) return c;
+  AdamConsts r;
+  r.lr = dev[0]; r.b1 = dev[1]; r.b2 = dev[2]; r.eps = dev[3]; r.wd = dev[4];
+  r.step_size = dev[5]; r.inv_sqrt_bc2 = dev[6];
+  return r;
+}
+
+template <bool G32>
 __global__ void __launch_bounds__(256)
-adamw_bf16_kernel(bf16* __restrict__ p, const bf16* __restrict__ g, bf16* __restrict__ m,
-                  bf16* __restrict__ v, long long n, AdamConsts c,
+adamw_bf16_kernel(bf16* __restrict__ p, const void* __restrict__ gv, bf16* __restrict__ m,
+                  bf16* __restrict__ v, long long n, AdamConsts c0, const float* __restrict__ dev_hyper,
                   const float* __restrict__ grad_scale) {
+  const AdamConsts c = load_consts(c0, dev_hyper);
   const float gs = grad_scale ? grad_scale[0] : 1.f;
   const long long nv = n >> 3;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
        i += (long long)gridDim.x * blockDim.x) {
     float fp[8], fg[8], fm[8], fv[8];
     unpack8(ld_v4(p + i * 8), fp);
-    unpack8(ld_nc_v4(g + i * 8), fg);
+    if (G32) {
+      const float* g = (const float*)gv;
+      const uint4 u0 = ld_nc_v4(g + i * 8), u1 = ld_nc_v4(g + i * 8 + 4);
+      fg[0] = __uint_as_float(u0.x); fg[1] = __uint_as_float(u0.y); fg[2] = __uint_as_float(u0.z); fg[3] = __uint_as_float(u0.w);
+      fg[4] = __uint_as_float(u1.x); fg[5] = __uint_as_float(u1.y); fg[6] = __uint_as_float(u1.z); fg[7] = __uint_as_float(u1.w);
+    } else {
+      unpack8(ld_nc_v4((const bf16*)gv + i * 8), fg);
+    }
     unpack8(ld_v4(m + i * 8), fm);
     unpack8(ld_v4(v + i * 8), fv);
 #pragma unroll
@@ -177,7 +215,8 @@ adamw_bf16_kernel(bf16* __restrict__ p, const bf16* __restrict__ g, bf16* __rest
   if (blockIdx.x == 0 && threadIdx.x == 0)
     for (long long k = nv * 8; k < n; ++k) {
       float fp = __bfloat162float(p[k]), fm = __bfloat162float(m[k]), fv = __bfloat162float(v[k]);
-      adam_update(fp, bf16_round(__bfloat162float(g[k]) * gs), fm, fv, c);
+      const float g = G32 ? ((const float*)gv)[k] : __bfloat162float(((const bf16*)gv)[k]);
+      adam_update(fp, bf16_round(g * gs), fm, fv, c);
       p[k] = __float2bfloat16_rn(fp);
       m[k] = __float2bfloat16_rn(fm);
       v[k] = __float2bfloat16_rn(fv);
@@ -186,8 +225,9 @@ adamw_bf16_kernel(bf16* __restrict__ p, const bf16* __restrict__ g, bf16* __rest
 
 __global__ void __launch_bounds__(256)
 adamw_f32_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                 float* __restrict__ v, long long n, AdamConsts c,
+                 float* __restrict__ v, long long n, AdamConsts c0, const float* __restrict__ dev_hyper,
                  const float* __restrict__ grad_scale) {
+  const AdamConsts c = load_consts(c0, dev_hyper);
   const float gs = grad_scale ? grad_scale[0] : 1.f;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x) {
@@ -249,15 +289,16 @@ extern "C" size_t b200_grad_norm_workspace_bytes(int64_t n) {
   return (size_t)GN_MAX_BLOCKS * sizeof(float);
 }
 
-extern "C" int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, float* out,
-                                   void* workspace, size_t workspace_bytes, void* stream) {
+static int grad_norm_impl(const void* g, int g_is_f32, int64_t n, float max_norm, float* out,
+                          void* workspace, size_t workspace_bytes, void* stream) {
   B200_CHECK_ARG(g && out && workspace && n > 0, "grad_norm: null pointer or empty");
   B200_CHECK_ARG(b200_aligned16(g), "grad_norm: gradient buffer must be 16-B aligned");
   B200_CHECK_ARG(workspace_bytes >= b200_grad_norm_workspace_bytes(n), "grad_norm: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   int blocks = ew_grid(n / 8 + 1, 256);
   if (blocks > GN_MAX_BLOCKS) blocks = GN_MAX_BLOCKS;
-  sumsq_partial_kernel<<<blocks, 256, 0, st>>>((const bf16*)g, n, (float*)workspace);
+  if (g_is_f32) sumsq_partial_f32_kernel<<<blocks, 256, 0, st>>>((const float*)g, n, (float*)workspace);
+  else sumsq_partial_kernel<<<blocks, 256, 0, st>>>((const bf16*)g, n, (float*)workspace);
   B200_CHECK_LAUNCH();
   norm_finish_kernel<<<1, 1024, 0, st>>>((const float*)workspace, blocks, max_norm, out);
   B200_CHECK_LAUNCH();
@@ -265,13 +306,37 @@ extern "C" int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, flo
   return 0;
 }
 
-extern "C" int b200_adamw_bf16(void* p, const void* g, void* m, void* v, int64_t n, float lr,
-                               float beta1, float beta2, float eps, float weight_decay,
-                               int64_t step, const float* grad_scale, void* stream) {
-  B200_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw: null pointer, empty, or step < 1");
+extern "C" int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, float* out,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+  return grad_norm_impl(g, 0, n, max_norm, out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_grad_norm_f32(const float* g, int64_t n, float max_norm, float* out,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  return grad_norm_impl(g, 1, n, max_norm, out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_adam_hyper(float* host7, float lr, float beta1, float beta2, float eps,
+                               float weight_decay, int64_t step) {
+  B200_CHECK_ARG(host7 && step >= 1, "adam_hyper: null pointer or step < 1");
+  const AdamConsts c = make_consts(lr, beta1, beta2, eps, weight_decay, step);
+  host7[0] = c.lr; host7[1] = c.b1; host7[2] = c.b2; host7[3] = c.eps; host7[4] = c.wd;
+  host7[5] = c.step_size; host7[6] = c.inv_sqrt_bc2;
+  return 0;
+}
+
+extern "C" int b200_adamw_bf16(void* p, const void* g, int g_is_f32, void* m, void* v, int64_t n,
+                               float lr, float beta1, float beta2, float eps, float weight_decay,
+                               int64_t step, const float* dev_hyper, const float* grad_scale,
+                               void* stream) {
+  B200_CHECK_ARG(p && g && m && v && n > 0 && (step >= 1 || dev_hyper), "adamw: null pointer, empty, or step < 1");
   B200_CHECK_ARG(b200_aligned16(p) && b200_aligned16(g) && b200_aligned16(m) && b200_aligned16(v), "adamw: buffers must be 16-B aligned");
-  adamw_bf16_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
-      (bf16*)p, (const bf16*)g, (bf16*)m, (bf16*)v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step), grad_scale);
+  const AdamConsts c = make_consts(lr, beta1, beta2, eps, weight_decay, step >= 1 ? step : 1);
+  const int grid = ew_grid(n / 8 + 1, 256);
+  if (g_is_f32)
+    adamw_bf16_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((bf16*)p, g, (bf16*)m, (bf16*)v, n, c, dev_hyper, grad_scale);
+  else
+    adamw_bf16_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((bf16*)p, g, (bf16*)m, (bf16*)v, n, c, dev_hyper, grad_scale);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -279,10 +344,10 @@ extern "C" int b200_adamw_bf16(void* p, const void* g, void* m, void* v, int64_t
 
 extern "C" int b200_adamw_f32(float* p, const float* g, float* m, float* v, int64_t n, float lr,
                               float beta1, float beta2, float eps, float weight_decay, int64_t step,
-                              const float* grad_scale, void* stream) {
-  B200_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw: null pointer, empty, or step < 1");
+                              const float* dev_hyper, const float* grad_scale, void* stream) {
+  B200_CHECK_ARG(p && g && m && v && n > 0 && (step >= 1 || dev_hyper), "adamw: null pointer, empty, or step < 1");
   adamw_f32_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(
-      p, g, m, v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step), grad_scale);
+      p, g, m, v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step >= 1 ? step : 1), dev_hyper, grad_scale);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;

@@ -1,0 +1,116 @@
+"""Static-shape training-step runner with CUDA-graph replay.
+
+Runs exactly Trainer.train_batch's sequence (zero_grad, LR for the step, fused forward + CE,
+backward, [data-parallel gradient mean], clip 1.0, AdamW) on static device buffers so the ~1.5 k
+kernel launches of a step can be captured once and replayed without host launch cost
+(SURVEY.md H8). Per-step scalars (learning rate, Adam bias corrections) are read by the kernels from
+device memory that is refreshed before each replay.
+"""
+from __future__ import annotations
+
+import torch
+
+from .ddp import B200DDP
+from .optim import B200AdamW
+from .train import Trainer
+
+
+class TrainStep:
+    def __init__(self, trainer: Trainer, batch_shape, use_graph: bool = True):
+        assert isinstance(trainer.optimizer, B200AdamW), "TrainStep drives the fused optimizer"
+        self.tr = trainer
+        self.opt = trainer.optimizer
+        self.model = trainer.model
+        self.core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        self.ddp = self.model if isinstance(self.model, B200DDP) and self.model.world_size > 1 else None
+        dev = next(self.core.parameters()).device
+        self.x = torch.zeros(batch_shape, dtype=torch.int64, device=dev)
+        self.y = torch.zeros(batch_shape, dtype=torch.int64, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.use_graph = use_graph
+        self.graphs = None
+        self.launches_per_step = 0
+        self.opt.graph_safe = True
+        self.core.train()
+
+    # -- the two halves of a step (split where the data-parallel exchange goes) -------------
+    def _fwd_bwd(self):
+        self.opt.zero_grad()
+        loss = self.core.forward_loss(self.x, self.y)
+        loss.backward()
+        self.loss.copy_(loss.detach())
+
+    def _update(self):
+        self.opt.step()
+
+    def _eager_step(self):
+        self._fwd_bwd()
+        if self.ddp is not None:
+            self.ddp.reduce_gradients(self.opt.flat_grads)
+        self._update()
+
+    def capture(self, warmup: int = 3):
+        """Warm up eagerly on a side stream (lazy initialisation, allocator), then capture."""
+        self._refresh_hyper(peek=True)
+        # warm-up steps must not move the weights or the optimizer state: snapshot and restore
+        saved = [(g["p"].clone(), g["m"].clone(), g["v"].clone()) for g in self.opt._groups.values()]
+        saved_step = self.opt._step
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        from . import _lib
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                n0 = _lib.launch_count()
+                self._eager_step()
+                self.launches_per_step = _lib.launch_count() - n0   # b200llm kernels in one step
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        for g, (p0, m0, v0) in zip(self.opt._groups.values(), saved):
+            g["p"].copy_(p0)
+            g["m"].copy_(m0)
+            g["v"].copy_(v0)
+        self.opt._step = saved_step
+        if not self.use_graph:
+            return
+        if self.ddp is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._fwd_bwd()
+                self._update()
+            self.graphs = (g,)
+        else:
+            g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g1):
+                self._fwd_bwd()
+            with torch.cuda.graph(g2, pool=g1.pool()):
+                self._update()
+            self.graphs = (g1, g2)
+
+    def _refresh_hyper(self, peek: bool = False):
+        tr = self.tr
+        step = tr.global_step + (1 if peek else 0)
+        lr = tr.lr_for_step(max(step, 0))
+        for pg in self.opt.param_groups:
+            pg["lr"] = lr
+        self.opt.set_hyper(lr, max(step, 0) + 1)
+        return lr
+
+    def run(self, x_src: torch.Tensor, y_src: torch.Tensor):
+        """One optimizer step on (x_src, y_src) — device tensors or pinned host tensors.
+        Returns the device scalar holding this step's loss (no synchronisation)."""
+        tr = self.tr
+        tr.global_step += 1
+        lr = self._refresh_hyper()
+        tr.track_lrs.append(lr)
+        self.x.copy_(x_src, non_blocking=True)
+        self.y.copy_(y_src, non_blocking=True)
+        if self.graphs is None:
+            self._eager_step()
+        elif len(self.graphs) == 1:
+            self.graphs[0].replay()
+        else:
+            self.graphs[0].replay()
+            self.ddp.reduce_gradients(self.opt.flat_grads)
+            self.graphs[1].replay()
+        tr.tokens_seen += self.x.numel()
+        return self.loss

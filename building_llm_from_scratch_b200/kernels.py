@@ -36,6 +36,51 @@ def _rowmajor2d(t):
     return t, t.stride(0)
 
 
+class GemmProfile:
+    """Opt-in per-launch timing of the GEMM (CUDA events on the launching stream) for bench.py's
+    roofline figure: algorithmic FLOPs = 2*M*N*(K1+K2) per launch."""
+
+    def __init__(self):
+        self.records = []
+
+    def reset(self):
+        self.records = []
+
+    def begin(self):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def end(self, start, flops, shape):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.records.append((start, e, flops, shape))
+
+    def totals(self):
+        torch.cuda.synchronize()
+        flops = sum(r[2] for r in self.records)
+        ms = sum(r[0].elapsed_time(r[1]) for r in self.records)
+        return flops, ms, len(self.records)
+
+    def by_shape(self):
+        torch.cuda.synchronize()
+        out = {}
+        for s, e, f, shape in self.records:
+            d = out.setdefault(shape, [0, 0.0, 0.0])
+            d[0] += 1
+            d[1] += s.elapsed_time(e)
+            d[2] += f
+        return out
+
+
+_gemm_profile = None
+
+
+def set_gemm_profile(p):
+    global _gemm_profile
+    _gemm_profile = p
+
+
 def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, b2_mn=False, bias=None,
             residual=None, gelu=False, out=None, out_dtype=BF16, accumulate=False, trans_out=False,
             alpha=1.0, splitk=0, M=None, N=None):
@@ -67,11 +112,15 @@ def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, 
     ldr = 0
     if residual is not None:
         residual, ldr = _rowmajor2d(residual)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
     rc = lib.b200_gemm_ex(_p(a1), lda1, int(a1_mn), _p(b1), ldb1, int(b1_mn), k1, _p(a2), lda2, int(a2_mn),
                           _p(b2), ldb2, int(b2_mn), K2, _p(bias), _p(residual), ldr, _p(out2), ldc, M, N, flags,
                           int(out.dtype == torch.float32), int(accumulate), int(trans_out), float(alpha),
                           int(splitk), _stream())
     _lib.check(rc, "gemm_ex")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (k1 + K2), (M, N, k1, K2, int(a1_mn), int(b1_mn), int(accumulate)))
     return out
 
 
@@ -234,7 +283,7 @@ def cross_entropy_(logits2d, targets, write_grad=True):
 
 
 def grad_norm(g_flat, max_norm=1.0, out=None, ws=None):
-    """-> fp32 tensor [norm, clip_coef]."""
+    """-> fp32 tensor [norm, clip_coef]; g_flat bf16 or fp32."""
     _need_cuda(g_flat)
     lib = _lib.load()
     n = g_flat.numel()
@@ -243,16 +292,29 @@ def grad_norm(g_flat, max_norm=1.0, out=None, ws=None):
         ws = torch.empty(nbytes, device=g_flat.device, dtype=torch.uint8)
     if out is None:
         out = torch.empty(2, device=g_flat.device, dtype=torch.float32)
-    _lib.check(lib.b200_grad_norm_bf16(_p(g_flat), n, float(max_norm), _p(out), _p(ws), nbytes, _stream()), "grad_norm")
+    fn = lib.b200_grad_norm_f32 if g_flat.dtype == torch.float32 else lib.b200_grad_norm_bf16
+    _lib.check(fn(_p(g_flat), n, float(max_norm), _p(out), _p(ws), nbytes, _stream()), "grad_norm")
     return out
 
 
-def adamw_(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.1, grad_scale=None):
-    _need_cuda(p, g, m, v, grad_scale)
+def adam_hyper(lr, beta1, beta2, eps, weight_decay, step):
+    """7 floats (pinned host tensor) for adamw_'s dev_hyper argument."""
+    host = torch.empty(7, dtype=torch.float32, pin_memory=torch.cuda.is_available())
+    _lib.check(_lib.load().b200_adam_hyper(host.data_ptr(), lr, beta1, beta2, eps, weight_decay, int(step)), "adam_hyper")
+    return host
+
+
+def adamw_(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.1, grad_scale=None,
+           dev_hyper=None):
+    _need_cuda(p, g, m, v, grad_scale, dev_hyper)
     lib = _lib.load()
-    fn = lib.b200_adamw_f32 if p.dtype == torch.float32 else lib.b200_adamw_bf16
-    _lib.check(fn(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, weight_decay, int(step),
-                  _p(grad_scale), _stream()), "adamw")
+    if p.dtype == torch.float32:
+        rc = lib.b200_adamw_f32(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, weight_decay, int(step),
+                                _p(dev_hyper), _p(grad_scale), _stream())
+    else:
+        rc = lib.b200_adamw_bf16(_p(p), _p(g), int(g.dtype == torch.float32), _p(m), _p(v), p.numel(), lr, beta1, beta2,
+                                 eps, weight_decay, int(step), _p(dev_hyper), _p(grad_scale), _stream())
+    _lib.check(rc, "adamw")
 
 
 def cast(x, dtype):
@@ -284,6 +346,18 @@ def add(a, b):
     _need_cuda(a, b)
     out = torch.empty_like(a)
     _lib.check(_lib.load().b200_add_bf16(_p(a), _p(b), _p(out), a.numel(), _stream()), "add")
+    return out
+
+
+def colsum(x2d, like=None):
+    """Column sums of a [M, N] bf16 matrix (fp32 accumulate) -> [N] in like.dtype (default fp32)."""
+    _need_cuda(x2d)
+    x2d, ld = _rowmajor2d(x2d)
+    M, N = x2d.shape
+    out = torch.zeros(N, device=x2d.device, dtype=torch.float32)
+    _lib.check(_lib.load().b200_colsum_bf16(_p(x2d), ld, _p(out), M, N, _stream()), "colsum")
+    if like is not None and like.dtype == BF16:
+        return cast(out, BF16)
     return out
 
 

@@ -1,0 +1,416 @@
+"""torch.library custom ops (namespace ``b200llm``) — the middle face of the drop-in boundary.
+
+One op per fused unit of the decoder training step; each has a fake (meta) implementation for
+shape/dtype propagation and an autograd formula whose backward launches the matching sm_100a
+kernels through the C-ABI (kernels.py). There is no CPU or library fallback: every op raises on
+non-CUDA tensors.
+
+Weight gradients: if a parameter carries a ``main_grad`` attribute (an fp32 view into the flat
+gradient buffer owned by optim.B200AdamW), the backward GEMM accumulates straight into it with
+split-K fp32 atomics and autograd receives ``None`` for that parameter; otherwise a bf16 gradient
+tensor is returned and autograd accumulates it the usual way.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import kernels as K
+
+BF16 = torch.bfloat16
+
+
+def _pitch_ok(t: Optional[Tensor]) -> Optional[Tensor]:
+    """TMA needs 16-byte row pitches. LoRA's B [r, out] has an odd pitch when `out` is GPT-2's
+    vocabulary (50257): hand the GEMM a copy whose rows are padded to a multiple of 8 elements."""
+    if t is None or t.dim() != 2 or (t.stride(0) % 8 == 0 and t.stride(1) == 1 and t.data_ptr() % 16 == 0):
+        return t
+    ld = (t.shape[1] + 7) // 8 * 8
+    buf = t.new_zeros((t.shape[0], ld))
+    buf[:, :t.shape[1]].copy_(t)
+    return buf[:, :t.shape[1]]
+
+
+def _flat2d(x: Tensor) -> Tensor:
+    x2 = x.reshape(-1, x.shape[-1])
+    return x2 if x2.stride(-1) == 1 else x2.contiguous()
+
+
+# ======================================================================================
+# RMSNorm  (Models/Llama/common_components.py:54-70)
+# ======================================================================================
+@torch.library.custom_op("b200llm::rmsnorm", mutates_args=())
+def rmsnorm(x: Tensor, weight: Tensor, eps: float) -> Tensor:
+    return K.rmsnorm_fwd(x.contiguous(), weight, eps)
+
+
+@rmsnorm.register_fake
+def _(x, weight, eps):
+    return torch.empty_like(x)
+
+
+def _rmsnorm_setup(ctx, inputs, output):
+    x, w, eps = inputs
+    ctx.save_for_backward(x, w)
+    ctx.eps = eps
+
+
+def _rmsnorm_bwd(ctx, dy):
+    x, w = ctx.saved_tensors
+    need_dw = ctx.needs_input_grad[1]
+    dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps, need_dw=need_dw)
+    return dx, dw, None
+
+
+rmsnorm.register_autograd(_rmsnorm_bwd, setup_context=_rmsnorm_setup)
+
+
+# ======================================================================================
+# LayerNorm (nn.LayerNorm in Models/GPT2/GPT2.py:79-80,105)
+# ======================================================================================
+@torch.library.custom_op("b200llm::layernorm", mutates_args=())
+def layernorm(x: Tensor, weight: Tensor, bias: Tensor, eps: float) -> Tuple[Tensor, Tensor, Tensor]:
+    return K.layernorm_fwd(x.contiguous(), weight, bias, eps)
+
+
+@layernorm.register_fake
+def _(x, weight, bias, eps):
+    rows = x.numel() // x.shape[-1]
+    return (torch.empty_like(x), x.new_empty((rows,), dtype=torch.float32),
+            x.new_empty((rows,), dtype=torch.float32))
+
+
+def _layernorm_setup(ctx, inputs, output):
+    x, w, b, eps = inputs
+    _, mean, rstd = output
+    ctx.save_for_backward(x, w, mean, rstd)
+
+
+def _layernorm_bwd(ctx, dy, _dm, _dr):
+    x, w, mean, rstd = ctx.saved_tensors
+    need_dw = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+    dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_dw)
+    if need_dw:
+        dw, db = dw.to(w.dtype), db.to(w.dtype)
+    return dx, dw, db, None
+
+
+layernorm.register_autograd(_layernorm_bwd, setup_context=_layernorm_setup)
+
+
+# ======================================================================================
+# Linear / LinearWithLoRA  (lora.py:26,46; every nn.Linear of the two model families)
+# ======================================================================================
+@torch.library.custom_op("b200llm::lora_linear", mutates_args=())
+def lora_linear(x: Tensor, weight: Tensor, bias: Optional[Tensor], A: Optional[Tensor], B: Optional[Tensor],
+                scaling: float, residual: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    """y = x W^T (+ bias) (+ scaling (x A) B) (+ residual) -> (y, t) with t = scaling * x A."""
+    x2 = _flat2d(x)
+    out_f = weight.shape[0]
+    res2 = None if residual is None else _flat2d(residual)
+    if A is not None:
+        # A [in, r] and B [r, out] are read as MN-major operands: no transposes are materialised
+        t = K.gemm_ex(x2, A, b1_mn=True, alpha=scaling)
+        y = K.gemm_ex(x2, weight, a2=t, b2=_pitch_ok(B), b2_mn=True, bias=bias, residual=res2)
+    else:
+        t = x2.new_empty((0,))
+        y = K.gemm_ex(x2, weight, bias=bias, residual=res2)
+    return y.view(*x.shape[:-1], out_f), t
+
+
+@lora_linear.register_fake
+def _(x, weight, bias, A, B, scaling, residual):
+    rows = x.numel() // x.shape[-1]
+    y = x.new_empty((*x.shape[:-1], weight.shape[0]))
+    t = x.new_empty((rows, A.shape[1])) if A is not None else x.new_empty((0,))
+    return y, t
+
+
+def _lora_linear_setup(ctx, inputs, output):
+    x, weight, bias, A, B, scaling, residual = inputs
+    _, t = output
+    ctx.save_for_backward(x, weight, A, B, t)
+    ctx.scaling = scaling
+    ctx.has_bias = bias is not None
+    ctx.has_res = residual is not None
+    ctx.bias_ref = bias
+
+
+def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: bool = False):
+    """param-shaped gradient = a_mn_src^T · b_mn_src (both stored [tokens, *])."""
+    mg = getattr(param, "main_grad", None)
+    if mg is not None:
+        K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
+        return None
+    g32 = torch.zeros(param.shape, device=param.device, dtype=torch.float32)
+    K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=g32, accumulate=True, trans_out=trans_out)
+    return K.cast(g32, param.dtype) if param.dtype == BF16 else g32
+
+
+def _lora_linear_bwd(ctx, dy, _dt):
+    x, weight, A, B, t = ctx.saved_tensors   # saved tensors are the Parameter objects themselves
+    wref, bref, aref, bbref = weight, ctx.bias_ref, A, B
+    need = ctx.needs_input_grad
+    x2 = _flat2d(x)
+    dy2 = _flat2d(dy)
+    dx = dW = dbias = dA = dB = None
+    u = None
+    if A is not None and (need[0] or need[3]):
+        u = K.gemm_ex(dy2, _pitch_ok(B), alpha=ctx.scaling)           # s * dY B^T   [M, r]
+    if need[0]:
+        if u is not None:
+            dx2 = K.gemm_ex(dy2, weight, b1_mn=True, a2=u, b2=A)      # dY W + u A^T
+        else:
+            dx2 = K.gemm_ex(dy2, weight, b1_mn=True)
+        dx = dx2.view(x.shape)
+    if A is not None and need[3]:
+        dA = _weight_grad(x2, u, aref)                                # x^T u          [in, r]
+    if B is not None and need[4]:
+        dB = _weight_grad(dy2, t, bbref, trans_out=True)              # (dY^T t)^T     [r, out]
+    if need[1]:
+        dW = _weight_grad(dy2, x2, wref)                              # dY^T x         [out, in]
+    if ctx.has_bias and need[2]:
+        dbias = K.colsum(dy2, bref)
+    dres = dy if (ctx.has_res and need[6]) else None
+    return dx, dW, dbias, dA, dB, None, dres
+
+
+lora_linear.register_autograd(_lora_linear_bwd, setup_context=_lora_linear_setup)
+
+
+def linear(x, weight, bias=None, residual=None):
+    return lora_linear(x, weight, bias, None, None, 0.0, residual)[0]
+
+
+# ======================================================================================
+# attention (+ RoPE)  (Models/Llama/Llama3.py:131-153, Models/GPT2/GPT2.py:29-47)
+# ======================================================================================
+@torch.library.custom_op("b200llm::attention", mutates_args=())
+def attention(q: Tensor, k: Tensor, v: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: int, T: int,
+              h: int, hkv: int, hd: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """q [B*T, h*hd], k/v [B*T, hkv*hd] (row-major 2-D views) -> (o, lse, q_rot, k_rot)."""
+    if cos is not None:
+        qr = K.rope(q, cos, sin, B, T, h, hd)
+        kr = K.rope(k, cos, sin, B, T, hkv, hd)
+        o, lse = K.attention_fwd(qr, kr, v, B, T, h, hkv, hd)
+        return o, lse, qr, kr
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
+    return o, lse, q.new_empty((0,)), q.new_empty((0,))   # no rotated copies to hand back
+
+
+@attention.register_fake
+def _(q, k, v, cos, sin, B, T, h, hkv, hd):
+    o, lse = q.new_empty((B * T, h * hd)), q.new_empty((B, h, T), dtype=torch.float32)
+    if cos is None:
+        return o, lse, q.new_empty((0,)), q.new_empty((0,))
+    return o, lse, q.new_empty((B * T, h * hd)), q.new_empty((B * T, hkv * hd))
+
+
+def _attention_setup(ctx, inputs, output):
+    q, k, v, cos, sin, B, T, h, hkv, hd = inputs
+    o, lse, qr, kr = output
+    if cos is None:
+        qr, kr = q, k
+    ctx.save_for_backward(qr, kr, v, o, lse, cos, sin)
+    ctx.dims = (B, T, h, hkv, hd)
+
+
+def _attention_bwd(ctx, do, _dl, _dq, _dk):
+    qr, kr, v, o, lse, cos, sin = ctx.saved_tensors
+    B, T, h, hkv, hd = ctx.dims
+    v2 = v if v.stride(-1) == 1 else v.contiguous()
+    dq, dk, dv = K.attention_bwd(qr, kr, v2, o, _flat2d(do), lse, B, T, h, hkv, hd)
+    if cos is not None:
+        K.rope_(dq, cos, sin, B, T, h, hd, inverse=True)
+        K.rope_(dk, cos, sin, B, T, hkv, hd, inverse=True)
+    return dq, dk, dv, None, None, None, None, None, None, None
+
+
+attention.register_autograd(_attention_bwd, setup_context=_attention_setup)
+
+
+# ======================================================================================
+# SwiGLU / GELU
+# ======================================================================================
+@torch.library.custom_op("b200llm::swiglu", mutates_args=())
+def swiglu(a: Tensor, b: Tensor) -> Tensor:
+    return K.swiglu_fwd(_flat2d(a), _flat2d(b)).view(a.shape)
+
+
+@swiglu.register_fake
+def _(a, b):
+    return torch.empty(a.shape, device=a.device, dtype=a.dtype)
+
+
+def _swiglu_setup(ctx, inputs, output):
+    ctx.save_for_backward(*inputs)
+
+
+def _swiglu_bwd(ctx, dh):
+    a, b = ctx.saved_tensors
+    da, db = K.swiglu_bwd(_flat2d(a), _flat2d(b), dh.contiguous())
+    return da.view(a.shape), db.view(b.shape)
+
+
+swiglu.register_autograd(_swiglu_bwd, setup_context=_swiglu_setup)
+
+
+@torch.library.custom_op("b200llm::gelu", mutates_args=())
+def gelu(x: Tensor) -> Tensor:
+    return K.gelu_fwd(x.contiguous())
+
+
+@gelu.register_fake
+def _(x):
+    return torch.empty_like(x)
+
+
+def _gelu_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0])
+
+
+def _gelu_bwd(ctx, dy):
+    (x,) = ctx.saved_tensors
+    return K.gelu_bwd(x.contiguous(), dy.contiguous())
+
+
+gelu.register_autograd(_gelu_bwd, setup_context=_gelu_setup)
+
+
+# ======================================================================================
+# embedding  (Llama3.py:197; GPT2.py:110-112)
+# ======================================================================================
+@torch.library.custom_op("b200llm::embedding", mutates_args=())
+def embedding(idx: Tensor, tok_w: Tensor, pos_w: Optional[Tensor]) -> Tensor:
+    return K.embedding_fwd(idx, tok_w, pos_w)
+
+
+@embedding.register_fake
+def _(idx, tok_w, pos_w):
+    return tok_w.new_empty((*idx.shape, tok_w.shape[1]))
+
+
+def _embedding_setup(ctx, inputs, output):
+    idx, tok_w, pos_w = inputs
+    ctx.save_for_backward(idx)
+    ctx.vocab = tok_w.shape[0]
+    ctx.ctx_len = None if pos_w is None else pos_w.shape[0]
+    ctx.dtype = tok_w.dtype
+
+
+def _embedding_bwd(ctx, dout):
+    (idx,) = ctx.saved_tensors
+    if not (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]):
+        return None, None, None
+    dtok, dpos = K.embedding_bwd(idx, dout.contiguous(), ctx.vocab, ctx.ctx_len)
+    dtok = K.cast(dtok, ctx.dtype) if ctx.dtype == BF16 else dtok
+    if dpos is not None:
+        dpos = K.cast(dpos, ctx.dtype) if ctx.dtype == BF16 else dpos
+    return None, dtok, dpos
+
+
+embedding.register_autograd(_embedding_bwd, setup_context=_embedding_setup)
+
+
+# ======================================================================================
+# cross-entropy and the vocab projection fused with it  (train.py:90-91)
+# ======================================================================================
+@torch.library.custom_op("b200llm::cross_entropy", mutates_args=())
+def cross_entropy(logits: Tensor, targets: Tensor) -> Tuple[Tensor, Tensor]:
+    """F.cross_entropy(logits.flatten(0,1), targets.flatten()) -> (loss fp32 [], dlogits)."""
+    V = logits.shape[-1]
+    M = logits.numel() // V
+    ld = (V + 7) // 8 * 8
+    buf = torch.empty((M, ld), device=logits.device, dtype=BF16)
+    buf[:, :V].copy_(logits.reshape(M, V))
+    loss = K.cross_entropy_(buf[:, :V], targets)
+    return loss.reshape(()), buf
+
+
+@cross_entropy.register_fake
+def _(logits, targets):
+    V = logits.shape[-1]
+    return logits.new_empty((), dtype=torch.float32), logits.new_empty((logits.numel() // V, (V + 7) // 8 * 8))
+
+
+def _ce_setup(ctx, inputs, output):
+    ctx.save_for_backward(output[1])
+    ctx.shape = inputs[0].shape
+
+
+def _ce_bwd(ctx, dloss, _db):
+    (buf,) = ctx.saved_tensors
+    V = ctx.shape[-1]
+    g = buf[:, :V].reshape(ctx.shape)
+    return g * dloss.to(g.dtype), None
+
+
+cross_entropy.register_autograd(_ce_bwd, setup_context=_ce_setup)
+
+
+@torch.library.custom_op("b200llm::linear_cross_entropy", mutates_args=())
+def linear_cross_entropy(x: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
+                         targets: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """loss = CE(x W^T + scaling (x A) B, targets) -> (loss fp32 [], dlogits [M, Vpad], t).
+
+    The logits live only in the returned work buffer, which the cross-entropy kernel overwrites
+    in place with dloss/dlogits for the backward GEMMs."""
+    x2 = _flat2d(x)
+    M, V = x2.shape[0], weight.shape[0]
+    ld = (V + 7) // 8 * 8
+    buf = torch.empty((M, ld), device=x.device, dtype=BF16)
+    if A is not None:
+        t = K.gemm_ex(x2, A, b1_mn=True, alpha=scaling)
+        K.gemm_ex(x2, weight, a2=t, b2=_pitch_ok(B), b2_mn=True, out=buf[:, :V])
+    else:
+        t = x2.new_empty((0,))
+        K.gemm_ex(x2, weight, out=buf[:, :V])
+    loss = K.cross_entropy_(buf[:, :V], targets)
+    return loss.reshape(()), buf, t
+
+
+@linear_cross_entropy.register_fake
+def _(x, weight, A, B, scaling, targets):
+    M, V = x.numel() // x.shape[-1], weight.shape[0]
+    t = x.new_empty((M, A.shape[1])) if A is not None else x.new_empty((0,))
+    return x.new_empty((), dtype=torch.float32), x.new_empty((M, (V + 7) // 8 * 8)), t
+
+
+def _lce_setup(ctx, inputs, output):
+    x, weight, A, B, scaling, targets = inputs
+    _, buf, t = output
+    ctx.save_for_backward(x, weight, A, B, t, buf)
+    ctx.scaling = scaling
+
+
+def _lce_bwd(ctx, dloss, _dbuf, _dt):
+    """Assumes dloss == 1 (loss.backward() on the scalar loss, as train.py:112 does); a different
+    upstream factor is applied to the (small) outputs rather than to the [M, V] buffer."""
+    x, weight, A, B, t, buf = ctx.saved_tensors
+    wref, aref, bref = weight, A, B
+    need = ctx.needs_input_grad
+    V = weight.shape[0]
+    dl = buf[:, :V]
+    x2 = _flat2d(x)
+    dx = dW = dA = dB = None
+    u = None
+    if A is not None and (need[0] or need[2]):
+        u = K.gemm_ex(dl, _pitch_ok(B), alpha=ctx.scaling)
+    if need[0]:
+        if u is not None:
+            dx2 = K.gemm_ex(dl, weight, b1_mn=True, a2=u, b2=A)
+        else:
+            dx2 = K.gemm_ex(dl, weight, b1_mn=True)
+        dx = dx2.view(x.shape)
+    if A is not None and need[2]:
+        dA = _weight_grad(x2, u, aref)
+    if B is not None and need[3]:
+        dB = _weight_grad(dl, t, bref, trans_out=True)
+    if need[1]:
+        dW = _weight_grad(dl, x2, wref)
+    return dx, dW, dA, dB, None, None
+
+
+linear_cross_entropy.register_autograd(_lce_bwd, setup_context=_lce_setup)

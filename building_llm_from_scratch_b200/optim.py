@@ -1,0 +1,118 @@
+"""Fused AdamW + gradient clipping over flat buffers (replaces torch.optim.AdamW at
+build_components.py:258 and clip_grad_norm_ at train.py:115-120 on the b200llm path).
+
+All trainable parameters of one dtype live in ONE flat buffer (each nn.Parameter's .data is
+re-pointed to a view of it); their gradients accumulate in ONE fp32 flat buffer whose views are
+published as ``param.main_grad`` — the backward GEMMs of ops.py add into them directly, so there is
+no per-parameter gradient tensor, no foreach launch train and the data-parallel all-reduce runs on
+one contiguous buffer. A step is: grad-norm kernel -> clip coefficient (device scalar) -> one AdamW
+kernel that also applies the coefficient. State (exp_avg, exp_avg_sq) has the parameter dtype,
+like the reference's optimizer.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import kernels as K
+
+
+def _align(n, a=64):
+    return (n + a - 1) // a * a
+
+
+class B200AdamW(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
+        params = [p for p in params]
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        super().__init__(params, defaults)
+        # the reference hands every parameter to AdamW; frozen ones never get a gradient
+        self._trainable = [p for g in self.param_groups for p in g["params"] if p.requires_grad]
+        if not self._trainable:
+            raise ValueError("B200AdamW: no trainable parameters")
+        dev = self._trainable[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("B200AdamW needs CUDA parameters (no CPU fallback)")
+        self._groups = {}
+        for dtype in (torch.bfloat16, torch.float32):
+            ps = [p for p in self._trainable if p.dtype == dtype]
+            if not ps:
+                continue
+            offs, total = [], 0
+            for p in ps:
+                offs.append(total)
+                total += _align(p.numel())
+            flat_p = torch.zeros(total, device=dev, dtype=dtype)
+            flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+            for p, o in zip(ps, offs):
+                flat_p[o:o + p.numel()].copy_(p.data.reshape(-1))
+                p.data = flat_p[o:o + p.numel()].view(p.shape)
+                p.main_grad = flat_g[o:o + p.numel()].view(p.shape)
+            self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g, m=torch.zeros_like(flat_p),
+                                       v=torch.zeros_like(flat_p))
+        other = [p for p in self._trainable if p.dtype not in self._groups]
+        if other:
+            raise RuntimeError(f"B200AdamW: unsupported parameter dtypes {set(p.dtype for p in other)}")
+        self._step = 0
+        self._norm_out = torch.zeros(2, device=dev, dtype=torch.float32)
+        self._ws = torch.empty(K._lib.load().b200_grad_norm_workspace_bytes(1), device=dev, dtype=torch.uint8)
+        self._hyper_dev = torch.zeros(7, device=dev, dtype=torch.float32)
+        self._partial = torch.zeros(2 * len(self._groups), device=dev, dtype=torch.float32)
+        self.max_norm = None  # set by Trainer (train.py:115-120 uses 1.0)
+        self.graph_safe = False
+
+    # ------------------------------------------------------------------
+    @property
+    def flat_grads(self):
+        return [g["g"] for g in self._groups.values()]
+
+    def zero_grad(self, set_to_none: bool = True):
+        for g in self._groups.values():
+            g["g"].zero_()
+        for p in self._trainable:
+            p.grad = None
+
+    def _absorb_autograd_grads(self):
+        # parameters whose gradient came back through autograd (ops outside this package) are folded in
+        for p in self._trainable:
+            if p.grad is not None:
+                p.main_grad.add_(p.grad.to(torch.float32))
+                p.grad = None
+
+    def grad_norm(self, max_norm: float):
+        """Global L2 norm over every gradient -> device tensor [norm, clip_coef]."""
+        groups = list(self._groups.values())
+        if len(groups) == 1:
+            return K.grad_norm(groups[0]["g"], max_norm, out=self._norm_out, ws=self._ws)
+        parts = [K.grad_norm(g["g"], max_norm)[0] for g in groups]
+        total = torch.sqrt(sum(p * p for p in parts))
+        self._norm_out[0] = total
+        self._norm_out[1] = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+        return self._norm_out
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        assert closure is None
+        self._absorb_autograd_grads()
+        self._step += 1
+        scale = None
+        if self.max_norm is not None:
+            scale = self.grad_norm(self.max_norm)[1:2]
+        pg = self.param_groups[0]
+        lr, (b1, b2), eps, wd = pg["lr"], pg["betas"], pg["eps"], pg["weight_decay"]
+        hyper = None
+        if self.graph_safe:
+            # replayable: hyper-parameters are read from device memory, refreshed by set_hyper()
+            hyper = self._hyper_dev
+        for g in self._groups.values():
+            K.adamw_(g["p"], g["g"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
+                     dev_hyper=hyper)
+
+    def set_hyper(self, lr: float, step: int):
+        """Upload (lr, bias corrections for `step`) for the graph-captured step."""
+        pg = self.param_groups[0]
+        host = K.adam_hyper(lr, pg["betas"][0], pg["betas"][1], pg["eps"], pg["weight_decay"], step)
+        self._hyper_dev.copy_(host, non_blocking=True)
+        self._host_keepalive = host
+
+    def last_grad_norm(self):
+        return self._norm_out[0]

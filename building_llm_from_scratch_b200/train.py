@@ -1,0 +1,97 @@
+"""Drop-in for the hot-path part of train.py: Trainer with the reference's constructor,
+attributes, LR schedule (train.py:100-107) and step order (zero_grad, lr, forward + CE, backward,
+clip 1.0, optimizer step; train.py:94-123). Evaluation / sampling / checkpoint orchestration is
+out of scope except evaluate-style loss computation, which reuses calc_loss_batch.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import ops
+from .ddp import B200DDP
+from .optim import B200AdamW
+
+
+class Trainer:
+    def __init__(self, model, optimizer, config, data_files, loaderObj, save_dir, warmup_steps=10, initial_lr=1e-5,
+                 min_lr=1e-6, device="cpu", rank=0, eval_freq=1, save_ckpt_freq=1, print_sample_iter=1, eval_iter=1):
+        self.config = config
+        self.model = model
+        self.optimizer = optimizer
+        self.data_files = data_files
+        self.loaderObj = loaderObj
+        self.save_dir = save_dir
+        self.device = device
+        self.rank = rank
+        self.warmup_steps = warmup_steps
+        self.initial_lr = initial_lr
+        self.min_lr = min_lr
+        self.eval_freq = eval_freq
+        self.save_ckpt_freq = save_ckpt_freq
+        self.print_sample_iter = print_sample_iter
+        self.eval_iter = eval_iter
+        self.global_step = -1
+        self.tokens_seen = 0
+        self.train_losses = []
+        self.val_losses = []
+        self.track_lrs = []
+        self.track_tokens_seen = []
+        self.last_loss = None
+        if isinstance(optimizer, B200AdamW):
+            optimizer.max_norm = 1.0  # train.py:115-120
+
+    # train.py:154-156
+    def set_schedule(self, total_training_steps, peak_lr=None):
+        self.peak_lr = self.optimizer.param_groups[0]["lr"] if peak_lr is None else peak_lr
+        self.total_training_steps = total_training_steps
+        self.lr_increment = (self.peak_lr - self.initial_lr) / self.warmup_steps
+
+    def lr_for_step(self, step):
+        if step < self.warmup_steps:
+            return self.initial_lr + step * self.lr_increment
+        progress = (step - self.warmup_steps) / (self.total_training_steps - self.warmup_steps)
+        return self.min_lr + (self.peak_lr - self.min_lr) * 0.5 * (1 + math.cos(math.pi * progress))
+
+    # train.py:88-92
+    def calc_loss_batch(self, input_batch, target_batch):
+        input_batch = input_batch.to(self.device, non_blocking=True)
+        target_batch = target_batch.to(self.device, non_blocking=True)
+        core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        if core.training and hasattr(core, "forward_loss"):
+            loss = core.forward_loss(input_batch, target_batch)
+        else:
+            logits = self.model(input_batch)
+            loss = ops.cross_entropy(logits, target_batch)[0]
+        return loss.to(torch.bfloat16) if self._loss_bf16(core) else loss
+
+    @staticmethod
+    def _loss_bf16(core):
+        p = next(core.parameters())
+        return p.dtype == torch.bfloat16
+
+    # train.py:94-126 (exceptions propagate instead of being logged and swallowed)
+    def train_batch(self, input_batch, target_batch):
+        self.optimizer.zero_grad()
+        self.global_step += 1
+        lr = self.lr_for_step(self.global_step)
+        for param_group in self.optimizer.param_groups:
+            param_group["lr"] = lr
+        self.track_lrs.append(lr)
+        loss = self.calc_loss_batch(input_batch, target_batch)
+        loss.backward()
+        fused = isinstance(self.optimizer, B200AdamW)
+        if isinstance(self.model, B200DDP):
+            if fused:
+                self.optimizer._absorb_autograd_grads()
+                self.model.reduce_gradients(self.optimizer.flat_grads)
+            else:
+                self.model.reduce_gradients([p.grad for p in self.model.parameters() if p.grad is not None])
+        if not fused:
+            core = self.model.module if isinstance(self.model, B200DDP) else self.model
+            torch.nn.utils.clip_grad_norm_(core.parameters(), max_norm=1.0)
+        self.optimizer.step()
+        self.tokens_seen += input_batch.numel()
+        self.last_loss = loss.detach()
+        return self.last_loss

@@ -149,21 +149,28 @@ int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets, fl
                             size_t workspace_bytes, void* stream);
 
 /* ---- K8a: global gradient norm + clip coefficient (train.py:115-120) ----------------------
- * out[0] = ||g||_2 over n bf16 elements; out[1] = min(1, max_norm / (out[0] + 1e-6)), the
- * factor clip_grad_norm_ multiplies every gradient by. workspace:
- * b200_grad_norm_workspace_bytes(n). */
+ * out[0] = ||g||_2 over n elements; out[1] = min(1, max_norm / (out[0] + 1e-6)), the factor
+ * clip_grad_norm_ multiplies every gradient by. workspace: b200_grad_norm_workspace_bytes(n)
+ * bytes of scratch for the per-block partial sums. _f32 reads an fp32 gradient buffer. */
 size_t b200_grad_norm_workspace_bytes(int64_t n);
 int b200_grad_norm_bf16(const void* g, int64_t n, float max_norm, float* out, void* workspace,
                         size_t workspace_bytes, void* stream);
+int b200_grad_norm_f32(const float* g, int64_t n, float max_norm, float* out, void* workspace,
+                       size_t workspace_bytes, void* stream);
 
 /* ---- K8b: AdamW over a flat buffer (torch.optim.AdamW, build_components.py:258) ------------
  * decoupled weight decay, bias correction from `step` (1-based); grad_scale (device pointer,
- * may be NULL) is the clip coefficient from b200_grad_norm_bf16 (out + 1). p,g,m,v bf16. */
-int b200_adamw_bf16(void* p, const void* g, void* m, void* v, int64_t n, float lr, float beta1,
-                    float beta2, float eps, float weight_decay, int64_t step,
-                    const float* grad_scale, void* stream);
+ * may be NULL) is the clip coefficient from b200_grad_norm_* (out + 1). p, m, v bf16; g bf16
+ * or (g_is_f32) fp32. dev_hyper (may be NULL): 7 floats in device memory that override the
+ * scalar arguments — fill a host copy with b200_adam_hyper and upload it before replaying a
+ * captured CUDA graph. */
+int b200_adam_hyper(float* host7, float lr, float beta1, float beta2, float eps, float weight_decay,
+                    int64_t step);
+int b200_adamw_bf16(void* p, const void* g, int g_is_f32, void* m, void* v, int64_t n, float lr,
+                    float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                    const float* dev_hyper, const float* grad_scale, void* stream);
 int b200_adamw_f32(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
-                   float beta2, float eps, float weight_decay, int64_t step,
+                   float beta2, float eps, float weight_decay, int64_t step, const float* dev_hyper,
                    const float* grad_scale, void* stream);
 
 /* ---- K9: dtype casts (datautils/mixed_precision.py:10-35) ---------------------------------- */
@@ -175,6 +182,9 @@ int b200_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
 int b200_transpose_bf16(const void* in, int64_t ldi, void* out, int64_t ldo, int64_t rows,
                         int64_t cols, float alpha, void* stream);
 int b200_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream);
+/* out[n] += sum_m x[m, n] (fp32 atomics; zero `out` first): the bias gradient of
+ * nn.Linear(bias=True) in Models/GPT2/GPT2.py:23,59-61. */
+int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N, void* stream);
 
 /* ---- K2: fused causal attention (Models/Llama/Llama3.py:131-153; GPT2.py:29-47) ------------
  * q [B*T, ldq] with h heads of width hd starting at q, k/v likewise with hkv heads; head j

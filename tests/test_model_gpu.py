@@ -1,0 +1,175 @@
+"""GPU: the drop-in modules (same class names / state_dict keys as the reference) against fixtures
+recorded from the live reference modules, and against the oracle on the same weights.
+bf16 tolerance 2e-2 relative per op (north star); end-to-end gradients through a whole bf16 model
+are compared at 5e-2; the 30-step loss curve must track the reference's within 1 % + 0.02 abs."""
+import copy
+
+import pytest
+import torch
+
+from conftest import close, rel_err
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+BF16_TOL = 2e-2
+
+
+def to_cuda(sd, dtype=None):
+    out = {}
+    for k, v in sd.items():
+        v = v.cuda()
+        if dtype is not None and v.is_floating_point() and not k.endswith("norm1.weight") and not k.endswith(
+                "norm2.weight") and not k.endswith("final_norm.weight"):
+            v = v.to(dtype)
+        out[k] = v
+    return out
+
+
+def test_llama_modules_against_reference_fixtures(golden):
+    from building_llm_from_scratch_b200.Models.Llama import Llama3 as L
+    from building_llm_from_scratch_b200.Models.Llama.common_components import FeedForward, RMSNorm, compute_rope
+    g = golden("llama_modules.pt")
+    # GroupedQueryAttention (bf16)
+    f = g["gqa/torch.bfloat16"]
+    L.SharedBuffers._buffers.clear()
+    fc = dict(factor=32.0, low_freq_factor=1.0, high_freq_factor=4.0, original_context_length=8192)
+    att = L.GroupedQueryAttention(256, 256, 64, 4, 2, rope_base=31250.0, rope_config=fc, dtype=torch.bfloat16).cuda()
+    att.load_state_dict(f["sd"])
+    assert torch.equal(att.cos.cpu(), f["sd"]["cos"]) and torch.equal(att.sin.cpu(), f["sd"]["sin"])
+    x = f["x"].cuda().requires_grad_(True)
+    y = att(x)
+    y.backward(f["gy"].cuda())
+    assert rel_err(y.cpu().float(), f["y"].float()) < BF16_TOL
+    assert rel_err(x.grad.cpu().float(), f["dx"].float()) < BF16_TOL
+    for k, v in f["grads"].items():
+        assert rel_err(dict(att.named_parameters())[k].grad.cpu().float(), v.float()) < BF16_TOL, k
+    # FeedForward
+    f = g["ffn/torch.bfloat16"]
+    ff = FeedForward(dict(emb_dim=64, hidden_dim=160, dtype=torch.bfloat16)).cuda()
+    ff.load_state_dict(f["sd"])
+    x = f["x"].cuda().requires_grad_(True)
+    y = ff(x)
+    y.backward(f["gy"].cuda())
+    assert rel_err(y.cpu().float(), f["y"].float()) < BF16_TOL
+    assert rel_err(x.grad.cpu().float(), f["dx"].float()) < BF16_TOL
+    for k, v in f["grads"].items():
+        assert rel_err(dict(ff.named_parameters())[k].grad.cpu().float(), v.float()) < BF16_TOL, k
+    # RMSNorm module + compute_rope function
+    f = g["rmsnorm/torch.bfloat16"]
+    n = RMSNorm(64).cuda()
+    n.load_state_dict({"weight": f["w"]})
+    x = f["x"].cuda().requires_grad_(True)
+    y = n(x)
+    y.backward(f["gy"].cuda())
+    assert rel_err(y.cpu().float(), f["y"].float()) < 5e-3
+    assert rel_err(x.grad.cpu().float(), f["dx"].float()) < BF16_TOL
+    assert rel_err(n.weight.grad.cpu(), f["dw"].float()) < BF16_TOL
+    f = g["rope/torch.bfloat16"]
+    assert torch.equal(compute_rope(f["x"].cuda(), f["cos"].cuda(), f["sin"].cuda()).cpu(), f["y"])
+
+
+def build_llama(g, fused_opt):
+    from building_llm_from_scratch_b200.Models.Llama import Llama3 as L
+    from building_llm_from_scratch_b200.lora import replace_linear_with_lora
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    L.SharedBuffers._buffers.clear()
+    model = L.Llama3Model(copy.deepcopy(g["cfg"]))
+    for p in model.parameters():
+        p.requires_grad = False
+    replace_linear_with_lora(model, rank=g["rank"], alpha=g["alpha"], dtype=torch.bfloat16)
+    model.load_state_dict(g["sd"])
+    model.cuda().train()
+    opt = B200AdamW(model.parameters(), lr=5e-4, weight_decay=0.1) if fused_opt else None
+    return model, opt
+
+
+@pytest.mark.parametrize("fused_opt", [False, True])
+def test_llama3_lora_model_against_reference_fixture(golden, fused_opt):
+    g = golden("llama_model.pt")
+    model, opt = build_llama(g, fused_opt)
+    x, y = g["x"].cuda(), g["y"].cuda()
+    with torch.no_grad():
+        model.eval()
+        logits = model(x)
+        model.train()
+    assert logits.shape == g["logits"].shape and logits.dtype == torch.bfloat16
+    assert rel_err(logits.cpu().float(), g["logits"].float()) < BF16_TOL
+    if opt is not None:
+        opt.zero_grad()
+    loss = model.forward_loss(x, y)
+    loss.backward()
+    assert rel_err(loss.cpu(), g["loss"].float()) < BF16_TOL
+    named = dict(model.named_parameters())
+    assert set(g["grads"]) == {k for k, p in named.items() if p.requires_grad}
+    for k, v in g["grads"].items():
+        got = named[k].main_grad if fused_opt else named[k].grad
+        assert got is not None, k
+        assert close(got.cpu().float(), v.float(), 5e-2, atol=1e-6), (k, rel_err(got.cpu().float(), v.float()))
+    # the materialised-logits path (evaluate_model / generate) gives the same loss
+    from building_llm_from_scratch_b200 import ops
+    loss2 = ops.cross_entropy(model(x), y)[0]
+    assert rel_err(loss2.cpu(), loss.detach().cpu()) < 1e-3
+
+
+def test_llama3_loss_curve_tracks_reference(golden):
+    from building_llm_from_scratch_b200.train import Trainer
+    g = golden("llama_model.pt")
+    c = g["curve"]
+    model, opt = build_llama(g, True)
+    tr = Trainer(model, opt, g["cfg"], [], None, "/tmp", warmup_steps=c["warmup"], initial_lr=1e-5, min_lr=1e-6,
+                 device="cuda")
+    tr.set_schedule(c["total"], peak_lr=c["peak_lr"])
+    losses = []
+    for s in range(c["total"]):
+        xb, yb = c["batches"][s % 2]
+        with torch.no_grad():
+            losses.append(float(model.forward_loss(xb.cuda(), yb.cuda())))
+        tr.train_batch(xb, yb)
+    assert tr.track_lrs == pytest.approx(c["lrs"], rel=1e-12)
+    ref = c["losses"]
+    assert ref[-1] < ref[0] - 0.05, "fixture should actually learn"
+    for s, (a, b) in enumerate(zip(losses, ref)):
+        assert abs(a - b) <= 0.01 * abs(b) + 0.02, (s, a, b)
+
+
+@pytest.mark.parametrize("which", ["model", "model_lora"])
+def test_gpt2_model_against_reference_fixture(golden, which):
+    from building_llm_from_scratch_b200.Models.GPT2.GPT2 import GPTModel
+    from building_llm_from_scratch_b200.lora import replace_linear_with_lora
+    g = golden("gpt2.pt")[which]
+    model = GPTModel(copy.deepcopy(g["cfg"]))
+    if which == "model_lora":
+        for p in model.parameters():
+            p.requires_grad = False
+        replace_linear_with_lora(model, rank=g["rank"], alpha=g["alpha"], dtype=torch.float32)
+    model.load_state_dict(g["sd"])
+    model = model.cuda().to(torch.bfloat16).train()     # harness cast, SURVEY.md R1/R2
+    x, y = g["x"].cuda(), g["y"].cuda()
+    logits = model(x)
+    assert rel_err(logits.detach().cpu().float(), g["logits"]) < BF16_TOL
+    loss = model.forward_loss(x, y)
+    loss.backward()
+    assert rel_err(loss.cpu(), g["loss"]) < BF16_TOL
+    named = dict(model.named_parameters())
+    for k, v in g["grads"].items():
+        assert named[k].grad is not None, k
+        assert close(named[k].grad.cpu().float(), v, 6e-2, atol=2e-5), (k, rel_err(named[k].grad.cpu().float(), v))
+
+
+def test_activation_checkpointing_matches_plain(golden):
+    g = golden("llama_model.pt")
+    model, _ = build_llama(g, False)
+    x, y = g["x"].cuda(), g["y"].cuda()
+    model.forward_loss(x, y).backward()
+    plain = {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
+    model.zero_grad()
+    model.use_actv_ckpt = True
+    model.forward_loss(x, y).backward()
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            assert close(p.grad.float(), plain[k].float(), 1e-3, atol=1e-6), k
+
+
+def test_ops_reject_cpu_tensors():
+    from building_llm_from_scratch_b200 import ops
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.rmsnorm(torch.zeros(4, 64, dtype=torch.bfloat16), torch.ones(64), 1e-5)
