@@ -105,38 +105,34 @@ class ClockSampler(threading.Thread):
 # --------------------------------------------------------------------------------------
 # CPU baseline: the oracle (port of the reference modules) on the host cores
 # --------------------------------------------------------------------------------------
-def cpu_reference_sample(seq_len=256, budget_s=25.0):
+def cpu_reference_sample(seq_len=1024):
     """One bounded sample of the same workload on CPU: Llama-3.2-1B dims, LoRA r=64, bf16,
-    B=1 x T=seq_len, forward + CE + backward through the oracle with 1 and 2 blocks; the per-block
-    and head+embedding costs are separated and extrapolated to the 16-block model."""
+    B=1 x T=seq_len, forward + CE + backward through the oracle with 1 and 3 blocks (second of two
+    runs each, the first warms the CPU kernels up); per-block and head+embedding costs are
+    separated and extrapolated to the 16-block model."""
     from oracle import reference_ops as R
     torch.manual_seed(123)
     times = {}
-    cfg = None
-    for nl in (1, 2):
+    for nl in (1, 3):
         cfg = llama32_1b_cfg(seq_len, n_layers=nl)
         sd = oracle_state(cfg, LORA_RANK)
         x = torch.randint(0, cfg["vocab_size"], (1, seq_len))
         y = torch.roll(x, -1, 1)
         y[:, : seq_len // 2] = -100
-        t0 = time.perf_counter()
-        logits = R.llama3_forward(x, sd, cfg, LORA_ALPHA / LORA_RANK)
-        loss = R.cross_entropy(logits, y)
-        loss.backward()
-        times[nl] = time.perf_counter() - t0
-        del sd, logits, loss
-        if times[nl] > budget_s:
-            break
-    if 2 in times:
-        per_block = max(times[2] - times[1], 1e-6)
-        rest = max(times[1] - per_block, 0.0)
-    else:  # very slow host: scale the single-block run by FLOPs
-        per_block = times[1] * 0.3
-        rest = times[1] * 0.7
+        for rep in range(2):
+            t0 = time.perf_counter()
+            logits = R.llama3_forward(x, sd, cfg, LORA_ALPHA / LORA_RANK)
+            loss = R.cross_entropy(logits, y)
+            loss.backward()
+            times[nl] = time.perf_counter() - t0
+            del logits, loss
+        del sd
+    per_block = max((times[3] - times[1]) / 2, 0.02 * times[1])
+    rest = max(times[1] - per_block, 0.0)
     full = rest + 16 * per_block
     return dict(tokens_per_s=seq_len / full, seconds=sum(times.values()),
-                sample=f"oracle Llama-3.2-1B dims LoRA r={LORA_RANK} bf16 CPU, B=1xT={seq_len}, fwd+CE+bwd with 1 and 2 "
-                       f"blocks ({times.get(1, 0):.1f}s, {times.get(2, 0):.1f}s), extrapolated to 16 blocks + head")
+                sample=f"oracle Llama-3.2-1B dims LoRA r={LORA_RANK} bf16 CPU, B=1xT={seq_len}, fwd+CE+bwd with 1 and 3 "
+                       f"blocks ({times[1]:.2f}s, {times[3]:.2f}s), extrapolated to 16 blocks + head")
 
 
 def oracle_state(cfg, rank):
@@ -174,7 +170,7 @@ def run_reference_arm(args):
     vals = []
     sample = None
     for i in range(args.warmup + args.steps):
-        r = cpu_reference_sample(seq_len=128 if i < args.warmup else 512)
+        r = cpu_reference_sample(seq_len=256 if i < args.warmup else 1024)
         if i >= args.warmup:
             vals.append(r["tokens_per_s"])
             sample = r["sample"]
@@ -338,7 +334,7 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(os.cpu_count() or 1)
-        r = cpu_reference_sample(seq_len=1024)
+        r = cpu_reference_sample(seq_len=2048)
         cpu = {"value": r["tokens_per_s"], "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                "sample": r["sample"]}
 

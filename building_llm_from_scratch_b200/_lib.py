@@ -59,7 +59,8 @@ SIGNATURES = {
     "b200_add_bf16": (I, [P, P, P, I64, P]),
     "b200_colsum_bf16": (I, [P, I64, P, I64, I64, P]),
     "b200_attention_fwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, I64, I64, F, P]),
-    "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, P, I64, P, I64, P,
+    "b200_attention_bwd_workspace_bytes": (SZ, [I64, I64, I64, I64]),
+    "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,
                                     I64, I64, I64, I64, I64, I64, F, P]),
 }
 

@@ -11,7 +11,30 @@
 //
 // Roofline: tensor pipe. Algorithmic FLOPs (causal): fwd 2*T*T*hd per (batch, head),
 // bwd 2.5x that (recompute included: 3.5x executed).
+#include <cstdlib>
+
 #include "common.cuh"
+
+// tcgen05 paths (attention_tc.cu), head_dim 64
+int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                            int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
+                            int64_t h, int64_t hkv, float scale, cudaStream_t st);
+
+size_t b200_attention_bwd_tc64_workspace(int64_t B, int64_t T, int64_t h);
+int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                            int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
+                            const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
+                            int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
+                            int64_t hkv, float scale, cudaStream_t st);
+
+static bool attn_legacy() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_ATTN_LEGACY");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
 
 namespace {
 
@@ -531,6 +554,8 @@ extern "C" int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k
   if (rc) return rc;
   B200_CHECK_ARG(o && lse, "attention_fwd: null output");
   cudaStream_t st = (cudaStream_t)stream;
+  if (hd == 64 && !attn_legacy())
+    return b200_attention_fwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, st);
   dim3 grid((unsigned)((T + 127) / 128), (unsigned)h, (unsigned)B);
   static bool f64[64] = {false}, f128[64] = {false};
   int dev = 0;
@@ -549,17 +574,28 @@ extern "C" int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k
   return 0;
 }
 
+extern "C" size_t b200_attention_bwd_workspace_bytes(int64_t B, int64_t T, int64_t h, int64_t hd) {
+  if (hd == 64) return b200_attention_bwd_tc64_workspace(B, T, h);
+  return (size_t)(B * h * T) * sizeof(float);
+}
+
 extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk,
                                        const void* v, int64_t ldv, const void* o, int64_t ldo,
                                        const void* dout, int64_t lddo, const float* lse,
-                                       float* delta, void* dq, int64_t lddq, void* dk, int64_t lddk,
-                                       void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                                       int64_t hkv, int64_t hd, float scale, void* stream) {
+                                       void* workspace, size_t workspace_bytes, void* dq,
+                                       int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                                       int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd,
+                                       float scale, void* stream) {
+  float* delta = (float*)workspace;
   const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
   int rc = check_common(q, k, v, B, T, h, hkv, hd, lds, 8);
   if (rc) return rc;
   B200_CHECK_ARG(o && dout && lse && delta && dq && dk && dv, "attention_bwd: null pointer");
+  B200_CHECK_ARG(workspace_bytes >= b200_attention_bwd_workspace_bytes(B, T, h, hd), "attention_bwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
+  if (hd == 64 && !attn_legacy())
+    return b200_attention_bwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk,
+                                   lddk, dv, lddv, B, T, h, hkv, scale, st);
   {
     const long long total = B * T * h;
     long long blocks = (total + 7) / 8;

@@ -385,9 +385,11 @@ def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=No
     dq = torch.empty((B * T, h * hd), device=dev, dtype=BF16) if dq is None else dq
     dk = torch.empty((B * T, hkv * hd), device=dev, dtype=BF16) if dk is None else dk
     dv = torch.empty((B * T, hkv * hd), device=dev, dtype=BF16) if dv is None else dv
-    delta = torch.empty((B, h, T), device=dev, dtype=torch.float32)
-    _lib.check(_lib.load().b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
-                                                   _p(delta), _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
-                                                   dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _stream()),
+    lib = _lib.load()
+    nbytes = lib.b200_attention_bwd_workspace_bytes(B, T, h, hd)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    _lib.check(lib.b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
+                                           _p(ws), nbytes, _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
+                                           dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _stream()),
                "attention_bwd")
     return dq, dk, dv

@@ -83,12 +83,15 @@ def _(x, weight, bias, eps):
 
 
 def _layernorm_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
     x, w, b, eps = inputs
     _, mean, rstd = output
     ctx.save_for_backward(x, w, mean, rstd)
 
 
 def _layernorm_bwd(ctx, dy, _dm, _dr):
+    if dy is None:
+        return None, None, None, None
     x, w, mean, rstd = ctx.saved_tensors
     need_dw = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
     dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_dw)
@@ -129,6 +132,7 @@ def _(x, weight, bias, A, B, scaling, residual):
 
 
 def _lora_linear_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
     x, weight, bias, A, B, scaling, residual = inputs
     _, t = output
     ctx.save_for_backward(x, weight, A, B, t)
@@ -150,6 +154,8 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
 
 
 def _lora_linear_bwd(ctx, dy, _dt):
+    if dy is None:
+        return (None,) * 7
     x, weight, A, B, t = ctx.saved_tensors   # saved tensors are the Parameter objects themselves
     wref, bref, aref, bbref = weight, ctx.bias_ref, A, B
     need = ctx.needs_input_grad
@@ -209,6 +215,7 @@ def _(q, k, v, cos, sin, B, T, h, hkv, hd):
 
 
 def _attention_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
     q, k, v, cos, sin, B, T, h, hkv, hd = inputs
     o, lse, qr, kr = output
     if cos is None:
@@ -218,6 +225,8 @@ def _attention_setup(ctx, inputs, output):
 
 
 def _attention_bwd(ctx, do, _dl, _dq, _dk):
+    if do is None:
+        return (None,) * 10
     qr, kr, v, o, lse, cos, sin = ctx.saved_tensors
     B, T, h, hkv, hd = ctx.dims
     v2 = v if v.stride(-1) == 1 else v.contiguous()
@@ -336,11 +345,14 @@ def _(logits, targets):
 
 
 def _ce_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
     ctx.save_for_backward(output[1])
     ctx.shape = inputs[0].shape
 
 
 def _ce_bwd(ctx, dloss, _db):
+    if dloss is None:
+        return None, None
     (buf,) = ctx.saved_tensors
     V = ctx.shape[-1]
     g = buf[:, :V].reshape(ctx.shape)
@@ -379,6 +391,7 @@ def _(x, weight, A, B, scaling, targets):
 
 
 def _lce_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
     x, weight, A, B, scaling, targets = inputs
     _, buf, t = output
     ctx.save_for_backward(x, weight, A, B, t, buf)
@@ -388,6 +401,8 @@ def _lce_setup(ctx, inputs, output):
 def _lce_bwd(ctx, dloss, _dbuf, _dt):
     """Assumes dloss == 1 (loss.backward() on the scalar loss, as train.py:112 does); a different
     upstream factor is applied to the (small) outputs rather than to the [M, V] buffer."""
+    if dloss is None:
+        return (None,) * 6
     x, weight, A, B, t, buf = ctx.saved_tensors
     wref, aref, bref = weight, A, B
     need = ctx.needs_input_grad

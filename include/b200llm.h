@@ -193,13 +193,16 @@ int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N
 int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
                             int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
-/* delta [B, h, T] fp32 scratch (rowsum(dO*O)), written by the call. dq/dk/dv have the layouts
- * of q/k/v. */
+/* Backward. dq/dk/dv have the layouts of q/k/v. `workspace` is scratch of
+ * b200_attention_bwd_workspace_bytes(B, T, h, hd) bytes: rowsum(dO*O) per (b, h, t) and, on the
+ * tcgen05 path (hd 64), the fp32 dQ accumulator that the key-tile CTAs add into. */
+size_t b200_attention_bwd_workspace_bytes(int64_t B, int64_t T, int64_t h, int64_t hd);
 int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, const void* o, int64_t ldo, const void* dout,
-                            int64_t lddo, const float* lse, float* delta, void* dq, int64_t lddq,
-                            void* dk, int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
+                            int64_t lddo, const float* lse, void* workspace, size_t workspace_bytes,
+                            void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                            int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd, float scale,
+                            void* stream);
 
 #ifdef __cplusplus
 }

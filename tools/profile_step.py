@@ -1,0 +1,50 @@
+"""One eager training step of the bench workload inside a cudaProfilerStart/Stop range, for
+`ncu --profile-from-start off` (launch list / full capture). Not a benchmark."""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--layers", type=int, default=2)
+    ap.add_argument("--shapes", default=None, help="write per-GEMM-shape timing JSON here")
+    args = ap.parse_args()
+    from building_llm_from_scratch_b200 import kernels
+    from building_llm_from_scratch_b200.datautils.synthetic import alpaca_batch
+    from building_llm_from_scratch_b200.engine import TrainStep
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    cfg = bench.llama32_1b_cfg(bench.SEQ_LEN, n_layers=args.layers)
+    tr = bench.build_trainer(cfg, dev, 1)
+    x, y = alpaca_batch(torch.Generator().manual_seed(1234), bench.MICRO_BATCH, bench.SEQ_LEN, cfg["vocab_size"])
+    step = TrainStep(tr, (bench.MICRO_BATCH, bench.SEQ_LEN), use_graph=False)
+    step.x.copy_(x.to(dev)); step.y.copy_(y.to(dev))
+    step._refresh_hyper(peek=True)
+    for _ in range(2):
+        step._eager_step()
+    torch.cuda.synchronize()
+    if args.shapes:
+        prof = kernels.GemmProfile()
+        kernels.set_gemm_profile(prof)
+        step._eager_step()
+        torch.cuda.synchronize()
+        kernels.set_gemm_profile(None)
+        rows = [dict(shape=list(k), launches=v[0], ms=v[1], tflops=v[2] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0)
+                for k, v in sorted(prof.by_shape().items(), key=lambda kv: -kv[1][1])]
+        json.dump(rows, open(args.shapes, "w"), indent=1)
+    torch.cuda.profiler.start()
+    step._eager_step()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
+    print("profiled one step, loss", float(step.loss))
+
+
+if __name__ == "__main__":
+    main()
