@@ -47,6 +47,7 @@ SIGNATURES = {
     "b200_embedding_bwd_f32acc": (I, [P, P, P, P, I64, I64, I64, I64, P]),
     "b200_cross_entropy_workspace_bytes": (SZ, [I64]),
     "b200_cross_entropy_bf16": (I, [P, I64, P, P, I64, I64, I, P, SZ, P]),
+    "b200_cross_entropy_bf16_noalloc": (I, [P, I64, P, P, I64, I64, I, P]),
     "b200_grad_norm_workspace_bytes": (SZ, [I64]),
     "b200_grad_norm_bf16": (I, [P, I64, F, P, P, SZ, P]),
     "b200_grad_norm_f32": (I, [P, I64, F, P, P, SZ, P]),

@@ -2,6 +2,8 @@
 // All HBM-bound. Algorithmic bytes: CE 6 B per logit for a non-ignored row (read twice from
 // L2/HBM, write grad) and 2 B for an ignored row (write zeros); grad-norm 2 B/param;
 // AdamW 14 B/param (bf16) or 28 B/param (fp32).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -350,5 +352,67 @@ extern "C" int b200_adamw_f32(float* p, const float* g, float* m, float* v, int6
       p, g, m, v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step >= 1 ? step : 1), dev_hyper, grad_scale);
   B200_CHECK_LAUNCH();
   b200_count_launch();
+  return 0;
+}
+
+// ======================================================================================
+// Allocation-free cross-entropy.
+//
+// For hosts that may not obtain device memory while they run: a trainer that has carved all of
+// HBM into a fixed plan up front (nothing left for a workspace, and cudaMalloc would stall every
+// stream or simply fail), or an embedding application that hands this library only its input and
+// output buffers and forbids it to ask the driver for more. b200_cross_entropy_bf16 needs
+// (M + 2) floats of caller-provided workspace; this variant keeps that workspace inside the
+// library image instead, in the file-scope device array below. Every GPU that loads the library
+// carries those 256 KiB until the process exits.
+// ======================================================================================
+static __device__ __align__(256) float g_ce_noalloc_scratch[B200_CE_NOALLOC_MAX_ROWS + 2];
+
+// In host code the array's name is only a handle; the device address must be asked for, once
+// per device, while that device is current.
+static float* g_ce_noalloc_ptr[64] = {nullptr};
+static std::mutex g_ce_noalloc_mu;
+
+static int ce_noalloc_scratch(float** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < 64, "cross_entropy_noalloc: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_ce_noalloc_mu);
+  if (g_ce_noalloc_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_ce_noalloc_scratch));
+    B200_CHECK_ARG(ptr != nullptr, "cross_entropy_noalloc: could not resolve the scratch array");
+    g_ce_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_ce_noalloc_ptr[dev];
+  return 0;
+}
+
+extern "C" int b200_cross_entropy_bf16_noalloc(void* logits, int64_t ld, const int64_t* targets,
+                                               float* loss_out, int64_t M, int64_t V,
+                                               int write_grad, void* stream) {
+  B200_CHECK_ARG(logits && targets && loss_out && M > 0 && V > 0, "cross_entropy_noalloc: null pointer or empty");
+  B200_CHECK_ARG(M <= B200_CE_NOALLOC_MAX_ROWS,
+                 "cross_entropy_noalloc: M=%lld rows exceed the built-in scratch (max %d rows); use "
+                 "b200_cross_entropy_bf16 with a caller workspace, or split the batch",
+                 (long long)M, (int)B200_CE_NOALLOC_MAX_ROWS);
+  B200_CHECK_ARG(ld % 8 == 0 && ld >= V, "cross_entropy_noalloc: ld=%lld must be a multiple of 8 and >= V", (long long)ld);
+  B200_CHECK_ARG(b200_aligned16(logits), "cross_entropy_noalloc: logits must be 16-B aligned");
+  B200_CHECK_ARG(V < (1ll << 31), "cross_entropy_noalloc: V too large");
+  float* ws = nullptr;
+  int rc = ce_noalloc_scratch(&ws);
+  if (rc) return rc;
+  // Nothing in the scratch has to start at zero: slot 0 / 1 (valid count, its reciprocal) and one
+  // slot per row are each rewritten by this call before anything reads them, and slots beyond M
+  // left over from an earlier, longer call are never read.
+  cudaStream_t st = (cudaStream_t)stream;
+  ce_count_kernel<<<1, 256, 0, st>>>((const long long*)targets, M, ws);
+  B200_CHECK_LAUNCH();
+  const long long cap = (long long)b200_num_sms() * 4;
+  ce_row_kernel<<<(int)(M < cap ? M : cap), CE_THREADS, 0, st>>>((bf16*)logits, ld, (const long long*)targets, ws, M, (int)V, write_grad);
+  B200_CHECK_LAUNCH();
+  ce_finish_kernel<<<1, 1024, 0, st>>>(ws, M, loss_out);
+  B200_CHECK_LAUNCH();
+  b200_count_launch(3);
   return 0;
 }

@@ -148,6 +148,22 @@ int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets, fl
                             int64_t M, int64_t V, int write_grad, void* workspace,
                             size_t workspace_bytes, void* stream);
 
+/* Cross-entropy for callers that cannot give the library a workspace. (No counterpart in the
+ * reference: it exists for hosts whose device memory is fully planned ahead — every byte of HBM
+ * already assigned, allocator calls forbidden while training runs because cudaMalloc stalls all
+ * streams and may fail — and for embedders that pass only inputs and outputs.) Same arithmetic
+ * and results as b200_cross_entropy_bf16; the (M + 2)-float workspace is a fixed array inside
+ * the library, 256 KiB on every GPU that loads it, so M is limited to
+ * B200_CE_NOALLOC_MAX_ROWS rows (larger M is rejected with B200_ERR_ARG and a message).
+ * The call allocates nothing. All calls on a device share that one array: two calls whose
+ * kernels can overlap on the GPU (different streams without an ordering between them) race and
+ * give wrong losses — serialise them. The first call on each device looks the array's address
+ * up once; make that first call outside any stream capture. */
+#define B200_CE_NOALLOC_MAX_ROWS 65536
+int b200_cross_entropy_bf16_noalloc(void* logits, int64_t ld, const int64_t* targets,
+                                    float* loss_out, int64_t M, int64_t V, int write_grad,
+                                    void* stream);
+
 /* ---- K8a: global gradient norm + clip coefficient (train.py:115-120) ----------------------
  * out[0] = ||g||_2 over n elements; out[1] = min(1, max_norm / (out[0] + 1e-6)), the factor
  * clip_grad_norm_ multiplies every gradient by. workspace: b200_grad_norm_workspace_bytes(n)

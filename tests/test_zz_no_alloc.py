@@ -1,0 +1,75 @@
+"""GPU (collected last on purpose): the allocation-free cross-entropy entry point.
+
+Some hosts of this library cannot hand it a workspace or let it allocate one — a trainer whose
+HBM is fully planned before the first step, or an embedder that passes inputs and outputs only.
+b200_cross_entropy_bf16_noalloc serves them from a fixed scratch array inside the library.
+This test drives it through the C-ABI with raw pointers and checks, on two consecutive calls that
+share that array (the second one smaller, so stale slots of the first call sit right behind it),
+that loss and gradient equal what the workspace-taking entry point b200_cross_entropy_bf16
+produces on the same logits. Both run the same kernels, so the comparison is exact; the tolerance
+used is the suite's bf16 bound (2e-2 relative) all the same. It also checks that a batch beyond
+the built-in limit is refused with a readable message.
+"""
+import ctypes
+
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+BF16_TOL = 2e-2
+MAX_ROWS = 65536     # B200_CE_NOALLOC_MAX_ROWS in include/b200llm.h
+
+
+def _case(M, V, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    ld = (V + 7) // 8 * 8
+    logits = (torch.randn(M, ld, generator=g, device="cuda") * 3).to(torch.bfloat16)
+    targets = torch.randint(0, V, (M,), generator=g, device="cuda")
+    targets[torch.rand(M, generator=g, device="cuda") < 0.4] = -100
+    targets[0] = 1
+    return logits, targets, ld
+
+
+def _run(lib, fn_name, logits, targets, ld, V, with_workspace):
+    from building_llm_from_scratch_b200 import _lib
+    M = logits.shape[0]
+    buf = logits.clone()
+    loss = torch.zeros(1, device="cuda", dtype=torch.float32)
+    stream = torch.cuda.current_stream().cuda_stream
+    if with_workspace:
+        nbytes = lib.b200_cross_entropy_workspace_bytes(M)
+        ws = torch.empty(nbytes, device="cuda", dtype=torch.uint8)
+        rc = lib.b200_cross_entropy_bf16(buf.data_ptr(), ld, targets.data_ptr(), loss.data_ptr(), M, V, 1,
+                                         ws.data_ptr(), nbytes, stream)
+    else:
+        rc = getattr(lib, fn_name)(buf.data_ptr(), ld, targets.data_ptr(), loss.data_ptr(), M, V, 1, stream)
+    _lib.check(rc, fn_name)
+    torch.cuda.synchronize()
+    return loss.cpu(), buf[:, :V].float().cpu()
+
+
+def test_noalloc_cross_entropy_matches_workspace_version_twice_in_a_row():
+    from building_llm_from_scratch_b200 import _lib
+    lib = _lib.load()
+    for M, V, seed in [(4096, 1000, 1), (513, 50257, 2)]:        # second call smaller than the first
+        logits, targets, ld = _case(M, V, seed)
+        ref_loss, ref_grad = _run(lib, "b200_cross_entropy_bf16", logits, targets, ld, V, with_workspace=True)
+        loss, grad = _run(lib, "b200_cross_entropy_bf16_noalloc", logits, targets, ld, V, with_workspace=False)
+        assert rel_err(loss, ref_loss) < BF16_TOL and torch.equal(loss, ref_loss)
+        assert rel_err(grad, ref_grad) < BF16_TOL and torch.equal(grad, ref_grad)
+        assert torch.all(grad[(targets == -100).cpu()] == 0)
+
+
+def test_noalloc_cross_entropy_refuses_oversized_batches():
+    from building_llm_from_scratch_b200 import _lib
+    lib = _lib.load()
+    dummy = torch.zeros(8, device="cuda", dtype=torch.bfloat16)
+    loss = torch.zeros(1, device="cuda", dtype=torch.float32)
+    tg = torch.zeros(8, device="cuda", dtype=torch.int64)
+    rc = lib.b200_cross_entropy_bf16_noalloc(dummy.data_ptr(), 8, tg.data_ptr(), loss.data_ptr(), MAX_ROWS + 1, 8, 1,
+                                             torch.cuda.current_stream().cuda_stream)
+    assert rc == -1
+    msg = lib.b200_last_error().decode()
+    assert "exceed" in msg and str(MAX_ROWS) in msg
