@@ -311,6 +311,7 @@ def main():
         prof = kernels.GemmProfile()
         kernels.set_gemm_profile(prof)
         eager = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=False)
+        eager.ddp = None                          # rank-0-only pass: no collective may be issued here
         eager.x.copy_(dev[0][0]); eager.y.copy_(dev[0][1])
         eager._refresh_hyper(peek=True)
         eager._eager_step()                       # warm
