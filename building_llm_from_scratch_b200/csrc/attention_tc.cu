@@ -166,24 +166,23 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mx = fmaxf(mx, x);
       }
       const float m_new = fmaxf(m, mx);
-      const float alpha = exp2f(m - m_new);
+      const float alpha = fast_exp2(m - m_new);
       float sum = 0.f;
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float p0 = exp2f(__uint_as_float(r[2 * i]) - m_new);
-        const float p1 = exp2f(__uint_as_float(r[2 * i + 1]) - m_new);
+        const float p0 = fast_exp2(__uint_as_float(r[2 * i]) - m_new);
+        const float p1 = fast_exp2(__uint_as_float(r[2 * i + 1]) - m_new);
         sum += p0 + p1;
         pk[i] = f2_to_bf2(p0, p1);
       }
       l = l * alpha + sum;
       m = m_new;
       // P row -> smem, K-major 128B-swizzled (16-byte chunk index XOR row % 8)
-      uint8_t* prow = sP + buf * P_BYTES + row * 128;
+      const uint32_t prow = smem_u32(sP) + buf * P_BYTES + row * 128;
 #pragma unroll
       for (int c = 0; c < 8; ++c)
-        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) =
-            make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+        sts_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       fence_proxy_async_smem();
       if (j > 0) {
         mbar_wait(o_done, (j - 1) & 1);
@@ -268,92 +267,87 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
 }
 
 // =====================================================================================
-// backward (head_dim 64): dK, dV and dQ in one kernel.
+// backward (head_dim 64), dK / dV kernel.
 //
 // CTA = 128 keys of one (batch, kv head); it streams every (query head of the GQA group) x
-// (128-row query tile at or below the diagonal). Working transposed (keys on the M / TMEM-lane
-// axis) lets one thread own one key row:
-//   S^T  = K Q^T            dP^T = V dO^T                      (128 x 128 each, TMEM)
-//   P^T  = exp2(S^T c - lse[q]),  dS^T = P^T (dP^T - delta[q]) scale   -> bf16, swizzled smem
-//   dV  += P^T dO           dK  += dS^T Q                      (accumulate in TMEM over the loop)
-//   dQ   = dS K             (fresh per query tile; reduced across key tiles with fp32 vector
-//                            atomics into a [tokens, h*64] workspace)
+// (64-row query step at or below the diagonal). Working transposed (keys on the M / TMEM-lane
+// axis) lets a thread own one key row:
+//   S^T  = K Q^T            dP^T = V dO^T                      (128 x 64 each, TMEM, double buffered)
+//   P^T  = exp2(S^T c - lse[q]),  dS^T = P^T (dP^T - delta[q]) scale   -> bf16, swizzled smem panels
+//   dV  += P^T dO           dK  += dS^T Q                      (accumulate in TMEM over the whole loop)
 // The same swizzled Q / dO tiles serve as K-major operands (first two products) and as MN-major
-// operands (dV, dK); dS^T in smem is read back as an MN-major A operand for dQ. TMEM: 448 of 512
-// columns, one CTA per SM.
+// operands (the accumulating two). The MMA issuer runs one step ahead (S/dP of step s+1 and the
+// accumulation of step s-1 execute while the 8 softmax warps work on step s).
+// TMEM: 384 of 512 columns, one CTA per SM.
 // =====================================================================================
 namespace {
 
-constexpr int BK2 = 128;                  // keys per CTA and query rows per step
+constexpr int BK2 = 128;                  // keys per CTA (also the query tile of the dQ kernel's maps)
 constexpr int T2_BYTES = BK2 * HD * 2;    // 16 KB  [128 x 64] bf16 tile
-constexpr int PT_BYTES = BK2 * BK2 * 2;   // 32 KB  [128 x 128] bf16 (two 64-wide panels)
-constexpr int BWD_SMEM = 2 * T2_BYTES + 4 * T2_BYTES + 2 * PT_BYTES + 4 * BK2 * 4 + 1024 + 256;
+constexpr int QS = 64;                    // query rows per step
+constexpr int QS_BYTES = QS * HD * 2;     // 8 KB
+constexpr int PANEL_BYTES = BK2 * QS * 2; // 16 KB  [128 keys x 64 q] bf16
+constexpr int NSTG = 4;
+constexpr int LD_BYTES = 2 * QS * 4;       // 64 x (lse * log2e) then 64 x delta for one query step
+constexpr int BWD_SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 4 * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
 
 struct BwdParams {
-  int B, T, H, HKV, nqt;
+  int B, T, H, HKV, nkt, nq64;
   float scale, scale_log2;
-  const float* lse;
-  const float* delta;
-  float* dq_acc;      // [B*T, H*64] fp32
+  const float* ld2;   // [B, H, nq64, 2, 64]: lse * log2e (inf beyond T) and delta (0 beyond T)
   bf16* dk;
   long long lddk;
   bf16* dv;
   long long lddv;
 };
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-               : "memory");
-}
-
-__global__ void __launch_bounds__(192, 1)
-attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
-                   const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                   const BwdParams p) {
+__global__ void __launch_bounds__(320, 1)
+attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                       const BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sK = smem;
   uint8_t* sV = sK + T2_BYTES;
-  uint8_t* sQ = sV + T2_BYTES;          // [2]
-  uint8_t* sdO = sQ + 2 * T2_BYTES;     // [2]
-  uint8_t* sPt = sdO + 2 * T2_BYTES;
-  uint8_t* sdSt = sPt + PT_BYTES;
-  float* sLse = (float*)(sdSt + PT_BYTES);  // [2][128]
-  float* sDel = sLse + 2 * BK2;             // [2][128]
-  uint64_t* bars = (uint64_t*)(sDel + 2 * BK2);
-  uint64_t* kv_full = bars;            // 1
-  uint64_t* qdo_full = bars + 1;       // 2
-  uint64_t* qdo_empty = bars + 3;      // 2
-  uint64_t* s_full = bars + 5;         // 1
-  uint64_t* s_empty = bars + 6;        // 1 (4 arrivals)
-  uint64_t* ps_full = bars + 7;        // 1 (4 arrivals)
-  uint64_t* dq_full = bars + 8;        // 1
-  uint64_t* dq_empty = bars + 9;       // 1 (4 arrivals)
-  uint64_t* acc_done = bars + 10;      // 1
-  uint32_t* tmem_slot = (uint32_t*)(bars + 11);
+  uint8_t* sQ = sV + T2_BYTES;              // [NSTG] x 8 KB
+  uint8_t* sdO = sQ + NSTG * QS_BYTES;      // [NSTG] x 8 KB
+  uint8_t* sPt = sdO + NSTG * QS_BYTES;     // [2] x 16 KB
+  uint8_t* sdSt = sPt + 2 * PANEL_BYTES;    // [2] x 16 KB
+  uint8_t* sLd = sdSt + 2 * PANEL_BYTES;           // [NSTG] x 512 B
+  uint64_t* bars = (uint64_t*)(sLd + NSTG * LD_BYTES);
+  uint64_t* kv_full = bars;                 // 1
+  uint64_t* qdo_full = bars + 1;            // NSTG
+  uint64_t* qdo_empty = qdo_full + NSTG;    // NSTG
+  uint64_t* s_full = qdo_empty + NSTG;      // 2
+  uint64_t* st_empty = s_full + 2;          // 2 (8 arrivals)
+  uint64_t* ps_full = st_empty + 2;         // 2 (8 arrivals)
+  uint64_t* panel_free = ps_full + 2;       // 2
+  uint64_t* acc_done = panel_free + 2;      // 1
+  uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int per_kt = p.B * p.HKV;
-  const int kt = (int)(blockIdx.x / per_kt);   // early key tiles (most query tiles) first
+  const int kt = (int)(blockIdx.x / per_kt);   // early key tiles (most query steps) first
   const int rem = (int)(blockIdx.x % per_kt);
   const int kvh = rem % p.HKV, b = rem / p.HKV;
   const int G = p.H / p.HKV;
   const int kv0 = kt * BK2;
   const int row_base = b * p.T;
-  const int nq = p.nqt - kt;
-  const int iters = G * nq;
+  const int spp = p.nq64 - 2 * kt;             // query steps per head
+  const int steps = G * spp;
 
   if (threadIdx.x == 0) {
     mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NSTG; ++i) {
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
     }
-    mbar_init(s_full, 1);
-    mbar_init(s_empty, 4);
-    mbar_init(ps_full, 4);
-    mbar_init(dq_full, 1);
-    mbar_init(dq_empty, 4);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&st_empty[i], 8);
+      mbar_init(&ps_full[i], 8);
+      mbar_init(&panel_free[i], 1);
+    }
     mbar_init(acc_done, 1);
     mbar_fence_init();
   }
@@ -368,164 +362,152 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  constexpr uint32_t C_ST = 0, C_DPT = 128, C_DV = 256, C_DK = 320, C_DQ = 384;
+  constexpr uint32_t C_ST = 0, C_DPT = 128, C_DV = 256, C_DK = 320;
 
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(kv_full, 2 * T2_BYTES);
       tma_load_2d(sK, &tmK, kv_full, kvh * HD, row_base + kv0);
       tma_load_2d(sV, &tmV, kv_full, kvh * HD, row_base + kv0);
-      for (int it = 0; it < iters; ++it) {
-        const int st = it & 1;
-        const int head = kvh * G + it / nq, qi = kt + it % nq;
-        mbar_wait(&qdo_empty[st], ((it >> 1) & 1) ^ 1);
-        mbar_expect_tx(&qdo_full[st], 2 * T2_BYTES);
-        tma_load_2d(sQ + st * T2_BYTES, &tmQ, &qdo_full[st], head * HD, row_base + qi * BK2);
-        tma_load_2d(sdO + st * T2_BYTES, &tmdO, &qdo_full[st], head * HD, row_base + qi * BK2);
+      int head = kvh * G, q64 = 2 * kt;
+      for (int s = 0; s < steps; ++s) {
+        const int stg = s % NSTG;
+        mbar_wait(&qdo_empty[stg], ((s / NSTG) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[stg], 2 * QS_BYTES + LD_BYTES);
+        tma_load_2d(sQ + stg * QS_BYTES, &tmQ, &qdo_full[stg], head * HD, row_base + q64 * QS);
+        tma_load_2d(sdO + stg * QS_BYTES, &tmdO, &qdo_full[stg], head * HD, row_base + q64 * QS);
+        bulk_load_1d(sLd + stg * LD_BYTES, p.ld2 + (((long long)b * p.H + head) * p.nq64 + q64) * (2 * QS),
+                     LD_BYTES, &qdo_full[stg]);
+        if (++q64 == p.nq64) {
+          q64 = 2 * kt;
+          ++head;
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t id_s = umma_idesc_bf16(128, 128, 0, 0);    // S^T, dP^T
-      const uint32_t id_acc = umma_idesc_bf16(128, 64, 0, 1);   // dV, dK: A K-major, B MN-major
-      const uint32_t id_dq = umma_idesc_bf16(128, 64, 1, 1);    // dQ: A (dS^T read transposed) and B MN-major
-      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aPt = smem_u32(sPt), adSt = smem_u32(sdSt);
+      const uint32_t id_s = umma_idesc_bf16(128, QS, 0, 0);     // S^T, dP^T
+      const uint32_t id_acc = umma_idesc_bf16(128, HD, 0, 1);   // dV, dK: A K-major, B MN-major
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
       mbar_wait(kv_full, 0);
-      for (int it = 0; it < iters; ++it) {
-        const int st = it & 1;
-        const uint32_t aQ = smem_u32(sQ + st * T2_BYTES), adO = smem_u32(sdO + st * T2_BYTES);
-        mbar_wait(&qdo_full[st], (it >> 1) & 1);
-        if (it > 0) mbar_wait(s_empty, (it - 1) & 1);
+      auto issue_s = [&](int s) {
+        const int stg = s % NSTG, buf = s & 1;
+        const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
+        mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
+        if (s >= 2) mbar_wait(&st_empty[buf], ((s >> 1) - 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + C_ST, umma_desc_k128(aK + k * 32), umma_desc_k128(aQ + k * 32), id_s, k > 0);
+          umma_bf16_ss(tmem_base + C_ST + buf * QS, umma_desc_k128(aK + k * 32), umma_desc_k128(aQ + k * 32), id_s, k > 0);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DPT, umma_desc_k128(aV + k * 32), umma_desc_k128(adO + k * 32), id_s, k > 0);
-        umma_commit(s_full);
-        mbar_wait(ps_full, it & 1);
-        if (it > 0) mbar_wait(dq_empty, (it - 1) & 1);
+          umma_bf16_ss(tmem_base + C_DPT + buf * QS, umma_desc_k128(aV + k * 32), umma_desc_k128(adO + k * 32), id_s, k > 0);
+        umma_commit(&s_full[buf]);
+      };
+      auto issue_acc = [&](int s) {
+        const int stg = s % NSTG, buf = s & 1;
+        const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
+        const uint32_t aPt = smem_u32(sPt + buf * PANEL_BYTES), adSt = smem_u32(sdSt + buf * PANEL_BYTES);
+        mbar_wait(&ps_full[buf], (s >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < BK2 / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DV, umma_desc_k128(aPt + (k >> 2) * T2_BYTES + (k & 3) * 32),
-                       umma_desc_mn128(adO + k * 2048, 8192), id_acc, (it > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < QS / 16; ++k)
+          umma_bf16_ss(tmem_base + C_DV, umma_desc_k128(aPt + k * 32), umma_desc_mn128(adO + k * 2048, 8192), id_acc,
+                       (s > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
-        for (int k = 0; k < BK2 / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DK, umma_desc_k128(adSt + (k >> 2) * T2_BYTES + (k & 3) * 32),
-                       umma_desc_mn128(aQ + k * 2048, 8192), id_acc, (it > 0 || k > 0) ? 1u : 0u);
-#pragma unroll
-        for (int k = 0; k < BK2 / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DQ, umma_desc_mn128(adSt + k * 2048, T2_BYTES),
-                       umma_desc_mn128(aK + k * 2048, 8192), id_dq, k > 0 ? 1u : 0u);
-        umma_commit(dq_full);
-        umma_commit(&qdo_empty[st]);
+        for (int k = 0; k < QS / 16; ++k)
+          umma_bf16_ss(tmem_base + C_DK, umma_desc_k128(adSt + k * 32), umma_desc_mn128(aQ + k * 2048, 8192), id_acc,
+                       (s > 0 || k > 0) ? 1u : 0u);
+        umma_commit(&panel_free[buf]);
+        umma_commit(&qdo_empty[stg]);
+      };
+      issue_s(0);
+      for (int s = 0; s < steps; ++s) {
+        if (s + 1 < steps) issue_s(s + 1);
+        issue_acc(s);
       }
       umma_commit(acc_done);
     }
   } else {
+    // 8 softmax warps: quad = TMEM lane quadrant (key rows), half = which 32 of the 64 query columns
     const int quad = warp & 3;
-    const int row = quad * 32 + lane;     // key row (S^T, dV, dK) and query row (dQ)
+    const int half = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int key = kv0 + row;
-    for (int it = 0; it < iters; ++it) {
-      const int st = it & 1;
-      const int head = kvh * G + it / nq, qi = kt + it % nq;
-      const int qrow0 = qi * BK2;
-      {
-        const int t = qrow0 + row;
-        const long long base = ((long long)b * p.H + head) * p.T;
-        sLse[st * BK2 + row] = t < p.T ? p.lse[base + t] * LOG2E : INFINITY;
-        sDel[st * BK2 + row] = t < p.T ? p.delta[base + t] : 0.f;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      mbar_wait(s_full, it & 1);
+    int q64 = 2 * kt;
+    for (int s = 0; s < steps; ++s) {
+      const int buf = s & 1, stg = s % NSTG;
+      const int qrow0 = q64 * QS;
+      if (++q64 == p.nq64) q64 = 2 * kt;
+      // s_full is committed after the MMAs that needed this step's Q/dO stage, so the lse/delta that
+      // travelled with that stage (same mbarrier) are in shared memory as well
+      mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
+      mbar_wait(&s_full[buf], (s >> 1) & 1);
       tc_fence_after();
-      const bool diag = (qi == kt);
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t s[32], d[32];
-        tmem_ld_32x32(tlane + C_ST + c * 32, s);
-        tmem_ld_32x32(tlane + C_DPT + c * 32, d);
-        tmem_ld_wait();
-        uint32_t pp[16], dd[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float pv[2], dv2[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int q = c * 32 + 2 * i + e;
-            float pr = exp2f(__uint_as_float(s[2 * i + e]) * p.scale_log2 - sLse[st * BK2 + q]);
-            if (diag && key > qrow0 + q) pr = 0.f;
-            pv[e] = pr;
-            dv2[e] = pr * (__uint_as_float(d[2 * i + e]) - sDel[st * BK2 + q]) * p.scale;
-          }
-          pp[i] = f2_to_bf2(pv[0], pv[1]);
-          dd[i] = f2_to_bf2(dv2[0], dv2[1]);
-        }
-        // columns [c*32, c*32+32) of row `row`: panel c/2, 16-byte chunks (c&1)*4 .. +3
-        uint8_t* prow = sPt + (c >> 1) * T2_BYTES + row * 128;
-        uint8_t* drow = sdSt + (c >> 1) * T2_BYTES + row * 128;
-#pragma unroll
-        for (int t4 = 0; t4 < 4; ++t4) {
-          const int ch = ((c & 1) * 4 + t4) ^ (row & 7);
-          *reinterpret_cast<uint4*>(prow + (ch << 4)) = make_uint4(pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
-          *reinterpret_cast<uint4*>(drow + (ch << 4)) = make_uint4(dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
-        }
-      }
+      uint32_t sv[32], dv[32];
+      tmem_ld_32x32(tlane + C_ST + buf * QS + half * 32, sv);
+      tmem_ld_32x32(tlane + C_DPT + buf * QS + half * 32, dv);
+      tmem_ld_wait();
       tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&st_empty[buf]);
+      const bool diag = qrow0 < kv0 + BK2;
+      const uint32_t lse_s = smem_u32(sLd) + stg * LD_BYTES + half * 128;
+      const uint32_t del_s = lse_s + QS * 4;
+      uint32_t pp[16], dd[16];
+#pragma unroll
+      for (int i4 = 0; i4 < 8; ++i4) {
+        const float4 l4 = lds_f4(lse_s + i4 * 16);
+        const float4 d4 = lds_f4(del_s + i4 * 16);
+        const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+        float pv[4], dsv[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = i4 * 4 + e;
+          float pr = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -ls[e]));
+          if (diag && key > qrow0 + half * 32 + c) pr = 0.f;
+          pv[e] = pr;
+          dsv[e] = pr * (__uint_as_float(dv[c]) - ds[e]) * p.scale;
+        }
+        pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
+        pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
+        dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
+        dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
+      }
+      if (s >= 2) mbar_wait(&panel_free[buf], ((s >> 1) - 1) & 1);
+      const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
+      const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
+#pragma unroll
+      for (int t4 = 0; t4 < 4; ++t4) {
+        const int ch = (half * 4 + t4) ^ (row & 7);
+        sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
+        sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+      }
       fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(s_empty);
-        mbar_arrive(ps_full);
-      }
-      // dQ tile of this step: thread <-> query row
-      mbar_wait(dq_full, it & 1);
-      tc_fence_after();
-      {
-        const int t = qrow0 + row;
-        float* dst = p.dq_acc + (long long)(row_base + t) * ((long long)p.H * HD) + (long long)head * HD;
-#pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
-          uint32_t o[32];
-          tmem_ld_32x32(tlane + C_DQ + h2 * 32, o);
-          tmem_ld_wait();
-          if (t < p.T) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              red_add_v4(dst + h2 * 32 + i * 4, __uint_as_float(o[4 * i]), __uint_as_float(o[4 * i + 1]),
-                         __uint_as_float(o[4 * i + 2]), __uint_as_float(o[4 * i + 3]));
-          }
-        }
-      }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(dq_empty);
+      if (lane == 0) mbar_arrive(&ps_full[buf]);
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD;
-    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD;
+    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + half * 32;
+    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + half * 32;
+    uint32_t a[32], c2[32];
+    tmem_ld_32x32(tlane + C_DV + half * 32, a);
+    tmem_ld_32x32(tlane + C_DK + half * 32, c2);
+    tmem_ld_wait();
+    if (key < p.T) {
 #pragma unroll
-    for (int h2 = 0; h2 < 2; ++h2) {
-      uint32_t a[32], c2[32];
-      tmem_ld_32x32(tlane + C_DV + h2 * 32, a);
-      tmem_ld_32x32(tlane + C_DK + h2 * 32, c2);
-      tmem_ld_wait();
-      if (key < p.T) {
+      for (int c = 0; c < 4; ++c) {
+        float f[8], g[8];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          float f[8], g[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            f[i] = __uint_as_float(a[c * 8 + i]);
-            g[i] = __uint_as_float(c2[c * 8 + i]);
-          }
-          st_v4(dvrow + h2 * 32 + c * 8, pack8(f));
-          st_v4(dkrow + h2 * 32 + c * 8, pack8(g));
+        for (int i = 0; i < 8; ++i) {
+          f[i] = __uint_as_float(a[c * 8 + i]);
+          g[i] = __uint_as_float(c2[c * 8 + i]);
         }
+        st_v4(dvrow + c * 8, pack8(f));
+        st_v4(dkrow + c * 8, pack8(g));
       }
     }
   }
@@ -538,19 +520,225 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   }
 }
 
-// delta[b, h, t] = sum_c dO * O over one head: 8 lanes per (token, head), 4 pairs per warp
+// ---- dQ: CTA = 128 query rows of one (batch, head); streams 64-key tiles up to the diagonal ----
+//   S = Q K_j^T, dP = dO V_j^T (TMEM)  ->  dS = exp2(S c - lse) (dP - delta) scale  (thread = query
+//   row, lse / delta live in registers)  ->  bf16 smem  ->  dQ += dS K_j (K as MN-major B), dQ
+//   accumulates in TMEM over the key loop and is written once: no atomics, deterministic.
+// Fused dQ inside the key-tile kernel was limited by the SM's RED issue rate (8192 fp32 atomics per
+// 128x128 step ~ 10.5 k cycles); recomputing S / dP here costs two extra MMAs per tile instead.
+constexpr int DQ_NS = 2;
+constexpr int DQ_SMEM = 2 * Q_BYTES + DQ_NS * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;
+
+struct DqParams {
+  int B, T, H, HKV, nqt;
+  float scale, scale_log2;
+  const float* ld2;   // [B, H, nq64, 2, 64]
+  int nq64;
+  bf16* dq;
+  long long lddq;
+};
+
+__global__ void __launch_bounds__(192, 2)
+attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                      const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                      const DqParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint8_t* sdO = sQ + Q_BYTES;
+  uint8_t* sK = sdO + Q_BYTES;
+  uint8_t* sV = sK + DQ_NS * KV_BYTES;
+  uint8_t* sdS = sV + DQ_NS * KV_BYTES;   // [2] x [128 x 64] bf16
+  uint64_t* bars = (uint64_t*)(sdS + 2 * P_BYTES);
+  uint64_t* q_full = bars;                // 1
+  uint64_t* kv_full = bars + 1;           // DQ_NS
+  uint64_t* kv_empty = kv_full + DQ_NS;   // DQ_NS
+  uint64_t* s_full = kv_empty + DQ_NS;    // 1
+  uint64_t* s_empty = s_full + 1;         // 1 (4 arrivals)
+  uint64_t* ds_full = s_empty + 1;        // 2 (4 arrivals)
+  uint64_t* dq_done = ds_full + 2;        // 1
+  uint32_t* tmem_slot = (uint32_t*)(dq_done + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_qt = p.B * p.H;
+  const int qt = p.nqt - 1 - (int)(blockIdx.x / per_qt);
+  const int rem = (int)(blockIdx.x % per_qt);
+  const int head = rem % p.H, b = rem / p.H;
+  const int kvh = head / (p.H / p.HKV);
+  const int q0 = qt * BQ;
+  const int row_base = b * p.T;
+  const int n_kv = (min(q0 + BQ, p.T) + BKV - 1) / BKV;
+
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, 1);
+    for (int i = 0; i < DQ_NS; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_empty, 4);
+    mbar_init(&ds_full[0], 4);
+    mbar_init(&ds_full[1], 4);
+    mbar_init(dq_done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmdO);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t D_S = 0, D_DP = 64, D_DQ = 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, 2 * Q_BYTES);
+      tma_load_2d(sQ, &tmQ, q_full, head * HD, row_base + q0);
+      tma_load_2d(sdO, &tmdO, q_full, head * HD, row_base + q0);
+      for (int j = 0; j < n_kv; ++j) {
+        const int s = j % DQ_NS;
+        mbar_wait(&kv_empty[s], ((j / DQ_NS) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
+        tma_load_2d(sK + s * KV_BYTES, &tmK, &kv_full[s], kvh * HD, row_base + j * BKV);
+        tma_load_2d(sV + s * KV_BYTES, &tmV, &kv_full[s], kvh * HD, row_base + j * BKV);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t id_s = umma_idesc_bf16(BQ, BKV, 0, 0);
+      const uint32_t id_dq = umma_idesc_bf16(BQ, HD, 0, 1);
+      const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO);
+      mbar_wait(q_full, 0);
+      auto issue_s = [&](int j) {
+        const int s = j % DQ_NS;
+        mbar_wait(&kv_full[s], (j / DQ_NS) & 1);
+        if (j > 0) mbar_wait(s_empty, (j - 1) & 1);
+        tc_fence_after();
+        const uint32_t aK = smem_u32(sK + s * KV_BYTES), aV = smem_u32(sV + s * KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16_ss(tmem_base + D_S, umma_desc_k128(aQ + k * 32), umma_desc_k128(aK + k * 32), id_s, k > 0);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16_ss(tmem_base + D_DP, umma_desc_k128(adO + k * 32), umma_desc_k128(aV + k * 32), id_s, k > 0);
+        umma_commit(s_full);
+      };
+      issue_s(0);
+      for (int j = 0; j < n_kv; ++j) {
+        // S/dP of the next tile go first: they only need the softmax threads to have pulled tile j
+        // out of TMEM, so they run while those threads are still forming dS_j
+        if (j + 1 < n_kv) issue_s(j + 1);
+        const int s = j % DQ_NS, buf = j & 1;
+        mbar_wait(&ds_full[buf], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t adS = smem_u32(sdS + buf * P_BYTES), aK = smem_u32(sK + s * KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k)
+          umma_bf16_ss(tmem_base + D_DQ, umma_desc_k128(adS + k * 32), umma_desc_mn128(aK + k * 2048, 8192),
+                       id_dq, (j > 0 || k > 0) ? 1u : 0u);
+        umma_commit(&kv_empty[s]);
+      }
+      umma_commit(dq_done);
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const int t = q0 + row;
+    const float* ldrow = p.ld2 + (((long long)b * p.H + head) * p.nq64 + (t >> 6)) * (2 * QS) + (t & 63);
+    const float lse2 = ldrow[0];     // already * log2e, +inf for padding rows
+    const float dl = ldrow[QS];
+    for (int j = 0; j < n_kv; ++j) {
+      const int buf = j & 1;
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      uint32_t s[64], d[64];
+      tmem_ld_32x32(tlane + D_S, s);
+      tmem_ld_32x32(tlane + D_S + 32, s + 32);
+      tmem_ld_32x32(tlane + D_DP, d);
+      tmem_ld_32x32(tlane + D_DP + 32, d + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_empty);
+      const int kv0 = j * BKV;
+      const bool diag = kv0 + BKV - 1 > q0 + quad * 32;
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        float v2[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = 2 * i + e;
+          float pr = fast_exp2(fmaf(__uint_as_float(s[c]), p.scale_log2, -lse2));
+          if (diag && kv0 + c > t) pr = 0.f;
+          v2[e] = pr * (__uint_as_float(d[c]) - dl) * p.scale;
+        }
+        pk[i] = f2_to_bf2(v2[0], v2[1]);
+      }
+      // buffer `buf` was last read by the dQ MMA of tile j-2, issued before S_j: retired once s_full fired
+      const uint32_t drow = smem_u32(sdS) + buf * P_BYTES + row * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        sts_v4(drow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ds_full[buf]);
+    }
+    mbar_wait(dq_done, 0);
+    tc_fence_after();
+    bf16* orow = p.dq + (long long)(row_base + t) * p.lddq + (long long)head * HD;
+#pragma unroll
+    for (int h2 = 0; h2 < 2; ++h2) {
+      uint32_t o[32];
+      tmem_ld_32x32(tlane + D_DQ + h2 * 32, o);
+      tmem_ld_wait();
+      if (t < p.T) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(o[c * 8 + i]);
+          st_v4(orow + h2 * 32 + c * 8, pack8(f));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// ld2[b, h, step, 0, j] = lse[b, h, 64*step + j] * log2e (+inf beyond T),
+// ld2[b, h, step, 1, j] = delta = sum_c dO * O (0 beyond T); 8 lanes per (token, head).
 __global__ void __launch_bounds__(256)
 attn_delta64_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ dout,
-                    long long lddo, float* __restrict__ delta, long long B, int T, int H) {
-  const long long total = B * T * H;
+                    long long lddo, const float* __restrict__ lse, float* __restrict__ ld2, long long B,
+                    int T, int H, int nq64) {
+  const long long Tpad = (long long)nq64 * QS;
+  const long long total = B * Tpad * H;
   const int lane = threadIdx.x & 31, sub = lane >> 3, l8 = lane & 7;
   for (long long w = ((long long)blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + sub; w < total + 3;
        w += (long long)gridDim.x * 8 * 4) {
     float acc = 0.f;
     const bool ok = w < total;
     const int head = ok ? (int)(w % H) : 0;
-    const long long tok = ok ? w / H : 0;
-    if (ok) {
+    const long long tp = ok ? w / H : 0;
+    const long long bb = tp / Tpad;
+    const int t = (int)(tp % Tpad);
+    const bool real = ok && t < T;
+    if (real) {
+      const long long tok = bb * T + t;
       float a[8], g[8];
       unpack8(ld_nc_v4(o + tok * ldo + (long long)head * HD + l8 * 8), a);
       unpack8(ld_nc_v4(dout + tok * lddo + (long long)head * HD + l8 * 8), g);
@@ -560,31 +748,19 @@ attn_delta64_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __res
     acc += __shfl_xor_sync(0xffffffffu, acc, 1);
     acc += __shfl_xor_sync(0xffffffffu, acc, 2);
     acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-    if (ok && l8 == 0) delta[((tok / T) * H + head) * T + (tok % T)] = acc;
-  }
-}
-
-// dq (bf16, pitch lddq) = dq_acc (fp32, contiguous [rows, cols])
-__global__ void __launch_bounds__(256)
-dq_finish_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long lddq, long long rows,
-                 int cols) {
-  const int cv = cols >> 3;
-  const long long total = rows * cv;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / cv;
-    const int c = (int)(i % cv) * 8;
-    const uint4 u0 = ld_nc_v4(acc + r * cols + c), u1 = ld_nc_v4(acc + r * cols + c + 4);
-    const float f[8] = {__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w),
-                        __uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w)};
-    st_v4(dq + r * lddq + c, pack8(f));
+    if (ok && l8 == 0) {
+      float* dst = ld2 + ((bb * H + head) * nq64 + (t >> 6)) * (2 * QS) + (t & 63);
+      dst[0] = real ? lse[(bb * H + head) * T + t] * LOG2E : INFINITY;
+      dst[QS] = real ? acc : 0.f;
+    }
   }
 }
 
 }  // namespace
 
 size_t b200_attention_bwd_tc64_workspace(int64_t B, int64_t T, int64_t h) {
-  return (size_t)(B * h * T) * 4 + (size_t)(B * T * h * HD) * 4 + 256;
+  const int64_t nq64 = (T + QS - 1) / QS;
+  return (size_t)(B * h * nq64 * 2 * QS) * 4 + 256;
 }
 
 int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
@@ -592,48 +768,58 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
                             const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                             int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
                             int64_t hkv, float scale, cudaStream_t st) {
-  float* delta = (float*)workspace;
-  float* dq_acc = (float*)(((uintptr_t)(delta + B * h * T) + 255) & ~(uintptr_t)255);
+  float* ld2 = (float*)workspace;   // cudaMalloc / caching-allocator memory: at least 256-B aligned
+  B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
   const long long rows = B * T;
+  const int nq64 = (int)((T + QS - 1) / QS);
   {
-    const long long total = rows * h;
+    const long long total = B * nq64 * QS * h;
     long long blocks = (total + 31) / 32;
     const long long cap = (long long)b200_num_sms() * 16;
     if (blocks > cap) blocks = cap;
-    attn_delta64_kernel<<<(int)blocks, 256, 0, st>>>((const bf16*)o, ldo, (const bf16*)dout, lddo, delta, B, (int)T, (int)h);
+    attn_delta64_kernel<<<(int)blocks, 256, 0, st>>>((const bf16*)o, ldo, (const bf16*)dout, lddo, lse, ld2, B, (int)T, (int)h, nq64);
     B200_CHECK_LAUNCH();
   }
-  B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * h * HD * 4, st));
-  CUtensorMap mq, mdo, mk, mv;
+  CUtensorMap mq, mdo, mk, mv, mk64, mv64;
   int rc;
   if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, BK2, HD))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mdo, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, BK2, HD))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BK2, HD))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mv, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BK2, HD))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mk64, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BKV, HD))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mv64, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BKV, HD))) return rc;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
     attr_set[dev & 63] = true;
   }
-  BwdParams p;
-  p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
-  p.nqt = (int)((T + BK2 - 1) / BK2);
-  p.scale = scale; p.scale_log2 = scale * LOG2E;
-  p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
-  p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
-  const long long grid = (long long)p.nqt * B * hkv;
-  attn_bwd_tc_kernel<<<(unsigned)grid, 192, BWD_SMEM, st>>>(mq, mdo, mk, mv, p);
-  B200_CHECK_LAUNCH();
+  const int nqt = (int)((T + BK2 - 1) / BK2);
   {
-    const long long total = rows * (h * HD / 8);
-    long long blocks = (total + 255) / 256;
-    const long long cap = (long long)b200_num_sms() * 16;
-    if (blocks > cap) blocks = cap;
-    dq_finish_kernel<<<(int)blocks, 256, 0, st>>>(dq_acc, (bf16*)dq, lddq, rows, (int)(h * HD));
+    DqParams p;
+    p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv; p.nqt = nqt;
+    p.scale = scale; p.scale_log2 = scale * LOG2E;
+    p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
+    const long long grid = (long long)nqt * B * h;
+    attn_bwd_dq_tc_kernel<<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
   }
-  b200_count_launch(4);
+  {
+    CUtensorMap mq64, mdo64;
+    if ((rc = b200_make_tmap_2d_bf16(&mq64, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, QS, HD))) return rc;
+    if ((rc = b200_make_tmap_2d_bf16(&mdo64, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, QS, HD))) return rc;
+    BwdParams p;
+    p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
+    p.nkt = nqt; p.nq64 = nq64;
+    p.scale = scale; p.scale_log2 = scale * LOG2E;
+    p.ld2 = ld2;
+    p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
+    const long long grid = (long long)p.nkt * B * hkv;
+    attn_bwd_dkv_tc_kernel<<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    B200_CHECK_LAUNCH();
+  }
+  b200_count_launch(3);
   return 0;
 }

@@ -15,6 +15,8 @@
 // shared-memory descriptor, so backward GEMMs (dX = dY·W, dW = dY^T·X) need no transposes.
 //
 // Roofline: tensor pipe. Algorithmic FLOPs per launch = 2·M·N·(K1+K2).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
@@ -50,6 +52,89 @@ struct GemmParams {
 
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+// Epilogue for 32 consecutive accumulator columns of one output row (one thread):
+// alpha, bias, GELU, residual, then bf16 / fp32 / atomic / transposed store with tail predicates.
+__device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, bool row_ok,
+                                            long long col0, const uint32_t* r) {
+  if (col0 >= p.N) return;
+  const bool full_cols = col0 + 32 <= p.N;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+  if (p.flags & EP_BIAS) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+  }
+  if (p.flags & EP_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+  }
+  if (p.flags & EP_TRANS_OUT) {
+    // C is [N, M]-shaped in memory: element (row, col) goes to C[col * ldc + row]
+    if (row_ok) {
+      if (p.flags & EP_OUT_F32) {
+        float* C = (float*)p.C;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) {
+            if (p.flags & EP_ATOMIC) atomicAdd(&C[(col0 + j) * p.ldc + row], v[j]);
+            else C[(col0 + j) * p.ldc + row] = v[j];
+          }
+      } else {
+        bf16* C = (bf16*)p.C;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) C[(col0 + j) * p.ldc + row] = __float2bfloat16_rn(v[j]);
+      }
+    }
+    return;
+  }
+  if (!row_ok) return;
+  if (p.flags & EP_RESIDUAL) {
+    const bf16* R = p.R + row * p.ldr + col0;
+    if (full_cols && (p.ldr & 7) == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float f[8];
+        unpack8(ld_v4(R + q * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[q * 8 + j] += f[j];
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) v[j] += __bfloat162float(R[j]);
+    }
+  }
+  if (p.flags & EP_OUT_F32) {
+    float* C = (float*)p.C + row * p.ldc + col0;
+    if (p.flags & EP_ATOMIC) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) atomicAdd(&C[j], v[j]);
+    } else if (full_cols && (p.ldc & 3) == 0) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<float4*>(C + q * 4) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) C[j] = v[j];
+    }
+  } else {
+    bf16* C = (bf16*)p.C + row * p.ldc + col0;
+    if (full_cols && (p.ldc & 7) == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) st_v4(C + q * 8, pack8(&v[q * 8]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) C[j] = __float2bfloat16_rn(v[j]);
+    }
+  }
 }
 
 template <int BN>
@@ -202,85 +287,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_const
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BN + c * 32);
         tmem_ld_32x32(taddr, r);
         tmem_ld_wait();
-        const long long col0 = (long long)n_blk * BN + c * 32;
-        if (col0 >= p.N) continue;
-        const bool full_cols = col0 + 32 <= p.N;
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-        if (p.flags & EP_BIAS) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
-        }
-        if (p.flags & EP_GELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-        }
-        if (p.flags & EP_TRANS_OUT) {
-          // C is [N, M]-shaped in memory: element (row, col) goes to C[col * ldc + row]
-          if (row_ok) {
-            if (p.flags & EP_OUT_F32) {
-              float* C = (float*)p.C;
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < p.N) {
-                  if (p.flags & EP_ATOMIC) atomicAdd(&C[(col0 + j) * p.ldc + row], v[j]);
-                  else C[(col0 + j) * p.ldc + row] = v[j];
-                }
-            } else {
-              bf16* C = (bf16*)p.C;
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < p.N) C[(col0 + j) * p.ldc + row] = __float2bfloat16_rn(v[j]);
-            }
-          }
-          continue;
-        }
-        if (!row_ok) continue;
-        if (p.flags & EP_RESIDUAL) {
-          const bf16* R = p.R + row * p.ldr + col0;
-          if (full_cols && (p.ldr & 7) == 0) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              float f[8];
-              unpack8(ld_v4(R + q * 8), f);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[q * 8 + j] += f[j];
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) v[j] += __bfloat162float(R[j]);
-          }
-        }
-        if (p.flags & EP_OUT_F32) {
-          float* C = (float*)p.C + row * p.ldc + col0;
-          if (p.flags & EP_ATOMIC) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) atomicAdd(&C[j], v[j]);
-          } else if (full_cols && (p.ldc & 3) == 0) {
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-              *reinterpret_cast<float4*>(C + q * 4) =
-                  make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) C[j] = v[j];
-          }
-        } else {
-          bf16* C = (bf16*)p.C + row * p.ldc + col0;
-          if (full_cols && (p.ldc & 7) == 0) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) st_v4(C + q * 8, pack8(&v[q * 8]));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.N) C[j] = __float2bfloat16_rn(v[j]);
-          }
-        }
+        store_chunk(p, row, row_ok, (long long)n_blk * BN + c * 32, r);
       }
       tc_fence_before();
       __syncwarp();
@@ -316,6 +323,200 @@ int launch_bn(const CUtensorMap* maps, const GemmParams& p, int grid, cudaStream
   return 0;
 }
 
+
+// ======================================================================================
+// CTA-pair variant: a cluster of two CTAs on one TPC computes a 256 x 256 tile with
+// tcgen05.mma.cta_group::2. Each CTA stages its own 128 A rows and HALF of the B tile, so the
+// shared-memory traffic per SM (TMA writes + MMA reads) drops from 192 to 128 B/clk at full MMA
+// rate — the single-CTA kernel above is capped near 2/3 of the tensor peak by exactly that.
+// Only the leader CTA issues MMAs; both CTAs run a producer, an epilogue over their own 128
+// TMEM lanes, and arrive remotely on the leader's accumulator-empty barrier.
+// ======================================================================================
+constexpr int P_BN = 256;                       // tile N of the pair
+constexpr int P_BHALF_BYTES = (P_BN / 2) * BK * 2;   // 16 KB: this CTA's half of B
+constexpr int P_STAGE_BYTES = A_BYTES + P_BHALF_BYTES;
+constexpr int P_STAGES = RING_BYTES / P_STAGE_BYTES; // 6
+constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 + 16;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                         const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                         const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + P_STAGES * P_STAGE_BYTES);
+  uint64_t* empty = full + P_STAGES;
+  uint64_t* tfull = empty + P_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 8);   // 4 epilogue warps of each CTA (leader's copy is the one used)
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc_2cta(tmem_slot, 512);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB1);
+    if (p.kb2 > 0) {
+      tma_prefetch_desc(&tmA2);
+      tma_prefetch_desc(&tmB2);
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_kb = p.kb1 + p.kb2;
+  const int num_work = p.m_tiles * p.n_tiles;          // m_tiles counts 256-row tiles here
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = cluster_id; w < num_work; w += num_clusters) {
+        const int m_blk = w % p.m_tiles, n_blk = w / p.m_tiles;
+        const int m0 = m_blk * 256 + (int)rank * 128;
+        const int n0 = n_blk * P_BN + (int)rank * 128;
+        for (int kb = 0; kb < total_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&full[stage], 2 * P_STAGE_BYTES);
+          uint8_t* sa = smem + stage * P_STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const bool ext = kb >= p.kb1;
+          const int kk = (ext ? kb - p.kb1 : kb) * BK;
+          const CUtensorMap* ma = ext ? &tmA2 : &tmA1;
+          const CUtensorMap* mb = ext ? &tmB2 : &tmB1;
+          const int a_mn = ext ? p.a2_mn : p.a1_mn;
+          const int b_mn = ext ? p.b2_mn : p.b1_mn;
+          if (!a_mn) {
+            tma_load_2d_2cta(sa, ma, &full[stage], kk, m0);
+          } else {
+            tma_load_2d_2cta(sa, ma, &full[stage], m0, kk);
+            tma_load_2d_2cta(sa + 8192, ma, &full[stage], m0 + 64, kk);
+          }
+          if (!b_mn) {
+            tma_load_2d_2cta(sb, mb, &full[stage], kk, n0);
+          } else {
+            tma_load_2d_2cta(sb, mb, &full[stage], n0, kk);
+            tma_load_2d_2cta(sb + 8192, mb, &full[stage], n0 + 64, kk);
+          }
+          if (++stage == P_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tempty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * P_BN);
+        for (int kb = 0; kb < total_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * P_STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+          const bool ext = kb >= p.kb1;
+          const int a_mn = ext ? p.a2_mn : p.a1_mn;
+          const int b_mn = ext ? p.b2_mn : p.b1_mn;
+          const uint32_t idesc = umma_idesc_bf16(256, P_BN, (uint32_t)a_mn, (uint32_t)b_mn);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = a_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
+            const uint64_t bd = b_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
+            umma_bf16_ss_2cta(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2cta(&empty[stage]);
+          if (++stage == P_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_2cta(&tfull[as]);
+      }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;
+    int it = 0;
+    for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
+      const int m_blk = w % p.m_tiles, n_blk = w / p.m_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(&tfull[as], aph);
+      tc_fence_after();
+      const long long row = (long long)m_blk * 256 + (long long)rank * 128 + ew * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < P_BN / 32; ++c) {
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32);
+        tmem_ld_32x32(taddr, r);
+        tmem_ld_wait();
+        store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tempty[as], 0);
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2cta(tmem_base, 512);
+  }
+}
+
+int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStream_t st) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    attr_set[dev] = true;
+  }
+  const int work = p.m_tiles * p.n_tiles;
+  int clusters = sms / 2;
+  if (work < clusters) clusters = work;
+  gemm_tcgen05_2cta_kernel<<<2 * clusters, 256, P_SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], p);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+bool use_pair_kernel() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_GEMM_1CTA");
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 struct Operand {
   const void* ptr;
   int64_t ld;
@@ -345,6 +546,7 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   B200_CHECK_ARG(!(accumulate && !out_f32), "gemm: accumulate needs fp32 output");
   B200_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31) && K1 < (1ll << 31), "gemm: sizes exceed int32");
 
+  const bool pair = use_pair_kernel() && !accumulate && !trans_out && M >= 256 && N >= 256;
   const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
   GemmParams p;
   p.M = (int)M;
@@ -352,7 +554,7 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   p.kb1 = (int)((K1 + BK - 1) / BK);
   p.kb2 = (int)((K2 + BK - 1) / BK);
   p.a1_mn = a1_mn; p.b1_mn = b1_mn; p.a2_mn = a2_mn; p.b2_mn = b2_mn;
-  p.m_tiles = (int)((M + BM - 1) / BM);
+  p.m_tiles = pair ? (int)((M + 255) / 256) : (int)((M + BM - 1) / BM);
   p.n_tiles = (int)((N + BN - 1) / BN);
   p.alpha = alpha;
   p.bias = (const bf16*)bias;
@@ -378,12 +580,13 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   CUtensorMap maps[4];
   int rc;
   Operand oa1{A1, lda1, a1_mn}, ob1{B1, ldb1, b1_mn};
+  const int b_box_rows = pair ? 128 : BN;   // the pair kernel loads half of the B tile per CTA
   if ((rc = make_operand_map(&maps[0], oa1, M, K1, BM))) return rc;
-  if ((rc = make_operand_map(&maps[1], ob1, N, K1, BN))) return rc;
+  if ((rc = make_operand_map(&maps[1], ob1, N, K1, b_box_rows))) return rc;
   if (K2 > 0) {
     Operand oa2{A2, lda2, a2_mn}, ob2{B2, ldb2, b2_mn};
     if ((rc = make_operand_map(&maps[2], oa2, M, K2, BM))) return rc;
-    if ((rc = make_operand_map(&maps[3], ob2, N, K2, BN))) return rc;
+    if ((rc = make_operand_map(&maps[3], ob2, N, K2, b_box_rows))) return rc;
   } else {
     maps[2] = maps[0];
     maps[3] = maps[1];
@@ -391,6 +594,7 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   const int work = tiles * splits;
   const int grid = work < sms ? work : sms;
   cudaStream_t st = (cudaStream_t)stream;
+  if (pair) return launch_2cta(maps, p, sms, st);
   switch (BN) {
     case 64: return launch_bn<64>(maps, p, grid, st);
     case 128: return launch_bn<128>(maps, p, grid, st);

@@ -1,0 +1,39 @@
+"""Micro-benchmark of the GEMM at the bench workload's shapes (not a bench value)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from building_llm_from_scratch_b200 import kernels as K
+
+flush = torch.empty(256 * 1024 * 1024, device="cuda", dtype=torch.uint8)
+
+
+def timeit(fn, n=8):
+    for _ in range(3):
+        fn()
+    ts = []
+    for _ in range(n):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return sorted(ts)[len(ts) // 2]
+
+
+def rnd(*s):
+    return (torch.randn(*s, device="cuda") * 0.05).to(torch.bfloat16)
+
+
+M = 8192
+tag = "1cta" if os.environ.get("B200_GEMM_1CTA") == "1" else "2cta"
+for (N, Kd, b_mn, r) in [(2048, 2048, 0, 64), (8192, 2048, 0, 64), (2048, 8192, 0, 64), (2048, 8192, 1, 64),
+                         (8192, 2048, 1, 64), (512, 2048, 0, 64), (128256, 2048, 0, 64), (2048, 128256, 1, 64),
+                         (3072, 2048, 0, 0), (16384, 2048, 0, 0)]:
+    a = rnd(M, Kd)
+    b = rnd(Kd, N) if b_mn else rnd(N, Kd)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    kw = {}
+    if r:
+        kw = dict(a2=rnd(M, r), b2=rnd(N, r))
+    ms = timeit(lambda: K.gemm_ex(a, b, b1_mn=bool(b_mn), out=out, **kw))
+    fl = 2.0 * M * N * (Kd + r)
+    print(f"{tag} M={M} N={N} K={Kd}+{r} b_mn={b_mn}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TF/s")
