@@ -226,6 +226,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=None, help="debug: fewer blocks (result is then not a bench value)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--full-head", action="store_true", help="project every row through the vocab head, ignored targets included")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -259,10 +260,14 @@ def main():
     host = [alpaca_batch(gen, MICRO_BATCH, SEQ_LEN, cfg["vocab_size"]) for _ in range(n_batches)]
     host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
     dev = [(x.to(device), y.to(device)) for x, y in host]
+    n_valid = [int((y != -100).sum()) for _, y in host]        # known from the host copy of each batch
     ignored = float(sum((y == -100).float().mean() for _, y in host) / n_batches)
 
     step = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=not args.no_graph)
+    step.compact_head = not args.full_head
     step.capture(warmup=2)
+    for n in n_valid:
+        step.prepare(n)
 
     def barrier():
         if world > 1:
@@ -271,13 +276,13 @@ def main():
 
     def timed(batches, read_loss):
         for i in range(args.warmup):
-            step.run(*batches[i % n_batches])
+            step.run(*batches[i % n_batches], n_valid=n_valid[i % n_batches])
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = _lib.launch_count()
         e0.record()
         for i in range(args.steps):
-            loss = step.run(*batches[i % n_batches])
+            loss = step.run(*batches[i % n_batches], n_valid=n_valid[i % n_batches])
             if read_loss:
                 last = float(loss)          # D2H read of the step's result, every step
         e1.record()
@@ -312,7 +317,9 @@ def main():
         kernels.set_gemm_profile(prof)
         eager = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=False)
         eager.ddp = None                          # rank-0-only pass: no collective may be issued here
+        eager.compact_head = step.compact_head
         eager.x.copy_(dev[0][0]); eager.y.copy_(dev[0][1])
+        eager._graphs_for(n_valid[0])             # same vocab-projection capacity as the timed steps
         eager._refresh_hyper(peek=True)
         eager._eager_step()                       # warm
         prof.reset()
@@ -347,7 +354,10 @@ def main():
                         "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "cuda_graph": step.graphs is not None, "final_loss": final_loss,
-                "ignored_target_fraction": ignored}
+                "ignored_target_fraction": ignored,
+                "vocab_projection": ("all rows" if args.full_head else
+                                     "non-ignored target rows only (exact: ignored rows reach neither the loss nor any "
+                                     f"gradient); capacities {sorted(set(step.bucket_graphs) | {0})} rows, 0 = all")}
         if args.layers is not None:
             line["debug_layers"] = args.layers
         print(json.dumps(line), flush=True)

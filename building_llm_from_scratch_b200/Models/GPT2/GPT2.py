@@ -54,9 +54,8 @@ class MultiHeadAttention(nn.Module):
         if self.training and self.dropout.p > 0:
             raise NotImplementedError("attention-weight dropout (GPT2.py:43) is not fused yet: use drop_rate=0.0")
         b, num_tokens, _ = x.shape
-        q = self.W_query(x).view(b * num_tokens, -1)
-        k = self.W_key(x).view(b * num_tokens, -1)
-        v = self.W_value(x).view(b * num_tokens, -1)
+        q, k, v = (t.view(b * num_tokens, -1)
+                   for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)[0]
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 
@@ -122,6 +121,6 @@ class GPTModel(nn.Module):
     def forward(self, x):
         return self.output_head(self.hidden_states(x))
 
-    def forward_loss(self, x, targets):
+    def forward_loss(self, x, targets, capacity=0):
         w, A, B, s = head_operands(self.output_head)
-        return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets)[0]
+        return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets, capacity)[0]

@@ -84,9 +84,8 @@ class GroupedQueryAttention(nn.Module):
 
     def forward(self, x, residual=None):
         b, num_tokens, _ = x.shape
-        q = self.W_query(x).view(b * num_tokens, -1)
-        k = self.W_key(x).view(b * num_tokens, -1)
-        v = self.W_value(x).view(b * num_tokens, -1)
+        q, k, v = (t.view(b * num_tokens, -1)
+                   for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         cos = self.cos if self.cos.dtype == torch.bfloat16 else self.cos.to(torch.bfloat16)
         sin = self.sin if self.sin.dtype == torch.bfloat16 else self.sin.to(torch.bfloat16)
         ctx = ops.attention(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)[0]
@@ -136,8 +135,8 @@ class Llama3Model(nn.Module):
     def forward(self, in_idx):
         return self.out_head(self.hidden_states(in_idx))
 
-    def forward_loss(self, in_idx, targets):
+    def forward_loss(self, in_idx, targets, capacity=0):
         """Fused vocab projection + cross-entropy (train.py:90-91) without a logits tensor
         handed back to Python; used by Trainer.calc_loss_batch in training mode."""
         w, A, B, s = head_operands(self.out_head)
-        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets)[0]
+        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity)[0]

@@ -54,5 +54,6 @@ class FeedForward(nn.Module):
         self.silu = SiLU()
 
     def forward(self, x, residual=None):
-        h = ops.swiglu(self.fc1(x), self.fc2(x))
+        a, b = ops.linears_of_same_input(x, [self.fc1, self.fc2])
+        h = ops.swiglu(a, b)
         return self.fc3(h, residual)

@@ -22,6 +22,18 @@ I = C.c_int
 F = C.c_float
 SZ = C.c_size_t
 
+class GemmProblem(C.Structure):
+    """b200_gemm_problem of include/b200llm.h."""
+    _fields_ = [("A", C.c_void_p), ("lda", C.c_int64), ("a_mn", C.c_int),
+                ("B", C.c_void_p), ("ldb", C.c_int64), ("b_mn", C.c_int),
+                ("C", C.c_void_p), ("ldc", C.c_int64),
+                ("M", C.c_int64), ("N", C.c_int64), ("K", C.c_int64),
+                ("out_f32", C.c_int), ("accumulate", C.c_int), ("trans_out", C.c_int),
+                ("alpha", C.c_float)]
+
+
+GEMM_GROUP_MAX = 16
+
 # name -> (restype, argtypes)
 SIGNATURES = {
     "b200_version": (I, []),
@@ -31,6 +43,7 @@ SIGNATURES = {
     "b200_gemm_nt_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, I, P]),
     "b200_gemm_ex": (I, [P, I64, I, P, I64, I, I64, P, I64, I, P, I64, I, I64, P, P, I64, P, I64,
                          I64, I64, I, I, I, I, F, I, P]),
+    "b200_gemm_grouped_bf16": (I, [I, C.POINTER(GemmProblem), P]),
     "b200_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I, I, F, I64, I64, I64, P]),
     "b200_rmsnorm_fwd_bf16": (I, [P, P, P, P, P, I64, I64, F, I, P]),
     "b200_rmsnorm_bwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),
@@ -47,6 +60,9 @@ SIGNATURES = {
     "b200_embedding_bwd_f32acc": (I, [P, P, P, P, I64, I64, I64, I64, P]),
     "b200_cross_entropy_workspace_bytes": (SZ, [I64]),
     "b200_cross_entropy_bf16": (I, [P, I64, P, P, I64, I64, I, P, SZ, P]),
+    "b200_compact_rows": (I, [P, I64, I64, P, P, P]),
+    "b200_gather_rows_bf16": (I, [P, I64, P, P, P, P, P, I64, I64, P]),
+    "b200_scatter_rows_bf16": (I, [P, P, P, I64, I64, I64, P]),
     "b200_cross_entropy_bf16_noalloc": (I, [P, I64, P, P, I64, I64, I, P]),
     "b200_grad_norm_workspace_bytes": (SZ, [I64]),
     "b200_grad_norm_bf16": (I, [P, I64, F, P, P, SZ, P]),

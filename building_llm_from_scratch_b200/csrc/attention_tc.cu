@@ -319,8 +319,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   uint64_t* qdo_full = bars + 1;            // NSTG
   uint64_t* qdo_empty = qdo_full + NSTG;    // NSTG
   uint64_t* s_full = qdo_empty + NSTG;      // 2
-  uint64_t* st_empty = s_full + 2;          // 2 (8 arrivals)
-  uint64_t* ps_full = st_empty + 2;         // 2 (8 arrivals)
+  uint64_t* st_empty = s_full + 2;          // 2 (4 arrivals: one softmax group each)
+  uint64_t* ps_full = st_empty + 2;         // 2 (4 arrivals)
   uint64_t* panel_free = ps_full + 2;       // 2
   uint64_t* acc_done = panel_free + 2;      // 1
   uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
@@ -344,8 +344,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&st_empty[i], 8);
-      mbar_init(&ps_full[i], 8);
+      mbar_init(&st_empty[i], 4);
+      mbar_init(&ps_full[i], 4);
       mbar_init(&panel_free[i], 1);
     }
     mbar_init(acc_done, 1);
@@ -429,60 +429,68 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       umma_commit(acc_done);
     }
   } else {
-    // 8 softmax warps: quad = TMEM lane quadrant (key rows), half = which 32 of the 64 query columns
+    // Two softmax groups of 4 warps ping-pong over the steps (group = step parity): each owns one of
+    // the two S^T/dP^T TMEM buffers and one P^T/dS^T smem panel pair, so the barrier / TMEM-load /
+    // proxy-fence latencies of one group hide behind the other group's arithmetic.
     const int quad = warp & 3;
-    const int half = (warp - 2) >> 2;
-    const int row = quad * 32 + lane;
+    const int grp = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;                 // key row
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int key = kv0 + row;
-    int q64 = 2 * kt;
-    for (int s = 0; s < steps; ++s) {
-      const int buf = s & 1, stg = s % NSTG;
+    const int buf = grp;
+    int q64 = 2 * kt + (grp % spp);
+    // advance (head, q64) by two steps at a time
+    for (int s = grp; s < steps; s += 2) {
+      const int stg = s % NSTG;
       const int qrow0 = q64 * QS;
-      if (++q64 == p.nq64) q64 = 2 * kt;
-      // s_full is committed after the MMAs that needed this step's Q/dO stage, so the lse/delta that
-      // travelled with that stage (same mbarrier) are in shared memory as well
-      mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
+      q64 += 2;
+      while (q64 >= p.nq64) q64 -= spp;
+      mbar_wait(&qdo_full[stg], (s / NSTG) & 1);      // lse/delta travelled with this stage
       mbar_wait(&s_full[buf], (s >> 1) & 1);
       tc_fence_after();
-      uint32_t sv[32], dv[32];
-      tmem_ld_32x32(tlane + C_ST + buf * QS + half * 32, sv);
-      tmem_ld_32x32(tlane + C_DPT + buf * QS + half * 32, dv);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&st_empty[buf]);
       const bool diag = qrow0 < kv0 + BK2;
-      const uint32_t lse_s = smem_u32(sLd) + stg * LD_BYTES + half * 128;
+      const uint32_t lse_s = smem_u32(sLd) + stg * LD_BYTES;
       const uint32_t del_s = lse_s + QS * 4;
-      uint32_t pp[16], dd[16];
-#pragma unroll
-      for (int i4 = 0; i4 < 8; ++i4) {
-        const float4 l4 = lds_f4(lse_s + i4 * 16);
-        const float4 d4 = lds_f4(del_s + i4 * 16);
-        const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
-        float pv[4], dsv[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int c = i4 * 4 + e;
-          float pr = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -ls[e]));
-          if (diag && key > qrow0 + half * 32 + c) pr = 0.f;
-          pv[e] = pr;
-          dsv[e] = pr * (__uint_as_float(dv[c]) - ds[e]) * p.scale;
-        }
-        pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
-        pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
-        dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
-        dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
-      }
       if (s >= 2) mbar_wait(&panel_free[buf], ((s >> 1) - 1) & 1);
       const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
       const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
+#pragma unroll 1
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t sv[32], dv[32];
+        tmem_ld_32x32(tlane + C_ST + buf * QS + hf * 32, sv);
+        tmem_ld_32x32(tlane + C_DPT + buf * QS + hf * 32, dv);
+        tmem_ld_wait();
+        if (hf == 1) {   // both halves are in registers: the MMA issuer may overwrite this TMEM buffer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&st_empty[buf]);
+        }
+        uint32_t pp[16], dd[16];
 #pragma unroll
-      for (int t4 = 0; t4 < 4; ++t4) {
-        const int ch = (half * 4 + t4) ^ (row & 7);
-        sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
-        sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 l4 = lds_f4(lse_s + hf * 128 + i4 * 16);
+          const float4 d4 = lds_f4(del_s + hf * 128 + i4 * 16);
+          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+          float pv[4], dsv[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = i4 * 4 + e;
+            float pr = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -ls[e]));
+            if (diag && key > qrow0 + hf * 32 + c) pr = 0.f;
+            pv[e] = pr;
+            dsv[e] = pr * (__uint_as_float(dv[c]) - ds[e]) * p.scale;
+          }
+          pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
+          pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
+          dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
+          dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
+        }
+#pragma unroll
+        for (int t4 = 0; t4 < 4; ++t4) {
+          const int ch = (hf * 4 + t4) ^ (row & 7);
+          sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
+          sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+        }
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -491,11 +499,12 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + half * 32;
-    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + half * 32;
+    // epilogue: group g writes columns [32g, 32g + 32) of dV and dK for its key row
+    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + grp * 32;
+    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + grp * 32;
     uint32_t a[32], c2[32];
-    tmem_ld_32x32(tlane + C_DV + half * 32, a);
-    tmem_ld_32x32(tlane + C_DK + half * 32, c2);
+    tmem_ld_32x32(tlane + C_DV + grp * 32, a);
+    tmem_ld_32x32(tlane + C_DK + grp * 32, c2);
     tmem_ld_wait();
     if (key < p.T) {
 #pragma unroll

@@ -301,7 +301,121 @@ colsum_kernel(const bf16* __restrict__ x, long long ld, float* __restrict__ out,
   for (int j = 0; j < 8 && c + j < N; ++j) atomicAdd(&out[c + j], acc[j]);
 }
 
+// ---------------- row compaction for the vocab projection ----------------
+// Rows whose target is ignore_index (-100) contribute nothing to the loss or to any gradient
+// (train.py:91: mean over non-ignored rows), so the fused vocab-projection + CE op only needs the
+// other rows. idx[j] (j < capacity) = j-th non-ignored row in ascending order, -1 for padding;
+// meta[0] = number of non-ignored rows, meta[1] = 1 if that number exceeds `capacity`.
+__global__ void __launch_bounds__(1024)
+compact_rows_kernel(const long long* __restrict__ targets, int M, int capacity, int* __restrict__ idx,
+                    int* __restrict__ meta) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  for (int j = threadIdx.x; j < capacity; j += 1024) idx[j] = -1;
+  __syncthreads();
+  for (int base = 0; base < M; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = (i < M && targets[i] != -100) ? 1 : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+      int t = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += n;
+      }
+      warp_tot[lane] = t;   // inclusive totals per warp
+    }
+    __syncthreads();
+    const int pos = carry + (w > 0 ? warp_tot[w - 1] : 0) + incl - v;
+    if (v && pos < capacity) idx[pos] = i;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += warp_tot[31];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    meta[0] = carry;
+    meta[1] = carry > capacity ? 1 : 0;
+  }
+}
+
+// out[j, :] = x[idx[j], :] (zeros for padding); tout[j] = targets[idx[j]] (-100 for padding).
+// If the compaction overflowed (meta[1]) the gathered activations are poisoned with NaNs so the
+// loss turns into NaN instead of silently dropping rows.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const bf16* __restrict__ x, long long ldx, const long long* __restrict__ targets,
+                   const int* __restrict__ idx, const int* __restrict__ meta, bf16* __restrict__ out,
+                   long long* __restrict__ tout, int capacity, int d) {
+  const int dv = d >> 3;
+  const long long total = (long long)capacity * dv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i / dv), c = (int)(i % dv) * 8;
+    const int r = idx[j];
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (r >= 0) v = ld_nc_v4(x + (long long)r * ldx + c);
+    if (meta[1]) v = make_uint4(0x7FC07FC0u, 0x7FC07FC0u, 0x7FC07FC0u, 0x7FC07FC0u);  // bf16 NaNs
+    st_v4(out + (long long)j * d + c, v);
+    if (c == 0) tout[j] = r >= 0 ? targets[r] : -100;
+  }
+}
+
+// dst[idx[j], :] = src[j, :]; dst rows that are not listed must have been zeroed by the caller
+__global__ void __launch_bounds__(256)
+scatter_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ idx, bf16* __restrict__ dst,
+                    long long ldd, int capacity, int d) {
+  const int dv = d >> 3;
+  const long long total = (long long)capacity * dv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i / dv), c = (int)(i % dv) * 8;
+    const int r = idx[j];
+    if (r >= 0) st_v4(dst + (long long)r * ldd + c, ld_nc_v4(src + (long long)j * d + c));
+  }
+}
+
 }  // namespace
+
+extern "C" int b200_compact_rows(const int64_t* targets, int64_t M, int64_t capacity, int32_t* idx,
+                                 int32_t* meta, void* stream) {
+  B200_CHECK_ARG(targets && idx && meta && M > 0 && capacity > 0 && M < (1ll << 31), "compact_rows: bad arguments");
+  compact_rows_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((const long long*)targets, (int)M, (int)capacity, idx, meta);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_gather_rows_bf16(const void* x, int64_t ldx, const int64_t* targets, const int32_t* idx,
+                                     const int32_t* meta, void* out, int64_t* targets_out,
+                                     int64_t capacity, int64_t d, void* stream) {
+  B200_CHECK_ARG(x && targets && idx && meta && out && targets_out && capacity > 0, "gather_rows: null pointer or empty");
+  B200_CHECK_ARG(d % 8 == 0 && ldx % 8 == 0, "gather_rows: d and ldx must be multiples of 8");
+  gather_rows_kernel<<<ew_grid(capacity * (d / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, ldx, (const long long*)targets, idx, meta, (bf16*)out, (long long*)targets_out, (int)capacity, (int)d);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_scatter_rows_bf16(const void* src, const int32_t* idx, void* dst, int64_t ldd,
+                                      int64_t capacity, int64_t d, void* stream) {
+  B200_CHECK_ARG(src && idx && dst && capacity > 0, "scatter_rows: null pointer or empty");
+  B200_CHECK_ARG(d % 8 == 0 && ldd % 8 == 0, "scatter_rows: d and ldd must be multiples of 8");
+  scatter_rows_kernel<<<ew_grid(capacity * (d / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)src, idx, (bf16*)dst, ldd, (int)capacity, (int)d);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
 
 extern "C" int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N,
                                 void* stream) {

@@ -508,6 +508,175 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   return 0;
 }
 
+// ======================================================================================
+// Grouped launch: up to GROUP_MAX independent skinny problems (N <= 64: the LoRA weight
+// gradients dA = x^T u and dB = (dY^T t)^T, or the rank-r projections t = x A) share ONE
+// persistent launch. Each of those problems alone fills at most 64-144 CTAs for ~20 us, most of it
+// launch / prologue / pipeline ramp; concatenating their (tile, split) work lists keeps all SMs
+// streaming and pays the fixed costs once.
+// ======================================================================================
+constexpr int GROUP_MAX = 16;
+constexpr int G_BN = 64;
+constexpr int G_B_BYTES = G_BN * BK * 2;
+constexpr int G_STAGE_BYTES = A_BYTES + G_B_BYTES;
+constexpr int G_STAGES = RING_BYTES / G_STAGE_BYTES;   // 8
+constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 + (2 * G_STAGES + 4) * 8 + 16;
+
+struct GroupedParams {
+  int nprob;
+  int work_end[GROUP_MAX];     // exclusive prefix sums of tiles * splits
+  GemmParams p[GROUP_MAX];
+};
+struct GroupedMaps {
+  CUtensorMap a[GROUP_MAX];
+  CUtensorMap b[GROUP_MAX];
+};
+
+__device__ __forceinline__ int find_problem(const GroupedParams& g, int w, int& local) {
+  int i = 0, begin = 0;
+  while (i < g.nprob - 1 && w >= g.work_end[i]) {
+    begin = g.work_end[i];
+    ++i;
+  }
+  local = w - begin;
+  return i;
+}
+
+__global__ void __launch_bounds__(256, 1)
+gemm_grouped_kernel(const __grid_constant__ GroupedMaps maps, const __grid_constant__ GroupedParams g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + G_STAGES * G_STAGE_BYTES);
+  uint64_t* empty = full + G_STAGES;
+  uint64_t* tfull = empty + G_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * G_BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_work = g.work_end[g.nprob - 1];
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        int local;
+        const int pi = find_problem(g, w, local);
+        const GemmParams& p = g.p[pi];
+        const int num_tiles = p.m_tiles * p.n_tiles;
+        const int split = local / num_tiles, tile = local % num_tiles;
+        const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+        const int kb_begin = (int)((long long)split * p.kb1 / p.splits);
+        const int kb_end = (int)((long long)(split + 1) * p.kb1 / p.splits);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], G_STAGE_BYTES);
+          uint8_t* sa = smem + stage * G_STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const int kk = kb * BK;
+          if (!p.a1_mn) {
+            tma_load_2d(sa, &maps.a[pi], &full[stage], kk, m_blk * BM);
+          } else {
+            tma_load_2d(sa, &maps.a[pi], &full[stage], m_blk * BM, kk);
+            tma_load_2d(sa + 8192, &maps.a[pi], &full[stage], m_blk * BM + 64, kk);
+          }
+          if (!p.b1_mn) tma_load_2d(sb, &maps.b[pi], &full[stage], kk, n_blk * G_BN);
+          else tma_load_2d(sb, &maps.b[pi], &full[stage], n_blk * G_BN, kk);
+          if (++stage == G_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++it) {
+        int local;
+        const int pi = find_problem(g, w, local);
+        const GemmParams& p = g.p[pi];
+        const int split = local / (p.m_tiles * p.n_tiles);
+        const int kb_begin = (int)((long long)split * p.kb1 / p.splits);
+        const int kb_end = (int)((long long)(split + 1) * p.kb1 / p.splits);
+        const int as = it & 1;
+        mbar_wait(&tempty[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * G_BN);
+        const uint32_t idesc = umma_idesc_bf16(BM, G_BN, (uint32_t)p.a1_mn, (uint32_t)p.b1_mn);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * G_STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = p.a1_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
+            const uint64_t bd = p.b1_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
+            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == G_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull[as]);
+      }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;
+    int it = 0;
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++it) {
+      int local;
+      const int pi = find_problem(g, w, local);
+      const GemmParams& p = g.p[pi];
+      const int tile = local % (p.m_tiles * p.n_tiles);
+      const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+      const int as = it & 1;
+      mbar_wait(&tfull[as], (it >> 1) & 1);
+      tc_fence_after();
+      const long long row = (long long)m_blk * BM + ew * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < G_BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * G_BN + c * 32), r);
+        tmem_ld_wait();
+        store_chunk(p, row, row_ok, (long long)n_blk * G_BN + c * 32, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * G_BN);
+  }
+}
+
 bool use_pair_kernel() {
   static int v = -1;
   if (v < 0) {
@@ -600,6 +769,66 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
     case 128: return launch_bn<128>(maps, p, grid, st);
     default: return launch_bn<256>(maps, p, grid, st);
   }
+}
+
+
+// One launch for up to B200_GEMM_GROUP_MAX skinny problems (every N <= 64, single operand pair).
+extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs, void* stream) {
+  B200_CHECK_ARG(nprob >= 1 && nprob <= GROUP_MAX && probs, "gemm_grouped: nprob=%d must be in [1, %d]", nprob, GROUP_MAX);
+  static_assert(B200_GEMM_GROUP_MAX == GROUP_MAX, "header / kernel group size mismatch");
+  GroupedParams g;
+  GroupedMaps maps;
+  g.nprob = nprob;
+  const int sms = b200_num_sms();
+  long long tiles_total = 0;
+  for (int i = 0; i < nprob; ++i) {
+    const b200_gemm_problem& q = probs[i];
+    B200_CHECK_ARG(q.A && q.B && q.C && q.M > 0 && q.N > 0 && q.K > 0, "gemm_grouped: problem %d has a null operand or empty size", i);
+    B200_CHECK_ARG(q.N <= G_BN, "gemm_grouped: problem %d has N=%lld > %d", i, (long long)q.N, G_BN);
+    B200_CHECK_ARG(!(q.accumulate && !q.out_f32), "gemm_grouped: accumulate needs fp32 output (problem %d)", i);
+    tiles_total += (q.M + BM - 1) / BM;
+  }
+  // give every problem a share of the SMs proportional to its tile count when it may split K
+  int work = 0;
+  for (int i = 0; i < nprob; ++i) {
+    const b200_gemm_problem& q = probs[i];
+    GemmParams& p = g.p[i];
+    p.M = (int)q.M; p.N = (int)q.N;
+    p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
+    p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
+    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1;
+    p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
+    p.C = q.C; p.ldc = q.ldc;
+    p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0);
+    int splits = 1;
+    if (q.accumulate) {
+      p.flags |= EP_ATOMIC;
+      const long long target = (long long)2 * sms * p.m_tiles / (tiles_total > 0 ? tiles_total : 1);  // ~2 waves overall
+      splits = (int)(target / p.m_tiles);
+      if (splits > p.kb1 / 2) splits = p.kb1 / 2;   // keep >= 2 K blocks per work item
+      if (splits < 1) splits = 1;
+    }
+    p.splits = splits;
+    work += p.m_tiles * splits;
+    g.work_end[i] = work;
+    Operand oa{q.A, q.lda, q.a_mn}, ob{q.B, q.ldb, q.b_mn};
+    int rc;
+    if ((rc = make_operand_map(&maps.a[i], oa, q.M, q.K, BM))) return rc;
+    if ((rc = make_operand_map(&maps.b[i], ob, q.N, q.K, G_BN))) return rc;
+  }
+  for (int i = nprob; i < GROUP_MAX; ++i) g.work_end[i] = work;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    attr_set[dev] = true;
+  }
+  const int grid = work < sms ? work : sms;
+  gemm_grouped_kernel<<<grid, 256, G_SMEM, (cudaStream_t)stream>>>(maps, g);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
 }
 
 extern "C" int b200_gemm_nt_bf16(const void* A1, int64_t lda1, const void* B1, int64_t ldb1,

@@ -28,7 +28,12 @@ class TrainStep:
         self.y = torch.zeros(batch_shape, dtype=torch.int64, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.use_graph = use_graph
-        self.graphs = None
+        self.graphs = None            # graphs of the full-capacity step
+        self.bucket_graphs = {}       # capacity -> graphs with a row-compacted vocab projection
+        self.pool = None
+        self.capacity = 0             # rows the vocab projection sees in the step being built (0 = all)
+        self.compact_head = True
+        self.bucket_rows = max(128, (batch_shape[0] * batch_shape[1]) // 8)
         self.launches_per_step = 0
         self.opt.graph_safe = True
         self.core.train()
@@ -36,7 +41,7 @@ class TrainStep:
     # -- the two halves of a step (split where the data-parallel exchange goes) -------------
     def _fwd_bwd(self):
         self.opt.zero_grad()
-        loss = self.core.forward_loss(self.x, self.y)
+        loss = self.core.forward_loss(self.x, self.y, capacity=self.capacity)
         loss.backward()
         self.loss.copy_(loss.detach())
 
@@ -72,19 +77,48 @@ class TrainStep:
         self.opt._step = saved_step
         if not self.use_graph:
             return
+        self.graphs = self._capture_graphs()
+
+    def _capture_graphs(self):
+        kw = {} if self.pool is None else dict(pool=self.pool)
         if self.ddp is None:
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, **kw):
                 self._fwd_bwd()
                 self._update()
-            self.graphs = (g,)
-        else:
-            g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g1):
-                self._fwd_bwd()
-            with torch.cuda.graph(g2, pool=g1.pool()):
-                self._update()
-            self.graphs = (g1, g2)
+            if self.pool is None:
+                self.pool = g.pool()
+            return (g,)
+        g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g1, **kw):
+            self._fwd_bwd()
+        if self.pool is None:
+            self.pool = g1.pool()
+        with torch.cuda.graph(g2, pool=self.pool):
+            self._update()
+        return (g1, g2)
+
+    def _graphs_for(self, n_valid):
+        """Pick (capturing on first use) the graph whose vocab projection covers n_valid rows."""
+        M = self.x.numel()
+        if not self.compact_head or n_valid is None or n_valid <= 0:
+            self.capacity = 0
+            return self.graphs
+        cap = (n_valid + self.bucket_rows - 1) // self.bucket_rows * self.bucket_rows
+        if cap >= M:
+            self.capacity = 0
+            return self.graphs
+        self.capacity = cap
+        if self.use_graph and cap not in self.bucket_graphs:
+            torch.cuda.synchronize()
+            self.bucket_graphs[cap] = self._capture_graphs()
+        return self.bucket_graphs.get(cap)
+
+    def prepare(self, n_valid):
+        """Capture (outside any timed region) the graph that a batch with n_valid non-ignored targets
+        will replay."""
+        self._graphs_for(n_valid)
+        self.capacity = 0
 
     def _refresh_hyper(self, peek: bool = False):
         tr = self.tr
@@ -95,22 +129,27 @@ class TrainStep:
         self.opt.set_hyper(lr, max(step, 0) + 1)
         return lr
 
-    def run(self, x_src: torch.Tensor, y_src: torch.Tensor):
+    def run(self, x_src: torch.Tensor, y_src: torch.Tensor, n_valid=None):
         """One optimizer step on (x_src, y_src) — device tensors or pinned host tensors.
+        n_valid: number of non-ignored targets in y_src if the caller knows it (counted here when
+        y_src is a host tensor); it selects the row-compacted vocab projection.
         Returns the device scalar holding this step's loss (no synchronisation)."""
         tr = self.tr
+        if n_valid is None and not y_src.is_cuda and self.compact_head:
+            n_valid = int((y_src != -100).sum())
+        graphs = self._graphs_for(n_valid)
         tr.global_step += 1
         lr = self._refresh_hyper()
         tr.track_lrs.append(lr)
         self.x.copy_(x_src, non_blocking=True)
         self.y.copy_(y_src, non_blocking=True)
-        if self.graphs is None:
+        if graphs is None:
             self._eager_step()
-        elif len(self.graphs) == 1:
-            self.graphs[0].replay()
+        elif len(graphs) == 1:
+            graphs[0].replay()
         else:
-            self.graphs[0].replay()
+            graphs[0].replay()
             self.ddp.reduce_gradients(self.opt.flat_grads)
-            self.graphs[1].replay()
+            graphs[1].replay()
         tr.tokens_seen += self.x.numel()
         return self.loss

@@ -124,6 +124,36 @@ def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, 
     return out
 
 
+def gemm_grouped(problems):
+    """problems: list of dicts(a, b, out, a_mn, b_mn, accumulate, trans_out, alpha) with N <= 64.
+    One persistent launch for all of them (chunks of GEMM_GROUP_MAX)."""
+    lib = _lib.load()
+    prof = _gemm_profile
+    for i0 in range(0, len(problems), _lib.GEMM_GROUP_MAX):
+        chunk = problems[i0:i0 + _lib.GEMM_GROUP_MAX]
+        arr = (_lib.GemmProblem * len(chunk))()
+        flops = 0.0
+        for q, pr in zip(arr, chunk):
+            a, b, out = pr["a"], pr["b"], pr["out"]
+            _need_cuda(a, b, out)
+            a_mn, b_mn = bool(pr.get("a_mn")), bool(pr.get("b_mn"))
+            M, K = (a.shape[1], a.shape[0]) if a_mn else a.shape
+            N = b.shape[1] if b_mn else b.shape[0]
+            q.A, q.lda, q.a_mn = a.data_ptr(), a.stride(0), int(a_mn)
+            q.B, q.ldb, q.b_mn = b.data_ptr(), b.stride(0), int(b_mn)
+            q.C, q.ldc = out.data_ptr(), out.stride(0)
+            q.M, q.N, q.K = M, N, K
+            q.out_f32 = int(out.dtype == torch.float32)
+            q.accumulate = int(bool(pr.get("accumulate")))
+            q.trans_out = int(bool(pr.get("trans_out")))
+            q.alpha = float(pr.get("alpha", 1.0))
+            flops += 2.0 * M * N * K
+        start = prof.begin() if prof is not None else None
+        _lib.check(lib.b200_gemm_grouped_bf16(len(chunk), arr, _stream()), "gemm_grouped")
+        if prof is not None:
+            prof.end(start, flops, ("grouped", len(chunk)))
+
+
 def rmsnorm_fwd(x, w, eps=1e-5, res=None, bf16_steps=True):
     """-> y (and the residual sum when res is given). x [M, d] bf16 (or fp32), w fp32 [d]."""
     _need_cuda(x, w, res)
@@ -280,6 +310,33 @@ def cross_entropy_(logits2d, targets, write_grad=True):
     _lib.check(lib.b200_cross_entropy_bf16(_p(logits2d), ld, _p(tg), _p(loss), M, V, int(write_grad), _p(ws), nbytes,
                                            _stream()), "cross_entropy")
     return loss
+
+
+def compact_gather(x2d, targets, capacity):
+    """Rows of x2d whose target != -100, packed into [capacity, d] (zero padded), their targets
+    (-100 padded) and the row index list (int32, -1 padded)."""
+    _need_cuda(x2d, targets)
+    lib = _lib.load()
+    x2d, ldx = _rowmajor2d(x2d)
+    M, d = x2d.shape
+    tg = targets.reshape(-1).contiguous()
+    idx = torch.empty(capacity, device=x2d.device, dtype=torch.int32)
+    meta = torch.empty(2, device=x2d.device, dtype=torch.int32)
+    xc = torch.empty((capacity, d), device=x2d.device, dtype=BF16)
+    tc = torch.empty(capacity, device=x2d.device, dtype=torch.int64)
+    _lib.check(lib.b200_compact_rows(_p(tg), M, capacity, _p(idx), _p(meta), _stream()), "compact_rows")
+    _lib.check(lib.b200_gather_rows_bf16(_p(x2d), ldx, _p(tg), _p(idx), _p(meta), _p(xc), _p(tc), capacity, d, _stream()),
+               "gather_rows")
+    return xc, tc, idx
+
+
+def scatter_rows(src, idx, M):
+    """[M, d] with src[j] at row idx[j] and zeros elsewhere."""
+    _need_cuda(src, idx)
+    C_, d = src.shape
+    dst = torch.zeros((M, d), device=src.device, dtype=BF16)
+    _lib.check(_lib.load().b200_scatter_rows_bf16(_p(src), _p(idx), _p(dst), dst.stride(0), C_, d, _stream()), "scatter_rows")
+    return dst
 
 
 def grad_norm(g_flat, max_norm=1.0, out=None, ws=None):

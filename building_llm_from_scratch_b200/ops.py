@@ -12,7 +12,7 @@ tensor is returned and autograd accumulates it the usual way.
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import List, Optional, Sequence, Tuple
 
 import torch
 from torch import Tensor
@@ -142,11 +142,33 @@ def _lora_linear_setup(ctx, inputs, output):
     ctx.bias_ref = bias
 
 
+# Weight-gradient GEMMs into main_grad accumulators are off the critical path of backward: they are
+# queued and issued as grouped launches (kernels.gemm_grouped) — one persistent kernel for up to 16
+# of these skinny problems instead of one ~20 us launch each.
+_wgrad_queue: list = []
+WGRAD_FLUSH_AT = 16
+
+
+def flush_weight_grads():
+    """Issue every queued weight-gradient GEMM (called before the optimizer / all-reduce read main_grad)."""
+    global _wgrad_queue
+    if _wgrad_queue:
+        q, _wgrad_queue = _wgrad_queue, []
+        K.gemm_grouped(q)
+
+
 def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: bool = False):
     """param-shaped gradient = a_mn_src^T · b_mn_src (both stored [tokens, *])."""
     mg = getattr(param, "main_grad", None)
     if mg is not None:
-        K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
+        n_cols = a_mn_src.shape[1] if trans_out else b_mn_src.shape[1]
+        if n_cols <= 64 and b_mn_src.shape[1] <= 64:
+            _wgrad_queue.append(dict(a=a_mn_src, b=b_mn_src, out=mg, a_mn=True, b_mn=True, accumulate=True,
+                                     trans_out=trans_out))
+            if len(_wgrad_queue) >= WGRAD_FLUSH_AT:
+                flush_weight_grads()
+        else:
+            K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
         return None
     g32 = torch.zeros(param.shape, device=param.device, dtype=torch.float32)
     K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=g32, accumulate=True, trans_out=trans_out)
@@ -184,6 +206,105 @@ def _lora_linear_bwd(ctx, dy, _dt):
 
 
 lora_linear.register_autograd(_lora_linear_bwd, setup_context=_lora_linear_setup)
+
+
+# --------------------------------------------------------------------------------------
+# several bias-free (LoRA) linears of the SAME input: q/k/v of an attention block, fc1/fc2 of SwiGLU
+# --------------------------------------------------------------------------------------
+@torch.library.custom_op("b200llm::lora_linear_multi", mutates_args=())
+def lora_linear_multi(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor], Bs: Sequence[Tensor],
+                      scaling: float) -> List[Tensor]:
+    """[x W_i^T + scaling (x A_i) B_i for i] + [t_i = scaling x A_i for i] (As/Bs empty: plain linears).
+    The rank-r projections of all members run as ONE grouped launch (x is streamed by one
+    persistent kernel instead of len(weights) separate ~17 us launches)."""
+    x2 = _flat2d(x)
+    n = len(weights)
+    ts: List[Tensor] = []
+    if len(As) > 0:
+        ts = [x2.new_empty((x2.shape[0], A.shape[1])) for A in As]
+        K.gemm_grouped([dict(a=x2, b=A, out=t, b_mn=True, alpha=scaling) for A, t in zip(As, ts)])
+        ys = [K.gemm_ex(x2, weights[i], a2=ts[i], b2=_pitch_ok(Bs[i]), b2_mn=True) for i in range(n)]
+    else:
+        ys = [K.gemm_ex(x2, weights[i]) for i in range(n)]
+    return [y.view(*x.shape[:-1], y.shape[-1]) for y in ys] + ts
+
+
+@lora_linear_multi.register_fake
+def _(x, weights, As, Bs, scaling):
+    rows = x.numel() // x.shape[-1]
+    ys = [x.new_empty((*x.shape[:-1], w.shape[0])) for w in weights]
+    return ys + [x.new_empty((rows, A.shape[1])) for A in As]
+
+
+def _llm_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    x, weights, As, Bs, scaling = inputs
+    n = len(weights)
+    ctx.n, ctx.lora = n, len(As) > 0
+    ctx.scaling = scaling
+    ctx.save_for_backward(x, *weights, *As, *Bs, *output[n:])
+
+
+def _llm_bwd(ctx, grads):
+    n = ctx.n
+    saved = ctx.saved_tensors
+    x = saved[0]
+    weights = saved[1:1 + n]
+    As = saved[1 + n:1 + 2 * n] if ctx.lora else ()
+    Bs = saved[1 + 2 * n:1 + 3 * n] if ctx.lora else ()
+    ts = saved[1 + 3 * n:1 + 4 * n] if ctx.lora else ()
+    dys = [None if g is None else _flat2d(g) for g in grads[:n]]
+    live = [i for i in range(n) if dys[i] is not None]
+    need_x = ctx.needs_input_grad[0]           # (needs_input_grad is flattened over the list arguments)
+    need_w = need_b = True
+    need_a = ctx.lora and any(A.requires_grad for A in As)
+    x2 = _flat2d(x)
+    us = {}
+    if ctx.lora and live and (need_x or need_a):
+        for i in live:
+            us[i] = dys[i].new_empty((dys[i].shape[0], Bs[i].shape[0]))
+        K.gemm_grouped([dict(a=dys[i], b=_pitch_ok(Bs[i]), out=us[i], alpha=ctx.scaling) for i in live])
+    dx = None
+    if need_x:
+        for i in live:   # dX accumulates through the residual epilogue: no separate add kernels
+            kw = dict(a2=us[i], b2=As[i]) if ctx.lora else {}
+            dx = K.gemm_ex(dys[i], weights[i], b1_mn=True, residual=dx, out=dx, **kw)
+        if dx is not None:
+            dx = dx.view(x.shape)
+    dWs = [None] * n
+    dAs = [None] * n if ctx.lora else []
+    dBs = [None] * n if ctx.lora else []
+    for i in live:
+        if ctx.lora and need_a and As[i].requires_grad:
+            dAs[i] = _weight_grad(x2, us[i], As[i])
+        if ctx.lora and need_b and Bs[i].requires_grad:
+            dBs[i] = _weight_grad(dys[i], ts[i], Bs[i], trans_out=True)
+        if need_w and weights[i].requires_grad:
+            dWs[i] = _weight_grad(dys[i], x2, weights[i])
+    return dx, dWs, dAs, dBs, None
+
+
+lora_linear_multi.register_autograd(_llm_bwd, setup_context=_llm_setup)
+
+
+def linears_of_same_input(x, modules):
+    """Apply several B200Linear / LinearWithLoRA modules to the same x; fused when they are all
+    bias-free and of the same kind, otherwise one op each."""
+    from .lora import LinearWithLoRA
+    lora = [isinstance(m, LinearWithLoRA) for m in modules]
+    bases = [m.linear if l else m for m, l in zip(modules, lora)]
+    if any(b.bias is not None for b in bases) or (any(lora) and not all(lora)):
+        return [m(x) for m in modules]
+    n = len(modules)
+    if all(lora):
+        scal = modules[0].lora.scaling
+        if any(m.lora.scaling != scal for m in modules):
+            return [m(x) for m in modules]
+        out = lora_linear_multi(x, [b.weight for b in bases], [m.lora.A for m in modules],
+                                [m.lora.B for m in modules], scal)
+    else:
+        out = lora_linear_multi(x, [b.weight for b in bases], [], [], 0.0)
+    return out[:n]
 
 
 def linear(x, weight, bias=None, residual=None):
@@ -364,51 +485,62 @@ cross_entropy.register_autograd(_ce_bwd, setup_context=_ce_setup)
 
 @torch.library.custom_op("b200llm::linear_cross_entropy", mutates_args=())
 def linear_cross_entropy(x: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
-                         targets: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
-    """loss = CE(x W^T + scaling (x A) B, targets) -> (loss fp32 [], dlogits [M, Vpad], t).
+                         targets: Tensor, capacity: int) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """loss = CE(x W^T + scaling (x A) B, targets) -> (loss fp32 [], dlogits, t, x_rows, row_index).
 
-    The logits live only in the returned work buffer, which the cross-entropy kernel overwrites
-    in place with dloss/dlogits for the backward GEMMs."""
+    The logits live only in the returned work buffer, which the cross-entropy kernel overwrites in
+    place with dloss/dlogits for the backward GEMMs. capacity > 0: only the rows whose target is not
+    ignore_index are projected (they are the only ones that reach the loss or any gradient);
+    capacity must be >= their count (otherwise the loss comes back NaN)."""
     x2 = _flat2d(x)
-    M, V = x2.shape[0], weight.shape[0]
+    V = weight.shape[0]
+    if capacity > 0 and capacity < x2.shape[0]:
+        rows, tg, idx = K.compact_gather(x2, targets, capacity)
+    else:
+        rows, tg, idx = x2, targets, x2.new_empty((0,), dtype=torch.int32)
+    M = rows.shape[0]
     ld = (V + 7) // 8 * 8
     buf = torch.empty((M, ld), device=x.device, dtype=BF16)
     if A is not None:
-        t = K.gemm_ex(x2, A, b1_mn=True, alpha=scaling)
-        K.gemm_ex(x2, weight, a2=t, b2=_pitch_ok(B), b2_mn=True, out=buf[:, :V])
+        t = K.gemm_ex(rows, A, b1_mn=True, alpha=scaling)
+        K.gemm_ex(rows, weight, a2=t, b2=_pitch_ok(B), b2_mn=True, out=buf[:, :V])
     else:
         t = x2.new_empty((0,))
-        K.gemm_ex(x2, weight, out=buf[:, :V])
-    loss = K.cross_entropy_(buf[:, :V], targets)
-    return loss.reshape(()), buf, t
+        K.gemm_ex(rows, weight, out=buf[:, :V])
+    loss = K.cross_entropy_(buf[:, :V], tg)
+    return loss.reshape(()), buf, t, (rows if idx.numel() else x2.new_empty((0,))), idx
 
 
 @linear_cross_entropy.register_fake
-def _(x, weight, A, B, scaling, targets):
+def _(x, weight, A, B, scaling, targets, capacity):
     M, V = x.numel() // x.shape[-1], weight.shape[0]
-    t = x.new_empty((M, A.shape[1])) if A is not None else x.new_empty((0,))
-    return x.new_empty((), dtype=torch.float32), x.new_empty((M, (V + 7) // 8 * 8)), t
+    compact = 0 < capacity < M
+    R = capacity if compact else M
+    t = x.new_empty((R, A.shape[1])) if A is not None else x.new_empty((0,))
+    rows = x.new_empty((R, x.shape[-1])) if compact else x.new_empty((0,))
+    idx = x.new_empty((R if compact else 0,), dtype=torch.int32)
+    return x.new_empty((), dtype=torch.float32), x.new_empty((R, (V + 7) // 8 * 8)), t, rows, idx
 
 
 def _lce_setup(ctx, inputs, output):
     ctx.set_materialize_grads(False)
-    x, weight, A, B, scaling, targets = inputs
-    _, buf, t = output
-    ctx.save_for_backward(x, weight, A, B, t, buf)
+    x, weight, A, B, scaling, targets, capacity = inputs
+    _, buf, t, rows, idx = output
+    ctx.save_for_backward(x, weight, A, B, t, buf, rows, idx)
     ctx.scaling = scaling
 
 
-def _lce_bwd(ctx, dloss, _dbuf, _dt):
-    """Assumes dloss == 1 (loss.backward() on the scalar loss, as train.py:112 does); a different
-    upstream factor is applied to the (small) outputs rather than to the [M, V] buffer."""
+def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
+    """Assumes dloss == 1 (loss.backward() on the scalar loss, as train.py:112 does)."""
     if dloss is None:
-        return (None,) * 6
-    x, weight, A, B, t, buf = ctx.saved_tensors
+        return (None,) * 7
+    x, weight, A, B, t, buf, rows, idx = ctx.saved_tensors
     wref, aref, bref = weight, A, B
     need = ctx.needs_input_grad
     V = weight.shape[0]
     dl = buf[:, :V]
-    x2 = _flat2d(x)
+    compact = idx.numel() > 0
+    x2 = rows if compact else _flat2d(x)
     dx = dW = dA = dB = None
     u = None
     if A is not None and (need[0] or need[2]):
@@ -418,6 +550,8 @@ def _lce_bwd(ctx, dloss, _dbuf, _dt):
             dx2 = K.gemm_ex(dl, weight, b1_mn=True, a2=u, b2=A)
         else:
             dx2 = K.gemm_ex(dl, weight, b1_mn=True)
+        if compact:
+            dx2 = K.scatter_rows(dx2, idx, x.numel() // x.shape[-1])
         dx = dx2.view(x.shape)
     if A is not None and need[2]:
         dA = _weight_grad(x2, u, aref)
@@ -425,7 +559,7 @@ def _lce_bwd(ctx, dloss, _dbuf, _dt):
         dB = _weight_grad(dl, t, bref, trans_out=True)
     if need[1]:
         dW = _weight_grad(dl, x2, wref)
-    return dx, dW, dA, dB, None, None
+    return dx, dW, dA, dB, None, None, None
 
 
 linear_cross_entropy.register_autograd(_lce_bwd, setup_context=_lce_setup)

@@ -63,9 +63,13 @@ class B200AdamW(torch.optim.Optimizer):
     # ------------------------------------------------------------------
     @property
     def flat_grads(self):
+        from . import ops
+        ops.flush_weight_grads()          # queued weight-gradient GEMMs must land before anyone reads main_grad
         return [g["g"] for g in self._groups.values()]
 
     def zero_grad(self, set_to_none: bool = True):
+        from . import ops
+        ops.flush_weight_grads()
         for g in self._groups.values():
             g["g"].zero_()
         for p in self._trainable:
@@ -80,6 +84,8 @@ class B200AdamW(torch.optim.Optimizer):
 
     def grad_norm(self, max_norm: float):
         """Global L2 norm over every gradient -> device tensor [norm, clip_coef]."""
+        from . import ops
+        ops.flush_weight_grads()
         groups = list(self._groups.values())
         if len(groups) == 1:
             return K.grad_norm(groups[0]["g"], max_norm, out=self._norm_out, ws=self._ws)
@@ -92,6 +98,8 @@ class B200AdamW(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None):
         assert closure is None
+        from . import ops
+        ops.flush_weight_grads()
         self._absorb_autograd_grads()
         self._step += 1
         scale = None

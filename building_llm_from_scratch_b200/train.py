@@ -56,15 +56,27 @@ class Trainer:
 
     # train.py:88-92
     def calc_loss_batch(self, input_batch, target_batch):
+        target_batch_host = target_batch if not target_batch.is_cuda else None
         input_batch = input_batch.to(self.device, non_blocking=True)
         target_batch = target_batch.to(self.device, non_blocking=True)
         core = self.model.module if isinstance(self.model, B200DDP) else self.model
         if core.training and hasattr(core, "forward_loss"):
-            loss = core.forward_loss(input_batch, target_batch)
+            loss = core.forward_loss(input_batch, target_batch, capacity=self._head_capacity(target_batch_host))
         else:
             logits = self.model(input_batch)
             loss = ops.cross_entropy(logits, target_batch)[0]
         return loss.to(torch.bfloat16) if self._loss_bf16(core) else loss
+
+    @staticmethod
+    def _head_capacity(targets_host, granule=128):
+        """Rows the vocab projection has to see: the non-ignored targets (counted on the host copy of
+        the batch, no device sync), rounded up; 0 = all rows (targets already on the device)."""
+        if targets_host is None:
+            return 0
+        n = int((targets_host != -100).sum())
+        if n == 0 or n >= targets_host.numel():
+            return 0
+        return (n + granule - 1) // granule * granule
 
     @staticmethod
     def _loss_bf16(core):

@@ -70,6 +70,21 @@ int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  int64_t ldc, int64_t M, int64_t N, int flags, int out_f32, int accumulate,
                  int trans_out, float alpha, int splitk, void* stream);
 
+/* Grouped launch of up to B200_GEMM_GROUP_MAX independent skinny GEMMs (every N <= 64, one
+ * operand pair each; same operand conventions as b200_gemm_ex) in ONE persistent kernel. Used
+ * for the LoRA weight gradients dA = x^T u, dB = (dY^T t)^T of several linears at once
+ * (lora.py:26 under autograd) and for the rank-r projections t = x A of linears that share x. */
+#define B200_GEMM_GROUP_MAX 16
+typedef struct {
+  const void* A; int64_t lda; int a_mn;
+  const void* B; int64_t ldb; int b_mn;
+  void* C; int64_t ldc;
+  int64_t M, N, K;
+  int out_f32, accumulate, trans_out;
+  float alpha;
+} b200_gemm_problem;
+int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs, void* stream);
+
 /* General bf16 GEMM with operand layouts, C[M,N] (+)= op(A)·op(B):
  *   transa = 0: A is [M,K] (K contiguous);  1: A is stored [K,M] (M contiguous)
  *   transb = 0: B is [N,K] (K contiguous);  1: B is stored [K,N] (N contiguous)
@@ -147,6 +162,21 @@ size_t b200_cross_entropy_workspace_bytes(int64_t M);
 int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets, float* loss_out,
                             int64_t M, int64_t V, int write_grad, void* workspace,
                             size_t workspace_bytes, void* stream);
+
+/* Row compaction in front of the vocab projection: rows whose target is ignore_index (-100)
+ * contribute nothing to the mean loss of train.py:91 nor to any gradient, so the projection and
+ * the cross-entropy only have to see the others. b200_compact_rows lists the non-ignored rows
+ * (idx[capacity], -1 padded; meta[0] = their count, meta[1] = 1 if count > capacity),
+ * b200_gather_rows_bf16 builds the compact activation / target arrays (an overflowing compaction
+ * is turned into a NaN loss downstream rather than silently dropping rows), and
+ * b200_scatter_rows_bf16 puts the compact input gradient back (caller zeroes dst first). */
+int b200_compact_rows(const int64_t* targets, int64_t M, int64_t capacity, int32_t* idx, int32_t* meta,
+                      void* stream);
+int b200_gather_rows_bf16(const void* x, int64_t ldx, const int64_t* targets, const int32_t* idx,
+                          const int32_t* meta, void* out, int64_t* targets_out, int64_t capacity,
+                          int64_t d, void* stream);
+int b200_scatter_rows_bf16(const void* src, const int32_t* idx, void* dst, int64_t ldd, int64_t capacity,
+                           int64_t d, void* stream);
 
 /* Cross-entropy for callers that cannot give the library a workspace. (No counterpart in the
  * reference: it exists for hosts whose device memory is fully planned ahead — every byte of HBM

@@ -96,3 +96,26 @@ def test_gemm_rejects_cpu_and_bad_args(K):
     from building_llm_from_scratch_b200 import _lib
     with pytest.raises(_lib.B200Error):
         K.gemm_ex(rnd(16, 12), rnd(16, 12))   # K = 12 breaks the 16-byte row pitch TMA needs
+
+
+def test_gemm_grouped_matches_individual_launches(K):
+    """Several LoRA weight-gradient problems of different sizes in one grouped launch."""
+    Mtok = 2048
+    probs, refs = [], []
+    for i, (d_in, d_out) in enumerate([(512, 768), (256, 2048), (1024, 264), (2048, 512)]):
+        x, u = rnd(Mtok, d_in, seed=10 + i), rnd(Mtok, 64, scale=0.1, seed=20 + i)
+        dY, t = rnd(Mtok, d_out, scale=0.1, seed=30 + i), rnd(Mtok, 64, seed=40 + i)
+        dA = torch.full((d_in, 64), 0.5, device="cuda", dtype=torch.float32)
+        dB = torch.zeros(64, d_out, device="cuda", dtype=torch.float32)
+        probs.append(dict(a=x, b=u, out=dA, a_mn=True, b_mn=True, accumulate=True))
+        probs.append(dict(a=dY, b=t, out=dB, a_mn=True, b_mn=True, accumulate=True, trans_out=True))
+        refs.append((dA, 0.5 + x.float().t() @ u.float()))
+        refs.append((dB, t.float().t() @ dY.float()))
+    # plus a plain bf16 (non-accumulating) rank-r projection t = x A, A read as an MN-major operand
+    x, A = rnd(Mtok, 512, seed=50), rnd(512, 64, scale=0.1, seed=51)
+    tt = torch.empty(Mtok, 64, device="cuda", dtype=torch.bfloat16)
+    probs.append(dict(a=x, b=A, out=tt, b_mn=True, alpha=0.5))
+    refs.append((tt, 0.5 * x.float() @ A.float()))
+    K.gemm_grouped(probs)
+    for got, ref in refs:
+        assert rel_err(got.float(), ref) < (1e-3 if got.dtype == torch.float32 else BF16_TOL)

@@ -97,6 +97,8 @@ def test_llama3_lora_model_against_reference_fixture(golden, fused_opt):
         opt.zero_grad()
     loss = model.forward_loss(x, y)
     loss.backward()
+    from building_llm_from_scratch_b200 import ops as _ops
+    _ops.flush_weight_grads()      # weight-gradient GEMMs into main_grad are queued and grouped
     assert rel_err(loss.cpu(), g["loss"].float()) < BF16_TOL
     named = dict(model.named_parameters())
     assert set(g["grads"]) == {k for k, p in named.items() if p.requires_grad}
@@ -173,3 +175,27 @@ def test_ops_reject_cpu_tensors():
     from building_llm_from_scratch_b200 import ops
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.rmsnorm(torch.zeros(4, 64, dtype=torch.bfloat16), torch.ones(64), 1e-5)
+
+
+def test_row_compacted_vocab_projection_is_exact(golden):
+    """Projecting only the non-ignored target rows gives the same loss and the same gradients."""
+    from building_llm_from_scratch_b200 import ops
+    g = golden("llama_model.pt")
+    x, y = g["x"].cuda(), g["y"].cuda()
+    n_valid = int((g["y"] != -100).sum())
+    assert 0 < n_valid < y.numel()
+    results = []
+    for cap in (0, (n_valid + 15) // 16 * 16):
+        model, _ = build_llama(g, False)
+        loss = model.forward_loss(x, y, capacity=cap)
+        loss.backward()
+        results.append((loss.detach().clone(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}))
+    (l0, g0), (l1, g1) = results
+    assert rel_err(l1, l0) < 1e-5
+    assert set(g0) == set(g1)
+    for k in g0:
+        assert close(g1[k].float(), g0[k].float(), 2e-3, atol=1e-6), (k, rel_err(g1[k].float(), g0[k].float()))
+    # an undersized capacity must not silently drop rows: the loss turns into NaN
+    model, _ = build_llama(g, False)
+    bad = model.forward_loss(x, y, capacity=16)
+    assert torch.isnan(bad)
