@@ -8,20 +8,20 @@
 //   warps 2..5  : softmax — one thread per query row (TMEM lane), so row max / row sum need no
 //                 shuffles: tcgen05.ld S, exp2 online softmax, P -> bf16 into 128B-swizzled smem,
 //                 rescale O in TMEM (tcgen05.ld/st) only when a row maximum moved, final O / l.
-// 96 KB smem and 256 TMEM columns per CTA -> two CTAs per SM, so one CTA's softmax overlaps the
-// other's MMAs. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
+// 65 KB smem and 128 TMEM columns per CTA -> three CTAs per SM, so one CTA's softmax overlaps the
+// others' MMAs and barrier / TMEM-load latencies. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
 //
 // Roofline: tensor pipe / MUFU (head_dim 64: 8192 exp2 per 128x64 tile vs 256 MMA cycles).
 #include "common.cuh"
 
 namespace {
 
-constexpr int BQ = 128, BKV = 64, HD = 64, NS = 3;
+constexpr int BQ = 128, BKV = 64, HD = 64, NS = 2;
 constexpr int Q_BYTES = BQ * HD * 2;     // 16 KB
 constexpr int KV_BYTES = BKV * HD * 2;   // 8 KB
 constexpr int P_BYTES = BQ * BKV * 2;    // 16 KB
-constexpr int FWD_SMEM = Q_BYTES + NS * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;
-constexpr uint32_t TMEM_COLS = 256;      // S0 [0,64) S1 [64,128) O [128,192)
+constexpr int FWD_SMEM = Q_BYTES + NS * 2 * KV_BYTES + P_BYTES + 1024 + 256;
+constexpr uint32_t TMEM_COLS = 128;      // S [0,64)  O [64,128)
 constexpr float LOG2E = 1.4426950408889634f;
 
 struct FwdParams {
@@ -32,7 +32,7 @@ struct FwdParams {
   float* lse;
 };
 
-__global__ void __launch_bounds__(192, 2)
+__global__ void __launch_bounds__(192, 3)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -41,15 +41,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint8_t* sK = sQ + Q_BYTES;
   uint8_t* sV = sK + NS * KV_BYTES;
   uint8_t* sP = sV + NS * KV_BYTES;
-  uint64_t* bars = (uint64_t*)(sP + 2 * P_BYTES);
+  uint64_t* bars = (uint64_t*)(sP + P_BYTES);
   uint64_t* q_full = bars;            // 1
   uint64_t* k_full = bars + 1;        // NS
   uint64_t* v_full = k_full + NS;     // NS
   uint64_t* kv_empty = v_full + NS;   // NS
-  uint64_t* s_full = kv_empty + NS;   // 2
-  uint64_t* s_empty = s_full + 2;     // 2
-  uint64_t* p_full = s_empty + 2;     // 2
-  uint64_t* o_done = p_full + 2;      // 1
+  uint64_t* s_full = kv_empty + NS;   // 1
+  uint64_t* s_empty = s_full + 1;     // 1 (4 arrivals)
+  uint64_t* p_full = s_empty + 1;     // 1 (4 arrivals)
+  uint64_t* o_done = p_full + 1;      // 1
   uint32_t* tmem_slot = (uint32_t*)(o_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -70,11 +70,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_init(&v_full[i], 1);
       mbar_init(&kv_empty[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], 4);
-      mbar_init(&p_full[i], 4);
-    }
+    mbar_init(s_full, 1);
+    mbar_init(s_empty, 4);
+    mbar_init(p_full, 4);
     mbar_init(o_done, 1);
     mbar_fence_init();
   }
@@ -109,29 +107,28 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t aQ = smem_u32(sQ);
       mbar_wait(q_full, 0);
       auto issue_s = [&](int j) {
-        const int s = j % NS, buf = j & 1, use = j >> 1;
+        const int s = j % NS;
         mbar_wait(&k_full[s], (j / NS) & 1);
-        if (use > 0) mbar_wait(&s_empty[buf], (use - 1) & 1);
+        if (j > 0) mbar_wait(s_empty, (j - 1) & 1);     // softmax threads hold S_{j-1} in registers
         tc_fence_after();
         const uint32_t aK = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + buf * BKV, umma_desc_k128(aQ + k * 32), umma_desc_k128(aK + k * 32),
-                       idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(&s_full[buf]);
+          umma_bf16_ss(tmem_base, umma_desc_k128(aQ + k * 32), umma_desc_k128(aK + k * 32), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(s_full);
       };
       issue_s(0);
       for (int j = 0; j < n_kv; ++j) {
         if (j + 1 < n_kv) issue_s(j + 1);
-        const int s = j % NS, buf = j & 1;
+        const int s = j % NS;
         mbar_wait(&v_full[s], (j / NS) & 1);
-        mbar_wait(&p_full[buf], (j >> 1) & 1);
+        mbar_wait(p_full, j & 1);
         tc_fence_after();
-        const uint32_t aP = smem_u32(sP + buf * P_BYTES);
+        const uint32_t aP = smem_u32(sP);
         const uint32_t aV = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16_ss(tmem_base + 128, umma_desc_k128(aP + k * 32), umma_desc_mn128(aV + k * 2048, 8192),
+          umma_bf16_ss(tmem_base + 64, umma_desc_k128(aP + k * 32), umma_desc_mn128(aV + k * 2048, 8192),
                        idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
         umma_commit(&kv_empty[s]);
         umma_commit(o_done);
@@ -144,16 +141,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     float m = -INFINITY, l = 0.f;
     for (int j = 0; j < n_kv; ++j) {
-      const int buf = j & 1;
-      mbar_wait(&s_full[buf], (j >> 1) & 1);
+      mbar_wait(s_full, j & 1);
       tc_fence_after();
       uint32_t r[64];
-      tmem_ld_32x32(tlane + buf * BKV, r);
-      tmem_ld_32x32(tlane + buf * BKV + 32, r + 32);
+      tmem_ld_32x32(tlane, r);
+      tmem_ld_32x32(tlane + 32, r + 32);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&s_empty[buf]);
+      if (lane == 0) mbar_arrive(s_empty);
 
       const int kv0 = j * BKV;
       const bool diag = kv0 + BKV - 1 > q0 + quad * 32;  // warp-uniform
@@ -178,31 +174,32 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       l = l * alpha + sum;
       m = m_new;
+      // the single P buffer and the O accumulator are free once PV_{j-1} has retired
+      if (j > 0) {
+        mbar_wait(o_done, (j - 1) & 1);
+        tc_fence_after();
+      }
       // P row -> smem, K-major 128B-swizzled (16-byte chunk index XOR row % 8)
-      const uint32_t prow = smem_u32(sP) + buf * P_BYTES + row * 128;
+      const uint32_t prow = smem_u32(sP) + row * 128;
 #pragma unroll
       for (int c = 0; c < 8; ++c)
         sts_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       fence_proxy_async_smem();
-      if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);
-        tc_fence_after();
-        if (!__all_sync(0xffffffffu, alpha == 1.f)) {
-          uint32_t o[32];
+      if (j > 0 && !__all_sync(0xffffffffu, alpha == 1.f)) {
+        uint32_t o[32];
 #pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-            tmem_ld_32x32(tlane + 128 + h2 * 32, o);
-            tmem_ld_wait();
+        for (int h2 = 0; h2 < 2; ++h2) {
+          tmem_ld_32x32(tlane + 64 + h2 * 32, o);
+          tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st_32x32(tlane + 128 + h2 * 32, o);
-          }
-          tmem_st_wait();
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32(tlane + 64 + h2 * 32, o);
         }
+        tmem_st_wait();
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[buf]);
+      if (lane == 0) mbar_arrive(p_full);
     }
     mbar_wait(o_done, (n_kv - 1) & 1);
     tc_fence_after();
@@ -212,7 +209,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
     for (int h2 = 0; h2 < 2; ++h2) {
       uint32_t o[32];
-      tmem_ld_32x32(tlane + 128 + h2 * 32, o);
+      tmem_ld_32x32(tlane + 64 + h2 * 32, o);
       tmem_ld_wait();
       if (t < p.T) {
 #pragma unroll

@@ -56,6 +56,13 @@ int b200_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, ui
                            uint64_t ld, uint32_t box_rows, uint32_t box_cols) {
   int rc = ensure_driver();
   if (rc) return rc;
+  // cuTensorMapEncodeTiled is a driver-API call: it needs the primary context bound to THIS thread.
+  // Autograd worker threads may reach a GEMM before any runtime-API call has done that for them.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    B200_CHECK_CUDA(cudaFree(nullptr));
+    ctx_bound = true;
+  }
   if ((((uintptr_t)base) & 15u) != 0 || (ld * 2) % 16 != 0)
     return b200_set_error(B200_ERR_ARG, "TMA operand needs 16-B aligned base and row pitch");
   cuuint64_t gdim[2] = {cols, rows};

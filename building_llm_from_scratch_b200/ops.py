@@ -161,8 +161,7 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
     """param-shaped gradient = a_mn_src^T · b_mn_src (both stored [tokens, *])."""
     mg = getattr(param, "main_grad", None)
     if mg is not None:
-        n_cols = a_mn_src.shape[1] if trans_out else b_mn_src.shape[1]
-        if n_cols <= 64 and b_mn_src.shape[1] <= 64:
+        if b_mn_src.shape[1] <= 64:      # GEMM N = width of the second operand (the LoRA rank)
             _wgrad_queue.append(dict(a=a_mn_src, b=b_mn_src, out=mg, a_mn=True, b_mn=True, accumulate=True,
                                      trans_out=trans_out))
             if len(_wgrad_queue) >= WGRAD_FLUSH_AT:

@@ -26,6 +26,7 @@ def main():
     x, y = alpaca_batch(torch.Generator().manual_seed(1234), bench.MICRO_BATCH, bench.SEQ_LEN, cfg["vocab_size"])
     step = TrainStep(tr, (bench.MICRO_BATCH, bench.SEQ_LEN), use_graph=False)
     step.x.copy_(x.to(dev)); step.y.copy_(y.to(dev))
+    step._graphs_for(int((y != -100).sum()))     # row-compacted vocab projection, like bench.py
     step._refresh_hyper(peek=True)
     for _ in range(2):
         step._eager_step()
