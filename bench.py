@@ -59,6 +59,10 @@ def flops_per_token(cfg, rank, seq_len):
     return 4 * p_lin + 6 * p_lora + attn
 
 
+def attn_flops_per_token(cfg, seq_len):
+    return 0.5 * (4 + 8) * seq_len * cfg["emb_dim"] * cfg["n_layers"]
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -335,7 +339,11 @@ def main():
                 "gemm_launches_per_step": n_gemm, "gemm_ms_per_step": ms_gemm,
                 "gemm_share_of_step": ms_gemm / (ms_dev / args.steps),
                 "step_frac_of_burst_peak": value / world * fpt / 1e12 / peaks["tf_burst"],
-                "algorithmic_gflops_per_token": fpt / 1e9}
+                "algorithmic_gflops_per_token": fpt / 1e9,
+                # FLOPs the kernels really executed (LoRA K-padding included, ignored-target rows of the
+                # vocab projection excluded when it is row-compacted) + causal attention
+                "executed_gflops_per_token": (flops / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e9,
+                "step_frac_of_burst_peak_executed": value / world * (flops / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e12 / peaks["tf_burst"]}
     if world > 1:
         dist.barrier()
 
