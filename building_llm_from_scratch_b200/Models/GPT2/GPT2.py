@@ -2,8 +2,9 @@
 
 Deviations (documented in DESIGN.md): the per-forward debug print (GPT2.py:123) is dropped; the
 modules compute in bf16 (the GPU configs of BASELINE.json; the reference's GPT-2 ignores
-cfg["dtype"]); dropout sites keep their nn.Dropout modules (identity at
-drop_rate 0, which is what parity runs use — SURVEY.md H5)."""
+cfg["dtype"]); dropout (embedding, residual and attention-weight sites) uses the
+b200llm counter-based masks, so it is statistically but not bit-wise the reference's Philox stream
+(per-op parity runs use drop_rate 0)."""
 from __future__ import annotations
 
 import torch
@@ -17,6 +18,15 @@ from ...lora import B200Linear, head_operands
 class B200LayerNorm(nn.LayerNorm):
     def forward(self, x):
         return ops.layernorm(x, self.weight, self.bias, self.eps)[0]
+
+
+class B200Dropout(nn.Dropout):
+    """nn.Dropout whose training-mode forward is the counter-based b200llm dropout kernel."""
+
+    def forward(self, x, residual=None):
+        if self.training and self.p > 0:
+            return ops.dropout(x, residual, self.p, ops.new_seed())
+        return x if residual is None else x + residual
 
 
 class GELU(nn.GELU):
@@ -38,7 +48,7 @@ class MultiHeadAttention(nn.Module):
         self.W_key = B200Linear(d_in, d_out, bias=qkv_bias)
         self.W_value = B200Linear(d_in, d_out, bias=qkv_bias)
         self.out_proj = B200Linear(d_out, d_out)
-        self.dropout = nn.Dropout(dropout)
+        self.dropout = B200Dropout(dropout)   # applied to the attention weights inside the fused kernel
         self.register_buffer("mask", torch.empty(0), persistent=False)  # see Llama3.GroupedQueryAttention
 
     def _save_to_state_dict(self, destination, prefix, keep_vars):
@@ -51,12 +61,12 @@ class MultiHeadAttention(nn.Module):
         super()._load_from_state_dict(state_dict, prefix, *args)
 
     def forward(self, x, residual=None):
-        if self.training and self.dropout.p > 0:
-            raise NotImplementedError("attention-weight dropout (GPT2.py:43) is not fused yet: use drop_rate=0.0")
         b, num_tokens, _ = x.shape
+        p_drop = self.dropout.p if self.training else 0.0
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
-        ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)[0]
+        ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim,
+                            p_drop, ops.new_seed() if p_drop > 0 else 0)[0]
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 
 
@@ -83,12 +93,12 @@ class TransformerBlock(nn.Module):
         self.ff = FeedForward(cfg)
         self.norm1 = B200LayerNorm(cfg["emb_dim"])
         self.norm2 = B200LayerNorm(cfg["emb_dim"])
-        self.dropout = nn.Dropout(cfg["drop_rate"])
+        self.dropout = B200Dropout(cfg["drop_rate"])
 
     def forward(self, x):
         if self.training and self.dropout.p > 0:
-            x = x + self.dropout(self.att(self.norm1(x)))
-            return x + self.dropout(self.ff(self.norm2(x)))
+            x = self.dropout(self.att(self.norm1(x)), residual=x)      # x + dropout(att(...)), GPT2.py:85
+            return self.dropout(self.ff(self.norm2(x)), residual=x)    # x + dropout(ff(...)),  GPT2.py:87
         x = self.att(self.norm1(x), residual=x)
         return self.ff(self.norm2(x), residual=x)
 
@@ -102,7 +112,7 @@ class GPTModel(nn.Module):
         self.use_actv_ckpt = use_actv_ckpt
         self.tok_emb = nn.Embedding(cfg["vocab_size"], cfg["emb_dim"])
         self.pos_emb = nn.Embedding(cfg["context_length"], cfg["emb_dim"])
-        self.drop_emb = nn.Dropout(cfg["drop_rate"])
+        self.drop_emb = B200Dropout(cfg["drop_rate"])
         self.blocks = nn.Sequential(*[TransformerBlock(cfg) for _ in range(cfg["n_layers"])])
         self.norm = B200LayerNorm(cfg["emb_dim"])
         self.output_head = B200Linear(cfg["emb_dim"], cfg["vocab_size"], bias=False)

@@ -18,14 +18,15 @@
 // tcgen05 paths (attention_tc.cu), head_dim 64
 int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, float scale, cudaStream_t st);
+                            int64_t h, int64_t hkv, float scale, float dropout_p, uint64_t seed,
+                            cudaStream_t st);
 
 size_t b200_attention_bwd_tc64_workspace(int64_t B, int64_t T, int64_t h);
 int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
                             const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                             int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                            int64_t hkv, float scale, cudaStream_t st);
+                            int64_t hkv, float scale, float dropout_p, uint64_t seed, cudaStream_t st);
 
 static bool attn_legacy() {
   static int v = -1;
@@ -548,14 +549,16 @@ int check_common(const void* q, const void* k, const void* v, int64_t B, int64_t
 extern "C" int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk,
                                        const void* v, int64_t ldv, void* o, int64_t ldo, float* lse,
                                        int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd,
-                                       float scale, void* stream) {
+                                       float scale, float dropout_p, uint64_t seed, void* stream) {
   const int64_t lds[4] = {ldq, ldk, ldv, ldo};
   int rc = check_common(q, k, v, B, T, h, hkv, hd, lds, 4);
   if (rc) return rc;
   B200_CHECK_ARG(o && lse, "attention_fwd: null output");
   cudaStream_t st = (cudaStream_t)stream;
+  B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
   if (hd == 64 && !attn_legacy())
-    return b200_attention_fwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, st);
+    return b200_attention_fwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
+  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the head_dim-64 tcgen05 path");
   dim3 grid((unsigned)((T + 127) / 128), (unsigned)h, (unsigned)B);
   static bool f64[64] = {false}, f128[64] = {false};
   int dev = 0;
@@ -585,7 +588,7 @@ extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k
                                        void* workspace, size_t workspace_bytes, void* dq,
                                        int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
                                        int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd,
-                                       float scale, void* stream) {
+                                       float scale, float dropout_p, uint64_t seed, void* stream) {
   float* delta = (float*)workspace;
   const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
   int rc = check_common(q, k, v, B, T, h, hkv, hd, lds, 8);
@@ -593,9 +596,11 @@ extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k
   B200_CHECK_ARG(o && dout && lse && delta && dq && dk && dv, "attention_bwd: null pointer");
   B200_CHECK_ARG(workspace_bytes >= b200_attention_bwd_workspace_bytes(B, T, h, hd), "attention_bwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
+  B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
   if (hd == 64 && !attn_legacy())
     return b200_attention_bwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk,
-                                   lddk, dv, lddv, B, T, h, hkv, scale, st);
+                                   lddk, dv, lddv, B, T, h, hkv, scale, dropout_p, seed, st);
+  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the head_dim-64 tcgen05 path");
   {
     const long long total = B * T * h;
     long long blocks = (total + 7) / 8;

@@ -24,8 +24,17 @@ constexpr int FWD_SMEM = Q_BYTES + NS * 2 * KV_BYTES + P_BYTES + 1024 + 256;
 constexpr uint32_t TMEM_COLS = 128;      // S [0,64)  O [64,128)
 constexpr float LOG2E = 1.4426950408889634f;
 
+// attention-weight dropout (Models/GPT2/GPT2.py:43): keep flag of score (b, h, q, k) =
+// dropout_keep2(((b*H + h)*T + q) * ceil(T/2) + k/2) half k&1; drop_thr16 == 0 disables it.
+struct DropParams {
+  uint32_t thr16;
+  float inv_keep;
+  unsigned long long seed;
+};
+
 struct FwdParams {
   int B, T, H, HKV, nqt;
+  DropParams drop;
   float scale_log2;
   bf16* o;
   long long ldo;
@@ -140,6 +149,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int row = quad * 32 + lane;
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     float m = -INFINITY, l = 0.f;
+    const unsigned long long drop_row =
+        (((unsigned long long)b * p.H + head) * p.T + (unsigned long long)(q0 + row)) * (unsigned long long)((p.T + 1) >> 1);
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
@@ -167,9 +178,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float p0 = fast_exp2(__uint_as_float(r[2 * i]) - m_new);
-        const float p1 = fast_exp2(__uint_as_float(r[2 * i + 1]) - m_new);
-        sum += p0 + p1;
+        float p0 = fast_exp2(__uint_as_float(r[2 * i]) - m_new);
+        float p1 = fast_exp2(__uint_as_float(r[2 * i + 1]) - m_new);
+        sum += p0 + p1;                       // the softmax denominator is taken before dropout
+        if (p.drop.thr16) {
+          bool k0, k1;
+          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, k0, k1);
+          p0 = k0 ? p0 * p.drop.inv_keep : 0.f;
+          p1 = k1 ? p1 * p.drop.inv_keep : 0.f;
+        }
         pk[i] = f2_to_bf2(p0, p1);
       }
       l = l * alpha + sum;
@@ -234,10 +251,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
 }  // namespace
 
+static DropParams make_drop(float p, uint64_t seed) {
+  DropParams d;
+  const float t = p * 65536.f + 0.5f;
+  d.thr16 = p <= 0.f ? 0u : (t > 65535.f ? 65535u : (uint32_t)t);
+  d.inv_keep = 1.f / (1.f - p);
+  d.seed = (unsigned long long)seed;
+  return d;
+}
+
 // Returns 0 on success; called by b200_attention_fwd_bf16 for head_dim 64.
 int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, float scale, cudaStream_t st) {
+                            int64_t h, int64_t hkv, float scale, float dropout_p, uint64_t seed,
+                            cudaStream_t st) {
   CUtensorMap mq, mk, mv;
   int rc;
   if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)(B * T), (uint64_t)(h * HD), (uint64_t)ldq, BQ, HD))) return rc;
@@ -254,6 +281,7 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
   p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
   p.nqt = (int)((T + BQ - 1) / BQ);
   p.scale_log2 = scale * LOG2E;
+  p.drop = make_drop(dropout_p, seed);
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
@@ -290,6 +318,7 @@ constexpr int BWD_SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 4 * PANEL_BYTES + 
 
 struct BwdParams {
   int B, T, H, HKV, nkt, nq64;
+  DropParams drop;
   float scale, scale_log2;
   const float* ld2;   // [B, H, nq64, 2, 64]: lse * log2e (inf beyond T) and delta (0 beyond T)
   bf16* dk;
@@ -440,6 +469,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     for (int s = grp; s < steps; s += 2) {
       const int stg = s % NSTG;
       const int qrow0 = q64 * QS;
+      const unsigned long long drop_bh = (unsigned long long)b * p.H + (unsigned long long)(kvh * G + s / spp);
       q64 += 2;
       while (q64 >= p.nq64) q64 -= spp;
       mbar_wait(&qdo_full[stg], (s / NSTG) & 1);      // lse/delta travelled with this stage
@@ -474,8 +504,18 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             const int c = i4 * 4 + e;
             float pr = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -ls[e]));
             if (diag && key > qrow0 + hf * 32 + c) pr = 0.f;
-            pv[e] = pr;
-            dsv[e] = pr * (__uint_as_float(dv[c]) - ds[e]) * p.scale;
+            float dpv = __uint_as_float(dv[c]);
+            float pdrop = pr;
+            if (p.drop.thr16) {
+              const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c);
+              const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
+                                               ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
+                                           p.drop.seed, p.drop.thr16);
+              dpv = kp ? dpv * p.drop.inv_keep : 0.f;
+              pdrop = kp ? pr * p.drop.inv_keep : 0.f;
+            }
+            pv[e] = pdrop;                                  // dV uses the dropped, rescaled P
+            dsv[e] = pr * (dpv - ds[e]) * p.scale;
           }
           pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
           pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
@@ -537,6 +577,7 @@ constexpr int DQ_SMEM = 2 * Q_BYTES + DQ_NS * 2 * KV_BYTES + 2 * P_BYTES + 1024 
 
 struct DqParams {
   int B, T, H, HKV, nqt;
+  DropParams drop;
   float scale, scale_log2;
   const float* ld2;   // [B, H, nq64, 2, 64]
   int nq64;
@@ -659,6 +700,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const float* ldrow = p.ld2 + (((long long)b * p.H + head) * p.nq64 + (t >> 6)) * (2 * QS) + (t & 63);
     const float lse2 = ldrow[0];     // already * log2e, +inf for padding rows
     const float dl = ldrow[QS];
+    const unsigned long long drop_row =
+        (((unsigned long long)b * p.H + head) * p.T + (unsigned long long)t) * (unsigned long long)((p.T + 1) >> 1);
     for (int j = 0; j < n_kv; ++j) {
       const int buf = j & 1;
       mbar_wait(s_full, j & 1);
@@ -678,12 +721,17 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         float v2[2];
+        bool keep[2] = {true, true};
+        if (p.drop.thr16)
+          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, keep[0], keep[1]);
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int c = 2 * i + e;
           float pr = fast_exp2(fmaf(__uint_as_float(s[c]), p.scale_log2, -lse2));
           if (diag && kv0 + c > t) pr = 0.f;
-          v2[e] = pr * (__uint_as_float(d[c]) - dl) * p.scale;
+          float dpv = __uint_as_float(d[c]);
+          if (p.drop.thr16) dpv = keep[e] ? dpv * p.drop.inv_keep : 0.f;
+          v2[e] = pr * (dpv - dl) * p.scale;
         }
         pk[i] = f2_to_bf2(v2[0], v2[1]);
       }
@@ -773,7 +821,7 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
                             int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
                             const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                             int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                            int64_t hkv, float scale, cudaStream_t st) {
+                            int64_t hkv, float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
   float* ld2 = (float*)workspace;   // cudaMalloc / caching-allocator memory: at least 256-B aligned
   B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
   const long long rows = B * T;
@@ -807,7 +855,9 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     DqParams p;
     p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv; p.nqt = nqt;
     p.scale = scale; p.scale_log2 = scale * LOG2E;
+    p.drop = make_drop(dropout_p, seed);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
+    p.drop = make_drop(dropout_p, seed);
     const long long grid = (long long)nqt * B * h;
     attn_bwd_dq_tc_kernel<<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
@@ -820,6 +870,7 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
     p.nkt = nqt; p.nq64 = nq64;
     p.scale = scale; p.scale_log2 = scale * LOG2E;
+    p.drop = make_drop(dropout_p, seed);
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     const long long grid = (long long)p.nkt * B * hkv;
@@ -827,5 +878,29 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(3);
+  return 0;
+}
+
+
+// keep mask of the attention-weight dropout for tests / oracles: out[b, h, q, k] in {0, 1}
+namespace {
+__global__ void __launch_bounds__(256)
+attn_dropout_mask_kernel(unsigned char* __restrict__ out, long long B, int H, int T, DropParams d) {
+  const long long total = B * H * (long long)T * T;
+  const unsigned long long tp2 = (unsigned long long)((T + 1) >> 1);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % T);
+    const unsigned long long row = (unsigned long long)(i / T);   // (b*H + h)*T + q
+    out[i] = dropout_keep(((row * tp2 + (unsigned long long)(k >> 1)) << 1) + (unsigned long long)(k & 1), d.seed, d.thr16) ? 1 : 0;
+  }
+}
+}  // namespace
+
+extern "C" int b200_attention_dropout_mask_u8(void* out, int64_t B, int64_t H, int64_t T, float dropout_p,
+                                              uint64_t seed, void* stream) {
+  B200_CHECK_ARG(out && B > 0 && H > 0 && T > 0 && dropout_p >= 0.f && dropout_p < 1.f, "attention_dropout_mask: bad arguments");
+  attn_dropout_mask_kernel<<<1024, 256, 0, (cudaStream_t)stream>>>((unsigned char*)out, B, (int)H, (int)T, make_drop(dropout_p, seed));
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
   return 0;
 }

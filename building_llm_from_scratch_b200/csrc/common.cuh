@@ -299,6 +299,29 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
       : "memory");
 }
 
+// ---- counter-based dropout (K10) ----------------------------------------------------------
+// One 32-bit hash of (seed, element index) per PAIR of elements; each 16-bit half is compared with
+// thr16 = round(p * 65536): keep iff half >= thr16. Stateless, so the backward kernels regenerate
+// exactly the mask the forward kernels used (nothing is stored).
+__host__ __device__ __forceinline__ uint32_t dropout_hash(unsigned long long pair_index, unsigned long long seed) {
+  unsigned long long z = pair_index + seed * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z = z ^ (z >> 31);
+  return (uint32_t)(z >> 16);
+}
+// keep flags of elements 2*pair_index and 2*pair_index+1
+__host__ __device__ __forceinline__ void dropout_keep2(unsigned long long pair_index, unsigned long long seed,
+                                                       uint32_t thr16, bool& k0, bool& k1) {
+  const uint32_t h = dropout_hash(pair_index, seed);
+  k0 = (h & 0xFFFFu) >= thr16;
+  k1 = (h >> 16) >= thr16;
+}
+__host__ __device__ __forceinline__ bool dropout_keep(unsigned long long index, unsigned long long seed, uint32_t thr16) {
+  const uint32_t h = dropout_hash(index >> 1, seed);
+  return ((index & 1) ? (h >> 16) : (h & 0xFFFFu)) >= thr16;
+}
+
 // ---- vector memory + math helpers ---------------------------------------------
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
   uint4 r;

@@ -383,7 +383,72 @@ scatter_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ idx, b
   }
 }
 
+// ---------------- dropout (nn.Dropout in Models/GPT2/GPT2.py:24,81,102; K10) ----------------
+// y = (res) + keep(i) * x / (1 - p); the mask is a pure function of (seed, element index), so the
+// same call on the upstream gradient is the backward. 6 B/elt (+2 with the residual).
+__global__ void __launch_bounds__(256)
+dropout_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res, bf16* __restrict__ y, long long n,
+               uint32_t thr16, float inv_keep, unsigned long long seed) {
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld_nc_v4(x + i * 8), f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      bool k0, k1;
+      dropout_keep2((unsigned long long)(i * 4 + q), seed, thr16, k0, k1);
+      f[2 * q] = k0 ? f[2 * q] * inv_keep : 0.f;
+      f[2 * q + 1] = k1 ? f[2 * q + 1] * inv_keep : 0.f;
+    }
+    if (res != nullptr) {
+      float g[8];
+      unpack8(ld_nc_v4(res + i * 8), g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = bf16_round(f[j]) + g[j];
+    }
+    st_v4(y + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) {
+      float v = dropout_keep((unsigned long long)k, seed, thr16) ? __bfloat162float(x[k]) * inv_keep : 0.f;
+      if (res != nullptr) v = bf16_round(v) + __bfloat162float(res[k]);
+      y[k] = __float2bfloat16_rn(v);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+dropout_mask_kernel(unsigned char* __restrict__ out, long long n, uint32_t thr16, unsigned long long seed) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    out[i] = dropout_keep((unsigned long long)i, seed, thr16) ? 1 : 0;
+}
+
 }  // namespace
+
+static inline uint32_t drop_thr16(float p) {
+  const float t = p * 65536.f + 0.5f;
+  return t < 0.f ? 0u : (t > 65535.f ? 65535u : (uint32_t)t);
+}
+
+extern "C" int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, uint64_t seed,
+                                 void* stream) {
+  B200_CHECK_ARG(x && y && n > 0, "dropout: null pointer or empty");
+  B200_CHECK_ARG(p >= 0.f && p < 1.f, "dropout: p=%f must be in [0, 1)", (double)p);
+  B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y) && (res == nullptr || b200_aligned16(res)), "dropout: pointers must be 16-B aligned");
+  dropout_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, (const bf16*)res, (bf16*)y, n, drop_thr16(p), 1.f / (1.f - p), (unsigned long long)seed);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_dropout_mask_u8(void* out, int64_t n, float p, uint64_t seed, void* stream) {
+  B200_CHECK_ARG(out && n > 0 && p >= 0.f && p < 1.f, "dropout_mask: bad arguments");
+  dropout_mask_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>((unsigned char*)out, n, drop_thr16(p), (unsigned long long)seed);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
 
 extern "C" int b200_compact_rows(const int64_t* targets, int64_t M, int64_t capacity, int32_t* idx,
                                  int32_t* meta, void* stream) {

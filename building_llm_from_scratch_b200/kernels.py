@@ -418,7 +418,30 @@ def colsum(x2d, like=None):
     return out
 
 
-def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None):
+def dropout(x, p, seed, residual=None):
+    """(residual +) keep * x / (1 - p) with the counter-based mask of (seed, element index)."""
+    _need_cuda(x, residual)
+    xc = x.contiguous()
+    y = torch.empty_like(xc)
+    rc = None if residual is None else residual.contiguous()
+    _lib.check(_lib.load().b200_dropout_bf16(_p(xc), _p(rc), _p(y), xc.numel(), float(p), int(seed), _stream()), "dropout")
+    return y
+
+
+def dropout_mask(n, p, seed, device="cuda"):
+    out = torch.empty(n, device=device, dtype=torch.uint8)
+    _lib.check(_lib.load().b200_dropout_mask_u8(_p(out), n, float(p), int(seed), _stream()), "dropout_mask")
+    return out
+
+
+def attention_dropout_mask(B, H, T, p, seed, device="cuda"):
+    out = torch.empty((B, H, T, T), device=device, dtype=torch.uint8)
+    _lib.check(_lib.load().b200_attention_dropout_mask_u8(_p(out), B, H, T, float(p), int(seed), _stream()),
+               "attention_dropout_mask")
+    return out
+
+
+def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None, dropout_p=0.0, seed=0):
     """q/k/v: 2-D row-major views [B*T, *] whose first h*hd (hkv*hd) columns are the heads."""
     _need_cuda(q, k, v)
     q, ldq = _rowmajor2d(q)
@@ -427,11 +450,12 @@ def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None):
     o = torch.empty((B * T, h * hd), device=q.device, dtype=BF16) if out is None else out
     lse = torch.empty((B, h, T), device=q.device, dtype=torch.float32)
     _lib.check(_lib.load().b200_attention_fwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), o.stride(0), _p(lse), B, T,
-                                                   h, hkv, hd, 1.0 / math.sqrt(hd), _stream()), "attention_fwd")
+                                                   h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p), int(seed), _stream()),
+               "attention_fwd")
     return o, lse
 
 
-def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None):
+def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None, dropout_p=0.0, seed=0):
     _need_cuda(q, k, v, o, do, lse)
     q, ldq = _rowmajor2d(q)
     k, ldk = _rowmajor2d(k)
@@ -447,6 +471,6 @@ def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=No
     ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
     _lib.check(lib.b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
                                            _p(ws), nbytes, _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
-                                           dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _stream()),
-               "attention_bwd")
+                                           dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p),
+                                           int(seed), _stream()), "attention_bwd")
     return dq, dk, dv

@@ -315,19 +315,21 @@ def linear(x, weight, bias=None, residual=None):
 # ======================================================================================
 @torch.library.custom_op("b200llm::attention", mutates_args=())
 def attention(q: Tensor, k: Tensor, v: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: int, T: int,
-              h: int, hkv: int, hd: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
-    """q [B*T, h*hd], k/v [B*T, hkv*hd] (row-major 2-D views) -> (o, lse, q_rot, k_rot)."""
+              h: int, hkv: int, hd: int, dropout_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """q [B*T, h*hd], k/v [B*T, hkv*hd] (row-major 2-D views) -> (o, lse, q_rot, k_rot).
+    dropout_p > 0 drops attention weights after the softmax (GPT2.py:43) with the counter-based mask
+    of `seed`; backward regenerates the same mask."""
     if cos is not None:
         qr = K.rope(q, cos, sin, B, T, h, hd)
         kr = K.rope(k, cos, sin, B, T, hkv, hd)
-        o, lse = K.attention_fwd(qr, kr, v, B, T, h, hkv, hd)
+        o, lse = K.attention_fwd(qr, kr, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed)
         return o, lse, qr, kr
-    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed)
     return o, lse, q.new_empty((0,)), q.new_empty((0,))   # no rotated copies to hand back
 
 
 @attention.register_fake
-def _(q, k, v, cos, sin, B, T, h, hkv, hd):
+def _(q, k, v, cos, sin, B, T, h, hkv, hd, dropout_p=0.0, seed=0):
     o, lse = q.new_empty((B * T, h * hd)), q.new_empty((B, h, T), dtype=torch.float32)
     if cos is None:
         return o, lse, q.new_empty((0,)), q.new_empty((0,))
@@ -336,28 +338,61 @@ def _(q, k, v, cos, sin, B, T, h, hkv, hd):
 
 def _attention_setup(ctx, inputs, output):
     ctx.set_materialize_grads(False)
-    q, k, v, cos, sin, B, T, h, hkv, hd = inputs
+    q, k, v, cos, sin, B, T, h, hkv, hd, dropout_p, seed = inputs
     o, lse, qr, kr = output
     if cos is None:
         qr, kr = q, k
     ctx.save_for_backward(qr, kr, v, o, lse, cos, sin)
     ctx.dims = (B, T, h, hkv, hd)
+    ctx.drop = (dropout_p, seed)
 
 
 def _attention_bwd(ctx, do, _dl, _dq, _dk):
     if do is None:
-        return (None,) * 10
+        return (None,) * 12
     qr, kr, v, o, lse, cos, sin = ctx.saved_tensors
     B, T, h, hkv, hd = ctx.dims
     v2 = v if v.stride(-1) == 1 else v.contiguous()
-    dq, dk, dv = K.attention_bwd(qr, kr, v2, o, _flat2d(do), lse, B, T, h, hkv, hd)
+    dq, dk, dv = K.attention_bwd(qr, kr, v2, o, _flat2d(do), lse, B, T, h, hkv, hd, dropout_p=ctx.drop[0],
+                                 seed=ctx.drop[1])
     if cos is not None:
         K.rope_(dq, cos, sin, B, T, h, hd, inverse=True)
         K.rope_(dk, cos, sin, B, T, hkv, hd, inverse=True)
-    return dq, dk, dv, None, None, None, None, None, None, None
+    return (dq, dk, dv) + (None,) * 9
 
 
 attention.register_autograd(_attention_bwd, setup_context=_attention_setup)
+
+
+# ======================================================================================
+# dropout (nn.Dropout sites of Models/GPT2/GPT2.py:24,81,102)
+# ======================================================================================
+@torch.library.custom_op("b200llm::dropout", mutates_args=())
+def dropout(x: Tensor, residual: Optional[Tensor], p: float, seed: int) -> Tensor:
+    """(residual +) keep * x / (1 - p); keep is a counter-based function of (seed, element index)."""
+    return K.dropout(x, p, seed, residual).view(x.shape)
+
+
+@dropout.register_fake
+def _(x, residual, p, seed):
+    return torch.empty_like(x)
+
+
+def _dropout_setup(ctx, inputs, output):
+    _, residual, p, seed = inputs
+    ctx.p, ctx.seed, ctx.has_res = p, seed, residual is not None
+
+
+def _dropout_bwd(ctx, dy):
+    return K.dropout(dy.contiguous(), ctx.p, ctx.seed).view(dy.shape), (dy if ctx.has_res else None), None, None
+
+
+dropout.register_autograd(_dropout_bwd, setup_context=_dropout_setup)
+
+
+def new_seed() -> int:
+    """A fresh 62-bit seed from torch's CPU generator (follows torch.manual_seed; no device sync)."""
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
 
 
 # ======================================================================================

@@ -238,7 +238,8 @@ int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N
  * logsumexp of the scaled scores) is saved for backward. scale = 1/sqrt(hd). hd in {64,128}. */
 int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
+                            int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p,
+                            uint64_t seed, void* stream);
 /* Backward. dq/dk/dv have the layouts of q/k/v. `workspace` is scratch of
  * b200_attention_bwd_workspace_bytes(B, T, h, hd) bytes: rowsum(dO*O) per (b, h, t) and, on the
  * tcgen05 path (hd 64), the fp32 dQ accumulator that the key-tile CTAs add into. */
@@ -248,7 +249,19 @@ int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t l
                             int64_t lddo, const float* lse, void* workspace, size_t workspace_bytes,
                             void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
                             int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd, float scale,
-                            void* stream);
+                            float dropout_p, uint64_t seed, void* stream);
+/* dropout_p > 0 (hd 64 only) drops attention weights after the softmax like GPT2.py:43; the mask is
+ * a counter-based function of (seed, b, h, q, k), so backward must be given the forward's seed.
+ * b200_attention_dropout_mask_u8 writes that keep mask ([B, H, T, T] bytes) for tests. */
+int b200_attention_dropout_mask_u8(void* out, int64_t B, int64_t H, int64_t T, float dropout_p,
+                                   uint64_t seed, void* stream);
+
+/* ---- K10: dropout (nn.Dropout, Models/GPT2/GPT2.py:24,81,102) ------------------------------
+ * y = (res +) keep(i) * x / (1 - p), keep a counter-based function of (seed, i): applying the
+ * same call to the upstream gradient is the backward. b200_dropout_mask_u8 dumps the mask. */
+int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, uint64_t seed,
+                      void* stream);
+int b200_dropout_mask_u8(void* out, int64_t n, float p, uint64_t seed, void* stream);
 
 #ifdef __cplusplus
 }

@@ -50,3 +50,22 @@ def test_synthetic_shapes():
     assert 0.2 < frac < 0.95
     x, y = gutenberg_batch(gen, 3, 64, 50257)
     assert x.shape == (3, 64) and torch.equal(x[:, 1:], y[:, :-1]) and (y != -100).all()
+
+
+def test_mixed_precision_policy_objects():
+    from building_llm_from_scratch_b200.datautils import mixed_precision as mp
+    assert set(mp.mixed_precision_policies) == {"fp16", "bf16", "bf16_hybrid", "fp32"}
+    assert mp.bf16_hybrid_policy.param_dtype == torch.float32 and mp.bf16_hybrid_policy.reduce_dtype == torch.bfloat16
+    assert mp.fpSixteen is mp.fp16_policy and mp.bfSixteen is mp.bf16_policy
+
+
+def test_llama2_module_tree_and_state_dict_keys():
+    from building_llm_from_scratch_b200.Models.Llama.Llama2 import Llama2Model
+    cfg = dict(vocab_size=64, context_length=16, emb_dim=128, n_heads=2, n_layers=1, hidden_dim=64, dtype=torch.bfloat16)
+    m = Llama2Model(cfg)
+    keys = set(m.state_dict())
+    assert {"tok_emb.weight", "trf_blocks.0.att.W_query.weight", "trf_blocks.0.att.mask", "trf_blocks.0.att.cos",
+            "trf_blocks.0.att.sin", "trf_blocks.0.ff.fc3.weight", "trf_blocks.0.norm1.weight", "final_norm.weight",
+            "out_head.weight"} <= keys
+    assert m.state_dict()["trf_blocks.0.att.cos"].dtype == torch.float32
+    assert m.load_state_dict(m.state_dict()).missing_keys == []

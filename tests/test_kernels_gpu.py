@@ -239,3 +239,43 @@ def test_attention_causality_property(K):
     qkv2[600:] = rnd(T - 600, qkv.shape[1], seed=4)
     o2, _ = K.attention_fwd(qkv2[:, :h * hd], qkv2[:, h * hd:(h + hkv) * hd], qkv2[:, (h + hkv) * hd:], B, T, h, hkv, hd)
     assert torch.equal(o1[:600], o2[:600])
+
+
+# ------------------------------------------------------------------ dropout
+def test_dropout_kernel_statistics_and_backward_mask(K):
+    n, p, seed = 1 << 20, 0.1, 1234
+    x = rnd(n, seed=1)
+    y = K.dropout(x, p, seed)
+    mask = K.dropout_mask(n, p, seed).bool()
+    assert abs(float((~mask).float().mean()) - p) < 3e-3                 # drop rate
+    assert torch.equal(y[~mask], torch.zeros_like(y[~mask]))
+    assert rel_err(y[mask].float(), x[mask].float() / (1 - p)) < 5e-3
+    assert torch.equal(K.dropout(x, p, seed), y)                           # same seed -> same mask (backward)
+    assert not torch.equal(K.dropout_mask(n, p, seed + 1).bool(), mask)
+    r = rnd(n, seed=2)
+    assert rel_err(K.dropout(x, p, seed, residual=r).float(), y.float() + r.float()) < 5e-3
+
+
+def test_attention_dropout_matches_oracle_with_same_mask(K):
+    """softmax -> dropout -> @V (GPT2.py:42-46) with the kernel's own keep mask fed to the oracle."""
+    B, T, h, hkv, hd, p, seed = 2, 200, 4, 2, 64, 0.2, 99
+    qkv = rnd(B * T, (h + 2 * hkv) * hd, seed=1)
+    q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
+    keep = K.attention_dropout_mask(B, h, T, p, seed).float()
+    assert abs(float(1 - keep.mean()) - p) < 5e-3
+    qr, kr, vr = (t.float().clone().requires_grad_(True) for t in (q, k, v))
+    qh = qr.view(B, T, h, hd).transpose(1, 2)
+    kh = kr.view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    vh = vr.view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    sc = (qh @ kh.transpose(2, 3)) / hd ** 0.5
+    sc = sc.masked_fill(torch.triu(torch.ones(T, T, device="cuda"), 1).bool(), -torch.inf)
+    w = torch.softmax(sc, -1) * keep / (1 - p)
+    ref = (w @ vh).transpose(1, 2).reshape(B * T, h * hd)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd, dropout_p=p, seed=seed)
+    assert rel_err(o.float(), ref) < BF16_TOL
+    do = rnd(B * T, h * hd, seed=2)
+    ref.backward(do.float())
+    dq, dk, dv = K.attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dropout_p=p, seed=seed)
+    assert rel_err(dq.float(), qr.grad) < BF16_TOL
+    assert rel_err(dk.float(), kr.grad) < BF16_TOL
+    assert rel_err(dv.float(), vr.grad) < BF16_TOL
