@@ -41,6 +41,7 @@ struct FwdParams {
   float* lse;
 };
 
+template <bool DROP>
 __global__ void __launch_bounds__(192, 3)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
@@ -181,7 +182,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         float p0 = fast_exp2(__uint_as_float(r[2 * i]) - m_new);
         float p1 = fast_exp2(__uint_as_float(r[2 * i + 1]) - m_new);
         sum += p0 + p1;                       // the softmax denominator is taken before dropout
-        if (p.drop.thr16) {
+        if (DROP) {
           bool k0, k1;
           dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, k0, k1);
           p0 = k0 ? p0 * p.drop.inv_keep : 0.f;
@@ -274,7 +275,8 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
     attr_set[dev & 63] = true;
   }
   FwdParams p;
@@ -285,7 +287,8 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
-  attn_fwd_tc_kernel<<<(unsigned)grid, 192, FWD_SMEM, st>>>(mq, mk, mv, p);
+  if (p.drop.thr16) attn_fwd_tc_kernel<true><<<(unsigned)grid, 192, FWD_SMEM, st>>>(mq, mk, mv, p);
+  else attn_fwd_tc_kernel<false><<<(unsigned)grid, 192, FWD_SMEM, st>>>(mq, mk, mv, p);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -327,6 +330,7 @@ struct BwdParams {
   long long lddv;
 };
 
+template <bool DROP>
 __global__ void __launch_bounds__(320, 1)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                        const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
@@ -506,7 +510,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             if (diag && key > qrow0 + hf * 32 + c) pr = 0.f;
             float dpv = __uint_as_float(dv[c]);
             float pdrop = pr;
-            if (p.drop.thr16) {
+            if (DROP) {
               const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c);
               const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
                                                ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
@@ -585,6 +589,7 @@ struct DqParams {
   long long lddq;
 };
 
+template <bool DROP>
 __global__ void __launch_bounds__(192, 2)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
@@ -722,7 +727,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       for (int i = 0; i < 32; ++i) {
         float v2[2];
         bool keep[2] = {true, true};
-        if (p.drop.thr16)
+        if (DROP)
           dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, keep[0], keep[1]);
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
@@ -730,7 +735,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           float pr = fast_exp2(fmaf(__uint_as_float(s[c]), p.scale_log2, -lse2));
           if (diag && kv0 + c > t) pr = 0.f;
           float dpv = __uint_as_float(d[c]);
-          if (p.drop.thr16) dpv = keep[e] ? dpv * p.drop.inv_keep : 0.f;
+          if (DROP) dpv = keep[e] ? dpv * p.drop.inv_keep : 0.f;
           v2[e] = pr * (dpv - dl) * p.scale;
         }
         pk[i] = f2_to_bf2(v2[0], v2[1]);
@@ -846,8 +851,10 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
     attr_set[dev & 63] = true;
   }
   const int nqt = (int)((T + BK2 - 1) / BK2);
@@ -859,7 +866,8 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
     p.drop = make_drop(dropout_p, seed);
     const long long grid = (long long)nqt * B * h;
-    attn_bwd_dq_tc_kernel<<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    if (p.drop.thr16) attn_bwd_dq_tc_kernel<true><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    else attn_bwd_dq_tc_kernel<false><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
   }
   {
@@ -874,7 +882,8 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     const long long grid = (long long)p.nkt * B * hkv;
-    attn_bwd_dkv_tc_kernel<<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<true><<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    else attn_bwd_dkv_tc_kernel<false><<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(3);
