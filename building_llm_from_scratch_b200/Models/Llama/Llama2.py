@@ -80,8 +80,10 @@ class TransformerBlock(nn.Module):
         self.norm2 = RMSNorm(cfg["emb_dim"])
 
     def forward(self, x):
-        x = self.att(self.norm1(x), residual=x)
-        return self.ff(self.norm2(x), residual=x)
+        h, res = ops.rmsnorm_with_residual(x, self.norm1.weight, self.norm1.eps)
+        x = self.att(h, residual=res)
+        h, res = ops.rmsnorm_with_residual(x, self.norm2.weight, self.norm2.eps)
+        return self.ff(h, residual=res)
 
 
 class Llama2Model(nn.Module):

@@ -105,9 +105,10 @@ class TransformerBlock(nn.Module):
         self.norm2 = RMSNorm(cfg["emb_dim"], eps=1e-5)
 
     def forward(self, x):
-        x = self.att(self.norm1(x).to(torch.bfloat16), residual=x)
-        x = self.ff(self.norm2(x).to(torch.bfloat16), residual=x)
-        return x
+        h, res = ops.rmsnorm_with_residual(x, self.norm1.weight, self.norm1.eps)
+        x = self.att(h.to(torch.bfloat16), residual=res)
+        h, res = ops.rmsnorm_with_residual(x, self.norm2.weight, self.norm2.eps)
+        return self.ff(h.to(torch.bfloat16), residual=res)
 
 
 class Llama3Model(nn.Module):

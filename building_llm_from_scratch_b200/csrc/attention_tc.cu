@@ -315,9 +315,11 @@ constexpr int T2_BYTES = BK2 * HD * 2;    // 16 KB  [128 x 64] bf16 tile
 constexpr int QS = 64;                    // query rows per step
 constexpr int QS_BYTES = QS * HD * 2;     // 8 KB
 constexpr int PANEL_BYTES = BK2 * QS * 2; // 16 KB  [128 keys x 64 q] bf16
-constexpr int NSTG = 4;
+constexpr int NG = 3;                      // softmax groups = S^T/dP^T TMEM buffers = smem panel pairs
+constexpr int NSTG = 5;
 constexpr int LD_BYTES = 2 * QS * 4;       // 64 x (lse * log2e) then 64 x delta for one query step
-constexpr int BWD_SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 4 * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
+constexpr int BWD_THREADS = 64 + NG * 128;
+constexpr int BWD_SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 2 * NG * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
 
 struct BwdParams {
   int B, T, H, HKV, nkt, nq64;
@@ -331,7 +333,7 @@ struct BwdParams {
 };
 
 template <bool DROP>
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                        const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                        const BwdParams p) {
@@ -341,18 +343,18 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   uint8_t* sV = sK + T2_BYTES;
   uint8_t* sQ = sV + T2_BYTES;              // [NSTG] x 8 KB
   uint8_t* sdO = sQ + NSTG * QS_BYTES;      // [NSTG] x 8 KB
-  uint8_t* sPt = sdO + NSTG * QS_BYTES;     // [2] x 16 KB
-  uint8_t* sdSt = sPt + 2 * PANEL_BYTES;    // [2] x 16 KB
-  uint8_t* sLd = sdSt + 2 * PANEL_BYTES;           // [NSTG] x 512 B
+  uint8_t* sPt = sdO + NSTG * QS_BYTES;     // [NG] x 16 KB
+  uint8_t* sdSt = sPt + NG * PANEL_BYTES;   // [NG] x 16 KB
+  uint8_t* sLd = sdSt + NG * PANEL_BYTES;          // [NSTG] x 512 B
   uint64_t* bars = (uint64_t*)(sLd + NSTG * LD_BYTES);
   uint64_t* kv_full = bars;                 // 1
   uint64_t* qdo_full = bars + 1;            // NSTG
   uint64_t* qdo_empty = qdo_full + NSTG;    // NSTG
-  uint64_t* s_full = qdo_empty + NSTG;      // 2
-  uint64_t* st_empty = s_full + 2;          // 2 (4 arrivals: one softmax group each)
-  uint64_t* ps_full = st_empty + 2;         // 2 (4 arrivals)
-  uint64_t* panel_free = ps_full + 2;       // 2
-  uint64_t* acc_done = panel_free + 2;      // 1
+  uint64_t* s_full = qdo_empty + NSTG;      // NG
+  uint64_t* st_empty = s_full + NG;         // NG (4 arrivals: one softmax group each)
+  uint64_t* ps_full = st_empty + NG;        // NG (4 arrivals)
+  uint64_t* panel_free = ps_full + NG;      // NG
+  uint64_t* acc_done = panel_free + NG;     // 1
   uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -372,7 +374,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NG; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&st_empty[i], 4);
       mbar_init(&ps_full[i], 4);
@@ -392,7 +394,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  constexpr uint32_t C_ST = 0, C_DPT = 128, C_DV = 256, C_DK = 320;
+  constexpr uint32_t C_ST = 0, C_DPT = NG * QS, C_DV = 2 * NG * QS, C_DK = 2 * NG * QS + HD;   // 512 columns for NG = 3
 
   if (warp == 0) {
     if (lane == 0) {
@@ -421,10 +423,10 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int s) {
-        const int stg = s % NSTG, buf = s & 1;
+        const int stg = s % NSTG, buf = s % NG, use = s / NG;
         const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
         mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
-        if (s >= 2) mbar_wait(&st_empty[buf], ((s >> 1) - 1) & 1);
+        if (use > 0) mbar_wait(&st_empty[buf], (use - 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -435,10 +437,10 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         umma_commit(&s_full[buf]);
       };
       auto issue_acc = [&](int s) {
-        const int stg = s % NSTG, buf = s & 1;
+        const int stg = s % NSTG, buf = s % NG;
         const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
         const uint32_t aPt = smem_u32(sPt + buf * PANEL_BYTES), adSt = smem_u32(sdSt + buf * PANEL_BYTES);
-        mbar_wait(&ps_full[buf], (s >> 1) & 1);
+        mbar_wait(&ps_full[buf], (s / NG) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < QS / 16; ++k)
@@ -451,38 +453,36 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         umma_commit(&panel_free[buf]);
         umma_commit(&qdo_empty[stg]);
       };
-      issue_s(0);
+      // run NG - 1 steps ahead of the accumulation so every softmax group has its S^T/dP^T waiting
+      for (int s = 0; s < NG - 1 && s < steps; ++s) issue_s(s);
       for (int s = 0; s < steps; ++s) {
-        if (s + 1 < steps) issue_s(s + 1);
+        if (s + NG - 1 < steps) issue_s(s + NG - 1);
         issue_acc(s);
       }
       umma_commit(acc_done);
     }
   } else {
-    // Two softmax groups of 4 warps ping-pong over the steps (group = step parity): each owns one of
-    // the two S^T/dP^T TMEM buffers and one P^T/dS^T smem panel pair, so the barrier / TMEM-load /
-    // proxy-fence latencies of one group hide behind the other group's arithmetic.
+    // NG softmax groups of 4 warps take the steps round-robin (group = step % NG): each owns one of
+    // the S^T/dP^T TMEM buffers and one P^T/dS^T smem panel pair, so the barrier / TMEM-load /
+    // proxy-fence latencies of one group hide behind the other groups' arithmetic.
     const int quad = warp & 3;
     const int grp = (warp - 2) >> 2;
     const int row = quad * 32 + lane;                 // key row
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int key = kv0 + row;
     const int buf = grp;
-    int q64 = 2 * kt + (grp % spp);
-    // advance (head, q64) by two steps at a time
-    for (int s = grp; s < steps; s += 2) {
-      const int stg = s % NSTG;
-      const int qrow0 = q64 * QS;
-      const unsigned long long drop_bh = (unsigned long long)b * p.H + (unsigned long long)(kvh * G + s / spp);
-      q64 += 2;
-      while (q64 >= p.nq64) q64 -= spp;
+    for (int s = grp; s < steps; s += NG) {
+      const int stg = s % NSTG, use = s / NG;
+      const int hq = s / spp;
+      const int qrow0 = (2 * kt + (s - hq * spp)) * QS;
+      const unsigned long long drop_bh = (unsigned long long)b * p.H + (unsigned long long)(kvh * G + hq);
       mbar_wait(&qdo_full[stg], (s / NSTG) & 1);      // lse/delta travelled with this stage
-      mbar_wait(&s_full[buf], (s >> 1) & 1);
+      mbar_wait(&s_full[buf], use & 1);
       tc_fence_after();
       const bool diag = qrow0 < kv0 + BK2;
       const uint32_t lse_s = smem_u32(sLd) + stg * LD_BYTES;
       const uint32_t del_s = lse_s + QS * 4;
-      if (s >= 2) mbar_wait(&panel_free[buf], ((s >> 1) - 1) & 1);
+      if (use > 0) mbar_wait(&panel_free[buf], (use - 1) & 1);
       const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
       const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
 #pragma unroll 1
@@ -540,7 +540,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    // epilogue: group g writes columns [32g, 32g + 32) of dV and dK for its key row
+    // epilogue: groups 0 and 1 write columns [32g, 32g + 32) of dV and dK for their key row
+    if (grp < 2) {
     bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + grp * 32;
     bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + grp * 32;
     uint32_t a[32], c2[32];
@@ -559,6 +560,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         st_v4(dvrow + c * 8, pack8(f));
         st_v4(dkrow + c * 8, pack8(g));
       }
+    }
     }
   }
 
@@ -882,8 +884,8 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     const long long grid = (long long)p.nkt * B * hkv;
-    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<true><<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
-    else attn_bwd_dkv_tc_kernel<false><<<(unsigned)grid, 320, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<true><<<(unsigned)grid, BWD_THREADS, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    else attn_bwd_dkv_tc_kernel<false><<<(unsigned)grid, BWD_THREADS, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(3);

@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <utility>
+
 #include "../../include/b200llm.h"
 
 // ----------------------------------------------------------------------------
@@ -37,6 +39,25 @@ static inline bool b200_aligned16(const void* p) { return (((uintptr_t)p) & 15u)
 void b200_count_launch(int n = 1);
 
 int b200_num_sms();
+
+#ifdef __CUDACC__
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait in the device section).
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                   cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+#endif
 
 // Build a 2-D bf16 TMA descriptor for a row-major [rows, cols] matrix with row pitch
 // `ld` elements; the box is [box_rows, box_cols] and smem is 128B-swizzled.
@@ -234,6 +255,16 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t m, uint32_t n, u
          | (b_mn_major << 16)      // B major
          | ((n >> 3) << 17)        // N / 8
          | ((m >> 4) << 24);       // M / 16
+}
+
+// ---- programmatic dependent launch -------------------------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its
+// predecessor in the stream is still draining; everything before pdl_wait() (barrier init, TMEM
+// allocation, descriptor prefetch) overlaps that tail, and nothing after it can observe stale data
+// because griddepcontrol.wait returns only when the prerequisite grids have completed and flushed.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 // ---- CTA-pair (cta_group::2) variants ----------------------------------------------

@@ -182,6 +182,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // the next kernel may start its own prologue on SMs this grid has left
+  pdl_wait();                // inputs written by the previous kernel are complete and visible from here
 
   const int total_kb = p.kb1 + p.kb2;
   const int num_tiles = p.m_tiles * p.n_tiles;
@@ -317,8 +319,8 @@ int launch_bn(const CUtensorMap* maps, const GemmParams& p, int grid, cudaStream
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set[dev] = true;
   }
-  gemm_tcgen05_kernel<BN><<<grid, 256, SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], p);
-  B200_CHECK_LAUNCH();
+  B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_kernel<BN>, dim3(grid), dim3(256), SMEM, st, maps[0], maps[1], maps[2],
+                                  maps[3], p));
   b200_count_launch();
   return 0;
 }
@@ -379,6 +381,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
 
   const int total_kb = p.kb1 + p.kb2;
   const int num_work = p.m_tiles * p.n_tiles;          // m_tiles counts 256-row tiles here
@@ -502,8 +506,8 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   const int work = p.m_tiles * p.n_tiles;
   int clusters = sms / 2;
   if (work < clusters) clusters = work;
-  gemm_tcgen05_2cta_kernel<<<2 * clusters, 256, P_SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], p);
-  B200_CHECK_LAUNCH();
+  B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0], maps[1],
+                                  maps[2], maps[3], p));
   b200_count_launch();
   return 0;
 }
@@ -570,6 +574,8 @@ gemm_grouped_kernel(const __grid_constant__ GroupedMaps maps, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
   const int num_work = g.work_end[g.nprob - 1];
 
   if (warp == 0) {
@@ -825,8 +831,7 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
     attr_set[dev] = true;
   }
   const int grid = work < sms ? work : sms;
-  gemm_grouped_kernel<<<grid, 256, G_SMEM, (cudaStream_t)stream>>>(maps, g);
-  B200_CHECK_LAUNCH();
+  B200_CHECK_CUDA(b200_launch_pdl(gemm_grouped_kernel, dim3(grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
   b200_count_launch();
   return 0;
 }

@@ -75,8 +75,12 @@ rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
 }
 
 // ---------------- RMSNorm backward (bf16) ----------------
+// Two sweeps over the row: the first forms sum(x^2) and sum(dy*w*x) together (the second dot product
+// only needs 1/rms as a factor afterwards), the second writes dx. Only x stays in registers; dy is
+// re-read (an L1/L2 hit: the same warp touched it a few hundred cycles earlier), which halves the
+// register footprint and doubles the resident warps of this bandwidth-bound kernel.
 template <int MAXV, bool HAS_DW>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, (MAXV <= 8 && !HAS_DW) ? 4 : 1)
 rmsnorm_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
                    const bf16* __restrict__ dy, const bf16* __restrict__ dres, bf16* __restrict__ dx,
                    float* __restrict__ dw, long long M, int d, float eps) {
@@ -90,55 +94,46 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
     for (int i = 0; i < (HAS_DW ? MAXV * 8 : 1); ++i) dwacc[i] = 0.f;
   }
   for (long long row = warp0; row < M; row += nwarps) {
-    uint4 vx[MAXV], vg[MAXV];
-    float ss = 0.f;
+    uint4 vx[MAXV];
+    float ss = 0.f, dot = 0.f;   // sum x^2, sum dy*w*x
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       const int idx = lane + 32 * i;
       if (idx < nvec) {
         vx[i] = ld_nc_v4(x + row * d + idx * 8);
-        vg[i] = ld_nc_v4(dy + row * d + idx * 8);
-        float f[8];
-        unpack8(vx[i], f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ss += f[j] * f[j];
-      }
-    }
-    ss = warp_sum(ss);
-    const float r = rsqrtf(ss / (float)d + eps);
-    float dot = 0.f;  // sum_j g_j * xn_j
-#pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < nvec) {
         float f[8], g[8];
         unpack8(vx[i], f);
-        unpack8(vg[i], g);
+        unpack8(ld_v4(dy + row * d + idx * 8), g);
         const float4 w0 = *reinterpret_cast<const float4*>(w + idx * 8);
         const float4 w1 = *reinterpret_cast<const float4*>(w + idx * 8 + 4);
         const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float xn = f[j] * r;
-          dot += g[j] * ww[j] * xn;
-          if (HAS_DW) dwacc[i * 8 + j] += g[j] * xn;
+          ss += f[j] * f[j];
+          dot += g[j] * ww[j] * f[j];
         }
       }
     }
+    ss = warp_sum(ss);
     dot = warp_sum(dot);
-    const float c = dot / (float)d;
+    const float r = rsqrtf(ss / (float)d + eps);
+    const float c = dot * r / (float)d;   // mean(g * xn), xn = x * r
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       const int idx = lane + 32 * i;
       if (idx < nvec) {
         float f[8], g[8], o[8];
         unpack8(vx[i], f);
-        unpack8(vg[i], g);
+        unpack8(ld_v4(dy + row * d + idx * 8), g);
         const float4 w0 = *reinterpret_cast<const float4*>(w + idx * 8);
         const float4 w1 = *reinterpret_cast<const float4*>(w + idx * 8 + 4);
         const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = r * (g[j] * ww[j] - f[j] * r * c);
+        for (int j = 0; j < 8; ++j) {
+          const float xn = f[j] * r;
+          o[j] = r * (g[j] * ww[j] - xn * c);
+          if (HAS_DW) dwacc[i * 8 + j] += g[j] * xn;
+        }
         if (dres != nullptr) {
           float e[8];
           unpack8(ld_nc_v4(dres + row * d + idx * 8), e);

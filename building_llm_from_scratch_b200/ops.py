@@ -67,6 +67,38 @@ def _rmsnorm_bwd(ctx, dy):
 rmsnorm.register_autograd(_rmsnorm_bwd, setup_context=_rmsnorm_setup)
 
 
+class _RMSNormWithResidual(torch.autograd.Function):
+    """y = rmsnorm(x) and x itself handed on as the residual stream. In a pre-norm block x feeds both
+    the norm and the residual add; autograd would sum the two gradient contributions with a separate
+    add kernel, here the norm's backward kernel adds the residual-stream gradient while it writes dx
+    (b200_rmsnorm_bwd_bf16's dres_in)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, eps):
+        y = K.rmsnorm_fwd(x.contiguous(), weight, eps)
+        ctx.save_for_backward(x, weight)
+        ctx.eps = eps
+        ctx.set_materialize_grads(False)
+        return y, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, dres):
+        x, w = ctx.saved_tensors
+        need_dw = ctx.needs_input_grad[1]
+        if dy is None:
+            return dres, None, None
+        dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps,
+                               dres=None if dres is None else dres.contiguous(), need_dw=need_dw)
+        return dx, dw, None
+
+
+def rmsnorm_with_residual(x, weight, eps):
+    """-> (rmsnorm(x), x as residual stream); see _RMSNormWithResidual."""
+    if x.dtype != BF16:
+        return rmsnorm(x, weight, eps), x
+    return _RMSNormWithResidual.apply(x, weight, eps)
+
+
 # ======================================================================================
 # LayerNorm (nn.LayerNorm in Models/GPT2/GPT2.py:79-80,105)
 # ======================================================================================
