@@ -198,6 +198,11 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
                                      trans_out=trans_out))
             if len(_wgrad_queue) >= WGRAD_FLUSH_AT:
                 flush_weight_grads()
+        elif getattr(param, "_b200_grad_fresh", False) and not trans_out:
+            # first (usually only) contribution since zero_grad: a plain fp32 store through the CTA-pair
+            # kernel instead of split-K atomics into a zeroed buffer (full-training dW = dY^T x)
+            param._b200_grad_fresh = False
+            K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg)
         else:
             K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
         return None

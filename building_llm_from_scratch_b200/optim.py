@@ -74,6 +74,7 @@ class B200AdamW(torch.optim.Optimizer):
             g["g"].zero_()
         for p in self._trainable:
             p.grad = None
+            p._b200_grad_fresh = True     # lets the first weight-gradient GEMM store instead of accumulate
 
     def _absorb_autograd_grads(self):
         # parameters whose gradient came back through autograd (ops outside this package) are folded in
