@@ -242,3 +242,35 @@ def test_gpt2_trains_with_dropout(golden):
     with torch.no_grad():
         a, b2 = model(x.cuda()), model(x.cuda())
     assert torch.equal(a, b2)
+
+
+def test_trainstep_graph_replay_matches_eager_trainer(golden):
+    """engine.TrainStep (CUDA-graph replay, row-compacted vocab projection, device-side LR / bias
+    corrections) follows the same loss trajectory as Trainer.train_batch run eagerly."""
+    from building_llm_from_scratch_b200.engine import TrainStep
+    from building_llm_from_scratch_b200.train import Trainer
+    g = golden("llama_model.pt")
+    c = g["curve"]
+
+    def make():
+        model, opt = build_llama(g, True)
+        tr = Trainer(model, opt, g["cfg"], [], None, "/tmp", warmup_steps=c["warmup"], initial_lr=1e-5, min_lr=1e-6,
+                     device="cuda")
+        tr.set_schedule(c["total"], peak_lr=c["peak_lr"])
+        return model, tr
+
+    _, tr_a = make()
+    eager = [float(tr_a.train_batch(*c["batches"][s % 2])) for s in range(12)]
+    _, tr_b = make()
+    step = TrainStep(tr_b, tuple(c["batches"][0][0].shape), use_graph=True)
+    step.bucket_rows = 16
+    step.capture(warmup=2)
+    graph = []
+    for s in range(12):
+        xb, yb = c["batches"][s % 2]
+        graph.append(float(step.run(xb.pin_memory(), yb.pin_memory())))
+    assert step.bucket_graphs, "the row-compacted graphs should have been used"
+    assert tr_b.track_lrs == tr_a.track_lrs
+    for s, (a, b) in enumerate(zip(graph, eager)):
+        assert abs(a - b) <= 0.01 * abs(b) + 0.02, (s, a, b)
+    assert graph[-1] < graph[0] - 0.05
