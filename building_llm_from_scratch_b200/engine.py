@@ -8,6 +8,8 @@ device memory that is refreshed before each replay.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .ddp import B200DDP
@@ -33,6 +35,9 @@ class TrainStep:
         self.pool = None
         self.capacity = 0             # rows the vocab projection sees in the step being built (0 = all)
         self.compact_head = True
+        # Capturing the NCCL all-reduce into the graph works but gained nothing measurable at N=2 and
+        # made process-group teardown hang with the graphs still alive: off unless asked for.
+        self.capture_collective = os.environ.get("B200_GRAPH_NCCL", "0") == "1"
         self.bucket_rows = max(128, (batch_shape[0] * batch_shape[1]) // 8)
         self.launches_per_step = 0
         self.opt.graph_safe = True
@@ -85,6 +90,16 @@ class TrainStep:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, **kw):
                 self._fwd_bwd()
+                self._update()
+            if self.pool is None:
+                self.pool = g.pool()
+            return (g,)
+        if self.capture_collective:
+            # the NCCL all-reduce is captured too: the whole data-parallel step is ONE graph launch
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, **kw):
+                self._fwd_bwd()
+                self.ddp.reduce_gradients(self.opt.flat_grads)
                 self._update()
             if self.pool is None:
                 self.pool = g.pool()
