@@ -234,20 +234,20 @@ def llama_model():
     loss.backward()
     out = dict(cfg=cfg, rank=8, alpha=16, sd=sd0, x=x, y=y, logits=logits.detach(), loss=loss.detach(),
                grads=grads_of(model))
-    # 30 reference Trainer steps on a repeating pair of batches (loss-curve fixture)
+    # 200 reference Trainer steps (the north star's loss-curve horizon) cycling over 8 batches
     opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=0.1)
-    tr = ref_train.Trainer(model, opt, cfg, [], None, "/tmp", warmup_steps=5, initial_lr=1e-5, min_lr=1e-6)
-    tr.peak_lr, tr.total_training_steps = 5e-4, 30
+    tr = ref_train.Trainer(model, opt, cfg, [], None, "/tmp", warmup_steps=10, initial_lr=1e-5, min_lr=1e-6)
+    tr.peak_lr, tr.total_training_steps = 5e-4, 200
     tr.lr_increment = (tr.peak_lr - tr.initial_lr) / tr.warmup_steps
-    batches = [alpaca_batch(gen, 2, 64, cfg["vocab_size"]) for _ in range(2)]
+    batches = [alpaca_batch(gen, 2, 64, cfg["vocab_size"]) for _ in range(8)]
     losses = []
     model.train()
-    for s in range(30):
-        xb, yb = batches[s % 2]
+    for s in range(200):
+        xb, yb = batches[s % 8]
         with torch.no_grad():
             losses.append(float(torch.nn.functional.cross_entropy(model(xb).flatten(0, 1), yb.flatten())))
         tr.train_batch(xb, yb)
-    out["curve"] = dict(batches=batches, losses=losses, lrs=tr.track_lrs, warmup=5, total=30, peak_lr=5e-4)
+    out["curve"] = dict(batches=batches, losses=losses, lrs=tr.track_lrs, warmup=10, total=200, peak_lr=5e-4)
     save("llama_model.pt", out)
 
 

@@ -1,7 +1,8 @@
 """GPU: the drop-in modules (same class names / state_dict keys as the reference) against fixtures
 recorded from the live reference modules, and against the oracle on the same weights.
 bf16 tolerance 2e-2 relative per op (north star); end-to-end gradients through a whole bf16 model
-are compared at 5e-2; the 30-step loss curve must track the reference's within 1 % + 0.02 abs."""
+are compared at 5e-2; the 200-step loss curve must track the reference's within 1 % (smoothed over
+8 steps, plus 0.02 abs for the bf16 loss read-out)."""
 import copy
 
 import pytest
@@ -122,14 +123,21 @@ def test_llama3_loss_curve_tracks_reference(golden):
     tr.set_schedule(c["total"], peak_lr=c["peak_lr"])
     losses = []
     for s in range(c["total"]):
-        xb, yb = c["batches"][s % 2]
+        xb, yb = c["batches"][s % len(c["batches"])]
         with torch.no_grad():
             losses.append(float(model.forward_loss(xb.cuda(), yb.cuda())))
         tr.train_batch(xb, yb)
     assert tr.track_lrs == pytest.approx(c["lrs"], rel=1e-12)
     ref = c["losses"]
-    assert ref[-1] < ref[0] - 0.05, "fixture should actually learn"
+    assert len(ref) == 200 and ref[-1] < ref[0] - 0.5, "fixture should actually learn"
+    # per-step: loose (bf16 weights / bf16 Adam state drift differently step to step);
+    # smoothed over one pass through the 8 batches: the north-star 1 % bound
     for s, (a, b) in enumerate(zip(losses, ref)):
+        assert abs(a - b) <= 0.03 * abs(b) + 0.05, (s, a, b)
+    w = 8
+    for s in range(0, 200 - w + 1, w):
+        a = sum(losses[s:s + w]) / w
+        b = sum(ref[s:s + w]) / w
         assert abs(a - b) <= 0.01 * abs(b) + 0.02, (s, a, b)
 
 
@@ -260,14 +268,14 @@ def test_trainstep_graph_replay_matches_eager_trainer(golden):
         return model, tr
 
     _, tr_a = make()
-    eager = [float(tr_a.train_batch(*c["batches"][s % 2])) for s in range(12)]
+    eager = [float(tr_a.train_batch(*c["batches"][s % len(c["batches"])])) for s in range(12)]
     _, tr_b = make()
     step = TrainStep(tr_b, tuple(c["batches"][0][0].shape), use_graph=True)
     step.bucket_rows = 16
     step.capture(warmup=2)
     graph = []
     for s in range(12):
-        xb, yb = c["batches"][s % 2]
+        xb, yb = c["batches"][s % len(c["batches"])]
         graph.append(float(step.run(xb.pin_memory(), yb.pin_memory())))
     assert step.bucket_graphs, "the row-compacted graphs should have been used"
     assert tr_b.track_lrs == tr_a.track_lrs
