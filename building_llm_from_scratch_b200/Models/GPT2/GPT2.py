@@ -131,6 +131,11 @@ class GPTModel(nn.Module):
     def forward(self, x):
         return self.output_head(self.hidden_states(x))
 
+    def forward_last(self, x):
+        """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
+        h = self.hidden_states(x)
+        return self.output_head(h[:, -1, :].contiguous())
+
     def forward_loss(self, x, targets, capacity=0):
         w, A, B, s = head_operands(self.output_head)
         return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets, capacity)[0]

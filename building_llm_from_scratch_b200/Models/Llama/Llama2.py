@@ -104,6 +104,11 @@ class Llama2Model(nn.Module):
     def forward(self, in_idx):
         return self.out_head(self.hidden_states(in_idx))
 
+    def forward_last(self, in_idx):
+        """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
+        h = self.hidden_states(in_idx)
+        return self.out_head(h[:, -1, :].contiguous())
+
     def forward_loss(self, in_idx, targets, capacity=0):
         w, A, B, s = head_operands(self.out_head)
         return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity)[0]

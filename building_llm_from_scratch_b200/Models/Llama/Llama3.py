@@ -136,6 +136,11 @@ class Llama3Model(nn.Module):
     def forward(self, in_idx):
         return self.out_head(self.hidden_states(in_idx))
 
+    def forward_last(self, in_idx):
+        """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
+        h = self.hidden_states(in_idx)
+        return self.out_head(h[:, -1, :].contiguous())
+
     def forward_loss(self, in_idx, targets, capacity=0):
         """Fused vocab projection + cross-entropy (train.py:90-91) without a logits tensor
         handed back to Python; used by Trainer.calc_loss_batch in training mode."""

@@ -41,6 +41,7 @@ struct GemmParams {
   int a1_mn, b1_mn, a2_mn, b2_mn;
   int splits;
   int m_tiles, n_tiles;
+  int n_fastest;   // pair kernel: walk the N tiles of an M tile-row back to back (A row stays in L2)
   int flags;
   float alpha;
   const bf16* bias;
@@ -56,8 +57,27 @@ __device__ __forceinline__ float gelu_erf(float x) {
 
 // Epilogue for 32 consecutive accumulator columns of one output row (one thread):
 // alpha, bias, GELU, residual, then bf16 / fp32 / atomic / transposed store with tail predicates.
+// Residual values for one 32-column chunk, fetched one chunk ahead of their use so the L2 latency of
+// the residual read does not serialise with the TMEM load / convert / store of every chunk (short-K
+// GEMMs with a residual epilogue were epilogue-bound: 23 % tensor-pipe activity at K = 512).
+struct ResChunk {
+  uint4 v[4];
+  bool vec;   // v[] holds the 32 residual values (fast path)
+};
+__device__ __forceinline__ ResChunk load_residual(const GemmParams& p, long long row, bool row_ok, long long col0) {
+  ResChunk rc;
+  rc.vec = false;
+  if ((p.flags & EP_RESIDUAL) && !(p.flags & EP_TRANS_OUT) && row_ok && col0 + 32 <= p.N && (p.ldr & 7) == 0) {
+    const bf16* R = p.R + row * p.ldr + col0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) rc.v[q] = ld_v4(R + q * 8);
+    rc.vec = true;
+  }
+  return rc;
+}
+
 __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, bool row_ok,
-                                            long long col0, const uint32_t* r) {
+                                            long long col0, const uint32_t* r, const ResChunk& rc) {
   if (col0 >= p.N) return;
   const bool full_cols = col0 + 32 <= p.N;
   float v[32];
@@ -95,11 +115,11 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
   if (!row_ok) return;
   if (p.flags & EP_RESIDUAL) {
     const bf16* R = p.R + row * p.ldr + col0;
-    if (full_cols && (p.ldr & 7) == 0) {
+    if (rc.vec) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         float f[8];
-        unpack8(ld_v4(R + q * 8), f);
+        unpack8(rc.v[q], f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[q * 8 + j] += f[j];
       }
@@ -283,13 +303,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_const
       tc_fence_after();
       const long long row = (long long)m_blk * BM + ew * 32 + lane;
       const bool row_ok = row < p.M;
+      ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * BN);
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BN + c * 32);
         tmem_ld_32x32(taddr, r);
+        const ResChunk cur = rc;
+        if (c + 1 < BN / 32) rc = load_residual(p, row, row_ok, (long long)n_blk * BN + (c + 1) * 32);
         tmem_ld_wait();
-        store_chunk(p, row, row_ok, (long long)n_blk * BN + c * 32, r);
+        store_chunk(p, row, row_ok, (long long)n_blk * BN + c * 32, r, cur);
       }
       tc_fence_before();
       __syncwarp();
@@ -394,7 +417,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       int stage = 0;
       uint32_t phase = 0;
       for (int w = cluster_id; w < num_work; w += num_clusters) {
-        const int m_blk = w % p.m_tiles, n_blk = w / p.m_tiles;
+        const int m_blk = p.n_fastest ? w / p.n_tiles : w % p.m_tiles;
+        const int n_blk = p.n_fastest ? w % p.n_tiles : w / p.m_tiles;
         const int m0 = m_blk * 256 + (int)rank * 128;
         const int n0 = n_blk * P_BN + (int)rank * 128;
         for (int kb = 0; kb < total_kb; ++kb) {
@@ -466,20 +490,24 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     const int ew = warp - 4;
     int it = 0;
     for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
-      const int m_blk = w % p.m_tiles, n_blk = w / p.m_tiles;
+      const int m_blk = p.n_fastest ? w / p.n_tiles : w % p.m_tiles;
+      const int n_blk = p.n_fastest ? w % p.n_tiles : w / p.m_tiles;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const long long row = (long long)m_blk * 256 + (long long)rank * 128 + ew * 32 + lane;
       const bool row_ok = row < p.M;
+      ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN);
 #pragma unroll 1
       for (int c = 0; c < P_BN / 32; ++c) {
         uint32_t r[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32);
         tmem_ld_32x32(taddr, r);
+        const ResChunk cur = rc;
+        if (c + 1 < P_BN / 32) rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
         tmem_ld_wait();
-        store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r);
+        store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
       }
       tc_fence_before();
       __syncwarp();
@@ -668,7 +696,9 @@ gemm_grouped_kernel(const __grid_constant__ GroupedMaps maps, const __grid_const
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * G_BN + c * 32), r);
         tmem_ld_wait();
-        store_chunk(p, row, row_ok, (long long)n_blk * G_BN + c * 32, r);
+        ResChunk none;
+        none.vec = false;
+        store_chunk(p, row, row_ok, (long long)n_blk * G_BN + c * 32, r, none);
       }
       tc_fence_before();
       __syncwarp();
@@ -731,6 +761,16 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   p.a1_mn = a1_mn; p.b1_mn = b1_mn; p.a2_mn = a2_mn; p.b2_mn = b2_mn;
   p.m_tiles = pair ? (int)((M + 255) / 256) : (int)((M + BM - 1) / BM);
   p.n_tiles = (int)((N + BN - 1) / BN);
+  // With M fastest every concurrent wave touches all of A; when A (M x K) is far larger than B (N x K)
+  // and than the L2, walking N fastest keeps ~74/n_tiles A tile-rows plus all of B resident instead.
+  p.n_fastest = 0;
+  if (pair) {
+    const double a_bytes = 2.0 * (double)M * (double)(K1 + K2), b_bytes = 2.0 * (double)N * (double)(K1 + K2);
+    const char* e = getenv("B200_GEMM_ORDER");
+    if (e && e[0] == 'n') p.n_fastest = 1;
+    else if (e && e[0] == 'm') p.n_fastest = 0;
+    else p.n_fastest = (a_bytes > 64e6 && b_bytes < 64e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
+  }
   p.alpha = alpha;
   p.bias = (const bf16*)bias;
   p.R = (const bf16*)R;
@@ -802,7 +842,7 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
     p.M = (int)q.M; p.N = (int)q.N;
     p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
     p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
-    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1;
+    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0;
     p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
     p.C = q.C; p.ldc = q.ldc;
     p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0);

@@ -1,7 +1,8 @@
 """Drop-in for the hot-path part of train.py: Trainer with the reference's constructor,
 attributes, LR schedule (train.py:100-107) and step order (zero_grad, lr, forward + CE, backward,
 clip 1.0, optimizer step; train.py:94-123). Evaluation / sampling / checkpoint orchestration is
-out of scope except evaluate-style loss computation, which reuses calc_loss_batch.
+kept behaviour-compatible (calc_loss_loader / evaluate_model / save_checkpoint below, generate.py) but
+not separately accelerated beyond running on the same kernels.
 """
 from __future__ import annotations
 
@@ -60,7 +61,7 @@ class Trainer:
         input_batch = input_batch.to(self.device, non_blocking=True)
         target_batch = target_batch.to(self.device, non_blocking=True)
         core = self.model.module if isinstance(self.model, B200DDP) else self.model
-        if core.training and hasattr(core, "forward_loss"):
+        if hasattr(core, "forward_loss"):   # fused vocab projection + CE, in training and in evaluation
             loss = core.forward_loss(input_batch, target_batch, capacity=self._head_capacity(target_batch_host))
         else:
             logits = self.model(input_batch)
@@ -107,3 +108,35 @@ class Trainer:
         self.tokens_seen += input_batch.numel()
         self.last_loss = loss.detach()
         return self.last_loss
+
+    # train.py:259-268
+    def calc_loss_loader(self, data_loader, num_batches=None):
+        total_loss = 0.0
+        if len(data_loader) == 0:
+            return float("nan")
+        num_batches = min(num_batches or len(data_loader), len(data_loader))
+        for i, (input_batch, target_batch) in enumerate(data_loader):
+            if i >= num_batches:
+                break              # the reference keeps iterating the whole loader; no need to
+            total_loss += float(self.calc_loss_batch(input_batch, target_batch))
+        return total_loss / num_batches
+
+    # train.py:270-276
+    def evaluate_model(self, train_loader, val_loader, eval_iter=5):
+        self.model.eval()
+        with torch.no_grad():
+            train_loss = self.calc_loss_loader(train_loader, eval_iter)
+            val_loss = self.calc_loss_loader(val_loader, eval_iter)
+        self.model.train()
+        return train_loss, val_loss
+
+    # train.py:231-257 (state_dict of the unwrapped model, rank 0 only)
+    def save_checkpoint(self, file_name):
+        import os
+        core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        if torch.distributed.is_initialized():
+            torch.distributed.barrier()
+        if self.rank == 0:
+            torch.save(core.state_dict(), os.path.join(str(self.save_dir), file_name))
+        if torch.distributed.is_initialized():
+            torch.distributed.barrier()

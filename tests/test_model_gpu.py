@@ -282,3 +282,33 @@ def test_trainstep_graph_replay_matches_eager_trainer(golden):
     for s, (a, b) in enumerate(zip(graph, eager)):
         assert abs(a - b) <= 0.01 * abs(b) + 0.02, (s, a, b)
     assert graph[-1] < graph[0] - 0.05
+
+
+def test_generate_and_evaluate_paths(golden, tmp_path):
+    """generate.py drop-in (greedy + top-k sampling) and Trainer.evaluate_model / save_checkpoint."""
+    from building_llm_from_scratch_b200.generate import generate
+    from building_llm_from_scratch_b200.train import Trainer
+    from oracle import reference_ops as R
+    g = golden("llama_model.pt")
+    model, _ = build_llama(g, False)
+    x = g["x"][:, :20].cuda()
+    out = generate(model, x, max_new_tokens=6, context_size=64, temperature=0.0)
+    assert out.shape == (2, 26) and torch.equal(out[:, :20], x)
+    # every greedy token is the arg-max of the oracle's last-position logits up to bf16 near-ties
+    sd = {k: v.cuda() for k, v in g["sd"].items()}
+    for t in range(20, 26):
+        ref = R.llama3_forward(out[:, :t], sd, g["cfg"], g["alpha"] / g["rank"])[:, -1, :].float()
+        chosen = ref.gather(1, out[:, t:t + 1])
+        assert torch.all(chosen >= ref.max(dim=-1, keepdim=True).values - 0.08)
+    assert rel_err(model.forward_last(x).float(), model(x)[:, -1, :].float()) < 1e-2
+    torch.manual_seed(0)
+    s1 = generate(model, x, max_new_tokens=5, context_size=64, temperature=1.0, top_k=5)
+    assert s1.shape == (2, 25)
+    tr = Trainer(model, torch.optim.AdamW([p for p in model.parameters() if p.requires_grad], lr=1e-4), g["cfg"], [], None,
+                 tmp_path, device="cuda")
+    loader = [g["curve"]["batches"][0], g["curve"]["batches"][1]]
+    tl, vl = tr.evaluate_model(loader, loader, eval_iter=2)
+    assert abs(tl - vl) < 1e-6 and 5.0 < tl < 8.0 and model.training
+    tr.save_checkpoint("model_pg_test.pth")
+    saved = torch.load(tmp_path / "model_pg_test.pth", weights_only=False)
+    assert "trf_blocks.0.att.mask" in saved and "out_head.lora.A" in saved

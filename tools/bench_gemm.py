@@ -37,3 +37,11 @@ for (N, Kd, b_mn, r) in [(2048, 2048, 0, 64), (8192, 2048, 0, 64), (2048, 8192, 
     ms = timeit(lambda: K.gemm_ex(a, b, b1_mn=bool(b_mn), out=out, **kw))
     fl = 2.0 * M * N * (Kd + r)
     print(f"{tag} M={M} N={N} K={Kd}+{r} b_mn={b_mn}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TF/s")
+
+# short-K GEMMs with a residual epilogue (the dX chain of the k / v projections) and o-proj
+for (N, Kd) in [(2048, 512), (2048, 2048)]:
+    a, b = rnd(M, Kd), rnd(Kd, N)
+    res = rnd(M, N)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ms = timeit(lambda: K.gemm_ex(a, b, b1_mn=True, out=out, residual=res, a2=rnd(M, 64), b2=rnd(N, 64)))
+    print(f"{tag} residual epilogue M={M} N={N} K={Kd}+64: {ms*1e3:8.1f} us  {2.0*M*N*(Kd+64)/ms/1e9:7.1f} TF/s")
