@@ -1,13 +1,16 @@
-// K2 — fused causal MHA / GQA attention, forward and backward (flash-style: the T x T score
-// matrix of Models/Llama/Llama3.py:148-153 / Models/GPT2/GPT2.py:38-46 is never materialised,
-// repeat_interleave of K/V (Llama3.py:144-145) is replaced by indexing the kv head, and the
-// causal mask buffer by a predicate).
+// K2 — fused causal MHA / GQA attention: C-ABI entry points and the head_dim-128 kernels.
 //
-// This first version runs the score / value contractions on the legacy warp-level tensor path
-// (mma.sync m16n8k16, bf16 in / fp32 accumulate) with cp.async double-buffered, XOR-swizzled
-// shared-memory tiles; one warp owns 16 query rows (forward, dQ) or 16 key rows (dK/dV), so no
-// cross-warp reductions or atomics are needed and the result is deterministic. GQA: the dK/dV
-// CTA loops over the query heads of its group.
+// Flash-style: the T x T score matrix of Models/Llama/Llama3.py:148-153 / Models/GPT2/GPT2.py:38-46
+// is never materialised, repeat_interleave of K/V (Llama3.py:144-145) is replaced by indexing the kv
+// head, and the causal mask buffer by a predicate.
+//
+// head_dim 64 (GPT-2, Llama-3.2-1B) dispatches to the tcgen05 / TMEM kernels in attention_tc.cu.
+// head_dim 128 (Llama-2-7B, Llama-3-8B) still runs the kernels in this file on the legacy warp-level
+// tensor path (mma.sync m16n8k16, bf16 in / fp32 accumulate) with cp.async double-buffered,
+// XOR-swizzled shared-memory tiles; one warp owns 16 query rows (forward, dQ) or 16 key rows
+// (dK/dV), so no cross-warp reductions or atomics are needed and the result is deterministic. GQA:
+// the dK/dV CTA loops over the query heads of its group. B200_ATTN_LEGACY=1 forces these kernels for
+// head_dim 64 as well (A/B comparisons).
 //
 // Roofline: tensor pipe. Algorithmic FLOPs (causal): fwd 2*T*T*hd per (batch, head),
 // bwd 2.5x that (recompute included: 3.5x executed).
@@ -41,11 +44,6 @@ namespace {
 
 constexpr float LOG2E = 1.4426950408889634f;
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool valid) {
-  const int sz = valid ? 16 : 0;
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(sz)
-               : "memory");
-}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
