@@ -44,6 +44,8 @@ SIGNATURES = {
     "b200_gemm_ex": (I, [P, I64, I, P, I64, I, I64, P, I64, I, P, I64, I, I64, P, P, I64, P, I64,
                          I64, I64, I, I, I, I, F, I, P]),
     "b200_gemm_grouped_bf16": (I, [I, C.POINTER(GemmProblem), P]),
+    "b200_gemm_grouped_workspace_bytes": (SZ, [I, C.POINTER(GemmProblem)]),
+    "b200_gemm_grouped_streamk_bf16": (I, [I, C.POINTER(GemmProblem), P, SZ, P]),
     "b200_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I, I, F, I64, I64, I64, P]),
     "b200_rmsnorm_fwd_bf16": (I, [P, P, P, P, P, I64, I64, F, I, P]),
     "b200_rmsnorm_bwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),

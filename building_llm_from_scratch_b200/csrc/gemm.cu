@@ -16,6 +16,7 @@
 //
 // Roofline: tensor pipe. Algorithmic FLOPs per launch = 2·M·N·(K1+K2).
 #include <cstdlib>
+#include <vector>
 
 #include "common.cuh"
 
@@ -713,6 +714,219 @@ gemm_grouped_kernel(const __grid_constant__ GroupedMaps maps, const __grid_const
   }
 }
 
+// ======================================================================================
+// Stream-K form of the grouped launch. The skinny problems are HBM-bound streams over an
+// activation (t = x A, u = dY B^T, dA = x^T u, dB = t^T dY: N <= 64, K up to 128 K), so what matters is
+// that all 148 SMs stream the same number of bytes. The (problem, 128-row tile, 64-wide K block)
+// units of the whole group are laid end to end and cut into gridDim.x equal ranges; a CTA's range
+// is a few "segments" (part of one tile's K range each).
+//   segment covers the tile's whole K range, or the problem accumulates into fp32 C: usual epilogue;
+//   otherwise: the raw partial sums are added (fp32 RED) into a workspace tile, a per-tile counter
+//   collects the K blocks done, and the CTA that completes the count converts the workspace tile
+//   (alpha, bf16 / fp32 store) and puts the zeros back, so the workspace is all-zero between launches.
+// ======================================================================================
+struct StreamKParams {
+  int nprob;
+  int unit_end[GROUP_MAX];        // exclusive prefix sums of m_tiles * kb1
+  int cnt_off[GROUP_MAX];         // first tile counter of the problem
+  long long ws_off[GROUP_MAX];    // first workspace float of the problem (partial tiles)
+  float* ws;
+  int* cnt;
+  GemmParams p[GROUP_MAX];
+};
+
+struct Segment {
+  int pi, tile, kb0, n;
+};
+__device__ __forceinline__ Segment streamk_segment(const StreamKParams& g, int u, int u_end) {
+  int i = 0, begin = 0;
+  while (i < g.nprob - 1 && u >= g.unit_end[i]) {
+    begin = g.unit_end[i];
+    ++i;
+  }
+  const int kb = g.p[i].kb1;
+  const int local = u - begin;
+  Segment s;
+  s.pi = i;
+  s.tile = local / kb;
+  s.kb0 = local - s.tile * kb;
+  s.n = min(kb - s.kb0, u_end - u);
+  return s;
+}
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__global__ void __launch_bounds__(256, 1)
+gemm_streamk_kernel(const __grid_constant__ GroupedMaps maps, const __grid_constant__ StreamKParams g) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ int s_last;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + G_STAGES * G_STAGE_BYTES);
+  uint64_t* empty = full + G_STAGES;
+  uint64_t* tfull = empty + G_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * G_BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int U = g.unit_end[g.nprob - 1];
+  const int u_begin = (int)((long long)blockIdx.x * U / gridDim.x);
+  const int u_end = (int)((long long)(blockIdx.x + 1) * U / gridDim.x);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int u = u_begin; u < u_end;) {
+        const Segment s = streamk_segment(g, u, u_end);
+        const GemmParams& p = g.p[s.pi];
+        for (int kb = s.kb0; kb < s.kb0 + s.n; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], G_STAGE_BYTES);
+          uint8_t* sa = smem + stage * G_STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const int kk = kb * BK;
+          if (!p.a1_mn) {
+            tma_load_2d(sa, &maps.a[s.pi], &full[stage], kk, s.tile * BM);
+          } else {
+            tma_load_2d(sa, &maps.a[s.pi], &full[stage], s.tile * BM, kk);
+            tma_load_2d(sa + 8192, &maps.a[s.pi], &full[stage], s.tile * BM + 64, kk);
+          }
+          if (!p.b1_mn) tma_load_2d(sb, &maps.b[s.pi], &full[stage], kk, 0);
+          else tma_load_2d(sb, &maps.b[s.pi], &full[stage], 0, kk);
+          if (++stage == G_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        u += s.n;
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int u = u_begin; u < u_end; ++it) {
+        const Segment s = streamk_segment(g, u, u_end);
+        const GemmParams& p = g.p[s.pi];
+        const int as = it & 1;
+        mbar_wait(&tempty[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * G_BN);
+        const uint32_t idesc = umma_idesc_bf16(BM, G_BN, (uint32_t)p.a1_mn, (uint32_t)p.b1_mn);
+        for (int kb = 0; kb < s.n; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * G_STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = p.a1_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
+            const uint64_t bd = p.b1_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
+            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == G_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull[as]);
+        u += s.n;
+      }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;
+    const int r_in_tile = ew * 32 + lane;
+    int it = 0;
+    for (int u = u_begin; u < u_end; ++it) {
+      const Segment s = streamk_segment(g, u, u_end);
+      const GemmParams& p = g.p[s.pi];
+      u += s.n;
+      const int as = it & 1;
+      mbar_wait(&tfull[as], (it >> 1) & 1);
+      tc_fence_after();
+      const long long row = (long long)s.tile * BM + r_in_tile;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * G_BN);
+      ResChunk none;
+      none.vec = false;
+      if (s.n == p.kb1 || (p.flags & EP_ATOMIC)) {
+#pragma unroll 1
+        for (int c = 0; c < G_BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          store_chunk(p, row, row_ok, c * 32, r, none);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[as]);
+        continue;
+      }
+      // partial tile: workspace is [column][row-in-tile] so a warp's RED / load touches one 128 B line
+      float* wt = g.ws + g.ws_off[s.pi] + (long long)s.tile * (BM * G_BN) + r_in_tile;
+#pragma unroll 1
+      for (int c = 0; c < G_BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) atomicAdd(wt + (c * 32 + j) * BM, __uint_as_float(r[j]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      __threadfence();
+      epi_bar_sync();
+      if (threadIdx.x == 128) {
+        const int old = atomicAdd(g.cnt + g.cnt_off[s.pi] + s.tile, s.n);
+        s_last = (old + s.n == p.kb1) ? 1 : 0;
+      }
+      epi_bar_sync();
+      if (s_last) {
+        __threadfence();
+#pragma unroll 1
+        for (int c = 0; c < G_BN / 32; ++c) {
+          uint32_t r[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            r[j] = __float_as_uint(__ldcg(wt + (c * 32 + j) * BM));
+            __stcg(wt + (c * 32 + j) * BM, 0.f);
+          }
+          store_chunk(p, row, row_ok, c * 32, r, none);
+        }
+        if (threadIdx.x == 128) g.cnt[g.cnt_off[s.pi] + s.tile] = 0;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * G_BN);
+  }
+}
+
 bool use_pair_kernel() {
   static int v = -1;
   if (v < 0) {
@@ -818,6 +1032,18 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
 }
 
 
+namespace {
+// K splits the tile-scheduled grouped kernel gives a problem: only accumulating problems may split
+int grouped_splits(const b200_gemm_problem& q, int sms, long long tiles_total) {
+  if (!q.accumulate) return 1;
+  const int m_tiles = (int)((q.M + BM - 1) / BM), kb = (int)((q.K + BK - 1) / BK);
+  const long long target = (long long)2 * sms * m_tiles / (tiles_total > 0 ? tiles_total : 1);  // ~2 waves overall
+  int splits = (int)(target / m_tiles);
+  if (splits > kb / 2) splits = kb / 2;   // keep >= 2 K blocks per work item
+  return splits < 1 ? 1 : splits;
+}
+}  // namespace
+
 // One launch for up to B200_GEMM_GROUP_MAX skinny problems (every N <= 64, single operand pair).
 extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs, void* stream) {
   B200_CHECK_ARG(nprob >= 1 && nprob <= GROUP_MAX && probs, "gemm_grouped: nprob=%d must be in [1, %d]", nprob, GROUP_MAX);
@@ -846,14 +1072,8 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
     p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
     p.C = q.C; p.ldc = q.ldc;
     p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0);
-    int splits = 1;
-    if (q.accumulate) {
-      p.flags |= EP_ATOMIC;
-      const long long target = (long long)2 * sms * p.m_tiles / (tiles_total > 0 ? tiles_total : 1);  // ~2 waves overall
-      splits = (int)(target / p.m_tiles);
-      if (splits > p.kb1 / 2) splits = p.kb1 / 2;   // keep >= 2 K blocks per work item
-      if (splits < 1) splits = 1;
-    }
+    if (q.accumulate) p.flags |= EP_ATOMIC;
+    const int splits = grouped_splits(q, sms, tiles_total);
     p.splits = splits;
     work += p.m_tiles * splits;
     g.work_end[i] = work;
@@ -872,6 +1092,110 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
   }
   const int grid = work < sms ? work : sms;
   B200_CHECK_CUDA(b200_launch_pdl(gemm_grouped_kernel, dim3(grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
+  b200_count_launch();
+  return 0;
+}
+
+namespace {
+// workspace = [one int per 128-row tile of every non-accumulating problem | padding to 256 B |
+//              one 128 x 64 fp32 tile per such tile]
+void streamk_workspace_layout(int nprob, const b200_gemm_problem* probs, long long* n_cnt, long long* n_floats) {
+  long long tiles = 0;
+  for (int i = 0; i < nprob; ++i)
+    if (!probs[i].accumulate) tiles += (probs[i].M + BM - 1) / BM;
+  *n_cnt = (tiles + 63) / 64 * 64;
+  *n_floats = tiles * (long long)(BM * G_BN);
+}
+}  // namespace
+
+extern "C" size_t b200_gemm_grouped_workspace_bytes(int nprob, const b200_gemm_problem* probs) {
+  if (nprob < 1 || !probs) return 0;
+  long long n_cnt, n_floats;
+  streamk_workspace_layout(nprob, probs, &n_cnt, &n_floats);
+  return (size_t)(n_cnt * 4 + n_floats * 4);
+}
+
+extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem* probs, void* workspace,
+                                              size_t workspace_bytes, void* stream) {
+  B200_CHECK_ARG(nprob >= 1 && nprob <= GROUP_MAX && probs, "gemm_grouped_streamk: nprob=%d must be in [1, %d]", nprob, GROUP_MAX);
+  StreamKParams g;
+  GroupedMaps maps;
+  g.nprob = nprob;
+  long long n_cnt, n_floats;
+  streamk_workspace_layout(nprob, probs, &n_cnt, &n_floats);
+  const size_t need = (size_t)(n_cnt * 4 + n_floats * 4);
+  B200_CHECK_ARG(need == 0 || (workspace && workspace_bytes >= need && ((uintptr_t)workspace & 255) == 0),
+                 "gemm_grouped_streamk: workspace of %zu bytes (256-B aligned, zero-filled) needed, got %zu", need, workspace_bytes);
+  g.cnt = (int*)workspace;
+  g.ws = (float*)((char*)workspace + n_cnt * 4);
+  long long units = 0, cnt_off = 0;
+  for (int i = 0; i < nprob; ++i) {
+    const b200_gemm_problem& q = probs[i];
+    B200_CHECK_ARG(q.A && q.B && q.C && q.M > 0 && q.N > 0 && q.K > 0, "gemm_grouped_streamk: problem %d has a null operand or empty size", i);
+    B200_CHECK_ARG(q.N <= G_BN, "gemm_grouped_streamk: problem %d has N=%lld > %d", i, (long long)q.N, G_BN);
+    B200_CHECK_ARG(!(q.accumulate && !q.out_f32), "gemm_grouped_streamk: accumulate needs fp32 output (problem %d)", i);
+    GemmParams& p = g.p[i];
+    p.M = (int)q.M; p.N = (int)q.N;
+    p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
+    p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
+    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0; p.splits = 1;
+    p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
+    p.C = q.C; p.ldc = q.ldc;
+    p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0) | (q.accumulate ? EP_ATOMIC : 0);
+    units += (long long)p.m_tiles * p.kb1;
+    B200_CHECK_ARG(units < (1ll << 31), "gemm_grouped_streamk: group too large (problem %d)", i);
+    g.unit_end[i] = (int)units;
+    g.cnt_off[i] = (int)cnt_off;
+    g.ws_off[i] = cnt_off * (long long)(BM * G_BN);
+    if (!q.accumulate) cnt_off += p.m_tiles;
+    Operand oa{q.A, q.lda, q.a_mn}, ob{q.B, q.ldb, q.b_mn};
+    int rc;
+    if ((rc = make_operand_map(&maps.a[i], oa, q.M, q.K, BM))) return rc;
+    if ((rc = make_operand_map(&maps.b[i], ob, q.N, q.K, G_BN))) return rc;
+  }
+  for (int i = nprob; i < GROUP_MAX; ++i) {
+    g.unit_end[i] = (int)units;
+    g.cnt_off[i] = 0;
+    g.ws_off[i] = 0;
+  }
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    attr_set[dev] = true;
+  }
+  const int sms = b200_num_sms();
+  {
+    // Stream-K pays ~16 K blocks' worth of time for the shared-tile fix-up (RED, fence, counter, reload).
+    // Replay the tile scheduler's round-robin on the host: if its busiest CTA is not clearly worse
+    // than an even cut, the tiles go out whole (t = x A with K = 2048 on 64 tiles: 19 vs 23 us).
+    const char* e = getenv("B200_GEMM_STREAMK_FORCE");
+    long long tiles_total = 0;
+    for (int i = 0; i < nprob; ++i) tiles_total += (probs[i].M + BM - 1) / BM;
+    long long items = 0;
+    for (int i = 0; i < nprob; ++i) items += (long long)g.p[i].m_tiles * grouped_splits(probs[i], sms, tiles_total);
+    const int tgrid = (int)(items < sms ? items : sms);
+    std::vector<long long> load((size_t)tgrid, 0);
+    long long w = 0;
+    for (int i = 0; i < nprob; ++i) {
+      const int sp = grouped_splits(probs[i], sms, tiles_total);
+      for (int s = 0; s < sp; ++s) {
+        const long long n = (long long)(s + 1) * g.p[i].kb1 / sp - (long long)s * g.p[i].kb1 / sp;
+        for (int t = 0; t < g.p[i].m_tiles; ++t, ++w) load[(size_t)(w % tgrid)] += n;
+      }
+    }
+    long long busiest = 0;
+    for (long long l : load) busiest = l > busiest ? l : busiest;
+    const double even = (double)units / sms;
+    const bool streamk = (e && e[0] == '1') || (!(e && e[0] == '0') && (double)busiest > 1.3 * even + 16.0);
+    if (!streamk) return b200_gemm_grouped_bf16(nprob, probs, stream);
+  }
+  // at least 4 K blocks per CTA: below that the fixed cost of a CTA outweighs its share of the stream
+  long long grid = units / 4;
+  if (grid > sms) grid = sms;
+  if (grid < 1) grid = 1;
+  B200_CHECK_CUDA(b200_launch_pdl(gemm_streamk_kernel, dim3((unsigned)grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
   b200_count_launch();
   return 0;
 }

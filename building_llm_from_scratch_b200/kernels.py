@@ -7,6 +7,7 @@ allocates). CPU tensors are rejected: there is no fallback path.
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 
@@ -106,6 +107,12 @@ def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, 
     if out is None:
         shape = (N, M) if trans_out else (M, N)
         out = (torch.zeros if accumulate else torch.empty)(shape, device=a1.device, dtype=out_dtype)
+    if (STREAMK and N <= 64 and a2 is None and bias is None and residual is None and not gelu and splitk == 0
+            and M == m1 and N == n1 and out.dim() == 2):
+        # skinny product (LoRA rank-r projection or weight gradient): HBM-bound stream, stream-K scheduled
+        gemm_grouped([dict(a=a1, b=b1, out=out, a_mn=a1_mn, b_mn=b1_mn, accumulate=accumulate,
+                           trans_out=trans_out, alpha=alpha)])
+        return out
     out2, ldc = _rowmajor2d(out)
     flags = (GEMM_BIAS if bias is not None else 0) | (GEMM_GELU if gelu else 0) | (
         GEMM_RESIDUAL if residual is not None else 0)
@@ -149,9 +156,37 @@ def gemm_grouped(problems):
             q.alpha = float(pr.get("alpha", 1.0))
             flops += 2.0 * M * N * K
         start = prof.begin() if prof is not None else None
-        _lib.check(lib.b200_gemm_grouped_bf16(len(chunk), arr, _stream()), "gemm_grouped")
+        if STREAMK:
+            need = int(lib.b200_gemm_grouped_workspace_bytes(len(chunk), arr))
+            ws = _streamk_workspace(chunk[0]["a"].device, need)
+            _lib.check(lib.b200_gemm_grouped_streamk_bf16(len(chunk), arr, _p(ws), ws.numel(), _stream()),
+                       "gemm_grouped_streamk")
+        else:
+            _lib.check(lib.b200_gemm_grouped_bf16(len(chunk), arr, _stream()), "gemm_grouped")
         if prof is not None:
             prof.end(start, flops, ("grouped", len(chunk)))
+
+
+# B200_GEMM_STREAMK=0 selects the tile-scheduled grouped kernel (A/B measurements)
+STREAMK = os.environ.get("B200_GEMM_STREAMK", "1") != "0"
+_streamk_ws: dict = {}
+_streamk_keep: list = []
+
+
+def _streamk_workspace(device, nbytes: int):
+    """Zero-filled scratch of the stream-K grouped GEMM, one per device (all b200llm work of a process
+    is issued on one stream at a time: forward, autograd and graph capture follow each other). The
+    kernel leaves it zero-filled, so it is allocated and cleared once — outside graph capture, TrainStep
+    warms up eagerly — and only re-made when a larger group shows up; earlier buffers stay alive
+    because captured graphs may hold their address."""
+    ws = _streamk_ws.get(device.index)
+    if ws is None or ws.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("stream-K GEMM workspace must be sized by an eager call before graph capture")
+        ws = torch.zeros(max(nbytes, 48 << 20), dtype=torch.uint8, device=device)
+        _streamk_keep.append(ws)
+        _streamk_ws[device.index] = ws
+    return ws
 
 
 def rmsnorm_fwd(x, w, eps=1e-5, res=None, bf16_steps=True):

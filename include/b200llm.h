@@ -85,6 +85,18 @@ typedef struct {
 } b200_gemm_problem;
 int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs, void* stream);
 
+/* Same group, stream-K scheduled: the (problem, 128-row tile, 64-wide K block) units of all problems
+ * are cut into equal ranges, one per SM, so every SM streams the same number of bytes whatever the
+ * shapes (u = dY·B^T of the vocab projection is 32 tiles x 2004 K blocks; t = x·A is 64 x 32).
+ * Tiles whose K range is shared by several CTAs are summed in `workspace` (fp32) and written by the
+ * CTA that completes them. The caller owns `workspace`: b200_gemm_grouped_workspace_bytes() bytes,
+ * 256-byte aligned, ZERO-FILLED before the first use; every launch leaves it zero-filled again, so one
+ * buffer serves all launches on a stream (launches on different streams need their own).
+ * Same call sites as b200_gemm_grouped_bf16 (lora.py:26 forward and under autograd). */
+size_t b200_gemm_grouped_workspace_bytes(int nprob, const b200_gemm_problem* probs);
+int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem* probs, void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
 /* General bf16 GEMM with operand layouts, C[M,N] (+)= op(A)·op(B):
  *   transa = 0: A is [M,K] (K contiguous);  1: A is stored [K,M] (M contiguous)
  *   transb = 0: B is [N,K] (K contiguous);  1: B is stored [K,N] (N contiguous)

@@ -119,3 +119,54 @@ def test_gemm_grouped_matches_individual_launches(K):
     K.gemm_grouped(probs)
     for got, ref in refs:
         assert rel_err(got.float(), ref) < (1e-3 if got.dtype == torch.float32 else BF16_TOL)
+
+
+@pytest.mark.parametrize("streamk", [True, False])
+def test_gemm_grouped_schedulers_agree_with_fp32(K, streamk, monkeypatch):
+    """Both schedulers of the grouped launch (stream-K with shared-tile fix-up, tile-scheduled) on the
+    shapes that stress the fix-up: K ranges cut across CTAs (vocab-sized K), ragged M, rank 8,
+    fp32 and transposed stores; the stream-K scratch must be all zero again afterwards."""
+    monkeypatch.setattr(K, "STREAMK", streamk)
+    monkeypatch.setenv("B200_GEMM_STREAMK_FORCE", "1")    # otherwise the host may pick whole tiles
+    probs, refs = [], []
+    # u = s * dY B^T of a vocab projection: 3 row tiles (ragged) x 501 K blocks
+    dl, Bh = rnd(300, 32064, scale=0.05, seed=60), rnd(64, 32064, scale=0.1, seed=61)
+    u = torch.empty(300, 64, device="cuda", dtype=torch.bfloat16)
+    probs.append(dict(a=dl, b=Bh, out=u, alpha=0.5))
+    refs.append((u, 0.5 * dl.float() @ Bh.float().t()))
+    # t = x A, rank 8
+    x, A8 = rnd(1000, 2048, seed=62), rnd(2048, 8, scale=0.1, seed=63)
+    t8 = torch.empty(1000, 8, device="cuda", dtype=torch.bfloat16)
+    probs.append(dict(a=x, b=A8, out=t8, b_mn=True))
+    refs.append((t8, x.float() @ A8.float()))
+    # fp32 store without accumulation (first weight-gradient contribution), transposed
+    dY, t = rnd(4096, 640, scale=0.1, seed=64), rnd(4096, 64, seed=65)
+    dB = torch.full((64, 640), 7.0, device="cuda", dtype=torch.float32)
+    probs.append(dict(a=dY, b=t, out=dB, a_mn=True, b_mn=True, trans_out=True))
+    refs.append((dB, t.float().t() @ dY.float()))
+    # accumulation on top of existing contents
+    dA = torch.ones(2048, 8, device="cuda", dtype=torch.float32)
+    u8 = rnd(1000, 8, scale=0.1, seed=66)
+    probs.append(dict(a=x, b=u8, out=dA, a_mn=True, b_mn=True, accumulate=True))
+    refs.append((dA, 1 + x.float().t() @ u8.float()))
+    K.gemm_grouped(probs)
+    K.gemm_grouped(probs[:3])          # second launch over the same scratch (dA left out: it accumulates)
+    for got, ref in refs:
+        assert rel_err(got.float(), ref) < (1e-3 if got.dtype == torch.float32 else BF16_TOL)
+    if streamk:
+        ws = K._streamk_ws[torch.cuda.current_device()]
+        assert int(torch.count_nonzero(ws)) == 0
+
+
+@pytest.mark.parametrize("force", ["1", ""])
+def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, monkeypatch):
+    """Integer-valued inputs: a single skinny product (one problem, K split over all SMs when forced,
+    scheduler's own choice otherwise) is bit-exact."""
+    if force:
+        monkeypatch.setenv("B200_GEMM_STREAMK_FORCE", force)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    a = torch.randint(-3, 4, (8192, 2048), generator=g, device="cuda").to(torch.bfloat16)
+    b = torch.randint(-3, 4, (64, 2048), generator=g, device="cuda").to(torch.bfloat16)
+    got = K.gemm_ex(a, b, alpha=0.125)
+    ref = (0.125 * (a.float() @ b.float().t())).to(torch.bfloat16)
+    assert torch.equal(got, ref)
