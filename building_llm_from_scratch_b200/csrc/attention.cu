@@ -18,18 +18,18 @@
 
 #include "common.cuh"
 
-// tcgen05 paths (attention_tc.cu), head_dim 64
-int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
-                            int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, float scale, float dropout_p, uint64_t seed,
-                            cudaStream_t st);
+// tcgen05 paths (attention_tc.cu), head_dim 64 and 128
+int b200_attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                          int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
+                          int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed,
+                          cudaStream_t st);
 
-size_t b200_attention_bwd_tc64_workspace(int64_t B, int64_t T, int64_t h);
-int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
-                            int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
-                            const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
-                            int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                            int64_t hkv, float scale, float dropout_p, uint64_t seed, cudaStream_t st);
+size_t b200_attention_bwd_tc_workspace(int64_t B, int64_t T, int64_t h);
+int b200_attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                          int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
+                          const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
+                          int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
+                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, cudaStream_t st);
 
 static bool attn_legacy() {
   static int v = -1;
@@ -554,9 +554,9 @@ extern "C" int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k
   B200_CHECK_ARG(o && lse, "attention_fwd: null output");
   cudaStream_t st = (cudaStream_t)stream;
   B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
-  if (hd == 64 && !attn_legacy())
-    return b200_attention_fwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
-  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the head_dim-64 tcgen05 path");
+  if (!attn_legacy())
+    return b200_attention_fwd_tc(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, hd, scale, dropout_p, seed, st);
+  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the tcgen05 path");
   dim3 grid((unsigned)((T + 127) / 128), (unsigned)h, (unsigned)B);
   static bool f64[64] = {false}, f128[64] = {false};
   int dev = 0;
@@ -576,8 +576,8 @@ extern "C" int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k
 }
 
 extern "C" size_t b200_attention_bwd_workspace_bytes(int64_t B, int64_t T, int64_t h, int64_t hd) {
-  if (hd == 64) return b200_attention_bwd_tc64_workspace(B, T, h);
-  return (size_t)(B * h * T) * sizeof(float);
+  (void)hd;   // the tcgen05 layout (lse and delta per 64-query step) also covers the legacy kernels' [B, h, T] floats
+  return b200_attention_bwd_tc_workspace(B, T, h);
 }
 
 extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk,
@@ -595,10 +595,10 @@ extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k
   B200_CHECK_ARG(workspace_bytes >= b200_attention_bwd_workspace_bytes(B, T, h, hd), "attention_bwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
-  if (hd == 64 && !attn_legacy())
-    return b200_attention_bwd_tc64(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk,
-                                   lddk, dv, lddv, B, T, h, hkv, scale, dropout_p, seed, st);
-  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the head_dim-64 tcgen05 path");
+  if (!attn_legacy())
+    return b200_attention_bwd_tc(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk,
+                                 lddk, dv, lddv, B, T, h, hkv, hd, scale, dropout_p, seed, st);
+  B200_CHECK_ARG(dropout_p == 0.f, "attention: dropout is only implemented on the tcgen05 path");
   {
     const long long total = B * T * h;
     long long blocks = (total + 7) / 8;

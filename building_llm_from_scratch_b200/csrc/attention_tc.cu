@@ -1,4 +1,6 @@
-// K2 on tcgen05 — fused causal MHA/GQA attention forward for head_dim 64.
+// K2 on tcgen05 — fused causal MHA/GQA attention, forward and backward, head_dim 64 and 128
+// (kernels are templates on HDIM; a [rows x HDIM] tile is HDIM/64 swizzled 64-column panels).
+// Forward:
 //
 // CTA = 128 query rows of one (batch, head); KV streamed in 64-key tiles by TMA (3-stage ring).
 //   warp 0      : TMA producer (Q once, then K/V tiles)
@@ -8,21 +10,39 @@
 //   warps 2..5  : softmax — one thread per query row (TMEM lane), so row max / row sum need no
 //                 shuffles: tcgen05.ld S, exp2 online softmax, P -> bf16 into 128B-swizzled smem,
 //                 rescale O in TMEM (tcgen05.ld/st) only when a row maximum moved, final O / l.
-// 65 KB smem and 128 TMEM columns per CTA -> three CTAs per SM, so one CTA's softmax overlaps the
-// others' MMAs and barrier / TMEM-load latencies. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
+// head_dim 64: 65 KB smem and 128 TMEM columns per CTA -> three CTAs per SM (head_dim 128: 113 KB, 256
+// columns, two CTAs), so one CTA's softmax overlaps the others' MMAs and barrier / TMEM-load latencies. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
 //
 // Roofline: tensor pipe / MUFU (head_dim 64: 8192 exp2 per 128x64 tile vs 256 MMA cycles).
 #include "common.cuh"
 
 namespace {
 
-constexpr int BQ = 128, BKV = 64, HD = 64, NS = 2;
-constexpr int Q_BYTES = BQ * HD * 2;     // 16 KB
-constexpr int KV_BYTES = BKV * HD * 2;   // 8 KB
+constexpr int BQ = 128, BKV = 64, NS = 2;
 constexpr int P_BYTES = BQ * BKV * 2;    // 16 KB
-constexpr int FWD_SMEM = Q_BYTES + NS * 2 * KV_BYTES + P_BYTES + 1024 + 256;
-constexpr uint32_t TMEM_COLS = 128;      // S [0,64)  O [64,128)
 constexpr float LOG2E = 1.4426950408889634f;
+
+template <int HDIM>
+struct FwdCfg {
+  static constexpr int Q_BYTES = BQ * HDIM * 2;     // 16 / 32 KB
+  static constexpr int KV_BYTES = BKV * HDIM * 2;   // 8 / 16 KB
+  static constexpr int SMEM = Q_BYTES + NS * 2 * KV_BYTES + P_BYTES + 1024 + 256;
+  static constexpr uint32_t TMEM_COLS = HDIM == 64 ? 128 : 256;   // S [0,64)  O [64, 64 + HDIM)
+  static constexpr int CTAS = HDIM == 64 ? 3 : 2;
+};
+
+// [rows x HDIM] bf16 tile = HDIM/64 panels of [rows x 64] (128 B per row, 128B-swizzled), panel after panel
+template <int HDIM>
+__device__ __forceinline__ void tma_load_tile(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int col0,
+                                              int row0, int rows) {
+#pragma unroll
+  for (int pn = 0; pn < HDIM / 64; ++pn) tma_load_2d(dst + pn * rows * 128, tm, bar, col0 + pn * 64, row0);
+}
+// byte offset of the k-th 16-element K step of a K-major [ROWS x HDIM] tile
+template <int ROWS>
+__device__ __forceinline__ uint32_t kstep(int k) {
+  return (uint32_t)((k >> 2) * (ROWS * 128) + (k & 3) * 32);
+}
 
 // attention-weight dropout (Models/GPT2/GPT2.py:43): keep flag of score (b, h, q, k) =
 // dropout_keep2(((b*H + h)*T + q) * ceil(T/2) + k/2) half k&1; drop_thr16 == 0 disables it.
@@ -41,12 +61,15 @@ struct FwdParams {
   float* lse;
 };
 
-template <bool DROP>
-__global__ void __launch_bounds__(192, 3)
+template <int HDIM, bool DROP>
+__global__ void __launch_bounds__(192, FwdCfg<HDIM>::CTAS)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int HD = HDIM;
+  constexpr int Q_BYTES = FwdCfg<HDIM>::Q_BYTES, KV_BYTES = FwdCfg<HDIM>::KV_BYTES;
+  constexpr uint32_t TMEM_COLS = FwdCfg<HDIM>::TMEM_COLS;
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + Q_BYTES;
   uint8_t* sV = sK + NS * KV_BYTES;
@@ -100,14 +123,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(q_full, Q_BYTES);
-      tma_load_2d(sQ, &tmQ, q_full, head * HD, row_base + q0);
+      tma_load_tile<HD>(sQ, &tmQ, q_full, head * HD, row_base + q0, BQ);
       for (int j = 0; j < n_kv; ++j) {
         const int s = j % NS;
         mbar_wait(&kv_empty[s], ((j / NS) & 1) ^ 1);
         mbar_expect_tx(&k_full[s], KV_BYTES);
-        tma_load_2d(sK + s * KV_BYTES, &tmK, &k_full[s], kvh * HD, row_base + j * BKV);
+        tma_load_tile<HD>(sK + s * KV_BYTES, &tmK, &k_full[s], kvh * HD, row_base + j * BKV, BKV);
         mbar_expect_tx(&v_full[s], KV_BYTES);
-        tma_load_2d(sV + s * KV_BYTES, &tmV, &v_full[s], kvh * HD, row_base + j * BKV);
+        tma_load_tile<HD>(sV + s * KV_BYTES, &tmV, &v_full[s], kvh * HD, row_base + j * BKV, BKV);
       }
     }
   } else if (warp == 1) {
@@ -124,7 +147,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const uint32_t aK = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base, umma_desc_k128(aQ + k * 32), umma_desc_k128(aK + k * 32), idesc_s, k > 0 ? 1u : 0u);
+          umma_bf16_ss(tmem_base, umma_desc_k128(aQ + kstep<BQ>(k)), umma_desc_k128(aK + kstep<BKV>(k)), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
       issue_s(0);
@@ -206,7 +229,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (j > 0 && !__all_sync(0xffffffffu, alpha == 1.f)) {
         uint32_t o[32];
 #pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
+        for (int h2 = 0; h2 < HD / 32; ++h2) {
           tmem_ld_32x32(tlane + 64 + h2 * 32, o);
           tmem_ld_wait();
 #pragma unroll
@@ -225,7 +248,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int t = q0 + row;
     bf16* orow = p.o + (long long)(row_base + t) * p.ldo + (long long)head * HD;
 #pragma unroll
-    for (int h2 = 0; h2 < 2; ++h2) {
+    for (int h2 = 0; h2 < HD / 32; ++h2) {
       uint32_t o[32];
       tmem_ld_32x32(tlane + 64 + h2 * 32, o);
       tmem_ld_wait();
@@ -261,22 +284,23 @@ static DropParams make_drop(float p, uint64_t seed) {
   return d;
 }
 
-// Returns 0 on success; called by b200_attention_fwd_bf16 for head_dim 64.
-int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
-                            int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
-                            int64_t h, int64_t hkv, float scale, float dropout_p, uint64_t seed,
-                            cudaStream_t st) {
+namespace {
+template <int HD>
+int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                     void* o, int64_t ldo, float* lse, int64_t B, int64_t T, int64_t h, int64_t hkv,
+                     float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
+  constexpr int SMEM = FwdCfg<HD>::SMEM;
   CUtensorMap mq, mk, mv;
   int rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)(B * T), (uint64_t)(h * HD), (uint64_t)ldq, BQ, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)(B * T), (uint64_t)(hkv * HD), (uint64_t)ldk, BKV, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mv, v, (uint64_t)(B * T), (uint64_t)(hkv * HD), (uint64_t)ldv, BKV, HD))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)(B * T), (uint64_t)(h * HD), (uint64_t)ldq, BQ, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)(B * T), (uint64_t)(hkv * HD), (uint64_t)ldk, BKV, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mv, v, (uint64_t)(B * T), (uint64_t)(hkv * HD), (uint64_t)ldv, BKV, 64))) return rc;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set[dev & 63] = true;
   }
   FwdParams p;
@@ -287,15 +311,25 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
-  if (p.drop.thr16) attn_fwd_tc_kernel<true><<<(unsigned)grid, 192, FWD_SMEM, st>>>(mq, mk, mv, p);
-  else attn_fwd_tc_kernel<false><<<(unsigned)grid, 192, FWD_SMEM, st>>>(mq, mk, mv, p);
+  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true><<<(unsigned)grid, 192, SMEM, st>>>(mq, mk, mv, p);
+  else attn_fwd_tc_kernel<HD, false><<<(unsigned)grid, 192, SMEM, st>>>(mq, mk, mv, p);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
 }
+}  // namespace
+
+// Returns 0 on success; called by b200_attention_fwd_bf16 (head_dim 64 or 128).
+int b200_attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                          int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
+                          int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed,
+                          cudaStream_t st) {
+  if (hd == 64) return attention_fwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
+  return attention_fwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
+}
 
 // =====================================================================================
-// backward (head_dim 64), dK / dV kernel.
+// backward, dK / dV kernel.
 //
 // CTA = 128 keys of one (batch, kv head); it streams every (query head of the GQA group) x
 // (64-row query step at or below the diagonal). Working transposed (keys on the M / TMEM-lane
@@ -306,20 +340,27 @@ int b200_attention_fwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
 // The same swizzled Q / dO tiles serve as K-major operands (first two products) and as MN-major
 // operands (the accumulating two). The MMA issuer runs one step ahead (S/dP of step s+1 and the
 // accumulation of step s-1 execute while the 8 softmax warps work on step s).
-// TMEM: 384 of 512 columns, one CTA per SM.
+// TMEM: all 512 columns (head_dim 64: 3 S^T/dP^T buffer pairs + 2 x 64 accumulator columns; head_dim 128:
+// 2 buffer pairs + 2 x 128), one CTA per SM.
 // =====================================================================================
 namespace {
 
 constexpr int BK2 = 128;                  // keys per CTA (also the query tile of the dQ kernel's maps)
-constexpr int T2_BYTES = BK2 * HD * 2;    // 16 KB  [128 x 64] bf16 tile
 constexpr int QS = 64;                    // query rows per step
-constexpr int QS_BYTES = QS * HD * 2;     // 8 KB
 constexpr int PANEL_BYTES = BK2 * QS * 2; // 16 KB  [128 keys x 64 q] bf16
-constexpr int NG = 3;                      // softmax groups = S^T/dP^T TMEM buffers = smem panel pairs
-constexpr int NSTG = 5;
 constexpr int LD_BYTES = 2 * QS * 4;       // 64 x (lse * log2e) then 64 x delta for one query step
-constexpr int BWD_THREADS = 64 + NG * 128;
-constexpr int BWD_SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 2 * NG * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
+
+template <int HDIM>
+struct DkvCfg {
+  static constexpr int NG = HDIM == 64 ? 3 : 2;      // softmax groups = S^T/dP^T TMEM buffers = smem panel pairs
+  static constexpr int NSTG = HDIM == 64 ? 5 : 3;    // Q / dO stages
+  static constexpr int T2_BYTES = BK2 * HDIM * 2;    // 16 / 32 KB  [128 x HDIM] bf16 tile
+  static constexpr int QS_BYTES = QS * HDIM * 2;     // 8 / 16 KB
+  static constexpr int THREADS = 64 + NG * 128;
+  static constexpr int SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 2 * NG * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
+  static_assert(SMEM <= 232448, "dK/dV kernel exceeds the 227 KB shared memory of an SM");
+  static_assert(2 * NG * QS + 2 * HDIM <= 512, "dK/dV kernel exceeds TMEM");
+};
 
 struct BwdParams {
   int B, T, H, HKV, nkt, nq64;
@@ -332,13 +373,15 @@ struct BwdParams {
   long long lddv;
 };
 
-template <bool DROP>
-__global__ void __launch_bounds__(BWD_THREADS, 1)
+template <int HDIM, bool DROP>
+__global__ void __launch_bounds__(DkvCfg<HDIM>::THREADS, 1)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                        const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                        const BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int HD = HDIM, NG = DkvCfg<HDIM>::NG, NSTG = DkvCfg<HDIM>::NSTG;
+  constexpr int T2_BYTES = DkvCfg<HDIM>::T2_BYTES, QS_BYTES = DkvCfg<HDIM>::QS_BYTES;
   uint8_t* sK = smem;
   uint8_t* sV = sK + T2_BYTES;
   uint8_t* sQ = sV + T2_BYTES;              // [NSTG] x 8 KB
@@ -399,15 +442,15 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(kv_full, 2 * T2_BYTES);
-      tma_load_2d(sK, &tmK, kv_full, kvh * HD, row_base + kv0);
-      tma_load_2d(sV, &tmV, kv_full, kvh * HD, row_base + kv0);
+      tma_load_tile<HD>(sK, &tmK, kv_full, kvh * HD, row_base + kv0, BK2);
+      tma_load_tile<HD>(sV, &tmV, kv_full, kvh * HD, row_base + kv0, BK2);
       int head = kvh * G, q64 = 2 * kt;
       for (int s = 0; s < steps; ++s) {
         const int stg = s % NSTG;
         mbar_wait(&qdo_empty[stg], ((s / NSTG) & 1) ^ 1);
         mbar_expect_tx(&qdo_full[stg], 2 * QS_BYTES + LD_BYTES);
-        tma_load_2d(sQ + stg * QS_BYTES, &tmQ, &qdo_full[stg], head * HD, row_base + q64 * QS);
-        tma_load_2d(sdO + stg * QS_BYTES, &tmdO, &qdo_full[stg], head * HD, row_base + q64 * QS);
+        tma_load_tile<HD>(sQ + stg * QS_BYTES, &tmQ, &qdo_full[stg], head * HD, row_base + q64 * QS, QS);
+        tma_load_tile<HD>(sdO + stg * QS_BYTES, &tmdO, &qdo_full[stg], head * HD, row_base + q64 * QS, QS);
         bulk_load_1d(sLd + stg * LD_BYTES, p.ld2 + (((long long)b * p.H + head) * p.nq64 + q64) * (2 * QS),
                      LD_BYTES, &qdo_full[stg]);
         if (++q64 == p.nq64) {
@@ -430,10 +473,10 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + C_ST + buf * QS, umma_desc_k128(aK + k * 32), umma_desc_k128(aQ + k * 32), id_s, k > 0);
+          umma_bf16_ss(tmem_base + C_ST + buf * QS, umma_desc_k128(aK + kstep<BK2>(k)), umma_desc_k128(aQ + kstep<QS>(k)), id_s, k > 0);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DPT + buf * QS, umma_desc_k128(aV + k * 32), umma_desc_k128(adO + k * 32), id_s, k > 0);
+          umma_bf16_ss(tmem_base + C_DPT + buf * QS, umma_desc_k128(aV + kstep<BK2>(k)), umma_desc_k128(adO + kstep<QS>(k)), id_s, k > 0);
         umma_commit(&s_full[buf]);
       };
       auto issue_acc = [&](int s) {
@@ -540,13 +583,14 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    // epilogue: groups 0 and 1 write columns [32g, 32g + 32) of dV and dK for their key row
-    if (grp < 2) {
-    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + grp * 32;
-    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + grp * 32;
+    // epilogue: the groups share the 32-column chunks of dV and dK of their key row round-robin
+#pragma unroll 1
+    for (int c32 = grp; c32 < HD / 32; c32 += NG) {
+    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + c32 * 32;
+    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + c32 * 32;
     uint32_t a[32], c2[32];
-    tmem_ld_32x32(tlane + C_DV + grp * 32, a);
-    tmem_ld_32x32(tlane + C_DK + grp * 32, c2);
+    tmem_ld_32x32(tlane + C_DV + c32 * 32, a);
+    tmem_ld_32x32(tlane + C_DK + c32 * 32, c2);
     tmem_ld_wait();
     if (key < p.T) {
 #pragma unroll
@@ -579,7 +623,12 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 // Fused dQ inside the key-tile kernel was limited by the SM's RED issue rate (8192 fp32 atomics per
 // 128x128 step ~ 10.5 k cycles); recomputing S / dP here costs two extra MMAs per tile instead.
 constexpr int DQ_NS = 2;
-constexpr int DQ_SMEM = 2 * Q_BYTES + DQ_NS * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;
+template <int HDIM>
+struct DqCfg {
+  static constexpr int Q_BYTES = BQ * HDIM * 2, KV_BYTES = BKV * HDIM * 2;
+  static constexpr int SMEM = 2 * Q_BYTES + DQ_NS * 2 * KV_BYTES + 2 * P_BYTES + 1024 + 256;   // 97 / 161 KB
+  static constexpr int CTAS = HDIM == 64 ? 2 : 1;
+};
 
 struct DqParams {
   int B, T, H, HKV, nqt;
@@ -591,13 +640,14 @@ struct DqParams {
   long long lddq;
 };
 
-template <bool DROP>
-__global__ void __launch_bounds__(192, 2)
+template <int HDIM, bool DROP>
+__global__ void __launch_bounds__(192, DqCfg<HDIM>::CTAS)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                       const DqParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int HD = HDIM, Q_BYTES = DqCfg<HDIM>::Q_BYTES, KV_BYTES = DqCfg<HDIM>::KV_BYTES;
   uint8_t* sQ = smem;
   uint8_t* sdO = sQ + Q_BYTES;
   uint8_t* sK = sdO + Q_BYTES;
@@ -652,14 +702,14 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(q_full, 2 * Q_BYTES);
-      tma_load_2d(sQ, &tmQ, q_full, head * HD, row_base + q0);
-      tma_load_2d(sdO, &tmdO, q_full, head * HD, row_base + q0);
+      tma_load_tile<HD>(sQ, &tmQ, q_full, head * HD, row_base + q0, BQ);
+      tma_load_tile<HD>(sdO, &tmdO, q_full, head * HD, row_base + q0, BQ);
       for (int j = 0; j < n_kv; ++j) {
         const int s = j % DQ_NS;
         mbar_wait(&kv_empty[s], ((j / DQ_NS) & 1) ^ 1);
         mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
-        tma_load_2d(sK + s * KV_BYTES, &tmK, &kv_full[s], kvh * HD, row_base + j * BKV);
-        tma_load_2d(sV + s * KV_BYTES, &tmV, &kv_full[s], kvh * HD, row_base + j * BKV);
+        tma_load_tile<HD>(sK + s * KV_BYTES, &tmK, &kv_full[s], kvh * HD, row_base + j * BKV, BKV);
+        tma_load_tile<HD>(sV + s * KV_BYTES, &tmV, &kv_full[s], kvh * HD, row_base + j * BKV, BKV);
       }
     }
   } else if (warp == 1) {
@@ -676,10 +726,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const uint32_t aK = smem_u32(sK + s * KV_BYTES), aV = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + D_S, umma_desc_k128(aQ + k * 32), umma_desc_k128(aK + k * 32), id_s, k > 0);
+          umma_bf16_ss(tmem_base + D_S, umma_desc_k128(aQ + kstep<BQ>(k)), umma_desc_k128(aK + kstep<BKV>(k)), id_s, k > 0);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_bf16_ss(tmem_base + D_DP, umma_desc_k128(adO + k * 32), umma_desc_k128(aV + k * 32), id_s, k > 0);
+          umma_bf16_ss(tmem_base + D_DP, umma_desc_k128(adO + kstep<BQ>(k)), umma_desc_k128(aV + kstep<BKV>(k)), id_s, k > 0);
         umma_commit(s_full);
       };
       issue_s(0);
@@ -756,7 +806,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tc_fence_after();
     bf16* orow = p.dq + (long long)(row_base + t) * p.lddq + (long long)head * HD;
 #pragma unroll
-    for (int h2 = 0; h2 < 2; ++h2) {
+    for (int h2 = 0; h2 < HD / 32; ++h2) {
       uint32_t o[32];
       tmem_ld_32x32(tlane + D_DQ + h2 * 32, o);
       tmem_ld_wait();
@@ -781,16 +831,19 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 }
 
 // ld2[b, h, step, 0, j] = lse[b, h, 64*step + j] * log2e (+inf beyond T),
-// ld2[b, h, step, 1, j] = delta = sum_c dO * O (0 beyond T); 8 lanes per (token, head).
+// ld2[b, h, step, 1, j] = delta = sum_c dO * O (0 beyond T); HDIM/8 lanes per (token, head).
+template <int HDIM>
 __global__ void __launch_bounds__(256)
-attn_delta64_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ dout,
-                    long long lddo, const float* __restrict__ lse, float* __restrict__ ld2, long long B,
-                    int T, int H, int nq64) {
+attn_delta_tc_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ dout,
+                     long long lddo, const float* __restrict__ lse, float* __restrict__ ld2, long long B,
+                     int T, int H, int nq64) {
+  constexpr int LPH = HDIM / 8;      // lanes per (token, head)
+  constexpr int IPW = 32 / LPH;      // (token, head) items per warp
   const long long Tpad = (long long)nq64 * QS;
   const long long total = B * Tpad * H;
-  const int lane = threadIdx.x & 31, sub = lane >> 3, l8 = lane & 7;
-  for (long long w = ((long long)blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + sub; w < total + 3;
-       w += (long long)gridDim.x * 8 * 4) {
+  const int lane = threadIdx.x & 31, sub = lane / LPH, l8 = lane % LPH;
+  for (long long w = ((long long)blockIdx.x * 8 + (threadIdx.x >> 5)) * IPW + sub; w < total + IPW - 1;
+       w += (long long)gridDim.x * 8 * IPW) {
     float acc = 0.f;
     const bool ok = w < total;
     const int head = ok ? (int)(w % H) : 0;
@@ -801,14 +854,13 @@ attn_delta64_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __res
     if (real) {
       const long long tok = bb * T + t;
       float a[8], g[8];
-      unpack8(ld_nc_v4(o + tok * ldo + (long long)head * HD + l8 * 8), a);
-      unpack8(ld_nc_v4(dout + tok * lddo + (long long)head * HD + l8 * 8), g);
+      unpack8(ld_nc_v4(o + tok * ldo + (long long)head * HDIM + l8 * 8), a);
+      unpack8(ld_nc_v4(dout + tok * lddo + (long long)head * HDIM + l8 * 8), g);
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc += a[j] * g[j];
     }
-    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+#pragma unroll
+    for (int m = 1; m < LPH; m <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, m);
     if (ok && l8 == 0) {
       float* dst = ld2 + ((bb * H + head) * nq64 + (t >> 6)) * (2 * QS) + (t & 63);
       dst[0] = real ? lse[(bb * H + head) * T + t] * LOG2E : INFINITY;
@@ -819,16 +871,19 @@ attn_delta64_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __res
 
 }  // namespace
 
-size_t b200_attention_bwd_tc64_workspace(int64_t B, int64_t T, int64_t h) {
+size_t b200_attention_bwd_tc_workspace(int64_t B, int64_t T, int64_t h) {
   const int64_t nq64 = (T + QS - 1) / QS;
   return (size_t)(B * h * nq64 * 2 * QS) * 4 + 256;
 }
 
-int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
-                            int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
-                            const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
-                            int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                            int64_t hkv, float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
+namespace {
+template <int HD>
+int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                     const void* o, int64_t ldo, const void* dout, int64_t lddo, const float* lse,
+                     void* workspace, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
+                     int64_t lddv, int64_t B, int64_t T, int64_t h, int64_t hkv, float scale,
+                     float dropout_p, uint64_t seed, cudaStream_t st) {
+  constexpr int DKV_SMEM = DkvCfg<HD>::SMEM, DKV_THREADS = DkvCfg<HD>::THREADS, DQ_SMEM = DqCfg<HD>::SMEM;
   float* ld2 = (float*)workspace;   // cudaMalloc / caching-allocator memory: at least 256-B aligned
   B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
   const long long rows = B * T;
@@ -838,25 +893,26 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     long long blocks = (total + 31) / 32;
     const long long cap = (long long)b200_num_sms() * 16;
     if (blocks > cap) blocks = cap;
-    attn_delta64_kernel<<<(int)blocks, 256, 0, st>>>((const bf16*)o, ldo, (const bf16*)dout, lddo, lse, ld2, B, (int)T, (int)h, nq64);
+    attn_delta_tc_kernel<HD><<<(int)blocks, 256, 0, st>>>((const bf16*)o, ldo, (const bf16*)dout, lddo, lse, ld2, B, (int)T, (int)h, nq64);
     B200_CHECK_LAUNCH();
   }
+  // every map has a 64-column box: a [rows x HD] tile is fetched as HD/64 panels
   CUtensorMap mq, mdo, mk, mv, mk64, mv64;
   int rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, BK2, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mdo, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, BK2, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BK2, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mv, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BK2, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mk64, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BKV, HD))) return rc;
-  if ((rc = b200_make_tmap_2d_bf16(&mv64, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BKV, HD))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, BK2, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mdo, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, BK2, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BK2, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mv, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BK2, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mk64, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BKV, 64))) return rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mv64, v, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldv, BKV, 64))) return rc;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
     attr_set[dev & 63] = true;
   }
   const int nqt = (int)((T + BK2 - 1) / BK2);
@@ -866,16 +922,15 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.scale = scale; p.scale_log2 = scale * LOG2E;
     p.drop = make_drop(dropout_p, seed);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
-    p.drop = make_drop(dropout_p, seed);
     const long long grid = (long long)nqt * B * h;
-    if (p.drop.thr16) attn_bwd_dq_tc_kernel<true><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
-    else attn_bwd_dq_tc_kernel<false><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    else attn_bwd_dq_tc_kernel<HD, false><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
   }
   {
     CUtensorMap mq64, mdo64;
-    if ((rc = b200_make_tmap_2d_bf16(&mq64, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, QS, HD))) return rc;
-    if ((rc = b200_make_tmap_2d_bf16(&mdo64, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, QS, HD))) return rc;
+    if ((rc = b200_make_tmap_2d_bf16(&mq64, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, QS, 64))) return rc;
+    if ((rc = b200_make_tmap_2d_bf16(&mdo64, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, QS, 64))) return rc;
     BwdParams p;
     p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
     p.nkt = nqt; p.nq64 = nq64;
@@ -884,12 +939,25 @@ int b200_attention_bwd_tc64(const void* q, int64_t ldq, const void* k, int64_t l
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     const long long grid = (long long)p.nkt * B * hkv;
-    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<true><<<(unsigned)grid, BWD_THREADS, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
-    else attn_bwd_dkv_tc_kernel<false><<<(unsigned)grid, BWD_THREADS, BWD_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<HD, true><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    else attn_bwd_dkv_tc_kernel<HD, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(3);
   return 0;
+}
+}  // namespace
+
+int b200_attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                          int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
+                          const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
+                          int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
+                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
+  if (hd == 64)
+    return attention_bwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
+                                lddv, B, T, h, hkv, scale, dropout_p, seed, st);
+  return attention_bwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
+                               lddv, B, T, h, hkv, scale, dropout_p, seed, st);
 }
 
 

@@ -213,7 +213,8 @@ def ref_attention(q, k, v, B, T, h, hkv, hd):
 
 
 @pytest.mark.parametrize("B,T,h,hkv,hd", [(2, 256, 4, 2, 64), (1, 100, 2, 2, 64), (2, 517, 8, 2, 64),
-                                          (1, 2048, 4, 1, 64), (2, 192, 4, 2, 128), (1, 77, 2, 1, 128)])
+                                          (1, 2048, 4, 1, 64), (2, 192, 4, 2, 128), (1, 77, 2, 1, 128),
+                                          (2, 517, 4, 4, 128), (1, 2048, 8, 2, 128)])
 def test_attention_fwd_bwd(K, B, T, h, hkv, hd):
     qkv = rnd(B * T, (h + 2 * hkv) * hd, seed=1)
     q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
@@ -229,9 +230,10 @@ def test_attention_fwd_bwd(K, B, T, h, hkv, hd):
     assert rel_err(dv.float(), vr.grad) < BF16_TOL
 
 
-def test_attention_causality_property(K):
+@pytest.mark.parametrize("hd", [64, 128])
+def test_attention_causality_property(K, hd):
     """Size-independent property: output row t must not depend on tokens > t."""
-    B, T, h, hkv, hd = 1, 1024, 4, 2, 64
+    B, T, h, hkv = 1, 1024, 4, 2
     qkv = rnd(B * T, (h + 2 * hkv) * hd, seed=3)
     q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
     o1, _ = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
@@ -256,9 +258,10 @@ def test_dropout_kernel_statistics_and_backward_mask(K):
     assert rel_err(K.dropout(x, p, seed, residual=r).float(), y.float() + r.float()) < 5e-3
 
 
-def test_attention_dropout_matches_oracle_with_same_mask(K):
+@pytest.mark.parametrize("hd", [64, 128])
+def test_attention_dropout_matches_oracle_with_same_mask(K, hd):
     """softmax -> dropout -> @V (GPT2.py:42-46) with the kernel's own keep mask fed to the oracle."""
-    B, T, h, hkv, hd, p, seed = 2, 200, 4, 2, 64, 0.2, 99
+    B, T, h, hkv, p, seed = 2, 200, 4, 2, 0.2, 99
     qkv = rnd(B * T, (h + 2 * hkv) * hd, seed=1)
     q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
     keep = K.attention_dropout_mask(B, h, T, p, seed).float()
