@@ -370,6 +370,7 @@ def main():
             line["debug_layers"] = args.layers
         print(json.dumps(line), flush=True)
     if world > 1:
+        step.close()          # graphs that captured collectives must go before the communicator
         dist.destroy_process_group()
 
 

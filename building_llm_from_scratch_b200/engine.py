@@ -35,17 +35,25 @@ class TrainStep:
         self.pool = None
         self.capacity = 0             # rows the vocab projection sees in the step being built (0 = all)
         self.compact_head = True
-        # Capturing the NCCL all-reduce into the graph works but gained nothing measurable at N=2 and
-        # made process-group teardown hang with the graphs still alive: off unless asked for.
+        # B200_GRAPH_NCCL=1 captures the NCCL all-reduces into the graph (one launch per step, the bucket
+        # all-reduces overlap backward inside it). NCCL refuses to destroy a communicator while graphs
+        # that captured its collectives exist: call close() before destroy_process_group().
         self.capture_collective = os.environ.get("B200_GRAPH_NCCL", "0") == "1"
+        # bucketed all-reduce overlapped with backward (eager steps and captured collectives); with the
+        # default two-graph replay the exchange sits between the graphs and cannot overlap
+        self.overlap = os.environ.get("B200_DDP_OVERLAP", "1") != "0"
+        if self.ddp is not None:
+            self.ddp.attach(self.opt)
         self.bucket_rows = max(128, (batch_shape[0] * batch_shape[1]) // 8)
         self.launches_per_step = 0
         self.opt.graph_safe = True
         self.core.train()
 
     # -- the two halves of a step (split where the data-parallel exchange goes) -------------
-    def _fwd_bwd(self):
+    def _fwd_bwd(self, overlap: bool = False):
         self.opt.zero_grad()
+        if overlap:
+            self.ddp.begin_backward()
         loss = self.core.forward_loss(self.x, self.y, capacity=self.capacity)
         loss.backward()
         self.loss.copy_(loss.detach())
@@ -53,11 +61,26 @@ class TrainStep:
     def _update(self):
         self.opt.step()
 
-    def _eager_step(self):
-        self._fwd_bwd()
-        if self.ddp is not None:
+    def _exchange_step(self):
+        """forward, backward with the gradient mean over ranks (overlapped when enabled), update."""
+        overlap = self.ddp is not None and self.overlap
+        self._fwd_bwd(overlap)
+        if overlap:
+            self.ddp.finish_backward()
+        elif self.ddp is not None:
             self.ddp.reduce_gradients(self.opt.flat_grads)
         self._update()
+
+    def _eager_step(self):
+        self._exchange_step()
+
+    def close(self):
+        """Drop the captured graphs (needed before destroy_process_group() when they hold collectives)."""
+        import gc
+        self.graphs = None
+        self.bucket_graphs = {}
+        gc.collect()
+        torch.cuda.synchronize()
 
     def capture(self, warmup: int = 3):
         """Warm up eagerly on a side stream (lazy initialisation, allocator), then capture."""
@@ -98,9 +121,7 @@ class TrainStep:
             # the NCCL all-reduce is captured too: the whole data-parallel step is ONE graph launch
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, **kw):
-                self._fwd_bwd()
-                self.ddp.reduce_gradients(self.opt.flat_grads)
-                self._update()
+                self._exchange_step()
             if self.pool is None:
                 self.pool = g.pool()
             return (g,)

@@ -181,12 +181,24 @@ _wgrad_queue: list = []
 WGRAD_FLUSH_AT = 16
 
 
+# ddp.B200DDP subscribes here: called with the parameters whose weight-gradient GEMMs have just been
+# launched into main_grad (their gradient is final for this backward once those kernels ran)
+_grad_ready_cb = None
+
+
+def set_grad_ready_callback(cb):
+    global _grad_ready_cb
+    _grad_ready_cb = cb
+
+
 def flush_weight_grads():
     """Issue every queued weight-gradient GEMM (called before the optimizer / all-reduce read main_grad)."""
     global _wgrad_queue
     if _wgrad_queue:
         q, _wgrad_queue = _wgrad_queue, []
         K.gemm_grouped(q)
+        if _grad_ready_cb is not None:
+            _grad_ready_cb([e["param"] for e in q])
 
 
 def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: bool = False):
@@ -195,7 +207,7 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
     if mg is not None:
         if b_mn_src.shape[1] <= 64:      # GEMM N = width of the second operand (the LoRA rank)
             _wgrad_queue.append(dict(a=a_mn_src, b=b_mn_src, out=mg, a_mn=True, b_mn=True, accumulate=True,
-                                     trans_out=trans_out))
+                                     trans_out=trans_out, param=param))
             if len(_wgrad_queue) >= WGRAD_FLUSH_AT:
                 flush_weight_grads()
         elif getattr(param, "_b200_grad_fresh", False) and not trans_out:
@@ -205,6 +217,8 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
             K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg)
         else:
             K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
+        if _grad_ready_cb is not None and b_mn_src.shape[1] > 64:
+            _grad_ready_cb([param])
         return None
     g32 = torch.zeros(param.shape, device=param.device, dtype=torch.float32)
     K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=g32, accumulate=True, trans_out=trans_out)

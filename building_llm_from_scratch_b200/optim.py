@@ -61,10 +61,16 @@ class B200AdamW(torch.optim.Optimizer):
         self.graph_safe = False
 
     # ------------------------------------------------------------------
+    def flush_pending_grads(self):
+        """Everything backward produced is in main_grad after this: queued weight-gradient GEMMs are
+        launched and gradients autograd delivered as .grad (norm weights, biases) are folded in."""
+        from . import ops
+        ops.flush_weight_grads()
+        self._absorb_autograd_grads()
+
     @property
     def flat_grads(self):
-        from . import ops
-        ops.flush_weight_grads()          # queued weight-gradient GEMMs must land before anyone reads main_grad
+        self.flush_pending_grads()        # must land before anyone (all-reduce, norm) reads main_grad
         return [g["g"] for g in self._groups.values()]
 
     def zero_grad(self, set_to_none: bool = True):
