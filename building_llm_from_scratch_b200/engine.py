@@ -56,6 +56,9 @@ class TrainStep:
             self.ddp.begin_backward()
         loss = self.core.forward_loss(self.x, self.y, capacity=self.capacity)
         loss.backward()
+        # weight-gradient GEMMs still queued belong to THIS half of the step: with two graphs and the
+        # all-reduce between them they would otherwise be launched by the optimizer, after the exchange
+        self.opt.flush_pending_grads()
         self.loss.copy_(loss.detach())
 
     def _update(self):

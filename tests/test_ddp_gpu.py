@@ -1,0 +1,90 @@
+"""GPU, world_size 2 over NCCL (skipped on a single-GPU box): after a few TrainStep steps on different
+per-rank batches every rank must hold bit-identical parameters — the all-reduce result is identical on
+all ranks, so any gradient that escaped the exchange (e.g. a weight-gradient GEMM launched after it)
+shows up as divergence. Covers the two-graph replay, captured collectives with overlapped buckets, and
+eager steps."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, mode, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ["B200_GRAPH_NCCL"] = "1" if mode == "graph_nccl" else "0"
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from building_llm_from_scratch_b200.Models.Llama.Llama3 import Llama3Model
+    from building_llm_from_scratch_b200.lora import replace_linear_with_lora
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    from building_llm_from_scratch_b200.ddp import B200DDP
+    from building_llm_from_scratch_b200.train import Trainer
+    from building_llm_from_scratch_b200.engine import TrainStep
+    cfg = dict(vocab_size=1024, context_length=256, emb_dim=256, n_heads=4, n_layers=3, hidden_dim=512,
+               n_kv_groups=2, rope_base=10000.0, rope_freq=None, dtype=torch.bfloat16)
+    torch.manual_seed(123 + rank)                      # ranks start different: the wrapper broadcasts rank 0's
+    dev = torch.device("cuda", rank)
+    model = Llama3Model(cfg).to(dev)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    replace_linear_with_lora(model, rank=16, alpha=32, dtype=torch.bfloat16)
+    model.to(dev)
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("lora.B"):
+                p.normal_(0, 0.02)
+    ddp = B200DDP(model, bucket_mb=0.05)
+    opt = B200AdamW(model.parameters(), lr=1e-3, weight_decay=0.1)
+    tr = Trainer(ddp, opt, cfg, [], None, "/tmp", device=dev, warmup_steps=2)
+    tr.set_schedule(total_training_steps=100, peak_lr=1e-3)
+    step = TrainStep(tr, (2, 256), use_graph=(mode != "eager"))
+    step.compact_head = False
+    step.capture(warmup=2)
+    g = torch.Generator().manual_seed(1000 + rank)
+    for _ in range(4):
+        x = torch.randint(0, 1024, (2, 256), generator=g)
+        y = torch.randint(0, 1024, (2, 256), generator=g)
+        y[rank, :100 * (rank + 1)] = -100
+        step.run(x.to(dev), y.to(dev))
+    torch.cuda.synchronize()
+    flat = torch.cat([g_["p"].float().reshape(-1) for g_ in opt._groups.values()])
+    gathered = [torch.zeros_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    if rank == 0:
+        out.put(dict(equal=bool(torch.equal(gathered[0], gathered[1])),
+                     maxdiff=float((gathered[0] - gathered[1]).abs().max()),
+                     moved=float((flat - flat.mean()).abs().sum()), loss=float(step.loss)))
+    step.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("mode", ["two_graphs", "graph_nccl", "eager"])
+def test_ranks_stay_bit_identical(mode):
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, mode, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=400)
+        assert p.exitcode == 0, f"rank exited with {p.exitcode}"
+    res = out.get()
+    assert res["equal"], f"parameters diverged across ranks by {res['maxdiff']} ({mode})"
+    assert res["loss"] == res["loss"]      # not NaN
