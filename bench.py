@@ -71,6 +71,103 @@ def load_peaks():
     return dict(tf_burst=1590.0, tf_sustained=1400.0, hbm=6650.0, src="fallback")
 
 
+def kernel_rooflines(device, peaks):
+    """Every other kernel of the step against the roofline that bounds it, timed alone with CUDA events
+    (graph replays, a 256 MB write before each call evicts the L2) at the shapes of the bench workload:
+    HBM-bound kernels as algorithmic bytes / time vs the measured copy bandwidth, attention as causal
+    FLOPs / time vs the burst bf16 peak. Not part of the timed steps."""
+    from building_llm_from_scratch_b200 import kernels as K
+    M, d, F, V = MICRO_BATCH * SEQ_LEN, 2048, 8192, 128256
+    B, T, h, hkv, hd = MICRO_BATCH, SEQ_LEN, 32, 8, 64
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    bf = lambda *sh: (torch.randn(*sh, device=device) * 0.5).to(torch.bfloat16)
+
+    def timeit(fn):
+        """ms per call: a graph of 5 x (L2-evicting memset, fn) minus a graph of the 5 memsets alone, so
+        neither the host's launch latency nor the memset is in the number."""
+        fn()
+        torch.cuda.synchronize()
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga):
+            for _ in range(5):
+                flush.zero_()
+        with torch.cuda.graph(gb):
+            for _ in range(5):
+                flush.zero_()
+                fn()
+
+        def run(g):
+            ts = []
+            for _ in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); g.replay(); e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            return sorted(ts)[2]
+        ms = (run(gb) - run(ga)) / 5
+        del ga, gb
+        return ms
+
+    rows = []
+
+    def hbm(name, nbytes, fn):
+        ms = timeit(fn)
+        gbs = nbytes / ms / 1e6
+        rows.append({"kernel": name, "bound": "hbm", "us": round(ms * 1e3, 1), "achieved": round(gbs, 1),
+                     "peak": peaks["hbm"], "unit": "GB/s", "frac": round(gbs / peaks["hbm"], 3)})
+
+    x, r, w = bf(M, d), bf(M, d), torch.ones(d, device=device)
+    hbm("rmsnorm_fwd + residual add [8192x2048] (8 B/elt)", 8 * M * d, lambda: K.rmsnorm_fwd(x, w, res=r))
+    hbm("rmsnorm_bwd [8192x2048] (6 B/elt)", 6 * M * d, lambda: K.rmsnorm_bwd(x, w, r))
+    a, b, dh = bf(M, F), bf(M, F), bf(M, F)
+    hbm("swiglu_fwd [8192x8192] (6 B/elt)", 6 * M * F, lambda: K.swiglu_fwd(a, b))
+    da, db = torch.empty_like(a), torch.empty_like(a)
+    hbm("swiglu_bwd [8192x8192] (10 B/elt)", 10 * M * F, lambda: K.swiglu_bwd(a, b, dh, da=da, db=db))
+    del a, b, dh, da, db
+    cos, sin = bf(T, hd), bf(T, hd)
+    q = bf(M, h * hd)
+    hbm("rope q [8192 x 32 heads x 64] in place (4 B/elt)", 4 * M * h * hd, lambda: K.rope_(q, cos, sin, B, T, h, hd))
+    rows_ce = 4096
+    logits = bf(rows_ce, V)
+    tg = torch.randint(0, V, (rows_ce,), device=device)
+    hbm("cross-entropy fwd+bwd in place [4096x128256] (6 B/logit)", 6 * rows_ce * V, lambda: K.cross_entropy_(logits, tg))
+    del logits
+    n = 53_428_224
+    p_, g_, m_, v_ = (torch.zeros(n, device=device, dtype=torch.bfloat16), torch.zeros(n, device=device),
+                      torch.zeros(n, device=device, dtype=torch.bfloat16), torch.zeros(n, device=device, dtype=torch.bfloat16))
+    hbm("adamw bf16 params, fp32 grads [53.4 M] (16 B/param)", 16 * n, lambda: K.adamw_(p_, g_, m_, v_, 1, 1e-4))
+    hbm("grad-norm fp32 [53.4 M] (4 B/param)", 4 * n, lambda: K.grad_norm(g_))
+    del p_, g_, m_, v_
+    qkv = bf(M, (h + 2 * hkv) * hd)
+    q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
+    do = bf(M, h * hd)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
+    fl = 2.0 * 2 * B * h * T * T * hd / 2
+    for name, flops, fn in (("attention fwd B4 T2048 h32 kv8 hd64 (causal FLOPs)", fl, lambda: K.attention_fwd(q, k, v, B, T, h, hkv, hd)),
+                            ("attention bwd (2.5 x fwd FLOPs)", 2.5 * fl, lambda: K.attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd))):
+        ms = timeit(fn)
+        tf = flops / ms / 1e9
+        rows.append({"kernel": name, "bound": "tensor+mufu", "us": round(ms * 1e3, 1), "achieved": round(tf, 1),
+                     "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(tf / peaks["tf_burst"], 3)})
+    return rows
+
+
+def gemm_traffic_from_profile():
+    """DRAM bytes per launch of the dominant kernel (CTA-pair GEMM) from the committed ncu capture
+    (profiles/r1_gemm_traffic_2layer_step.json: dram__bytes_read.sum + dram__bytes_write.sum summed over the
+    launches of a 2-block step); None if the file is absent."""
+    path = os.path.join(ROOT, "profiles", "r1_gemm_traffic_2layer_step.json")
+    try:
+        d = json.load(open(path))
+        for name, v in d.items():
+            if "2cta" in name:
+                return {"dram_bytes_per_launch": v["dram_bytes"] / v["launches"], "launches": v["launches"],
+                        "tensor_active_pct": v.get("tensor_active_pct"), "source": "profiles/r1_gemm_traffic_2layer_step.json"}
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clocks / throttle reasons with nvidia-smi during the timed region."""
 
@@ -344,6 +441,11 @@ def main():
                 # vocab projection excluded when it is row-compacted) + causal attention
                 "executed_gflops_per_token": (flops / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e9,
                 "step_frac_of_burst_peak_executed": value / world * (flops / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e12 / peaks["tf_burst"]}
+        roof["other_kernels"] = kernel_rooflines(device, peaks)
+        tr_info = gemm_traffic_from_profile()
+        if tr_info is not None:       # bytes per launch of the CTA-pair GEMM, from the committed ncu capture
+            roof["traffic"] = tr_info["dram_bytes_per_launch"]
+            roof["traffic_detail"] = tr_info
     if world > 1:
         dist.barrier()
 

@@ -63,6 +63,11 @@ class MultiHeadAttention(nn.Module):
     def forward(self, x, residual=None):
         b, num_tokens, _ = x.shape
         p_drop = self.dropout.p if self.training else 0.0
+        qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])     # None with qkv_bias
+        if qkv is not None:
+            ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), None, None, b, num_tokens, self.num_heads,
+                                    self.num_heads, self.head_dim, p_drop, ops.new_seed() if p_drop > 0 else 0)[0]
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim,

@@ -61,9 +61,14 @@ class MultiHeadAttention(nn.Module):
 
     def forward(self, x, residual=None):
         b, num_tokens, _ = x.shape
+        cos, sin = self._tables()
+        qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])
+        if qkv is not None:
+            ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), cos, sin, b, num_tokens, self.num_heads,
+                                    self.num_heads, self.head_dim)[0]
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
-        cos, sin = self._tables()
         ctx = ops.attention(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)[0]
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 

@@ -84,10 +84,15 @@ class GroupedQueryAttention(nn.Module):
 
     def forward(self, x, residual=None):
         b, num_tokens, _ = x.shape
-        q, k, v = (t.view(b * num_tokens, -1)
-                   for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         cos = self.cos if self.cos.dtype == torch.bfloat16 else self.cos.to(torch.bfloat16)
         sin = self.sin if self.sin.dtype == torch.bfloat16 else self.sin.to(torch.bfloat16)
+        qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])
+        if qkv is not None:     # one packed projection: RoPE and the backward dX GEMM run once over q|k|v
+            ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), cos, sin, b, num_tokens, self.num_heads,
+                                    self.num_kv_groups, self.head_dim)[0]
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
+        q, k, v = (t.view(b * num_tokens, -1)
+                   for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         ctx = ops.attention(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)[0]
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 

@@ -54,6 +54,10 @@ class FeedForward(nn.Module):
         self.silu = SiLU()
 
     def forward(self, x, residual=None):
-        a, b = ops.linears_of_same_input(x, [self.fc1, self.fc2])
-        h = ops.swiglu(a, b)
+        ab = ops.linears_packed(x, [self.fc1, self.fc2])
+        if ab is not None:
+            h = ops.swiglu_packed(ab)
+        else:
+            a, b = ops.linears_of_same_input(x, [self.fc1, self.fc2])
+            h = ops.swiglu(a, b)
         return self.fc3(h, residual)

@@ -12,7 +12,20 @@ inline int ew_grid(long long nvec, int threads) {
   return (int)blocks;
 }
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+// MUFU.EX2 + MUFU.RCP: the IEEE division this replaces cost more issue slots than the rest of SwiGLU and
+// made the forward kernel instruction-bound (4.5 TB/s) instead of HBM-bound
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+
+// (rows, 16-byte column vectors) launch shape for row-pitched elementwise kernels: blockIdx.x covers
+// the vectors of a row, blockIdx.y strides over rows — no 64-bit division per element
+inline dim3 row_grid(long long M, int vec_per_row, int threads) {
+  long long gx = (vec_per_row + threads - 1) / threads;
+  long long gy = (long long)b200_num_sms() * 16 / gx;
+  if (gy > M) gy = M;
+  if (gy > 65535) gy = 65535;
+  if (gy < 1) gy = 1;
+  return dim3((unsigned)gx, (unsigned)gy);
+}
 
 // ---------------- SwiGLU ----------------
 // Reference (common_components.py:87,123): silu(a) = a * sigmoid(a) -> bf16 each op, then * b.
@@ -20,12 +33,9 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf
 __global__ void __launch_bounds__(256)
 swiglu_fwd_kernel(const bf16* __restrict__ pa, long long lda, const bf16* __restrict__ pb,
                   long long ldb, bf16* __restrict__ h, long long M, int F, int bf16_steps) {
-  const int fv = F >> 3;
-  const long long total = M * fv;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long row = i / fv;
-    const int c = (int)(i % fv) * 8;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= F) return;
+  for (long long row = blockIdx.y; row < M; row += gridDim.y) {
     float a[8], b[8], o[8];
     unpack8(ld_nc_v4(pa + row * lda + c), a);
     unpack8(ld_nc_v4(pb + row * ldb + c), b);
@@ -47,12 +57,9 @@ __global__ void __launch_bounds__(256)
 swiglu_bwd_kernel(const bf16* __restrict__ pa, long long lda, const bf16* __restrict__ pb,
                   long long ldb, const bf16* __restrict__ dh, bf16* __restrict__ pda, long long ldda,
                   bf16* __restrict__ pdb, long long lddb, long long M, int F) {
-  const int fv = F >> 3;
-  const long long total = M * fv;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long row = i / fv;
-    const int c = (int)(i % fv) * 8;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= F) return;
+  for (long long row = blockIdx.y; row < M; row += gridDim.y) {
     float a[8], b[8], g[8], da[8], db[8];
     unpack8(ld_nc_v4(pa + row * lda + c), a);
     unpack8(ld_nc_v4(pb + row * ldb + c), b);
@@ -119,15 +126,16 @@ __global__ void __launch_bounds__(256)
 rope_kernel(const bf16* x, long long ld, bf16* y, long long ldy, const bf16* __restrict__ cosT,
             const bf16* __restrict__ sinT, long long B, int T, int nheads, int hd, int inverse,
             int bf16_steps) {
+  // block = (vectors of one token, tokens): threadIdx.x walks the nheads * vh vectors of a token,
+  // threadIdx.y + blockIdx.x * blockDim.y strides over tokens; 32-bit index arithmetic only
   const int half = hd >> 1;
   const int vh = half >> 3;  // vectors per half head
-  const long long total = B * T * (long long)nheads * vh;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % vh);
-    const long long rest = i / vh;
-    const int head = (int)(rest % nheads);
-    const long long tok = rest / nheads;
+  const int per_tok = nheads * vh;
+  const long long ntok = B * T;
+  for (long long tok = (long long)blockIdx.x * blockDim.y + threadIdx.y; tok < ntok; tok += (long long)gridDim.x * blockDim.y)
+  for (int j = threadIdx.x; j < per_tok; j += blockDim.x) {
+    const int head = j / vh;
+    const int v = j - head * vh;
     const int t = (int)(tok % T);
     const bf16* p1 = x + tok * ld + (long long)head * hd + v * 8;
     const bf16* p2 = p1 + half;
@@ -499,7 +507,7 @@ extern "C" int b200_swiglu_fwd_bf16(const void* a, int64_t lda, const void* b, i
   B200_CHECK_ARG(a && b && h && M > 0 && F > 0, "swiglu_fwd: null pointer or empty");
   B200_CHECK_ARG(F % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && lda >= F && ldb >= F, "swiglu_fwd: F, lda, ldb must be multiples of 8 and pitches >= F");
   B200_CHECK_ARG(b200_aligned16(a) && b200_aligned16(b) && b200_aligned16(h), "swiglu_fwd: pointers must be 16-B aligned");
-  swiglu_fwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+  swiglu_fwd_kernel<<<row_grid(M, (int)(F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
       (const bf16*)a, lda, (const bf16*)b, ldb, (bf16*)h, M, (int)F, bf16_steps);
   B200_CHECK_LAUNCH();
   b200_count_launch();
@@ -513,7 +521,7 @@ extern "C" int b200_swiglu_bwd_bf16(const void* a, int64_t lda, const void* b, i
   B200_CHECK_ARG(F % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldda % 8 == 0 && lddb % 8 == 0,
                  "swiglu_bwd: F and all pitches must be multiples of 8");
   B200_CHECK_ARG(b200_aligned16(a) && b200_aligned16(b) && b200_aligned16(dh) && b200_aligned16(da) && b200_aligned16(db), "swiglu_bwd: pointers must be 16-B aligned");
-  swiglu_bwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+  swiglu_bwd_kernel<<<row_grid(M, (int)(F / 8), 256), 256, 0, (cudaStream_t)stream>>>(
       (const bf16*)a, lda, (const bf16*)b, ldb, (const bf16*)dh, (bf16*)da, ldda, (bf16*)db, lddb, M, (int)F);
   B200_CHECK_LAUNCH();
   b200_count_launch();
@@ -545,8 +553,14 @@ extern "C" int b200_rope_bf16(const void* x, int64_t ldx, void* y, int64_t ldy, 
   B200_CHECK_ARG(hd % 16 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && ldx >= nheads * hd && ldy >= nheads * hd,
                  "rope: hd must be a multiple of 16, pitches multiples of 8 and >= nheads*hd");
   B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y) && b200_aligned16(cos) && b200_aligned16(sin), "rope: pointers must be 16-B aligned");
-  const long long total = B * T * nheads * (hd / 16);
-  rope_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
+  const int per_tok = (int)(nheads * (hd / 16));
+  int bx = 1;
+  while (bx < per_tok && bx < 256) bx <<= 1;           // power of two <= 256 covering a token's vectors
+  const dim3 block((unsigned)bx, (unsigned)(256 / bx));
+  long long blocks = (B * T + block.y - 1) / block.y;
+  const long long cap = (long long)b200_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  rope_kernel<<<(unsigned)blocks, block, 0, (cudaStream_t)stream>>>(
       (const bf16*)x, ldx, (bf16*)y, ldy, (const bf16*)cos, (const bf16*)sin, B, (int)T, (int)nheads, (int)hd, inverse, bf16_steps);
   B200_CHECK_LAUNCH();
   b200_count_launch();

@@ -1,153 +1,208 @@
 // K4 / K4' — RMSNorm and LayerNorm, forward and backward (HBM-bound).
 //
-// One warp owns one row: the row is read once with 128-bit loads, kept in registers, reduced
-// with warp shuffles (no block barrier) and written once. Algorithmic bytes per element:
+// One warp owns one row (RMSNorm: 1-8 cooperating warps, by row width): the row is read once with
+// 128-bit loads, kept in registers, reduced with warp shuffles and written once. Algorithmic bytes per element:
 // fwd 4 B (read x, write y; +4 B with the fused residual add), bwd 6 B (read x, dy; write dx).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
 
 constexpr int WARPS = 8;
 
+// All loads of a row are issued before anything depends on them (plain streaming loads the compiler
+// may batch; lanes past the row end read nothing and hold zeros), so a warp has its whole 4-16 KB in
+// flight at once instead of one 512-byte round trip per 256 columns.
+__device__ __forceinline__ uint4 ld_row_v4(const bf16* p, bool ok) {
+  return ok ? __ldcs(reinterpret_cast<const uint4*>(p)) : make_uint4(0u, 0u, 0u, 0u);
+}
+__device__ __forceinline__ void ld_w8(const float* __restrict__ w, int idx, bool ok, float* ww) {
+  const int c = ok ? idx * 8 : 0;
+  const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + c));
+  const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + c + 4));
+  ww[0] = w0.x; ww[1] = w0.y; ww[2] = w0.z; ww[3] = w0.w;
+  ww[4] = w1.x; ww[5] = w1.y; ww[6] = w1.z; ww[7] = w1.w;
+}
+
+// Row partition shared by the RMSNorm kernels: a row is covered by WPR cooperating warps of the
+// 8-warp CTA (WPR = 1 up to 2048 columns, 2 up to 4096, ...), each lane holding NV <= 8 vectors, so
+// the register footprint does not grow with d. Partial sums meet in shared memory.
+template <int WPR>
+__device__ __forceinline__ void row_sum2(float& a, float& b, float (*red)[2], int warp) {
+  a = warp_sum(a);
+  b = warp_sum(b);
+  if (WPR > 1) {
+    const int lane = threadIdx.x & 31;
+    __syncthreads();                       // previous use of red[] is over
+    if (lane == 0) {
+      red[warp][0] = a;
+      red[warp][1] = b;
+    }
+    __syncthreads();
+    const int w0 = warp - warp % WPR;
+    a = 0.f;
+    b = 0.f;
+#pragma unroll
+    for (int k = 0; k < WPR; ++k) {
+      a += red[w0 + k][0];
+      b += red[w0 + k][1];
+    }
+  }
+}
+
 // ---------------- RMSNorm forward (bf16) ----------------
 // Reference: Models/Llama/common_components.py:66-70. In bf16 eager mode every op rounds:
 // x.pow(2) -> bf16, mean -> bf16 (fp32 accumulate), + eps -> bf16, rsqrt -> bf16,
 // x * r -> bf16, * weight(fp32) -> fp32, .to(bf16).
-template <int MAXV>
+template <int NV, int WPR, bool RES, bool STEPS>
 __global__ void __launch_bounds__(WARPS * 32)
 rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
                    const float* __restrict__ w, bf16* __restrict__ sum_out, bf16* __restrict__ y,
-                   long long M, int d, float eps, int bf16_steps) {
-  const int lane = threadIdx.x & 31;
-  const long long warp0 = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5);
-  const long long nwarps = (long long)gridDim.x * WARPS;
+                   long long M, int d, float eps) {
+  __shared__ float red[WARPS][2];
+  constexpr int RPB = WARPS / WPR;          // rows per CTA pass
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col0 = (warp % WPR) * (NV * 32) + lane;   // first vector of this lane
   const int nvec = d >> 3;
-  for (long long row = warp0; row < M; row += nwarps) {
-    uint4 v[MAXV];
-    float ss = 0.f;
+  for (long long row0 = (long long)blockIdx.x * RPB; row0 < M; row0 += (long long)gridDim.x * RPB) {
+    const long long row = row0 + warp / WPR;
+    const bool rok = row < M;
+    uint4 v[NV], g4[RES ? NV : 1];
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < nvec) {
-        v[i] = ld_nc_v4(x + row * d + idx * 8);
-        float f[8];
-        unpack8(v[i], f);
-        if (res != nullptr) {
-          float g[8];
-          unpack8(ld_nc_v4(res + row * d + idx * 8), g);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = bf16_round(f[j] + g[j]);
-          v[i] = pack8(f);
-          st_v4(sum_out + row * d + idx * 8, v[i]);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ss += bf16_steps ? bf16_round(f[j] * f[j]) : f[j] * f[j];
-      }
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      v[i] = ld_row_v4(x + row * d + idx * 8, rok && idx < nvec);
+      if (RES) g4[i] = ld_row_v4(res + row * d + idx * 8, rok && idx < nvec);
     }
-    ss = warp_sum(ss);
+    float ss = 0.f, unused = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      float f[8];
+      unpack8(v[i], f);
+      if (RES) {
+        float g[8];
+        unpack8(g4[i], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = bf16_round(f[j] + g[j]);
+        v[i] = pack8(f);
+        if (rok && idx < nvec) st_v4(sum_out + row * d + idx * 8, v[i]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += STEPS ? bf16_round(f[j] * f[j]) : f[j] * f[j];
+    }
+    row_sum2<WPR>(ss, unused, red, warp);
     float mean = ss / (float)d;
     float r;
-    if (bf16_steps) {
+    if (STEPS) {
       mean = bf16_round(mean);
       r = bf16_round(rsqrtf(bf16_round(mean + eps)));
     } else {
       r = rsqrtf(mean + eps);
     }
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < nvec) {
-        float f[8];
-        unpack8(v[i], f);
-        const float4 w0 = *reinterpret_cast<const float4*>(w + idx * 8);
-        const float4 w1 = *reinterpret_cast<const float4*>(w + idx * 8 + 4);
-        const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      const bool ok = rok && idx < nvec;
+      float f[8], ww[8];
+      unpack8(v[i], f);
+      ld_w8(w, idx, ok, ww);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float xn = f[j] * r;
-          if (bf16_steps) xn = bf16_round(xn);
-          f[j] = xn * ww[j];
-        }
-        st_v4(y + row * d + idx * 8, pack8(f));
+      for (int j = 0; j < 8; ++j) {
+        float xn = f[j] * r;
+        if (STEPS) xn = bf16_round(xn);
+        f[j] = xn * ww[j];
       }
+      if (ok) st_v4(y + row * d + idx * 8, pack8(f));
     }
   }
 }
 
 // ---------------- RMSNorm backward (bf16) ----------------
-// Two sweeps over the row: the first forms sum(x^2) and sum(dy*w*x) together (the second dot product
-// only needs 1/rms as a factor afterwards), the second writes dx. Only x stays in registers; dy is
-// re-read (an L1/L2 hit: the same warp touched it a few hundred cycles earlier), which halves the
-// register footprint and doubles the resident warps of this bandwidth-bound kernel.
-template <int MAXV, bool HAS_DW>
-__global__ void __launch_bounds__(WARPS * 32, (MAXV <= 8 && !HAS_DW) ? 4 : 1)
+// x and dy of the row are fetched up front and stay in registers (with a weight gradient to
+// accumulate, dy is re-read in the second sweep instead — an L1/L2 hit — to stay within the register
+// file); sum(x^2) and sum(dy*w*x) are formed together (the second only needs 1/rms as a factor
+// afterwards); the residual-stream gradient is fetched at the start of the second sweep.
+template <int NV, int WPR, bool HAS_DW, bool DRES>
+__global__ void __launch_bounds__(WARPS * 32, HAS_DW ? 1 : 2)   // two CTAs per SM: 16 rows in flight
 rmsnorm_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
                    const bf16* __restrict__ dy, const bf16* __restrict__ dres, bf16* __restrict__ dx,
                    float* __restrict__ dw, long long M, int d, float eps) {
-  const int lane = threadIdx.x & 31;
-  const long long warp0 = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5);
-  const long long nwarps = (long long)gridDim.x * WARPS;
+  __shared__ float red[WARPS][2];
+  constexpr int RPB = WARPS / WPR;
+  constexpr bool KEEP_G = !HAS_DW;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col0 = (warp % WPR) * (NV * 32) + lane;
   const int nvec = d >> 3;
-  float dwacc[HAS_DW ? MAXV * 8 : 1];
+  float dwacc[HAS_DW ? NV * 8 : 1];
   if (HAS_DW) {
 #pragma unroll
-    for (int i = 0; i < (HAS_DW ? MAXV * 8 : 1); ++i) dwacc[i] = 0.f;
+    for (int i = 0; i < (HAS_DW ? NV * 8 : 1); ++i) dwacc[i] = 0.f;
   }
-  for (long long row = warp0; row < M; row += nwarps) {
-    uint4 vx[MAXV];
+  for (long long row0 = (long long)blockIdx.x * RPB; row0 < M; row0 += (long long)gridDim.x * RPB) {
+    const long long row = row0 + warp / WPR;
+    const bool rok = row < M;
+    uint4 vx[NV], vg[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      vx[i] = ld_row_v4(x + row * d + idx * 8, rok && idx < nvec);
+      vg[i] = ld_row_v4(dy + row * d + idx * 8, rok && idx < nvec);
+    }
     float ss = 0.f, dot = 0.f;   // sum x^2, sum dy*w*x
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < nvec) {
-        vx[i] = ld_nc_v4(x + row * d + idx * 8);
-        float f[8], g[8];
-        unpack8(vx[i], f);
-        unpack8(ld_v4(dy + row * d + idx * 8), g);
-        const float4 w0 = *reinterpret_cast<const float4*>(w + idx * 8);
-        const float4 w1 = *reinterpret_cast<const float4*>(w + idx * 8 + 4);
-        const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      float f[8], g[8], ww[8];
+      unpack8(vx[i], f);
+      unpack8(vg[i], g);
+      ld_w8(w, idx, idx < nvec, ww);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          ss += f[j] * f[j];
-          dot += g[j] * ww[j] * f[j];
-        }
+      for (int j = 0; j < 8; ++j) {
+        ss += f[j] * f[j];
+        dot += g[j] * ww[j] * f[j];
       }
     }
-    ss = warp_sum(ss);
-    dot = warp_sum(dot);
+    row_sum2<WPR>(ss, dot, red, warp);
     const float r = rsqrtf(ss / (float)d + eps);
     const float c = dot * r / (float)d;   // mean(g * xn), xn = x * r
+    uint4 ve[DRES ? NV : 1];
+    if (DRES || !KEEP_G) {
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
-      if (idx < nvec) {
-        float f[8], g[8], o[8];
-        unpack8(vx[i], f);
-        unpack8(ld_v4(dy + row * d + idx * 8), g);
-        const float4 w0 = *reinterpret_cast<const float4*>(w + idx * 8);
-        const float4 w1 = *reinterpret_cast<const float4*>(w + idx * 8 + 4);
-        const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float xn = f[j] * r;
-          o[j] = r * (g[j] * ww[j] - xn * c);
-          if (HAS_DW) dwacc[i * 8 + j] += g[j] * xn;
-        }
-        if (dres != nullptr) {
-          float e[8];
-          unpack8(ld_nc_v4(dres + row * d + idx * 8), e);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] += e[j];
-        }
-        st_v4(dx + row * d + idx * 8, pack8(o));
+      for (int i = 0; i < NV; ++i) {
+        const int idx = col0 + 32 * i;
+        if (DRES) ve[i] = ld_row_v4(dres + row * d + idx * 8, rok && idx < nvec);
+        if (!KEEP_G) vg[i] = ld_row_v4(dy + row * d + idx * 8, rok && idx < nvec);
       }
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
+      const bool ok = rok && idx < nvec;
+      float f[8], g[8], o[8], ww[8];
+      unpack8(vx[i], f);
+      unpack8(vg[i], g);
+      ld_w8(w, idx, idx < nvec, ww);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xn = f[j] * r;
+        o[j] = r * (g[j] * ww[j] - xn * c);
+        if (HAS_DW) dwacc[i * 8 + j] += g[j] * xn;
+      }
+      if (DRES) {
+        float e[8];
+        unpack8(ve[i], e);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += e[j];
+      }
+      if (ok) st_v4(dx + row * d + idx * 8, pack8(o));
     }
   }
   if (HAS_DW) {
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int idx = lane + 32 * i;
+    for (int i = 0; i < NV; ++i) {
+      const int idx = col0 + 32 * i;
       if (idx < nvec) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) atomicAdd(&dw[idx * 8 + j], dwacc[i * 8 + j]);
@@ -350,6 +405,28 @@ int grid_for_rows(long long M) {
     else { CALL(64); }                         \
   } while (0)
 
+// (vectors per lane, warps per row) for a row of d columns. Many light warps beat few heavy ones:
+// at d = 2048, 2 warps x 4 vectors ran the backward in 20.9 us against 27.2 us for 1 warp x 8 vectors
+// (more CTAs resident, loads of one row overlap the arithmetic of another).
+#define DISPATCH_ROW(d, CALL)                      \
+  do {                                             \
+    if ((d) <= 1024) { CALL(4, 1); }               \
+    else if ((d) <= 2048) { CALL(4, 2); }          \
+    else if ((d) <= 4096) { CALL(4, 4); }          \
+    else if ((d) <= 8192) { CALL(8, 4); }          \
+    else { CALL(8, 8); }                           \
+  } while (0)
+
+namespace {
+int grid_for_rows_wpr(long long M, long long d) {
+  const int wpr = d <= 1024 ? 1 : (d <= 2048 ? 2 : (d <= 8192 ? 4 : 8));
+  const long long rpb = WARPS / wpr;
+  const long long blocks = (M + rpb - 1) / rpb;
+  const long long cap = (long long)b200_num_sms() * 8;
+  return (int)(blocks < cap ? blocks : cap);
+}
+}  // namespace
+
 extern "C" int b200_rmsnorm_fwd_bf16(const void* x, const void* res, const float* w, void* sum_out,
                                      void* y, int64_t M, int64_t d, float eps, int bf16_steps,
                                      void* stream) {
@@ -358,10 +435,21 @@ extern "C" int b200_rmsnorm_fwd_bf16(const void* x, const void* res, const float
   B200_CHECK_ARG(res == nullptr || sum_out != nullptr, "rmsnorm_fwd: res given without sum_out");
   B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y) && b200_aligned16(w), "rmsnorm_fwd: pointers must be 16-B aligned");
   cudaStream_t st = (cudaStream_t)stream;
-  const int grid = grid_for_rows(M);
-#define CALL(NV) rmsnorm_fwd_kernel<NV><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)res, w, (bf16*)sum_out, (bf16*)y, M, (int)d, eps, bf16_steps)
-  DISPATCH_MAXV(d, CALL);
+  const int grid = grid_for_rows_wpr(M, d);
+#define FWD_ARGS (const bf16*)x, (const bf16*)res, w, (bf16*)sum_out, (bf16*)y, M, (int)d, eps
+#define CALL(NV, WPR)                                                                                    \
+  do {                                                                                                   \
+    if (res != nullptr) {                                                                                \
+      if (bf16_steps) rmsnorm_fwd_kernel<NV, WPR, true, true><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);   \
+      else rmsnorm_fwd_kernel<NV, WPR, true, false><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);             \
+    } else {                                                                                             \
+      if (bf16_steps) rmsnorm_fwd_kernel<NV, WPR, false, true><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);  \
+      else rmsnorm_fwd_kernel<NV, WPR, false, false><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);            \
+    }                                                                                                    \
+  } while (0)
+  DISPATCH_ROW(d, CALL);
 #undef CALL
+#undef FWD_ARGS
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -372,19 +460,22 @@ extern "C" int b200_rmsnorm_bwd_bf16(const void* x, const float* w, const void* 
                                      float eps, void* stream) {
   B200_CHECK_ARG(x && w && dy && dx && M > 0, "rmsnorm_bwd: null pointer or empty");
   B200_CHECK_ARG(d % 8 == 0 && d > 0 && d <= 16384, "rmsnorm_bwd: d=%lld must be a multiple of 8 and <= 16384", (long long)d);
-  B200_CHECK_ARG(dw == nullptr || d <= 4096, "rmsnorm_bwd: weight gradient supported for d <= 4096");
   cudaStream_t st = (cudaStream_t)stream;
-  const int grid = grid_for_rows(M);
-  if (dw) {
-    const int nv = (int)((d / 8 + 31) / 32);
-#define CALLW(NV) rmsnorm_bwd_kernel<NV, true><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, w, (const bf16*)dy, (const bf16*)dres_in, (bf16*)dx, dw, M, (int)d, eps)
-    if (nv <= 4) { CALLW(4); } else if (nv <= 8) { CALLW(8); } else { CALLW(16); }
-#undef CALLW
-  } else {
-#define CALL(NV) rmsnorm_bwd_kernel<NV, false><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, w, (const bf16*)dy, (const bf16*)dres_in, (bf16*)dx, nullptr, M, (int)d, eps)
-    DISPATCH_MAXV(d, CALL);
+  const int grid = grid_for_rows_wpr(M, d);
+#define BWD_ARGS (const bf16*)x, w, (const bf16*)dy, (const bf16*)dres_in, (bf16*)dx, dw, M, (int)d, eps
+#define CALL(NV, WPR)                                                                                   \
+  do {                                                                                                  \
+    if (dw) {                                                                                           \
+      if (dres_in) rmsnorm_bwd_kernel<NV, WPR, true, true><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);     \
+      else rmsnorm_bwd_kernel<NV, WPR, true, false><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);            \
+    } else {                                                                                            \
+      if (dres_in) rmsnorm_bwd_kernel<NV, WPR, false, true><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);    \
+      else rmsnorm_bwd_kernel<NV, WPR, false, false><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);           \
+    }                                                                                                   \
+  } while (0)
+  DISPATCH_ROW(d, CALL);
 #undef CALL
-  }
+#undef BWD_ARGS
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;

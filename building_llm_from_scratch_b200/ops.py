@@ -14,6 +14,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence, Tuple
 
+import os
+
 import torch
 from torch import Tensor
 
@@ -357,6 +359,154 @@ def linears_of_same_input(x, modules):
     return out[:n]
 
 
+# --------------------------------------------------------------------------------------
+# The same family with ONE packed output [.., sum(out_i)] (q|k|v, fc1|fc2): the consumers
+# (attention_qkv, swiglu_packed) read column ranges of it in place and hand back ONE packed gradient,
+# so backward is a single dX GEMM over K = sum(out_i) (+ n*r for LoRA) against the row-concatenated
+# frozen weights instead of n GEMMs chained through residual-accumulate epilogues.
+# --------------------------------------------------------------------------------------
+_wcat_cache: dict = {}
+
+
+def _packed_weight(weights):
+    """cat(weights, dim=0) for FROZEN weights, built once and rebuilt when any of them is written to
+    (load_state_dict bumps the version counters); None when a weight is trainable."""
+    if any(w.requires_grad for w in weights):
+        return None
+    key = tuple(w.data_ptr() for w in weights)
+    ver = tuple(w._version for w in weights)
+    hit = _wcat_cache.get(key)
+    if hit is None or hit[0] != ver:
+        with torch.no_grad():
+            hit = (ver, torch.cat([w.detach() for w in weights], dim=0).contiguous())
+        _wcat_cache[key] = hit
+    return hit[1]
+
+
+@torch.library.custom_op("b200llm::lora_linear_packed", mutates_args=())
+def lora_linear_packed(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor], Bs: Sequence[Tensor],
+                       scaling: float, w_cat: Optional[Tensor]) -> List[Tensor]:
+    """-> [y_packed [.., sum(out_i)], t_cat [M, n*r]] with y_packed[.., off_i:off_i+out_i] =
+    x W_i^T + scaling (x A_i) B_i and t_cat[:, i*r:(i+1)*r] = scaling x A_i."""
+    x2 = _flat2d(x)
+    M = x2.shape[0]
+    n = len(weights)
+    total = sum(w.shape[0] for w in weights)
+    y = x2.new_empty((M, total))
+    if len(As) > 0:
+        r = As[0].shape[1]
+        t_cat = x2.new_empty((M, n * r))
+        K.gemm_grouped([dict(a=x2, b=As[i], out=t_cat[:, i * r:(i + 1) * r], b_mn=True, alpha=scaling) for i in range(n)])
+    else:
+        t_cat = x2.new_empty((0,))
+    off = 0
+    for i, w in enumerate(weights):
+        o = y[:, off:off + w.shape[0]]
+        if len(As) > 0:
+            K.gemm_ex(x2, w, a2=t_cat[:, i * r:(i + 1) * r], b2=_pitch_ok(Bs[i]), b2_mn=True, out=o)
+        else:
+            K.gemm_ex(x2, w, out=o)
+        off += w.shape[0]
+    return [y.view(*x.shape[:-1], total), t_cat]
+
+
+@lora_linear_packed.register_fake
+def _(x, weights, As, Bs, scaling, w_cat):
+    rows = x.numel() // x.shape[-1]
+    total = sum(w.shape[0] for w in weights)
+    t = x.new_empty((rows, len(As) * As[0].shape[1])) if len(As) > 0 else x.new_empty((0,))
+    return [x.new_empty((*x.shape[:-1], total)), t]
+
+
+def _llp_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    x, weights, As, Bs, scaling, w_cat = inputs
+    ctx.n, ctx.lora, ctx.scaling = len(weights), len(As) > 0, scaling
+    ctx.has_cat = w_cat is not None
+    ctx.save_for_backward(x, *weights, *As, *Bs, output[1], *([w_cat] if w_cat is not None else []))
+
+
+def _llp_bwd(ctx, grads):
+    n = ctx.n
+    saved = ctx.saved_tensors
+    x = saved[0]
+    weights = saved[1:1 + n]
+    As = saved[1 + n:1 + 2 * n] if ctx.lora else ()
+    Bs = saved[1 + 2 * n:1 + 3 * n] if ctx.lora else ()
+    pos = 1 + (3 * n if ctx.lora else n)
+    t_cat = saved[pos]
+    w_cat = saved[pos + 1] if ctx.has_cat else None
+    none = (None, [None] * n, [None] * len(As), [None] * len(Bs), None, None)
+    if grads[0] is None:
+        return none
+    dy = _flat2d(grads[0])
+    if dy.stride(1) != 1:
+        dy = dy.contiguous()
+    x2 = _flat2d(x)
+    offs = [0]
+    for w in weights:
+        offs.append(offs[-1] + w.shape[0])
+    dys = [dy[:, offs[i]:offs[i + 1]] for i in range(n)]
+    need_x = ctx.needs_input_grad[0]
+    need_a = ctx.lora and any(A.requires_grad for A in As)
+    u_cat, r = None, 0
+    if ctx.lora and (need_x or need_a):
+        r = As[0].shape[1]
+        u_cat = dy.new_empty((dy.shape[0], n * r))
+        K.gemm_grouped([dict(a=dys[i], b=_pitch_ok(Bs[i]), out=u_cat[:, i * r:(i + 1) * r], alpha=ctx.scaling)
+                        for i in range(n)])
+    dx = None
+    if need_x:
+        if w_cat is not None:
+            # dX = dY_packed W_cat + u_cat A_cat^T : one launch over K = sum(out_i) + n*r
+            if ctx.lora:
+                a_cat = torch.cat(list(As), dim=1)
+                dx = K.gemm_ex(dy, w_cat, b1_mn=True, a2=u_cat, b2=a_cat)
+            else:
+                dx = K.gemm_ex(dy, w_cat, b1_mn=True)
+        else:
+            for i in range(n):
+                kw = dict(a2=u_cat[:, i * r:(i + 1) * r], b2=As[i]) if ctx.lora else {}
+                dx = K.gemm_ex(dys[i], weights[i], b1_mn=True, residual=dx, out=dx, **kw)
+        dx = dx.view(x.shape)
+    dWs = [None] * n
+    dAs = [None] * n if ctx.lora else []
+    dBs = [None] * n if ctx.lora else []
+    for i in range(n):
+        if ctx.lora and need_a and As[i].requires_grad:
+            dAs[i] = _weight_grad(x2, u_cat[:, i * r:(i + 1) * r], As[i])
+        if ctx.lora and Bs[i].requires_grad:
+            dBs[i] = _weight_grad(dys[i], t_cat[:, i * r:(i + 1) * r], Bs[i], trans_out=True)
+        if weights[i].requires_grad:
+            dWs[i] = _weight_grad(dys[i], x2, weights[i])
+    return dx, dWs, dAs, dBs, None, None
+
+
+lora_linear_packed.register_autograd(_llp_bwd, setup_context=_llp_setup)
+
+
+def linears_packed(x, modules):
+    """Packed output of several bias-free linears (all plain or all LoRA-wrapped with one scaling and one
+    rank) of the same x, or None when they cannot be fused that way."""
+    if os.environ.get("B200_PACKED", "1") == "0":
+        return None
+    from .lora import LinearWithLoRA
+    lora = [isinstance(m, LinearWithLoRA) for m in modules]
+    bases = [m.linear if l else m for m, l in zip(modules, lora)]
+    if any(b.bias is not None for b in bases) or (any(lora) and not all(lora)):
+        return None
+    if any(b.weight.shape[0] % 8 for b in bases):
+        return None
+    weights = [b.weight for b in bases]
+    if all(lora):
+        scal, r = modules[0].lora.scaling, modules[0].lora.A.shape[1]
+        if any(m.lora.scaling != scal or m.lora.A.shape[1] != r for m in modules) or r % 8:
+            return None
+        return lora_linear_packed(x, weights, [m.lora.A for m in modules], [m.lora.B for m in modules], scal,
+                                  _packed_weight(weights))[0]
+    return lora_linear_packed(x, weights, [], [], 0.0, _packed_weight(weights))[0]
+
+
 def linear(x, weight, bias=None, residual=None):
     return lora_linear(x, weight, bias, None, None, 0.0, residual)[0]
 
@@ -415,6 +565,57 @@ def _attention_bwd(ctx, do, _dl, _dq, _dk):
 attention.register_autograd(_attention_bwd, setup_context=_attention_setup)
 
 
+@torch.library.custom_op("b200llm::attention_qkv", mutates_args=())
+def attention_qkv(qkv: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: int, T: int, h: int, hkv: int,
+                  hd: int, dropout_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
+    """attention() on a packed [B*T, (h + 2 hkv) * hd] projection (q heads | k heads | v heads):
+    RoPE of q and k is one launch, the kernels read the column ranges in place. -> (o, lse, qk_rot)."""
+    qkv = _flat2d(qkv)
+    nq, nk = h * hd, hkv * hd
+    if cos is not None:
+        qk = K.rope(qkv, cos, sin, B, T, h + hkv, hd)          # [M, (h + hkv) * hd]
+    else:
+        qk = qkv
+    o, lse = K.attention_fwd(qk[:, :nq], qk[:, nq:nq + nk], qkv[:, nq + nk:], B, T, h, hkv, hd,
+                             dropout_p=dropout_p, seed=seed)
+    return o, lse, (qk if cos is not None else qkv.new_empty((0,)))
+
+
+@attention_qkv.register_fake
+def _(qkv, cos, sin, B, T, h, hkv, hd, dropout_p=0.0, seed=0):
+    o, lse = qkv.new_empty((B * T, h * hd)), qkv.new_empty((B, h, T), dtype=torch.float32)
+    return o, lse, (qkv.new_empty((B * T, (h + hkv) * hd)) if cos is not None else qkv.new_empty((0,)))
+
+
+def _attention_qkv_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    qkv, cos, sin, B, T, h, hkv, hd, dropout_p, seed = inputs
+    o, lse, qk = output
+    ctx.save_for_backward(qkv, qk, o, lse, cos, sin)
+    ctx.dims = (B, T, h, hkv, hd)
+    ctx.drop = (dropout_p, seed)
+
+
+def _attention_qkv_bwd(ctx, do, _dl, _dqk):
+    if do is None:
+        return (None,) * 10
+    qkv, qk, o, lse, cos, sin = ctx.saved_tensors
+    B, T, h, hkv, hd = ctx.dims
+    nq, nk = h * hd, hkv * hd
+    qkv2 = _flat2d(qkv)
+    src = qk if cos is not None else qkv2
+    dqkv = qkv2.new_empty(qkv2.shape)
+    K.attention_bwd(src[:, :nq], src[:, nq:nq + nk], qkv2[:, nq + nk:], o, _flat2d(do), lse, B, T, h, hkv, hd,
+                    dq=dqkv[:, :nq], dk=dqkv[:, nq:nq + nk], dv=dqkv[:, nq + nk:], dropout_p=ctx.drop[0],
+                    seed=ctx.drop[1])
+    if cos is not None:
+        K.rope_(dqkv, cos, sin, B, T, h + hkv, hd, inverse=True)      # q and k heads in one launch
+    return (dqkv.view(qkv.shape),) + (None,) * 9
+
+
+attention_qkv.register_autograd(_attention_qkv_bwd, setup_context=_attention_qkv_setup)
+
+
 # ======================================================================================
 # dropout (nn.Dropout sites of Models/GPT2/GPT2.py:24,81,102)
 # ======================================================================================
@@ -470,6 +671,35 @@ def _swiglu_bwd(ctx, dh):
 
 
 swiglu.register_autograd(_swiglu_bwd, setup_context=_swiglu_setup)
+
+
+@torch.library.custom_op("b200llm::swiglu_packed", mutates_args=())
+def swiglu_packed(ab: Tensor) -> Tensor:
+    """swiglu() on a packed [.., 2F] = (fc1 x | fc2 x); backward writes one packed [.., 2F] gradient."""
+    ab2 = _flat2d(ab)
+    F = ab2.shape[1] // 2
+    return K.swiglu_fwd(ab2[:, :F], ab2[:, F:]).view(*ab.shape[:-1], F)
+
+
+@swiglu_packed.register_fake
+def _(ab):
+    return ab.new_empty((*ab.shape[:-1], ab.shape[-1] // 2))
+
+
+def _swiglu_packed_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0])
+
+
+def _swiglu_packed_bwd(ctx, dh):
+    (ab,) = ctx.saved_tensors
+    ab2 = _flat2d(ab)
+    F = ab2.shape[1] // 2
+    dab = ab2.new_empty(ab2.shape)
+    K.swiglu_bwd(ab2[:, :F], ab2[:, F:], dh.contiguous(), da=dab[:, :F], db=dab[:, F:])
+    return dab.view(ab.shape)
+
+
+swiglu_packed.register_autograd(_swiglu_packed_bwd, setup_context=_swiglu_packed_setup)
 
 
 @torch.library.custom_op("b200llm::gelu", mutates_args=())

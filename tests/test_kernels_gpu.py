@@ -26,7 +26,7 @@ def rnd(*shape, scale=1.0, seed=0, dtype=torch.bfloat16):
 
 
 # ------------------------------------------------------------------ RMSNorm
-@pytest.mark.parametrize("M,d", [(8192, 2048), (333, 4096), (7, 64), (100, 1600), (64, 8192)])
+@pytest.mark.parametrize("M,d", [(8192, 2048), (333, 4096), (7, 64), (100, 1600), (64, 8192), (50, 5120), (9, 16384)])
 def test_rmsnorm_bf16_matches_reference_roundings(K, M, d):
     from oracle import reference_ops as R
     x, w = rnd(M, d, scale=2.0, seed=1), (1 + 0.1 * rnd(d, seed=2, dtype=torch.float32))
@@ -68,6 +68,25 @@ def test_rmsnorm_golden_and_dw_and_residual(K, golden):
     dx, _ = K.rmsnorm_bwd(s, wt, gy := rnd(300, 2048, seed=8), dres=dres)
     dx0, _ = K.rmsnorm_bwd(s, wt, gy)
     assert rel_err(dx.float(), dx0.float() + dres.float()) < 1e-2
+
+
+@pytest.mark.parametrize("M,d", [(257, 1024), (130, 4096), (35, 8192), (10, 16384)])
+def test_rmsnorm_wide_rows_weight_gradient_and_residual_stream(K, M, d):
+    """Rows covered by several cooperating warps: weight gradient, residual-stream gradient and fused
+    residual add at every width class, ragged row counts."""
+    from oracle import reference_ops as R
+    x, r = rnd(M, d, seed=11), rnd(M, d, seed=12)
+    w = 1 + 0.1 * rnd(d, seed=13, dtype=torch.float32)
+    y, s = K.rmsnorm_fwd(x, w, res=r)
+    assert torch.equal(s, x + r)
+    assert rel_err(y.float(), R.rmsnorm(x + r, w).float()) < 2e-3
+    gy, dres = rnd(M, d, seed=14), rnd(M, d, seed=15)
+    xr = x.float().requires_grad_(True)
+    wr = w.clone().requires_grad_(True)
+    R.rmsnorm(xr, wr).backward(gy.float())
+    dx, dw = K.rmsnorm_bwd(x, w, gy, dres=dres, need_dw=True)
+    assert rel_err(dx.float(), xr.grad + dres.float()) < BF16_TOL
+    assert rel_err(dw, wr.grad) < BF16_TOL
 
 
 # ------------------------------------------------------------------ LayerNorm / GELU

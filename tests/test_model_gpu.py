@@ -312,3 +312,37 @@ def test_generate_and_evaluate_paths(golden, tmp_path):
     tr.save_checkpoint("model_pg_test.pth")
     saved = torch.load(tmp_path / "model_pg_test.pth", weights_only=False)
     assert "trf_blocks.0.att.mask" in saved and "out_head.lora.A" in saved
+
+
+def test_packed_projections_match_separate_ones(golden, monkeypatch):
+    """q|k|v and fc1|fc2 as one packed projection (single RoPE launch, one backward dX GEMM against the
+    row-concatenated frozen weights) against the one-GEMM-per-linear path on the same LoRA model."""
+    g = golden("llama_model.pt")
+    x, y = g["x"].cuda(), g["y"].cuda()
+    results = []
+    for packed in ("1", "0"):
+        monkeypatch.setenv("B200_PACKED", packed)
+        model, opt = build_llama(g, fused_opt=True)
+        opt.zero_grad()
+        h = model.tok_emb(x).detach().requires_grad_(True)        # exposes dX of the first block
+        out = model.trf_blocks[0](h)
+        out.float().square().mean().backward()
+        loss = model.forward_loss(x, y)
+        loss.backward()
+        opt.flush_pending_grads()
+        results.append((out.detach().float(), h.grad.float(), float(loss),
+                        {k: p.main_grad.clone() for k, p in model.named_parameters() if p.requires_grad}))
+    (o1, d1, l1, g1), (o0, d0, l0, g0) = results
+    assert rel_err(o1, o0) < 1e-2 and rel_err(d1, d0) < BF16_TOL
+    assert abs(l1 - l0) < 1e-2 * abs(l0)
+    for k in g0:
+        assert close(g1[k], g0[k], 5e-2, atol=1e-6), (k, rel_err(g1[k], g0[k]))
+    # a frozen weight written to (load_state_dict) invalidates the cached row-concatenation
+    from building_llm_from_scratch_b200 import ops
+    att = model.trf_blocks[0].att
+    ws = [att.W_query.linear.weight, att.W_key.linear.weight, att.W_value.linear.weight]
+    c1 = ops._packed_weight(ws)
+    with torch.no_grad():
+        ws[1].mul_(2.0)
+    c2 = ops._packed_weight(ws)
+    assert torch.equal(c2, torch.cat(ws, 0)) and not torch.equal(c1, c2)
