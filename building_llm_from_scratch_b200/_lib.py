@@ -43,6 +43,8 @@ SIGNATURES = {
     "b200_gemm_nt_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, I, P]),
     "b200_gemm_ex": (I, [P, I64, I, P, I64, I, I64, P, I64, I, P, I64, I, I64, P, P, I64, P, I64,
                          I64, I64, I, I, I, I, F, I, P]),
+    "b200_gemm_workspace_bytes": (SZ, []),
+    "b200_gemm_set_workspace": (I, [P, SZ]),
     "b200_gemm_grouped_bf16": (I, [I, C.POINTER(GemmProblem), P]),
     "b200_gemm_grouped_workspace_bytes": (SZ, [I, C.POINTER(GemmProblem)]),
     "b200_gemm_grouped_streamk_bf16": (I, [I, C.POINTER(GemmProblem), P, SZ, P]),

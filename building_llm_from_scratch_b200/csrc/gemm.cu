@@ -43,6 +43,12 @@ struct GemmParams {
   int splits;
   int m_tiles, n_tiles;
   int n_fastest;   // pair kernel: walk the N tiles of an M tile-row back to back (A row stays in L2)
+  // pair kernel, tail splitting: tiles >= tail_start are each cut into tail_splits K ranges so the last,
+  // partly filled wave of tiles keeps every CTA pair busy; partial sums meet in tail_ws (fp32, zero
+  // between launches), tail_cnt counts the arrivals per (tile, CTA of the pair)
+  int tail_start, tail_splits;
+  float* tail_ws;
+  int* tail_cnt;
   int flags;
   float alpha;
   const bf16* bias;
@@ -51,6 +57,9 @@ struct GemmParams {
   void* C;
   long long ldc;
 };
+
+// barrier over the 4 epilogue warps (threads 128..255) of a CTA
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
@@ -409,20 +418,38 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   pdl_wait();
 
   const int total_kb = p.kb1 + p.kb2;
-  const int num_work = p.m_tiles * p.n_tiles;          // m_tiles counts 256-row tiles here
+  const int num_tiles = p.m_tiles * p.n_tiles;         // m_tiles counts 256-row tiles here
+  const int num_work = p.tail_start + (num_tiles - p.tail_start) * p.tail_splits;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
+  __shared__ int s_last;
+  // work unit -> (tile, K block range); units past tail_start are the K splits of the tail tiles
+  auto unit = [&](int w, int& tile, int& kb_begin, int& kb_end) {
+    if (w < p.tail_start) {
+      tile = w;
+      kb_begin = 0;
+      kb_end = total_kb;
+    } else {
+      const int j = w - p.tail_start;
+      tile = p.tail_start + j / p.tail_splits;
+      const int sp = j % p.tail_splits;
+      kb_begin = (int)((long long)sp * total_kb / p.tail_splits);
+      kb_end = (int)((long long)(sp + 1) * total_kb / p.tail_splits);
+    }
+  };
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int w = cluster_id; w < num_work; w += num_clusters) {
-        const int m_blk = p.n_fastest ? w / p.n_tiles : w % p.m_tiles;
-        const int n_blk = p.n_fastest ? w % p.n_tiles : w / p.m_tiles;
+        int tile, kb_begin, kb_end;
+        unit(w, tile, kb_begin, kb_end);
+        const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
+        const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
         const int m0 = m_blk * 256 + (int)rank * 128;
         const int n0 = n_blk * P_BN + (int)rank * 128;
-        for (int kb = 0; kb < total_kb; ++kb) {
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&full[stage], 2 * P_STAGE_BYTES);
           uint8_t* sa = smem + stage * P_STAGE_BYTES;
@@ -463,7 +490,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         mbar_wait(&tempty[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * P_BN);
-        for (int kb = 0; kb < total_kb; ++kb) {
+        int tile, kb_begin, kb_end;
+        unit(w, tile, kb_begin, kb_end);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * P_STAGE_BYTES);
@@ -476,7 +505,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = a_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
             const uint64_t bd = b_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
-            umma_bf16_ss_2cta(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_bf16_ss_2cta(d_tmem, ad, bd, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
           umma_commit_2cta(&empty[stage]);
           if (++stage == P_STAGES) {
@@ -491,14 +520,58 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     const int ew = warp - 4;
     int it = 0;
     for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
-      const int m_blk = p.n_fastest ? w / p.n_tiles : w % p.m_tiles;
-      const int n_blk = p.n_fastest ? w % p.n_tiles : w / p.m_tiles;
+      int tile, kb_begin, kb_end;
+      unit(w, tile, kb_begin, kb_end);
+      const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
+      const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const long long row = (long long)m_blk * 256 + (long long)rank * 128 + ew * 32 + lane;
       const bool row_ok = row < p.M;
+      if (w >= p.tail_start) {
+        // K-split tail tile: raw partial sums -> fp32 workspace ([column][row of the tile], so a warp's
+        // RED covers one 128-byte line); the CTA that brings this half-tile's counter to tail_splits
+        // reloads the sums, restores the zeros and runs the usual epilogue on them
+        const int tt = tile - p.tail_start;
+        float* wt = p.tail_ws + (long long)tt * (256 * P_BN) + (int)rank * 128 + ew * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < P_BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) atomicAdd(wt + (c * 32 + j) * 256, __uint_as_float(r[j]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty[as], 0);
+        __threadfence();
+        epi_bar_sync();
+        if (threadIdx.x == 128) {
+          const int old = atomicAdd(p.tail_cnt + tt * 2 + (int)rank, 1);
+          s_last = (old + 1 == p.tail_splits) ? 1 : 0;
+        }
+        epi_bar_sync();
+        if (s_last) {
+          __threadfence();
+          ResChunk none;
+          none.vec = false;
+#pragma unroll 1
+          for (int c = 0; c < P_BN / 32; ++c) {
+            uint32_t r[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              r[j] = __float_as_uint(__ldcg(wt + (c * 32 + j) * 256));
+              __stcg(wt + (c * 32 + j) * 256, 0.f);
+            }
+            store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, none);
+          }
+          if (threadIdx.x == 128) p.tail_cnt[tt * 2 + (int)rank] = 0;
+        }
+        continue;
+      }
       ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN);
 #pragma unroll 1
       for (int c = 0; c < P_BN / 32; ++c) {
@@ -532,7 +605,8 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
-  const int work = p.m_tiles * p.n_tiles;
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int work = p.tail_start + (tiles - p.tail_start) * p.tail_splits;
   int clusters = sms / 2;
   if (work < clusters) clusters = work;
   B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0], maps[1],
@@ -754,7 +828,6 @@ __device__ __forceinline__ Segment streamk_segment(const StreamKParams& g, int u
   return s;
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 __global__ void __launch_bounds__(256, 1)
 gemm_streamk_kernel(const __grid_constant__ GroupedMaps maps, const __grid_constant__ StreamKParams g) {
@@ -927,6 +1000,12 @@ gemm_streamk_kernel(const __grid_constant__ GroupedMaps maps, const __grid_const
   }
 }
 
+struct TailWs {
+  void* ptr;
+  size_t bytes;
+};
+TailWs g_tail_ws[64] = {};
+
 bool use_pair_kernel() {
   static int v = -1;
   if (v < 0) {
@@ -1005,6 +1084,34 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
     p.flags |= EP_ATOMIC;
   }
   p.splits = splits;
+  p.tail_start = tiles;
+  p.tail_splits = 1;
+  p.tail_ws = nullptr;
+  p.tail_cnt = nullptr;
+  if (pair) {
+    // Tail splitting: with T tiles on G CTA pairs the last wave holds L = T mod G tiles; when it is at
+    // most half full its tiles are cut into floor(G / L) K ranges (>= 4 K blocks each) so that wave
+    // takes 1/s of a tile time instead of a whole one (8192 x 2048 outputs: 256 tiles on 74 pairs =
+    // 3.46 waves -> 3.5 instead of 4 tile times). Needs the workspace of b200_gemm_set_workspace().
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const TailWs tw = (dev >= 0 && dev < 64) ? g_tail_ws[dev] : TailWs{nullptr, 0};
+    const int G = sms / 2;
+    const int L = tiles % G;
+    const char* e = getenv("B200_GEMM_TAIL");
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && !(e && e[0] == '0')) {
+      int s = G / L;
+      if (s > total_kb / 4) s = total_kb / 4;
+      if (s > 8) s = 8;
+      const size_t need = (size_t)L * 2 * sizeof(int) + 256 + (size_t)L * 256 * P_BN * sizeof(float);
+      if (s >= 2 && need <= tw.bytes) {
+        p.tail_start = tiles - L;
+        p.tail_splits = s;
+        p.tail_cnt = (int*)tw.ptr;
+        p.tail_ws = (float*)((char*)tw.ptr + (((size_t)L * 2 * sizeof(int) + 255) / 256) * 256);
+      }
+    }
+  }
 
   CUtensorMap maps[4];
   int rc;
@@ -1069,6 +1176,7 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
     p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
     p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
     p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0;
+    p.tail_start = p.m_tiles; p.tail_splits = 1; p.tail_ws = nullptr; p.tail_cnt = nullptr;
     p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
     p.C = q.C; p.ldc = q.ldc;
     p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0);
@@ -1138,7 +1246,8 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
     p.M = (int)q.M; p.N = (int)q.N;
     p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
     p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
-    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0; p.splits = 1;
+    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0;
+    p.tail_start = p.m_tiles; p.tail_splits = 1; p.tail_ws = nullptr; p.tail_cnt = nullptr; p.splits = 1;
     p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
     p.C = q.C; p.ldc = q.ldc;
     p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0) | (q.accumulate ? EP_ATOMIC : 0);
@@ -1197,6 +1306,21 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
   if (grid < 1) grid = 1;
   B200_CHECK_CUDA(b200_launch_pdl(gemm_streamk_kernel, dim3((unsigned)grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
   b200_count_launch();
+  return 0;
+}
+
+extern "C" size_t b200_gemm_workspace_bytes(void) {
+  // up to 37 tail tiles (half of the 74 CTA pairs) of 256 x 256 fp32 + their counters
+  return (size_t)37 * 256 * P_BN * sizeof(float) + 4096;
+}
+
+extern "C" int b200_gemm_set_workspace(void* workspace, size_t bytes) {
+  int dev = 0;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < 64, "gemm_set_workspace: device index %d out of range", dev);
+  B200_CHECK_ARG(workspace == nullptr || (((uintptr_t)workspace & 255) == 0 && bytes >= 4096),
+                 "gemm_set_workspace: workspace must be 256-B aligned and at least 4096 bytes");
+  g_tail_ws[dev] = TailWs{workspace, workspace ? bytes : 0};
   return 0;
 }
 

@@ -82,6 +82,23 @@ def set_gemm_profile(p):
     _gemm_profile = p
 
 
+_gemm_ws: dict = {}
+
+
+def _ensure_gemm_workspace(device):
+    """Register (once per device) the zero-filled scratch that lets the large-GEMM kernel split the
+    tiles of a partly filled last wave along K (b200_gemm_set_workspace)."""
+    if device.index in _gemm_ws:
+        return
+    if torch.cuda.is_current_stream_capturing():
+        return                      # first use inside a capture: run without until an eager call registers it
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        ws = torch.zeros(int(lib.b200_gemm_workspace_bytes()), dtype=torch.uint8, device=device)
+        _lib.check(lib.b200_gemm_set_workspace(_p(ws), ws.numel()), "gemm_set_workspace")
+    _gemm_ws[device.index] = ws
+
+
 def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, b2_mn=False, bias=None,
             residual=None, gelu=False, out=None, out_dtype=BF16, accumulate=False, trans_out=False,
             alpha=1.0, splitk=0, M=None, N=None):
@@ -90,6 +107,7 @@ def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, 
     K-major operands are [rows, K]; MN-major (x_mn=True) are stored [K, rows]."""
     _need_cuda(a1, b1, a2, b2, bias, residual, out)
     lib = _lib.load()
+    _ensure_gemm_workspace(a1.device)
     a1, lda1 = _rowmajor2d(a1)
     b1, ldb1 = _rowmajor2d(b1)
     m1, k1 = (a1.shape[1], a1.shape[0]) if a1_mn else a1.shape

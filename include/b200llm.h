@@ -70,6 +70,15 @@ int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  int64_t ldc, int64_t M, int64_t N, int flags, int out_f32, int accumulate,
                  int trans_out, float alpha, int splitk, void* stream);
 
+/* Optional scratch for the large-GEMM kernel (one per device, caller-owned, 256-byte aligned,
+ * b200_gemm_workspace_bytes() bytes, ZERO-FILLED when registered; pass NULL to unregister). With it,
+ * b200_gemm_ex / b200_gemm_nt_bf16 cut the tiles of a last, at most half-filled wave along K so every
+ * CTA pair stays busy (an 8192 x 2048 output is 256 tiles on 74 pairs); the partial sums meet in the
+ * scratch, which every launch leaves zero-filled again. GEMMs that use it must not run concurrently
+ * on different streams of the same device. No reference counterpart (scheduling detail of K1). */
+size_t b200_gemm_workspace_bytes(void);
+int b200_gemm_set_workspace(void* workspace, size_t bytes);
+
 /* Grouped launch of up to B200_GEMM_GROUP_MAX independent skinny GEMMs (every N <= 64, one
  * operand pair each; same operand conventions as b200_gemm_ex) in ONE persistent kernel. Used
  * for the LoRA weight gradients dA = x^T u, dB = (dY^T t)^T of several linears at once

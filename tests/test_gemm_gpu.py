@@ -170,3 +170,30 @@ def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, monkeypatch):
     got = K.gemm_ex(a, b, alpha=0.125)
     ref = (0.125 * (a.float() @ b.float().t())).to(torch.bfloat16)
     assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("M,N,K_,r", [(8192, 2048, 2048, 64), (8192, 3072, 512, 0), (8000, 2000, 1024, 8),
+                                     (8192, 2048, 256, 64)])
+def test_gemm_tail_split_wave(K, M, N, K_, r, monkeypatch):
+    """Shapes whose last wave of 256 x 256 tiles is at most half full (256 or 384 tiles on 74 CTA pairs):
+    the tail tiles are cut along K and summed through the registered workspace. Same results as with
+    tail splitting off (bias + residual + LoRA K extension in the epilogue of the fix-up), exact for
+    integer-valued inputs, workspace all zero afterwards."""
+    a, b = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2)
+    bias, res = rnd(N, seed=3), rnd(M, N, seed=4)
+    kw = dict(a2=rnd(M, r, seed=5), b2=rnd(N, r, scale=0.1, seed=6)) if r else {}
+    got = K.gemm_ex(a, b, bias=bias, residual=res, **kw)
+    ref = a.float() @ b.float().t() + bias.float() + res.float()
+    if r:
+        ref = ref + kw["a2"].float() @ kw["b2"].float().t()
+    assert rel_err(got.float(), ref) < BF16_TOL
+    monkeypatch.setenv("B200_GEMM_TAIL", "0")
+    plain = K.gemm_ex(a, b, bias=bias, residual=res, **kw)
+    monkeypatch.delenv("B200_GEMM_TAIL")
+    assert rel_err(got.float(), plain.float()) < 4e-3          # only the fp32 summation order differs
+    g = torch.Generator(device="cuda").manual_seed(9)
+    ai = torch.randint(-2, 3, (M, K_), generator=g, device="cuda").to(torch.bfloat16)
+    bi = torch.randint(-2, 3, (N, K_), generator=g, device="cuda").to(torch.bfloat16)
+    exact = K.gemm_ex(ai, bi, alpha=0.25)
+    assert torch.equal(exact, (0.25 * (ai.float() @ bi.float().t())).to(torch.bfloat16))
+    assert int(torch.count_nonzero(K._gemm_ws[torch.cuda.current_device()])) == 0

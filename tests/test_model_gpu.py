@@ -330,7 +330,7 @@ def test_packed_projections_match_separate_ones(golden, monkeypatch):
         loss = model.forward_loss(x, y)
         loss.backward()
         opt.flush_pending_grads()
-        results.append((out.detach().float(), h.grad.float(), float(loss),
+        results.append((out.detach().float(), h.grad.float(), float(loss.detach()),
                         {k: p.main_grad.clone() for k, p in model.named_parameters() if p.requires_grad}))
     (o1, d1, l1, g1), (o0, d0, l0, g0) = results
     assert rel_err(o1, o0) < 1e-2 and rel_err(d1, d0) < BF16_TOL
