@@ -44,11 +44,16 @@ struct GemmParams {
   int m_tiles, n_tiles;
   int n_fastest;   // pair kernel: walk the N tiles of an M tile-row back to back (A row stays in L2)
   // pair kernel, tail splitting: tiles >= tail_start are each cut into tail_splits K ranges so the last,
-  // partly filled wave of tiles keeps every CTA pair busy; partial sums meet in tail_ws (fp32, zero
-  // between launches), tail_cnt counts the arrivals per (tile, CTA of the pair)
+  // partly filled wave of tiles keeps every CTA pair busy; partial sums meet in tail_ws (one fp32 slot
+  // per tile and split), tail_cnt counts the arrivals per (tile, CTA of the pair), zero between launches
   int tail_start, tail_splits;
   float* tail_ws;
   int* tail_cnt;
+  // pair kernel, packed LoRA projections: output columns are nseg consecutive segments (q | k | v); a
+  // tile starting in segment s reads its A2 K blocks at column offset s * a2_seg_stride (t_cat holds
+  // one [M, r] block per segment). seg_start[i] = first column of segment i + 1; unused entries INT_MAX.
+  int seg_start[3];
+  int a2_seg_stride;
   int flags;
   float alpha;
   const bf16* bias;
@@ -461,7 +466,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           const int a_mn = ext ? p.a2_mn : p.a1_mn;
           const int b_mn = ext ? p.b2_mn : p.b1_mn;
           if (!a_mn) {
-            tma_load_2d_2cta(sa, ma, &full[stage], kk, m0);
+            const int nt0 = n_blk * P_BN;       // segment of this tile selects the A2 column block
+            const int seg = ext ? (nt0 >= p.seg_start[0]) + (nt0 >= p.seg_start[1]) + (nt0 >= p.seg_start[2]) : 0;
+            tma_load_2d_2cta(sa, ma, &full[stage], kk + seg * p.a2_seg_stride, m0);
           } else {
             tma_load_2d_2cta(sa, ma, &full[stage], m0, kk);
             tma_load_2d_2cta(sa + 8192, ma, &full[stage], m0 + 64, kk);
@@ -531,22 +538,27 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       const long long row = (long long)m_blk * 256 + (long long)rank * 128 + ew * 32 + lane;
       const bool row_ok = row < p.M;
       if (w >= p.tail_start) {
-        // K-split tail tile: raw partial sums -> fp32 workspace ([column][row of the tile], so a warp's
-        // RED covers one 128-byte line); the CTA that brings this half-tile's counter to tail_splits
-        // reloads the sums, restores the zeros and runs the usual epilogue on them
+        // K-split tail tile. Every split parks its raw partial sums in its own workspace slot (plain
+        // coalesced 16-byte stores: slot[(column/4)][row of the tile] float4 — RED atomics issue at ~1 per
+        // clock per SM, 32 K of them per CTA cost more than the tile), then bumps the (tile, CTA-of-pair)
+        // counter; the split that arrives last still holds its own sums in TMEM, adds the other slots
+        // to them and runs the usual epilogue. Slots need no clearing, the counter is reset here.
         const int tt = tile - p.tail_start;
-        float* wt = p.tail_ws + (long long)tt * (256 * P_BN) + (int)rank * 128 + ew * 32 + lane;
+        const int sp = (w - p.tail_start) % p.tail_splits;
+        const int rit = (int)rank * 128 + ew * 32 + lane;
+        float4* slot0 = reinterpret_cast<float4*>(p.tail_ws) + (long long)tt * p.tail_splits * (256 * (P_BN / 4));
+        float4* mine = slot0 + (long long)sp * (256 * (P_BN / 4)) + rit;
+        const uint32_t tacc = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN);
 #pragma unroll 1
         for (int c = 0; c < P_BN / 32; ++c) {
           uint32_t r[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
+          tmem_ld_32x32(tacc + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) atomicAdd(wt + (c * 32 + j) * 256, __uint_as_float(r[j]));
+          for (int q = 0; q < 8; ++q)
+            __stcg(mine + (c * 8 + q) * 256, make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                                         __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])));
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(&tempty[as], 0);
         __threadfence();
         epi_bar_sync();
         if (threadIdx.x == 128) {
@@ -561,15 +573,27 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
 #pragma unroll 1
           for (int c = 0; c < P_BN / 32; ++c) {
             uint32_t r[32];
+            tmem_ld_32x32(tacc + c * 32, r);
+            tmem_ld_wait();
+            for (int o = 0; o < p.tail_splits; ++o) {
+              if (o == sp) continue;
+              const float4* other = slot0 + (long long)o * (256 * (P_BN / 4)) + rit;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              r[j] = __float_as_uint(__ldcg(wt + (c * 32 + j) * 256));
-              __stcg(wt + (c * 32 + j) * 256, 0.f);
+              for (int q = 0; q < 8; ++q) {
+                const float4 v = __ldcg(other + (c * 8 + q) * 256);
+                r[4 * q] = __float_as_uint(__uint_as_float(r[4 * q]) + v.x);
+                r[4 * q + 1] = __float_as_uint(__uint_as_float(r[4 * q + 1]) + v.y);
+                r[4 * q + 2] = __float_as_uint(__uint_as_float(r[4 * q + 2]) + v.z);
+                r[4 * q + 3] = __float_as_uint(__uint_as_float(r[4 * q + 3]) + v.w);
+              }
             }
             store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, none);
           }
           if (threadIdx.x == 128) p.tail_cnt[tt * 2 + (int)rank] = 0;
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty[as], 0);
         continue;
       }
       ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN);
@@ -1027,14 +1051,18 @@ int make_operand_map(CUtensorMap* map, const Operand& o, int64_t rows, int64_t K
   return b200_make_tmap_2d_bf16(map, o.ptr, (uint64_t)K, (uint64_t)rows, (uint64_t)o.ld, BK, 64);
 }
 
-}  // namespace
+struct SegInfo {
+  int nseg;             // output column segments (<= 4)
+  int64_t start[4];     // first column of each segment (start[0] = 0), multiples of the 256-column tile
+  int64_t a2_stride;    // A2 column offset between consecutive segments
+};
 
-extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_t ldb1,
-                            int b1_mn, int64_t K1, const void* A2, int64_t lda2, int a2_mn,
-                            const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
-                            const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
-                            int flags, int out_f32, int accumulate, int trans_out, float alpha,
-                            int splitk, void* stream) {
+int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_t ldb1,
+                 int b1_mn, int64_t K1, const void* A2, int64_t lda2, int a2_mn,
+                 const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
+                 const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
+                 int flags, int out_f32, int accumulate, int trans_out, float alpha,
+                 int splitk, void* stream, const SegInfo* seg_info) {
   B200_CHECK_ARG(M > 0 && N > 0 && K1 > 0 && K2 >= 0, "gemm: bad sizes M=%lld N=%lld K1=%lld K2=%lld",
                  (long long)M, (long long)N, (long long)K1, (long long)K2);
   B200_CHECK_ARG(A1 && B1 && C, "gemm: null operand");
@@ -1045,6 +1073,7 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   B200_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31) && K1 < (1ll << 31), "gemm: sizes exceed int32");
 
   const bool pair = use_pair_kernel() && !accumulate && !trans_out && M >= 256 && N >= 256;
+  B200_CHECK_ARG(!seg_info || (pair && !a2_mn), "gemm: segmented LoRA columns need the CTA-pair kernel and a K-major A2");
   const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
   GemmParams p;
   p.M = (int)M;
@@ -1088,6 +1117,12 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   p.tail_splits = 1;
   p.tail_ws = nullptr;
   p.tail_cnt = nullptr;
+  p.seg_start[0] = p.seg_start[1] = p.seg_start[2] = 0x7fffffff;
+  p.a2_seg_stride = 0;
+  if (seg_info && seg_info->nseg > 1) {
+    for (int i = 0; i + 1 < seg_info->nseg && i < 3; ++i) p.seg_start[i] = (int)seg_info->start[i + 1];
+    p.a2_seg_stride = (int)seg_info->a2_stride;
+  }
   if (pair) {
     // Tail splitting: with T tiles on G CTA pairs the last wave holds L = T mod G tiles; when it is at
     // most half full its tiles are cut into floor(G / L) K ranges (>= 4 K blocks each) so that wave
@@ -1099,16 +1134,20 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
     const int G = sms / 2;
     const int L = tiles % G;
     const char* e = getenv("B200_GEMM_TAIL");
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && !(e && e[0] == '0')) {
+    // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
+    // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !(e && e[0] == '0')) {
       int s = G / L;
-      if (s > total_kb / 4) s = total_kb / 4;
-      if (s > 8) s = 8;
-      const size_t need = (size_t)L * 2 * sizeof(int) + 256 + (size_t)L * 256 * P_BN * sizeof(float);
-      if (s >= 2 && need <= tw.bytes) {
+      if (s > total_kb / 32) s = total_kb / 32;
+      if (s > 4) s = 4;
+      const size_t cnt_bytes = 4096;   // fixed: the counters of one launch must never be another launch's slot bytes
+      const size_t slot_bytes = (size_t)256 * P_BN * sizeof(float);
+      while (s >= 2 && cnt_bytes + (size_t)L * s * slot_bytes > tw.bytes) --s;
+      if (s >= 2) {
         p.tail_start = tiles - L;
         p.tail_splits = s;
         p.tail_cnt = (int*)tw.ptr;
-        p.tail_ws = (float*)((char*)tw.ptr + (((size_t)L * 2 * sizeof(int) + 255) / 256) * 256);
+        p.tail_ws = (float*)((char*)tw.ptr + cnt_bytes);
       }
     }
   }
@@ -1121,7 +1160,8 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   if ((rc = make_operand_map(&maps[1], ob1, N, K1, b_box_rows))) return rc;
   if (K2 > 0) {
     Operand oa2{A2, lda2, a2_mn}, ob2{B2, ldb2, b2_mn};
-    if ((rc = make_operand_map(&maps[2], oa2, M, K2, BM))) return rc;
+    const int64_t a2_cols = seg_info ? K2 + (seg_info->nseg - 1) * seg_info->a2_stride : K2;
+    if ((rc = make_operand_map(&maps[2], oa2, M, a2_cols, BM))) return rc;
     if ((rc = make_operand_map(&maps[3], ob2, N, K2, b_box_rows))) return rc;
   } else {
     maps[2] = maps[0];
@@ -1138,6 +1178,39 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
   }
 }
 
+}  // namespace
+
+extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_t ldb1,
+                            int b1_mn, int64_t K1, const void* A2, int64_t lda2, int a2_mn,
+                            const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
+                            const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
+                            int flags, int out_f32, int accumulate, int trans_out, float alpha,
+                            int splitk, void* stream) {
+  return gemm_ex_impl(A1, lda1, a1_mn, B1, ldb1, b1_mn, K1, A2, lda2, a2_mn, B2, ldb2, b2_mn, K2, bias, R, ldr, C,
+                      ldc, M, N, flags, out_f32, accumulate, trans_out, alpha, splitk, stream, nullptr);
+}
+
+// Several LoRA-wrapped linears of the same input as ONE GEMM: W is the row-concatenation of the base
+// weights [sum(out_i), K], T = [t_0 | t_1 | ...] with t_i = s x A_i [M, r], Bcat = [B_0 | B_1 | ...]
+// [r, sum(out_i)]; output columns of segment i get T[:, i*r:(i+1)*r] Bcat[:, segment i] added.
+extern "C" int b200_gemm_lora_packed_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K,
+                                          const void* T, int64_t ldt, const void* Bcat, int64_t ldb,
+                                          int64_t r, int nseg, const int64_t* seg_start, void* C,
+                                          int64_t ldc, int64_t M, int64_t N, void* stream) {
+  B200_CHECK_ARG(nseg >= 1 && nseg <= 4 && seg_start && seg_start[0] == 0, "gemm_lora_packed: 1..4 segments, the first starting at column 0");
+  B200_CHECK_ARG(r > 0 && r <= 64 && r % 8 == 0, "gemm_lora_packed: rank %lld must be a multiple of 8 and <= 64", (long long)r);
+  SegInfo si;
+  si.nseg = nseg;
+  si.a2_stride = r;
+  for (int i = 0; i < nseg; ++i) {
+    B200_CHECK_ARG(seg_start[i] % P_BN == 0 && seg_start[i] < N && (i == 0 || seg_start[i] > seg_start[i - 1]),
+                   "gemm_lora_packed: segment starts must be increasing multiples of %d below N", P_BN);
+    si.start[i] = seg_start[i];
+  }
+  B200_CHECK_ARG(M >= 256 && N >= 256, "gemm_lora_packed: needs M, N >= 256");
+  return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, T, ldt, 0, Bcat, ldb, 1, r, nullptr, nullptr, 0, C, ldc, M, N, 0, 0, 0,
+                      0, 1.0f, 0, stream, &si);
+}
 
 namespace {
 // K splits the tile-scheduled grouped kernel gives a problem: only accumulating problems may split
@@ -1310,8 +1383,8 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
 }
 
 extern "C" size_t b200_gemm_workspace_bytes(void) {
-  // up to 37 tail tiles (half of the 74 CTA pairs) of 256 x 256 fp32 + their counters
-  return (size_t)37 * 256 * P_BN * sizeof(float) + 4096;
+  // one 256 x 256 fp32 slot per (tail tile, K split): at most 74 CTA pairs' worth, + the counters
+  return (size_t)74 * 256 * P_BN * sizeof(float) + 4096;
 }
 
 extern "C" int b200_gemm_set_workspace(void* workspace, size_t bytes) {

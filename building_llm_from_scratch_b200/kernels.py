@@ -149,6 +149,31 @@ def gemm_ex(a1, b1, *, a1_mn=False, b1_mn=False, a2=None, b2=None, a2_mn=False, 
     return out
 
 
+def gemm_lora_packed(x, w_cat, t_cat, b_cat, r, seg_starts, out=None):
+    """y[M, N] = x w_cat^T + t_cat[:, seg*r:(seg+1)*r] b_cat[:, n]  (one launch for several LoRA linears of x)."""
+    _need_cuda(x, w_cat, t_cat, b_cat, out)
+    lib = _lib.load()
+    _ensure_gemm_workspace(x.device)
+    x, ldx = _rowmajor2d(x)
+    w_cat, ldw = _rowmajor2d(w_cat)
+    t_cat, ldt = _rowmajor2d(t_cat)
+    b_cat, ldb = _rowmajor2d(b_cat)
+    M, Kd = x.shape
+    N = w_cat.shape[0]
+    assert w_cat.shape[1] == Kd and b_cat.shape == (r, N) and t_cat.shape == (M, r * len(seg_starts))
+    if out is None:
+        out = torch.empty((M, N), device=x.device, dtype=BF16)
+    out2, ldc = _rowmajor2d(out)
+    segs = (_lib.C.c_int64 * len(seg_starts))(*seg_starts)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_lora_packed_bf16(_p(x), ldx, _p(w_cat), ldw, Kd, _p(t_cat), ldt, _p(b_cat), ldb, r,
+                                              len(seg_starts), segs, _p(out2), ldc, M, N, _stream()), "gemm_lora_packed")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (Kd + r), (M, N, Kd, r, 0, 0, 0))
+    return out
+
+
 def gemm_grouped(problems):
     """problems: list of dicts(a, b, out, a_mn, b_mn, accumulate, trans_out, alpha) with N <= 64.
     One persistent launch for all of them (chunks of GEMM_GROUP_MAX)."""

@@ -399,6 +399,14 @@ def lora_linear_packed(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor
         K.gemm_grouped([dict(a=x2, b=As[i], out=t_cat[:, i * r:(i + 1) * r], b_mn=True, alpha=scaling) for i in range(n)])
     else:
         t_cat = x2.new_empty((0,))
+    starts = [0]
+    for w in weights[:-1]:
+        starts.append(starts[-1] + w.shape[0])
+    if (w_cat is not None and len(As) > 0 and n <= 4 and M >= 256 and all(st % 256 == 0 for st in starts)
+            and all(B.shape[1] % 8 == 0 for B in Bs) and os.environ.get("B200_PACKED_FWD", "1") != "0"):
+        # one GEMM for all members: the tile's segment picks its t block, B's sit side by side
+        K.gemm_lora_packed(x2, w_cat, t_cat, torch.cat(list(Bs), dim=1), r, starts, out=y)
+        return [y.view(*x.shape[:-1], total), t_cat]
     off = 0
     for i, w in enumerate(weights):
         o = y[:, off:off + w.shape[0]]

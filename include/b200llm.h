@@ -70,11 +70,22 @@ int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  int64_t ldc, int64_t M, int64_t N, int flags, int out_f32, int accumulate,
                  int trans_out, float alpha, int splitk, void* stream);
 
+/* Several LoRA-wrapped linears of the SAME input (q | k | v, fc1 | fc2) as one GEMM:
+ *   C[M, N] = X[M, K]·W[N, K]^T + T[:, seg(n)*r : seg(n)*r + r]·Bcat[:, n]
+ * W = row-concatenation of the base weights, T = [t_0 | t_1 | ...] with t_i = s·x·A_i [M, r] (ldt >= nseg*r),
+ * Bcat = [B_0 | B_1 | ...] stored [r, N]; seg_start[i] = first output column of linear i (seg_start[0] = 0,
+ * multiples of 256, nseg <= 4). Replaces the per-linear forward of lora.py:46 for
+ * Models/Llama/Llama3.py:135-137 and common_components.py:121-122. */
+int b200_gemm_lora_packed_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K,
+                               const void* T, int64_t ldt, const void* Bcat, int64_t ldb, int64_t r,
+                               int nseg, const int64_t* seg_start, void* C, int64_t ldc, int64_t M,
+                               int64_t N, void* stream);
+
 /* Optional scratch for the large-GEMM kernel (one per device, caller-owned, 256-byte aligned,
  * b200_gemm_workspace_bytes() bytes, ZERO-FILLED when registered; pass NULL to unregister). With it,
  * b200_gemm_ex / b200_gemm_nt_bf16 cut the tiles of a last, at most half-filled wave along K so every
  * CTA pair stays busy (an 8192 x 2048 output is 256 tiles on 74 pairs); the partial sums meet in the
- * scratch, which every launch leaves zero-filled again. GEMMs that use it must not run concurrently
+ * scratch, whose counters every launch leaves zero again. GEMMs that use it must not run concurrently
  * on different streams of the same device. No reference counterpart (scheduling detail of K1). */
 size_t b200_gemm_workspace_bytes(void);
 int b200_gemm_set_workspace(void* workspace, size_t bytes);

@@ -172,13 +172,14 @@ def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, monkeypatch):
     assert torch.equal(got, ref)
 
 
-@pytest.mark.parametrize("M,N,K_,r", [(8192, 2048, 2048, 64), (8192, 3072, 512, 0), (8000, 2000, 1024, 8),
-                                     (8192, 2048, 256, 64)])
+@pytest.mark.parametrize("M,N,K_,r", [(8192, 2048, 4096, 64), (8192, 3072, 8192, 0), (8000, 2000, 4104, 8),
+                                     (8192, 2048, 2048, 64)])
 def test_gemm_tail_split_wave(K, M, N, K_, r, monkeypatch):
-    """Shapes whose last wave of 256 x 256 tiles is at most half full (256 or 384 tiles on 74 CTA pairs):
+    """Shapes whose last wave of 256 x 256 tiles is at most half full (256 or 384 tiles on 74 CTA pairs) and
+    whose K range is deep enough to split (the last case is below the threshold and runs unsplit):
     the tail tiles are cut along K and summed through the registered workspace. Same results as with
     tail splitting off (bias + residual + LoRA K extension in the epilogue of the fix-up), exact for
-    integer-valued inputs, workspace all zero afterwards."""
+    integer-valued inputs, arrival counters zero afterwards."""
     a, b = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2)
     bias, res = rnd(N, seed=3), rnd(M, N, seed=4)
     kw = dict(a2=rnd(M, r, seed=5), b2=rnd(N, r, scale=0.1, seed=6)) if r else {}
@@ -196,4 +197,23 @@ def test_gemm_tail_split_wave(K, M, N, K_, r, monkeypatch):
     bi = torch.randint(-2, 3, (N, K_), generator=g, device="cuda").to(torch.bfloat16)
     exact = K.gemm_ex(ai, bi, alpha=0.25)
     assert torch.equal(exact, (0.25 * (ai.float() @ bi.float().t())).to(torch.bfloat16))
-    assert int(torch.count_nonzero(K._gemm_ws[torch.cuda.current_device()])) == 0
+    assert int(torch.count_nonzero(K._gemm_ws[torch.cuda.current_device()][:4096])) == 0    # arrival counters
+
+
+@pytest.mark.parametrize("M,outs,K_,r", [(8192, (2048, 512, 512), 2048, 64), (1024, (768, 256), 512, 8),
+                                        (300, (256, 256, 256, 512), 128, 16)])
+def test_gemm_lora_packed_segments(K, M, outs, K_, r):
+    """q | k | v style packed forward: one GEMM, each 256-column tile adds its own segment's LoRA update."""
+    x = rnd(M, K_, seed=1)
+    ws = [rnd(o, K_, scale=0.05, seed=10 + i) for i, o in enumerate(outs)]
+    ts = [rnd(M, r, seed=20 + i) for i in range(len(outs))]
+    Bs = [rnd(r, o, scale=0.1, seed=30 + i) for i, o in enumerate(outs)]
+    starts = [0]
+    for o in outs[:-1]:
+        starts.append(starts[-1] + o)
+    got = K.gemm_lora_packed(x, torch.cat(ws, 0), torch.cat(ts, 1), torch.cat(Bs, 1), r, starts)
+    ref = torch.cat([x.float() @ w.float().t() + t.float() @ B.float() for w, t, B in zip(ws, ts, Bs)], dim=1)
+    assert rel_err(got.float(), ref) < BF16_TOL
+    for i, o in enumerate(outs):       # per segment too: a wrong t block would hide in the global norm
+        sl = slice(starts[i], starts[i] + o)
+        assert rel_err(got[:, sl].float(), ref[:, sl]) < BF16_TOL, i
