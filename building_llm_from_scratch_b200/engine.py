@@ -44,7 +44,9 @@ class TrainStep:
         self.overlap = os.environ.get("B200_DDP_OVERLAP", "1") != "0"
         if self.ddp is not None:
             self.ddp.attach(self.opt)
-        self.bucket_rows = max(128, (batch_shape[0] * batch_shape[1]) // 8)
+        # vocab-projection capacity buckets (one captured graph each): 1/16 of the rows, so a batch pays for
+        # at most ~6 % more rows than it has non-ignored targets
+        self.bucket_rows = max(128, (batch_shape[0] * batch_shape[1]) // 16)
         self.launches_per_step = 0
         self.opt.graph_safe = True
         self.core.train()
@@ -66,6 +68,10 @@ class TrainStep:
 
     def _exchange_step(self):
         """forward, backward with the gradient mean over ranks (overlapped when enabled), update."""
+        if getattr(self.opt, "zero", False):     # ZeRO-1: the optimizer reduce-scatters the gradients itself
+            self._fwd_bwd(False)
+            self._update()
+            return
         overlap = self.ddp is not None and self.overlap
         self._fwd_bwd(overlap)
         if overlap:
@@ -120,7 +126,7 @@ class TrainStep:
             if self.pool is None:
                 self.pool = g.pool()
             return (g,)
-        if self.capture_collective:
+        if self.capture_collective or getattr(self.opt, "zero", False):
             # the NCCL all-reduce is captured too: the whole data-parallel step is ONE graph launch
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, **kw):

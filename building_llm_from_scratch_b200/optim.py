@@ -8,6 +8,12 @@ no per-parameter gradient tensor, no foreach launch train and the data-parallel 
 one contiguous buffer. A step is: grad-norm kernel -> clip coefficient (device scalar) -> one AdamW
 kernel that also applies the coefficient. State (exp_avg, exp_avg_sq) has the parameter dtype,
 like the reference's optimizer.
+
+zero=True shards the optimizer state over the data-parallel group (the reference's --use_zero_opt,
+build_components.py:228-231,250-256: ZeroRedundancyOptimizer around AdamW): each rank keeps exp_avg /
+exp_avg_sq for 1/world of the flat buffer only; a step is reduce-scatter(AVG) of the flat gradients ->
+global norm from the per-shard sums of squares (one scalar all-reduce) -> AdamW on the local shard ->
+all-gather of the updated parameter shards. The result is the same update plain DDP + AdamW makes.
 """
 from __future__ import annotations
 
@@ -21,8 +27,14 @@ def _align(n, a=64):
 
 
 class B200AdamW(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, zero=False,
+                 process_group=None):
         params = [p for p in params]
+        import torch.distributed as dist
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if (zero and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(process_group) if self.world > 1 else 0
+        self.zero = bool(zero) and self.world > 1
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
         # the reference hands every parameter to AdamW; frozen ones never get a gradient
@@ -41,14 +53,24 @@ class B200AdamW(torch.optim.Optimizer):
             for p in ps:
                 offs.append(total)
                 total += _align(p.numel())
+            if self.zero:                       # equal shards of whole 64-element groups
+                total = _align(total, 64 * self.world)
             flat_p = torch.zeros(total, device=dev, dtype=dtype)
             flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
             for p, o in zip(ps, offs):
                 flat_p[o:o + p.numel()].copy_(p.data.reshape(-1))
                 p.data = flat_p[o:o + p.numel()].view(p.shape)
                 p.main_grad = flat_g[o:o + p.numel()].view(p.shape)
-            self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g, m=torch.zeros_like(flat_p),
-                                       v=torch.zeros_like(flat_p))
+            if self.zero:
+                shard = total // self.world
+                lo = self.rank * shard
+                self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g,
+                                           p_shard=flat_p[lo:lo + shard], g_shard=torch.zeros(shard, device=dev),
+                                           m=torch.zeros(shard, device=dev, dtype=dtype),
+                                           v=torch.zeros(shard, device=dev, dtype=dtype))
+            else:
+                self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g, m=torch.zeros_like(flat_p),
+                                           v=torch.zeros_like(flat_p))
         other = [p for p in self._trainable if p.dtype not in self._groups]
         if other:
             raise RuntimeError(f"B200AdamW: unsupported parameter dtypes {set(p.dtype for p in other)}")
@@ -109,6 +131,8 @@ class B200AdamW(torch.optim.Optimizer):
         ops.flush_weight_grads()
         self._absorb_autograd_grads()
         self._step += 1
+        if self.zero:
+            return self._zero_step()
         scale = None
         if self.max_norm is not None:
             scale = self.grad_norm(self.max_norm)[1:2]
@@ -121,6 +145,32 @@ class B200AdamW(torch.optim.Optimizer):
         for g in self._groups.values():
             K.adamw_(g["p"], g["g"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
                      dev_hyper=hyper)
+
+    def _zero_step(self):
+        """ZeRO-1 update (see the module docstring); every collective is on the current stream's
+        process group, so the whole thing can sit inside a captured graph."""
+        import torch.distributed as dist
+        groups = list(self._groups.values())
+        for g in groups:
+            dist.reduce_scatter_tensor(g["g_shard"], g["g"], op=dist.ReduceOp.AVG, group=self.pg)
+        scale = None
+        if self.max_norm is not None:
+            sq = None
+            for g in groups:
+                part = K.grad_norm(g["g_shard"], self.max_norm)[0:1]
+                sq = part * part if sq is None else sq + part * part
+            dist.all_reduce(sq, group=self.pg)
+            total = torch.sqrt(sq)
+            self._norm_out[0:1] = total
+            self._norm_out[1:2] = torch.clamp(self.max_norm / (total + 1e-6), max=1.0)
+            scale = self._norm_out[1:2]
+        pg = self.param_groups[0]
+        lr, (b1, b2), eps, wd = pg["lr"], pg["betas"], pg["eps"], pg["weight_decay"]
+        hyper = self._hyper_dev if self.graph_safe else None
+        for g in groups:
+            K.adamw_(g["p_shard"], g["g_shard"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
+                     dev_hyper=hyper)
+            dist.all_gather_into_tensor(g["p"], g["p_shard"], group=self.pg)
 
     def set_hyper(self, lr: float, step: int):
         """Upload (lr, bias corrections for `step`) for the graph-captured step."""

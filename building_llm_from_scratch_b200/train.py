@@ -96,7 +96,9 @@ class Trainer:
         loss.backward()
         fused = isinstance(self.optimizer, B200AdamW)
         if isinstance(self.model, B200DDP):
-            if fused:
+            if fused and self.optimizer.zero:
+                pass          # ZeRO-1: optimizer.step() reduce-scatters the flat gradients (optim.py)
+            elif fused:
                 self.optimizer._absorb_autograd_grads()
                 self.model.reduce_gradients(self.optimizer.flat_grads)
             else:
