@@ -60,8 +60,13 @@ class MultiHeadAttention(nn.Module):
         state_dict.pop(prefix + "mask", None)
         super()._load_from_state_dict(state_dict, prefix, *args)
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, cache=None, layer=0):
         b, num_tokens, _ = x.shape
+        if cache is not None:       # generation with a KV cache (kvcache.py); no RoPE, no dropout in eval
+            from ...kvcache import attend_with_cache, packed_qkv
+            ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), None, None, cache, layer,
+                                    b, num_tokens, self.num_heads, self.num_heads, self.head_dim)
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         p_drop = self.dropout.p if self.training else 0.0
         qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])     # None with qkv_bias
         if qkv is not None:
@@ -100,7 +105,10 @@ class TransformerBlock(nn.Module):
         self.norm2 = B200LayerNorm(cfg["emb_dim"])
         self.dropout = B200Dropout(cfg["drop_rate"])
 
-    def forward(self, x):
+    def forward(self, x, cache=None, layer=0):
+        if cache is not None:
+            x = self.att(self.norm1(x), residual=x, cache=cache, layer=layer)
+            return self.ff(self.norm2(x), residual=x)
         if self.training and self.dropout.p > 0:
             x = self.dropout(self.att(self.norm1(x)), residual=x)      # x + dropout(att(...)), GPT2.py:85
             return self.dropout(self.ff(self.norm2(x)), residual=x)    # x + dropout(ff(...)),  GPT2.py:87
@@ -140,6 +148,21 @@ class GPTModel(nn.Module):
         """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
         h = self.hidden_states(x)
         return self.output_head(h[:, -1, :].contiguous())
+
+    def new_kv_cache(self, batch, t_max=None):
+        from ...kvcache import KVCache
+        return KVCache(len(self.blocks), batch, t_max or self.cfg["context_length"], self.cfg["emb_dim"],
+                       self.tok_emb.weight.device, dtype=self.tok_emb.weight.dtype)
+
+    @torch.no_grad()
+    def forward_cached(self, x, cache):
+        """Logits [B, V] of the last of the new tokens x [B, T]; positions continue at cache.pos."""
+        T = x.shape[1]
+        h = ops.embedding(x, self.tok_emb.weight, None) + self.pos_emb.weight[cache.pos:cache.pos + T]
+        for i, blk in enumerate(self.blocks):
+            h = blk(h, cache=cache, layer=i)
+        cache.pos += T
+        return self.output_head(self.norm(h)[:, -1, :].contiguous())
 
     def forward_loss(self, x, targets, capacity=0):
         w, A, B, s = head_operands(self.output_head)

@@ -59,9 +59,14 @@ class MultiHeadAttention(nn.Module):
             t = self._tables_bf16 = (self.cos.to(torch.bfloat16), self.sin.to(torch.bfloat16))
         return t
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, cache=None, layer=0):
         b, num_tokens, _ = x.shape
         cos, sin = self._tables()
+        if cache is not None:       # generation with a KV cache (kvcache.py)
+            from ...kvcache import attend_with_cache, packed_qkv
+            ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), cos, sin, cache, layer,
+                                    b, num_tokens, self.num_heads, self.num_heads, self.head_dim)
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])
         if qkv is not None:
             ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), cos, sin, b, num_tokens, self.num_heads,
@@ -84,9 +89,9 @@ class TransformerBlock(nn.Module):
         self.norm1 = RMSNorm(cfg["emb_dim"])
         self.norm2 = RMSNorm(cfg["emb_dim"])
 
-    def forward(self, x):
+    def forward(self, x, cache=None, layer=0):
         h, res = ops.rmsnorm_with_residual(x, self.norm1.weight, self.norm1.eps)
-        x = self.att(h, residual=res)
+        x = self.att(h, residual=res, cache=cache, layer=layer)
         h, res = ops.rmsnorm_with_residual(x, self.norm2.weight, self.norm2.eps)
         return self.ff(h, residual=res)
 
@@ -113,6 +118,20 @@ class Llama2Model(nn.Module):
         """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
         h = self.hidden_states(in_idx)
         return self.out_head(h[:, -1, :].contiguous())
+
+    def new_kv_cache(self, batch, t_max=None):
+        from ...kvcache import KVCache
+        return KVCache(len(self.trf_blocks), batch, t_max or self.cfg["context_length"], self.cfg["emb_dim"],
+                       self.tok_emb.weight.device)
+
+    @torch.no_grad()
+    def forward_cached(self, in_idx, cache):
+        """Logits [B, V] of the last of the new tokens; their keys / values join the cache."""
+        x = ops.embedding(in_idx, self.tok_emb.weight, None)
+        for i, blk in enumerate(self.trf_blocks):
+            x = blk(x, cache=cache, layer=i)
+        cache.pos += in_idx.shape[1]
+        return self.out_head(self.final_norm(x)[:, -1, :].contiguous())
 
     def forward_loss(self, in_idx, targets, capacity=0):
         w, A, B, s = head_operands(self.out_head)

@@ -82,10 +82,15 @@ class GroupedQueryAttention(nn.Module):
         state_dict.pop(prefix + "mask", None)
         super()._load_from_state_dict(state_dict, prefix, *args)
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, cache=None, layer=0):
         b, num_tokens, _ = x.shape
         cos = self.cos if self.cos.dtype == torch.bfloat16 else self.cos.to(torch.bfloat16)
         sin = self.sin if self.sin.dtype == torch.bfloat16 else self.sin.to(torch.bfloat16)
+        if cache is not None:       # generation with a KV cache (kvcache.py)
+            from ...kvcache import attend_with_cache, packed_qkv
+            ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), cos, sin, cache, layer,
+                                    b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])
         if qkv is not None:     # one packed projection: RoPE and the backward dX GEMM run once over q|k|v
             ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), cos, sin, b, num_tokens, self.num_heads,
@@ -109,9 +114,9 @@ class TransformerBlock(nn.Module):
         self.norm1 = RMSNorm(cfg["emb_dim"], eps=1e-5)
         self.norm2 = RMSNorm(cfg["emb_dim"], eps=1e-5)
 
-    def forward(self, x):
+    def forward(self, x, cache=None, layer=0):
         h, res = ops.rmsnorm_with_residual(x, self.norm1.weight, self.norm1.eps)
-        x = self.att(h.to(torch.bfloat16), residual=res)
+        x = self.att(h.to(torch.bfloat16), residual=res, cache=cache, layer=layer)
         h, res = ops.rmsnorm_with_residual(x, self.norm2.weight, self.norm2.eps)
         return self.ff(h.to(torch.bfloat16), residual=res)
 
@@ -144,6 +149,23 @@ class Llama3Model(nn.Module):
     def forward_last(self, in_idx):
         """Logits of the last position only, [B, V] (generate.py:42-45 needs nothing else)."""
         h = self.hidden_states(in_idx)
+        return self.out_head(h[:, -1, :].contiguous())
+
+    def new_kv_cache(self, batch, t_max=None):
+        from ...kvcache import KVCache
+        att = self.trf_blocks[0].att
+        return KVCache(len(self.trf_blocks), batch, t_max or self.cfg["context_length"],
+                       att.num_kv_groups * att.head_dim, self.tok_emb.weight.device)
+
+    @torch.no_grad()
+    def forward_cached(self, in_idx, cache):
+        """Logits [B, V] of the last of the new tokens in_idx [B, T]; their keys / values join the cache
+        (T > 1 only as the prefill of an empty cache)."""
+        x = ops.embedding(in_idx, self.tok_emb.weight, None)
+        for i, blk in enumerate(self.trf_blocks):
+            x = blk(x, cache=cache, layer=i)
+        cache.pos += in_idx.shape[1]
+        h = self.final_norm(x).to(torch.bfloat16)
         return self.out_head(h[:, -1, :].contiguous())
 
     def forward_loss(self, in_idx, targets, capacity=0):

@@ -552,3 +552,17 @@ def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=No
                                            dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p),
                                            int(seed), _stream()), "attention_bwd")
     return dq, dk, dv
+
+
+def attention_decode(q, k_cache, v_cache, T, h, hkv, hd, out=None):
+    """One query token per sequence against the first T positions of a KV cache.
+    q [B, h*hd]; k_cache, v_cache [B, t_max, hkv*hd] (keys already rotated) -> o [B, h*hd]."""
+    _need_cuda(q, k_cache, v_cache)
+    q, ldq = _rowmajor2d(q)
+    B, t_max, width = k_cache.shape
+    assert v_cache.shape == k_cache.shape and k_cache.is_contiguous() and v_cache.is_contiguous() and width == hkv * hd
+    o = torch.empty((B, h * hd), device=q.device, dtype=BF16) if out is None else out
+    _lib.check(_lib.load().b200_attention_decode_bf16(_p(q), ldq, _p(k_cache), _p(v_cache), width, t_max, _p(o),
+                                                      o.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _stream()),
+               "attention_decode")
+    return o

@@ -295,6 +295,17 @@ int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float 
                       void* stream);
 int b200_dropout_mask_u8(void* out, int64_t n, float p, uint64_t seed, void* stream);
 
+/* ---- K2 decode: one new query token per sequence against a KV cache ---------------------------
+ * o[b, head, :] = softmax(q[b, head, :]·K[b, 0..T, kv(head), :]^T * scale)·V[b, 0..T, kv(head), :]
+ * q, o: [B, h*hd] (row pitches ldq, ldo); k_cache, v_cache: [B, t_max, hkv*hd] bf16 with row pitch ldc
+ * (elements) and batch stride t_max*ldc; keys are stored already rotated (RoPE at their own position).
+ * hd 64 or 128, h / hkv <= 8. The reference's generate.py:4-75 keeps no cache (every token re-runs
+ * the window through Models/Llama/Llama3.py:131-155 / Models/GPT2/GPT2.py:29-49); this is the same
+ * attention evaluated for the last position only. */
+int b200_attention_decode_bf16(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                               int64_t ldc, int64_t t_max, void* o, int64_t ldo, int64_t B, int64_t T,
+                               int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

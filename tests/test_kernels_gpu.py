@@ -301,3 +301,19 @@ def test_attention_dropout_matches_oracle_with_same_mask(K, hd):
     assert rel_err(dq.float(), qr.grad) < BF16_TOL
     assert rel_err(dk.float(), kr.grad) < BF16_TOL
     assert rel_err(dv.float(), vr.grad) < BF16_TOL
+
+
+@pytest.mark.parametrize("B,T,h,hkv,hd,tmax", [(2, 300, 8, 2, 64, 512), (1, 2048, 32, 8, 64, 2048), (3, 77, 4, 4, 128, 100),
+                                               (2, 1000, 8, 1, 128, 1024)])
+def test_attention_decode_against_oracle(K, B, T, h, hkv, hd, tmax):
+    """One query token per sequence against a KV cache = the last row of the oracle's causal attention."""
+    from oracle import reference_ops as R
+    kc, vc = rnd(B, tmax, hkv * hd, seed=1), rnd(B, tmax, hkv * hd, seed=2)
+    q = rnd(B, h * hd, seed=3)
+    o = K.attention_decode(q, kc, vc, T, h, hkv, hd)
+    qh = q.float().view(B, 1, h, hd).transpose(1, 2)                                  # [B, h, 1, hd]
+    kh = kc[:, :T].float().view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    vh = vc[:, :T].float().view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    w = torch.softmax(qh @ kh.transpose(2, 3) / hd ** 0.5, dim=-1)
+    ref = (w @ vh).transpose(1, 2).reshape(B, h * hd)
+    assert rel_err(o.float(), ref) < BF16_TOL

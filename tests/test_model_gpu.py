@@ -346,3 +346,41 @@ def test_packed_projections_match_separate_ones(golden, monkeypatch):
         ws[1].mul_(2.0)
     c2 = ops._packed_weight(ws)
     assert torch.equal(c2, torch.cat(ws, 0)) and not torch.equal(c1, c2)
+
+
+def test_kv_cache_generation_matches_full_window(golden):
+    """Prefill + one-token decode steps against the KV cache give the logits of re-running the whole window
+    (what the reference's generate.py does), for the Llama-3 LoRA model and for GPT-2."""
+    from building_llm_from_scratch_b200.generate import generate
+    g = golden("llama_model.pt")
+    model, _ = build_llama(g, False)
+    model.eval()
+    x = g["x"][:, :24].cuda()
+    cache = model.new_kv_cache(x.shape[0], 40)
+    seq = x[:, :17]
+    lg = model.forward_cached(seq, cache)
+    with torch.no_grad():
+        assert rel_err(lg.float(), model.forward_last(seq).float()) < BF16_TOL
+        for t in range(17, 24):
+            seq = x[:, :t + 1]
+            lg = model.forward_cached(seq[:, -1:], cache)
+            full = model.forward_last(seq).float()
+            assert rel_err(lg.float(), full) < BF16_TOL, t
+    assert cache.pos == 24
+    a = generate(model, x[:, :12], max_new_tokens=8, context_size=64, use_cache=True)
+    b = generate(model, x[:, :12], max_new_tokens=8, context_size=64, use_cache=False)
+    assert a.shape == b.shape and float((a == b).float().mean()) > 0.9      # bf16 near-ties may pick another token
+    # GPT-2 (learned positions, biases, LayerNorm)
+    from building_llm_from_scratch_b200.Models.GPT2.GPT2 import GPTModel
+    gg = golden("gpt2.pt")["model"]
+    m2 = GPTModel(copy.deepcopy(gg["cfg"]))
+    m2.load_state_dict(gg["sd"])
+    m2 = m2.cuda().to(torch.bfloat16).eval()
+    xs = gg["x"].cuda()[:, :16]
+    cache = m2.new_kv_cache(xs.shape[0], 32)
+    lg = m2.forward_cached(xs[:, :9], cache)
+    with torch.no_grad():
+        assert rel_err(lg.float(), m2.forward_last(xs[:, :9]).float()) < BF16_TOL
+        for t in range(9, 16):
+            lg = m2.forward_cached(xs[:, t:t + 1], cache)
+            assert rel_err(lg.float(), m2.forward_last(xs[:, :t + 1]).float()) < BF16_TOL, t
