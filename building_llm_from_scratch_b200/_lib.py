@@ -84,6 +84,8 @@ SIGNATURES = {
     "b200_attention_dropout_mask_u8": (I, [P, I64, I64, I64, F, C.c_uint64, P]),
     "b200_dropout_bf16": (I, [P, P, P, I64, F, C.c_uint64, P]),
     "b200_dropout_mask_u8": (I, [P, I64, F, C.c_uint64, P]),
+    "b200_collate_i64": (I, [P, P, P, I64, I64, I64, I64, I64, P, P, P]),
+    "b200_window_batch_i64": (I, [P, I64, P, I64, I64, P, P, P]),
     "b200_attention_decode_bf16": (I, [P, I64, P, P, I64, I64, P, I64, I64, I64, I64, I64, I64, F, P]),
     "b200_attention_bwd_workspace_bytes": (SZ, [I64, I64, I64, I64]),
     "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,

@@ -629,3 +629,85 @@ extern "C" int b200_transpose_bf16(const void* in, int64_t ldi, void* out, int64
   b200_count_launch();
   return 0;
 }
+
+// ======================================================================================
+// Data side of the step on the device, integer work, bit-exact:
+//   collate: datautils/dataloader_instruction_finetune.py:10-50 on a packed token buffer;
+//   windows: datautils/dataset.py:21-34 (input = tokens[i : i+L], target = tokens[i+1 : i+L+1]).
+// ======================================================================================
+namespace {
+
+// One CTA per sample. `width` = longest item of the batch + 1 (the appended end-of-text token) - 1 after
+// the shift, i.e. the untruncated row length of inputs/targets; out rows hold min(width, max_len) columns.
+__global__ void __launch_bounds__(256)
+collate_kernel(const long long* __restrict__ tokens, const long long* __restrict__ offsets,
+               const long long* __restrict__ instr_len, long long pad_id, long long ignore_index,
+               int width, int out_cols, long long* __restrict__ inputs, long long* __restrict__ targets) {
+  __shared__ int s_first;
+  const int r = blockIdx.x;
+  const long long* item = tokens + offsets[r];
+  const int len = (int)(offsets[r + 1] - offsets[r]);
+  if (threadIdx.x == 0) s_first = 0x7fffffff;
+  __syncthreads();
+  // padded[j] = item[j] for j < len, pad_id otherwise; target column j is padded[j + 1]
+  int first = 0x7fffffff;
+  for (int j = threadIdx.x; j < width; j += blockDim.x) {
+    const long long t = (j + 1 < len) ? item[j + 1] : pad_id;
+    if (t == pad_id) {
+      first = j;
+      break;                       // columns visited by a thread are increasing: its first hit is its minimum
+    }
+  }
+  if (first != 0x7fffffff) atomicMin(&s_first, first);
+  __syncthreads();
+  const int first_pad = s_first;
+  long long il = instr_len[r] - 1;          // targets[:instruction_length - 1] with Python slice semantics
+  if (il < 0) il = (long long)width + il;
+  if (il < 0) il = 0;
+  if (il > width) il = width;
+  for (int j = threadIdx.x; j < out_cols; j += blockDim.x) {
+    const long long in = (j < len) ? item[j] : pad_id;
+    long long t = (j + 1 < len) ? item[j + 1] : pad_id;
+    if (t == pad_id && j != first_pad) t = ignore_index;
+    if (j < il) t = ignore_index;
+    inputs[(long long)r * out_cols + j] = in;
+    targets[(long long)r * out_cols + j] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+window_batch_kernel(const long long* __restrict__ tokens, const long long* __restrict__ starts, int L,
+                    long long* __restrict__ inputs, long long* __restrict__ targets) {
+  const long long s = starts[blockIdx.x];
+  for (int j = threadIdx.x; j < L; j += blockDim.x) {
+    inputs[(long long)blockIdx.x * L + j] = tokens[s + j];
+    targets[(long long)blockIdx.x * L + j] = tokens[s + j + 1];
+  }
+}
+
+}  // namespace
+
+extern "C" int b200_collate_i64(const int64_t* tokens, const int64_t* offsets, const int64_t* instr_len,
+                                int64_t batch, int64_t width, int64_t out_cols, int64_t pad_id,
+                                int64_t ignore_index, int64_t* inputs, int64_t* targets, void* stream) {
+  B200_CHECK_ARG(tokens && offsets && instr_len && inputs && targets, "collate: null pointer");
+  B200_CHECK_ARG(batch > 0 && batch <= 65535 * 32 && width > 0 && out_cols > 0 && out_cols <= width && width < (1ll << 30),
+                 "collate: bad sizes batch=%lld width=%lld out_cols=%lld", (long long)batch, (long long)width, (long long)out_cols);
+  collate_kernel<<<(unsigned)batch, 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)tokens, (const long long*)offsets, (const long long*)instr_len, (long long)pad_id,
+      (long long)ignore_index, (int)width, (int)out_cols, (long long*)inputs, (long long*)targets);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_window_batch_i64(const int64_t* tokens, int64_t n_tokens, const int64_t* starts, int64_t batch,
+                                     int64_t L, int64_t* inputs, int64_t* targets, void* stream) {
+  B200_CHECK_ARG(tokens && starts && inputs && targets && batch > 0 && L > 0 && n_tokens > L && L < (1ll << 30),
+                 "window_batch: null pointer or bad sizes (every start must satisfy start + L < n_tokens)");
+  window_batch_kernel<<<(unsigned)batch, 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)tokens, (const long long*)starts, (int)L, (long long*)inputs, (long long*)targets);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}

@@ -306,6 +306,22 @@ int b200_attention_decode_bf16(const void* q, int64_t ldq, const void* k_cache, 
                                int64_t ldc, int64_t t_max, void* o, int64_t ldo, int64_t B, int64_t T,
                                int64_t h, int64_t hkv, int64_t hd, float scale, void* stream);
 
+/* ---- data side on the device: integer work, bit-exact ----------------------
+ * b200_collate_i64 = custom_collate_fn (datautils/dataloader_instruction_finetune.py:10-50) over a packed
+ * token buffer: item r is tokens[offsets[r] : offsets[r+1]] with instruction length instr_len[r];
+ * width = longest item of the batch (the row length after appending the end-of-text token and shifting),
+ * out_cols = min(width, allowed_max_length). inputs / targets: [batch, out_cols] int64.
+ * Every target equal to pad_id except the first one of its row becomes ignore_index (this also hits pad
+ * ids occurring naturally in the text, like the reference), then targets[:instr_len - 1] = ignore_index
+ * with Python slice semantics (instr_len 0 blanks all but the last column). */
+int b200_collate_i64(const int64_t* tokens, const int64_t* offsets, const int64_t* instr_len, int64_t batch,
+                     int64_t width, int64_t out_cols, int64_t pad_id, int64_t ignore_index,
+                     int64_t* inputs, int64_t* targets, void* stream);
+/* DatasetPT windows (datautils/dataset.py:21-34) gathered for one batch from a device-resident token
+ * stream: inputs[b] = tokens[starts[b] : starts[b]+L], targets[b] = tokens[starts[b]+1 : starts[b]+L+1]. */
+int b200_window_batch_i64(const int64_t* tokens, int64_t n_tokens, const int64_t* starts, int64_t batch,
+                          int64_t L, int64_t* inputs, int64_t* targets, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
