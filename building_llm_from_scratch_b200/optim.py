@@ -172,6 +172,29 @@ class B200AdamW(torch.optim.Optimizer):
                      dev_hyper=hyper)
             dist.all_gather_into_tensor(g["p"], g["p_shard"], group=self.pg)
 
+    # ---- checkpoint / resume (the reference saves the model only, train.py:231-257; a resume needs the
+    # moments and the step count too) ------------------------------------------------------------------
+    def state_dict(self):
+        return {"b200_adamw": 1, "step": self._step, "zero": self.zero, "world": self.world,
+                "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups],
+                "moments": {str(dt): {"m": g["m"].detach().cpu(), "v": g["v"].detach().cpu(), "numel": g["p"].numel()}
+                            for dt, g in self._groups.items()}}
+
+    def load_state_dict(self, state):
+        if not isinstance(state, dict) or state.get("b200_adamw") != 1:
+            raise ValueError("B200AdamW.load_state_dict: not a B200AdamW state (torch.optim.AdamW states are laid out per parameter)")
+        if bool(state["zero"]) != self.zero or (self.zero and state["world"] != self.world):
+            raise ValueError("B200AdamW.load_state_dict: ZeRO sharding of the checkpoint differs from this optimizer's")
+        for dt, g in self._groups.items():
+            src = state["moments"][str(dt)]
+            if src["numel"] != g["p"].numel() or src["m"].numel() != g["m"].numel():
+                raise ValueError("B200AdamW.load_state_dict: flat buffer sizes differ (different set of trainable parameters)")
+            g["m"].copy_(src["m"])
+            g["v"].copy_(src["v"])
+        self._step = int(state["step"])
+        for pg, saved in zip(self.param_groups, state["param_groups"]):
+            pg.update(saved)
+
     def set_hyper(self, lr: float, step: int):
         """Upload (lr, bias corrections for `step`) for the graph-captured step."""
         pg = self.param_groups[0]

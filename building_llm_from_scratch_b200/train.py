@@ -15,6 +15,14 @@ from .ddp import B200DDP
 from .optim import B200AdamW
 
 
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
 class Trainer:
     def __init__(self, model, optimizer, config, data_files, loaderObj, save_dir, warmup_steps=10, initial_lr=1e-5,
                  min_lr=1e-6, device="cpu", rank=0, eval_freq=1, save_ckpt_freq=1, print_sample_iter=1, eval_iter=1):
@@ -142,3 +150,59 @@ class Trainer:
             torch.save(core.state_dict(), os.path.join(str(self.save_dir), file_name))
         if torch.distributed.is_initialized():
             torch.distributed.barrier()
+
+    # Not in the reference (its checkpoints hold the model only and are never read back):
+    # everything a resume needs, written off the training stream.
+    def save_training_state(self, file_name, asynchronous=True):
+        """Model state_dict (reference format) + optimizer moments / step + trainer counters. The device ->
+        pinned-host copies run on a side stream and the file is written by a background thread, so the
+        training stream only waits for the snapshot copies to be ENQUEUED; call .join() on the returned
+        thread (or save with asynchronous=False) before relying on the file."""
+        import os
+        import threading
+        core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        side = torch.cuda.Stream() if torch.cuda.is_available() else None
+        snap = {}
+
+        def to_host(t):
+            if not t.is_cuda:
+                return t.detach().clone()
+            h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            h.copy_(t.detach(), non_blocking=True)
+            return h
+        if side is not None:
+            side.wait_stream(torch.cuda.current_stream())
+        ctx = torch.cuda.stream(side) if side is not None else _null()
+        with ctx:
+            snap["model"] = {k: to_host(v) for k, v in core.state_dict().items()}
+            snap["optimizer"] = self.optimizer.state_dict()     # B200AdamW: host copies of the flat moments
+        snap["trainer"] = dict(global_step=self.global_step, tokens_seen=self.tokens_seen, track_lrs=list(self.track_lrs),
+                               peak_lr=getattr(self, "peak_lr", None),
+                               total_training_steps=getattr(self, "total_training_steps", None))
+        done = torch.cuda.Event() if side is not None else None
+        if done is not None:
+            done.record(side)
+            torch.cuda.current_stream().wait_event(done)   # later steps must not overwrite what is being copied
+        path = os.path.join(str(self.save_dir), file_name)
+
+        def write():
+            if done is not None:
+                done.synchronize()
+            if self.rank == 0:
+                torch.save(snap, path)
+        th = threading.Thread(target=write, daemon=False)
+        th.start()
+        if not asynchronous:
+            th.join()
+        return th
+
+    def load_training_state(self, file_name):
+        import os
+        snap = torch.load(os.path.join(str(self.save_dir), file_name), weights_only=False)
+        core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        core.load_state_dict(snap["model"])
+        self.optimizer.load_state_dict(snap["optimizer"])
+        tr = snap["trainer"]
+        self.global_step, self.tokens_seen, self.track_lrs = tr["global_step"], tr["tokens_seen"], list(tr["track_lrs"])
+        if tr.get("total_training_steps") is not None:
+            self.set_schedule(tr["total_training_steps"], tr["peak_lr"])

@@ -384,3 +384,37 @@ def test_kv_cache_generation_matches_full_window(golden):
         for t in range(9, 16):
             lg = m2.forward_cached(xs[:, t:t + 1], cache)
             assert rel_err(lg.float(), m2.forward_last(xs[:, :t + 1]).float()) < BF16_TOL, t
+
+
+def test_training_state_resume(golden, tmp_path):
+    """save_training_state / load_training_state: a run resumed from the snapshot continues with the same
+    step count, learning rates and (up to fp32 summation order in the weight-gradient atomics) parameters."""
+    from building_llm_from_scratch_b200.train import Trainer
+    g = golden("llama_model.pt")
+    batches = g["curve"]["batches"]
+
+    def fresh():
+        model, opt = build_llama(g, True)
+        tr = Trainer(model, opt, g["cfg"], [], None, tmp_path, warmup_steps=2, device="cuda")
+        tr.set_schedule(50, peak_lr=1e-3)
+        return model, opt, tr
+    model, opt, tr = fresh()
+    for i in range(3):
+        tr.train_batch(*batches[i])
+    tr.save_training_state("state.pt").join()
+    for i in range(3, 5):
+        tr.train_batch(*batches[i])
+    want = {k: p.detach().float().clone() for k, p in model.named_parameters() if p.requires_grad}
+    lrs = list(tr.track_lrs)
+    model2, opt2, tr2 = fresh()
+    tr2.load_training_state("state.pt")
+    assert tr2.global_step == 2 and opt2._step == 3 and tr2.track_lrs == lrs[:3]
+    for i in range(3, 5):
+        tr2.train_batch(*batches[i])
+    assert tr2.track_lrs == lrs
+    for k, p in model2.named_parameters():
+        if p.requires_grad:
+            assert rel_err(p.detach().float(), want[k]) < 1e-2, k
+    # a torch.optim.AdamW state is refused rather than misread
+    with pytest.raises(ValueError):
+        opt2.load_state_dict({"state": {}, "param_groups": []})
