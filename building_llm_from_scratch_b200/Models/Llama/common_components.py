@@ -56,6 +56,9 @@ class FeedForward(nn.Module):
     def forward(self, x, residual=None):
         ab = ops.linears_packed(x, [self.fc1, self.fc2])
         if ab is not None:
+            fused = ops.swiglu_down_module(ab, self.fc3, residual)
+            if fused is not None:
+                return fused
             h = ops.swiglu_packed(ab)
         else:
             a, b = ops.linears_of_same_input(x, [self.fc1, self.fc2])

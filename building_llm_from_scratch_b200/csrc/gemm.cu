@@ -34,6 +34,7 @@ enum : int {
   EP_OUT_F32 = 8,
   EP_ATOMIC = 16,
   EP_TRANS_OUT = 32,
+  EP_SWIGLU_BWD = 64,   // pair kernel: the accumulator is dh; write (da | db) of SwiGLU into C, reading (a | b) from R
 };
 
 struct GemmParams {
@@ -372,13 +373,60 @@ int launch_bn(const CUtensorMap* maps, const GemmParams& p, int grid, cudaStream
 // Only the leader CTA issues MMAs; both CTAs run a producer, an epilogue over their own 128
 // TMEM lanes, and arrive remotely on the leader's accumulator-empty barrier.
 // ======================================================================================
+// SwiGLU backward in the epilogue of dh = dY·W3 (+ u·A3^T): for 32 columns of one row, (a | b) come from
+// the packed forward activations R [M, 2F] (b at column offset F = p.N), (da | db) go to C [M, 2F]:
+//   s = sigmoid(a), da = dh * b * s * (1 + a (1 - s)), db = dh * a * s      (common_components.py:87,123 under autograd)
+// The separate kernel this replaces moved 10 bytes per element of [M, F]; dh never reaches memory now.
+struct ABChunk {
+  uint4 a[4], b[4];
+};
+__device__ __forceinline__ ABChunk load_ab(const GemmParams& p, long long row, bool row_ok, long long col0) {
+  ABChunk c;
+  if (row_ok && col0 + 32 <= p.N) {
+    const bf16* A = p.R + row * p.ldr + col0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      c.a[q] = ld_v4(A + q * 8);
+      c.b[q] = ld_v4(A + p.N + q * 8);
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c.a[q] = c.b[q] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  return c;
+}
+__device__ __forceinline__ void swiglu_bwd_store(const GemmParams& p, long long row, bool row_ok, long long col0,
+                                                 const uint32_t* r, const ABChunk& ab) {
+  if (!row_ok || col0 + 32 > p.N) return;
+  bf16* C = (bf16*)p.C + row * p.ldc + col0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float a[8], b[8], da[8], db[8];
+    unpack8(ab.a[q], a);
+    unpack8(ab.b[q], b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float g = __uint_as_float(r[q * 8 + j]) * p.alpha;
+      const float sg = __fdividef(1.f, 1.f + __expf(-a[j]));
+      da[j] = g * b[j] * (sg * (1.f + a[j] * (1.f - sg)));
+      db[j] = g * (a[j] * sg);
+    }
+    st_v4(C + q * 8, pack8(da));
+    st_v4(C + p.N + q * 8, pack8(db));
+  }
+}
+
 constexpr int P_BN = 256;                       // tile N of the pair
 constexpr int P_BHALF_BYTES = (P_BN / 2) * BK * 2;   // 16 KB: this CTA's half of B
 constexpr int P_STAGE_BYTES = A_BYTES + P_BHALF_BYTES;
 constexpr int P_STAGES = RING_BYTES / P_STAGE_BYTES; // 6
 constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 + 16;
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+// SWIGLU variant: 384 threads — two epilogue warps per TMEM lane quadrant (each takes half of the tile's
+// columns); its epilogue moves three times the bytes of a plain store and would otherwise outlast the
+// main loop of the next tile.
+template <bool SWIGLU>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SWIGLU ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                          const GemmParams p) {
@@ -402,7 +450,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 8);   // 4 epilogue warps of each CTA (leader's copy is the one used)
+      mbar_init(&tempty[i], SWIGLU ? 16 : 8);   // the epilogue warps of both CTAs (leader's copy is the one used)
     }
     mbar_fence_init();
   }
@@ -523,8 +571,34 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         umma_commit_2cta(&tfull[as]);
       }
     }
+  } else if (SWIGLU && warp == 3) {
+    // The epilogue's (a | b) reads are one 64-byte piece per thread and chunk: with 128 epilogue threads per
+    // SM that is ~16 KB in flight, far too little to cover HBM latency (the fused GEMM ran 40 % longer).
+    // This otherwise idle warp pulls the tile's (a | b) rows into L2 with bulk prefetches while the tile's
+    // MMAs run (issued when the previous tile's accumulator completes), so the epilogue loads hit L2.
+    int it = 0;
+    for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
+      int tile, kb_begin, kb_end;
+      unit(w, tile, kb_begin, kb_end);
+      const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
+      const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
+      if (it > 0) mbar_wait(&tfull[(it - 1) & 1], (uint32_t)(((it - 1) >> 1) & 1));
+      const long long col0 = (long long)n_blk * P_BN;
+      if (col0 + P_BN <= p.N) {
+#pragma unroll 1
+        for (int rr = lane; rr < 128; rr += 32) {
+          const long long row = (long long)m_blk * 256 + (long long)rank * 128 + rr;
+          if (row < p.M) {
+            const bf16* A = p.R + row * p.ldr + col0;
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A), "r"(P_BN * 2) : "memory");
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + p.N), "r"(P_BN * 2) : "memory");
+          }
+        }
+      }
+    }
   } else if (warp >= 4) {
-    const int ew = warp - 4;
+    const int ew = (warp - 4) & 3;                 // TMEM lane quadrant
+    const int chalf = (warp - 4) >> 2;             // SWIGLU: which half of the tile's column chunks
     int it = 0;
     for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
       int tile, kb_begin, kb_end;
@@ -596,6 +670,19 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         if (lane == 0) mbar_arrive_cluster(&tempty[as], 0);
         continue;
       }
+      if constexpr (SWIGLU) {
+        const int c0 = chalf * (P_BN / 64), c1 = c0 + P_BN / 64;
+        ABChunk nx = load_ab(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
+#pragma unroll 1
+        for (int c = c0; c < c1; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
+          const ABChunk cur = nx;
+          if (c + 1 < c1) nx = load_ab(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
+          tmem_ld_wait();
+          swiglu_bwd_store(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
+        }
+      } else {
       ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN);
 #pragma unroll 1
       for (int c = 0; c < P_BN / 32; ++c) {
@@ -606,6 +693,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         if (c + 1 < P_BN / 32) rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
         tmem_ld_wait();
         store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
+      }
       }
       tc_fence_before();
       __syncwarp();
@@ -626,15 +714,20 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int work = p.tail_start + (tiles - p.tail_start) * p.tail_splits;
   int clusters = sms / 2;
   if (work < clusters) clusters = work;
-  B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0], maps[1],
-                                  maps[2], maps[3], p));
+  if (p.flags & EP_SWIGLU_BWD)
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<true>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
+                                    maps[1], maps[2], maps[3], p));
+  else
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<false>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
+                                    maps[1], maps[2], maps[3], p));
   b200_count_launch();
   return 0;
 }
@@ -1062,7 +1155,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
                  const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
                  int flags, int out_f32, int accumulate, int trans_out, float alpha,
-                 int splitk, void* stream, const SegInfo* seg_info) {
+                 int splitk, void* stream, const SegInfo* seg_info, bool swiglu_bwd = false) {
   B200_CHECK_ARG(M > 0 && N > 0 && K1 > 0 && K2 >= 0, "gemm: bad sizes M=%lld N=%lld K1=%lld K2=%lld",
                  (long long)M, (long long)N, (long long)K1, (long long)K2);
   B200_CHECK_ARG(A1 && B1 && C, "gemm: null operand");
@@ -1074,6 +1167,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
 
   const bool pair = use_pair_kernel() && !accumulate && !trans_out && M >= 256 && N >= 256;
   B200_CHECK_ARG(!seg_info || (pair && !a2_mn), "gemm: segmented LoRA columns need the CTA-pair kernel and a K-major A2");
+  B200_CHECK_ARG(!swiglu_bwd || (pair && N % 32 == 0 && R && !out_f32 && flags == 0), "gemm: the SwiGLU-backward epilogue needs the CTA-pair kernel, N %% 32 == 0 and the packed (a | b) in R");
   const int BN = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
   GemmParams p;
   p.M = (int)M;
@@ -1099,7 +1193,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.ldr = ldr;
   p.C = C;
   p.ldc = ldc;
-  p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0);
+  p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0) | (swiglu_bwd ? EP_SWIGLU_BWD : 0);
 
   const int sms = b200_num_sms();
   const int tiles = p.m_tiles * p.n_tiles;
@@ -1136,7 +1230,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const char* e = getenv("B200_GEMM_TAIL");
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !(e && e[0] == '0')) {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !(e && e[0] == '0')) {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1188,6 +1282,18 @@ extern "C" int b200_gemm_ex(const void* A1, int64_t lda1, int a1_mn, const void*
                             int splitk, void* stream) {
   return gemm_ex_impl(A1, lda1, a1_mn, B1, ldb1, b1_mn, K1, A2, lda2, a2_mn, B2, ldb2, b2_mn, K2, bias, R, ldr, C,
                       ldc, M, N, flags, out_f32, accumulate, trans_out, alpha, splitk, stream, nullptr);
+}
+
+// (da | db) = SwiGLU'(a, b) * (dY·W + U·A^T): the backward of fc3's input with the SwiGLU backward in the epilogue.
+extern "C" int b200_gemm_swiglu_bwd_bf16(const void* dY, int64_t lddy, const void* W, int64_t ldw, int64_t K,
+                                         const void* U, int64_t ldu, const void* A, int64_t lda, int64_t r,
+                                         const void* AB, int64_t ldab, void* dAB, int64_t lddab, int64_t M,
+                                         int64_t F, void* stream) {
+  B200_CHECK_ARG(AB && dAB && M >= 256 && F >= 256 && F % 32 == 0 && ldab >= 2 * F && lddab >= 2 * F && ldab % 8 == 0 && lddab % 8 == 0,
+                 "gemm_swiglu_bwd: needs M, F >= 256, F %% 32 == 0 and packed [M, 2F] buffers with 16-B aligned rows");
+  B200_CHECK_ARG(b200_aligned16(AB) && b200_aligned16(dAB), "gemm_swiglu_bwd: pointers must be 16-B aligned");
+  return gemm_ex_impl(dY, lddy, 0, W, ldw, 1, K, U, ldu, 0, A, lda, 0, r, nullptr, AB, ldab, dAB, lddab, M, F, 0, 0, 0,
+                      0, 1.0f, 0, stream, nullptr, true);
 }
 
 // Several LoRA-wrapped linears of the same input as ONE GEMM: W is the row-concatenation of the base

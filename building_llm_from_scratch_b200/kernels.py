@@ -174,6 +174,35 @@ def gemm_lora_packed(x, w_cat, t_cat, b_cat, r, seg_starts, out=None):
     return out
 
 
+def gemm_swiglu_bwd(dy, w, u, A, ab, out=None):
+    """(da | db) [M, 2F] = SwiGLU'(a, b) * (dy w + u A^T) with (a | b) = ab [M, 2F]; w [K, F] (fc3.weight), u [M, r]
+    and A [F, r] or both None."""
+    _need_cuda(dy, w, u, A, ab, out)
+    lib = _lib.load()
+    dy, lddy = _rowmajor2d(dy)
+    w, ldw = _rowmajor2d(w)
+    ab, ldab = _rowmajor2d(ab)
+    M, Kd = dy.shape
+    F = w.shape[1]
+    assert w.shape[0] == Kd and ab.shape == (M, 2 * F)
+    r = ldu = lda = 0
+    if u is not None:
+        u, ldu = _rowmajor2d(u)
+        A, lda = _rowmajor2d(A)
+        r = u.shape[1]
+        assert A.shape == (F, r)
+    if out is None:
+        out = torch.empty((M, 2 * F), device=dy.device, dtype=BF16)
+    out2, ldo = _rowmajor2d(out)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_swiglu_bwd_bf16(_p(dy), lddy, _p(w), ldw, Kd, _p(u), ldu, _p(A), lda, r, _p(ab), ldab,
+                                             _p(out2), ldo, M, F, _stream()), "gemm_swiglu_bwd")
+    if prof is not None:
+        prof.end(start, 2.0 * M * F * (Kd + r), (M, F, Kd, r, 0, 1, 0))
+    return out
+
+
 def gemm_grouped(problems):
     """problems: list of dicts(a, b, out, a_mn, b_mn, accumulate, trans_out, alpha) with N <= 64.
     One persistent launch for all of them (chunks of GEMM_GROUP_MAX)."""

@@ -710,6 +710,93 @@ def _swiglu_packed_bwd(ctx, dh):
 swiglu_packed.register_autograd(_swiglu_packed_bwd, setup_context=_swiglu_packed_setup)
 
 
+# --------------------------------------------------------------------------------------
+# SwiGLU + down projection as one op (common_components.py:121-124: fc3(silu(fc1 x) * fc2 x)), so that
+# backward can form (da | db) in the epilogue of the fc3 input-gradient GEMM: dh never reaches memory and
+# the 10-bytes-per-element SwiGLU backward kernel disappears.
+# --------------------------------------------------------------------------------------
+@torch.library.custom_op("b200llm::swiglu_down", mutates_args=())
+def swiglu_down(ab: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
+                residual: Optional[Tensor]) -> List[Tensor]:
+    """ab [.., 2F] = (fc1 x | fc2 x) -> [y = fc3(h) (+ residual), t = scaling h A, h = silu(a) * b]."""
+    ab2 = _flat2d(ab)
+    F = ab2.shape[1] // 2
+    h = K.swiglu_fwd(ab2[:, :F], ab2[:, F:])
+    res2 = _flat2d(residual) if residual is not None else None
+    if A is not None:
+        t = K.gemm_ex(h, A, b1_mn=True, alpha=scaling)
+        y = K.gemm_ex(h, weight, a2=t, b2=_pitch_ok(B), b2_mn=True, residual=res2)
+    else:
+        t = h.new_empty((0,))
+        y = K.gemm_ex(h, weight, residual=res2)
+    return [y.view(*ab.shape[:-1], weight.shape[0]), t, h]
+
+
+@swiglu_down.register_fake
+def _(ab, weight, A, B, scaling, residual):
+    rows = ab.numel() // ab.shape[-1]
+    F = ab.shape[-1] // 2
+    t = ab.new_empty((rows, A.shape[1])) if A is not None else ab.new_empty((0,))
+    return [ab.new_empty((*ab.shape[:-1], weight.shape[0])), t, ab.new_empty((rows, F))]
+
+
+def _swiglu_down_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    ab, weight, A, B, scaling, residual = inputs
+    ctx.save_for_backward(ab, weight, A, B, output[1], output[2])
+    ctx.scaling = scaling
+    ctx.has_res = residual is not None
+
+
+def _swiglu_down_bwd(ctx, grads):
+    dy = grads[0]
+    if dy is None:
+        return (None,) * 6
+    ab, weight, A, B, t, h = ctx.saved_tensors
+    need = ctx.needs_input_grad
+    ab2, dy2 = _flat2d(ab), _flat2d(dy)
+    M, F = h.shape
+    u = None
+    if A is not None and (need[0] or A.requires_grad):
+        u = K.gemm_ex(dy2, _pitch_ok(B), alpha=ctx.scaling)            # s * dY B^T   [M, r]
+    dab = None
+    if need[0]:
+        fused = (M >= 256 and F >= 256 and F % 32 == 0 and dy2.shape[1] % 8 == 0
+                 and os.environ.get("B200_SWIGLU_EPILOGUE", "1") != "0")
+        if fused:
+            dab = K.gemm_swiglu_bwd(dy2, weight, u, A if u is not None else None, ab2)
+        else:
+            dh = K.gemm_ex(dy2, weight, b1_mn=True, a2=u, b2=A) if u is not None else K.gemm_ex(dy2, weight, b1_mn=True)
+            dab = ab2.new_empty(ab2.shape)
+            K.swiglu_bwd(ab2[:, :F], ab2[:, F:], dh, da=dab[:, :F], db=dab[:, F:])
+        dab = dab.view(ab.shape)
+    dW = dA = dB = None
+    if A is not None and A.requires_grad:
+        dA = _weight_grad(h, u, A)
+    if B is not None and B.requires_grad:
+        dB = _weight_grad(dy2, t, B, trans_out=True)
+    if weight.requires_grad:
+        dW = _weight_grad(dy2, h, weight)
+    return dab, dW, dA, dB, None, (dy if (ctx.has_res and need[5]) else None)
+
+
+swiglu_down.register_autograd(_swiglu_down_bwd, setup_context=_swiglu_down_setup)
+
+
+def swiglu_down_module(ab, fc3, residual):
+    """swiglu_down for a bias-free fc3 module (plain or LoRA-wrapped); None when it does not apply."""
+    if os.environ.get("B200_PACKED", "1") == "0":
+        return None
+    from .lora import LinearWithLoRA
+    if isinstance(fc3, LinearWithLoRA):
+        if fc3.linear.bias is not None:
+            return None
+        return swiglu_down(ab, fc3.linear.weight, fc3.lora.A, fc3.lora.B, fc3.lora.scaling, residual)[0]
+    if getattr(fc3, "bias", None) is not None:
+        return None
+    return swiglu_down(ab, fc3.weight, None, None, 0.0, residual)[0]
+
+
 @torch.library.custom_op("b200llm::gelu", mutates_args=())
 def gelu(x: Tensor) -> Tensor:
     return K.gelu_fwd(x.contiguous())

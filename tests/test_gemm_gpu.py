@@ -217,3 +217,26 @@ def test_gemm_lora_packed_segments(K, M, outs, K_, r):
     for i, o in enumerate(outs):       # per segment too: a wrong t block would hide in the global norm
         sl = slice(starts[i], starts[i] + o)
         assert rel_err(got[:, sl].float(), ref[:, sl]) < BF16_TOL, i
+
+
+@pytest.mark.parametrize("M,F,K_,r", [(8192, 8192, 2048, 64), (512, 768, 256, 8), (1000, 1024, 512, 0)])
+def test_gemm_swiglu_backward_epilogue(K, M, F, K_, r):
+    """(da | db) from the epilogue of dh = dY W (+ u A^T) against the two-kernel path (GEMM, then swiglu_bwd)
+    and against autograd of the oracle's SwiGLU on the same dh."""
+    from oracle import reference_ops as R
+    dy, w = rnd(M, K_, scale=0.1, seed=1), rnd(K_, F, scale=0.05, seed=2)
+    ab = rnd(M, 2 * F, seed=3)
+    u = rnd(M, r, scale=0.1, seed=4) if r else None
+    A = rnd(F, r, scale=0.1, seed=5) if r else None
+    got = K.gemm_swiglu_bwd(dy, w, u, A, ab)
+    dh = dy.float() @ w.float()
+    if r:
+        dh = dh + u.float() @ A.float().t()
+    a = ab[:, :F].float().requires_grad_(True)
+    b = ab[:, F:].float().requires_grad_(True)
+    (torch.nn.functional.silu(a) * b).backward(dh)
+    assert rel_err(got[:, :F].float(), a.grad) < BF16_TOL
+    assert rel_err(got[:, F:].float(), b.grad) < BF16_TOL
+    dh16 = K.gemm_ex(dy, w, b1_mn=True, a2=u, b2=A) if r else K.gemm_ex(dy, w, b1_mn=True)
+    da, db = K.swiglu_bwd(ab[:, :F], ab[:, F:], dh16)
+    assert rel_err(got[:, :F].float(), da.float()) < 1e-2 and rel_err(got[:, F:].float(), db.float()) < 1e-2
