@@ -4,10 +4,9 @@
 //
 // CTA = 128 query rows of one (batch, head); KV streamed in 64-key tiles by TMA (3-stage ring).
 //   warp 0      : TMA producer (Q once, then K/V tiles)
-//   warp 1      : TMEM allocator + single-thread MMA issuer
-//                   S_j = Q K_j^T      (128 x 64, K-major operands)      -> TMEM, double buffered
-//                   O  += P_j V_j      (A = P from smem, B = V as MN-major) -> TMEM
-//   warps 2..5  : softmax — one thread per query row (TMEM lane), so row max / row sum need no
+//   warp 1      : TMEM allocator + issuer of  S_j = Q K_j^T  (128 x 64, K-major operands) -> TMEM
+//   warp 2      : issuer of  O += P_j V_j  (A = P from smem, B = V as MN-major) -> TMEM
+//   warps 3..6  : softmax — one thread per query row (TMEM lane), so row max / row sum need no
 //                 shuffles: tcgen05.ld S, exp2 online softmax, P -> bf16 into 128B-swizzled smem,
 //                 rescale O in TMEM (tcgen05.ld/st) only when a row maximum moved, final O / l.
 // head_dim 64: 65 KB smem and 128 TMEM columns per CTA -> three CTAs per SM (head_dim 128: 113 KB, 256
@@ -62,7 +61,7 @@ struct FwdParams {
 };
 
 template <int HDIM, bool DROP>
-__global__ void __launch_bounds__(192, FwdCfg<HDIM>::CTAS)
+__global__ void __launch_bounds__(224, FwdCfg<HDIM>::CTAS)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -136,7 +135,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, 0, 0);
-      const uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, 0, 1);
       const uint32_t aQ = smem_u32(sQ);
       mbar_wait(q_full, 0);
       auto issue_s = [&](int j) {
@@ -150,9 +148,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           umma_bf16_ss(tmem_base, umma_desc_k128(aQ + kstep<BQ>(k)), umma_desc_k128(aK + kstep<BKV>(k)), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
-      issue_s(0);
+      // score products only; P V is issued by warp 2 (one thread doing both was the slowest link of the
+      // dK/dV kernel, see there). s_empty throttles this loop: S is a single TMEM buffer.
+      for (int j = 0; j < n_kv; ++j) issue_s(j);
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      const uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, 0, 1);
       for (int j = 0; j < n_kv; ++j) {
-        if (j + 1 < n_kv) issue_s(j + 1);
         const int s = j % NS;
         mbar_wait(&v_full[s], (j / NS) & 1);
         mbar_wait(p_full, j & 1);
@@ -188,23 +191,28 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
       const int kv0 = j * BKV;
       const bool diag = kv0 + BKV - 1 > q0 + quad * 32;  // warp-uniform
+      if (diag) {
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+          if (kv0 + i > q0 + row) r[i] = 0xff800000u;     // -inf
+      }
+      // row maximum on the raw scores (the scale is positive), two columns per FMNMX3
       float mx = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        float x = __uint_as_float(r[i]) * p.scale_log2;
-        if (diag && kv0 + i > q0 + row) x = -INFINITY;
-        r[i] = __float_as_uint(x);
-        mx = fmaxf(mx, x);
-      }
-      const float m_new = fmaxf(m, mx);
+      for (int i = 0; i < 32; ++i) mx = fmax3(mx, __uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+      const float m_new = fmaxf(m, mx * p.scale_log2);
       const float alpha = fast_exp2(m - m_new);
-      float sum = 0.f;
+      // p = exp2(s * scale - m_new): one packed FFMA and one packed FADD per column pair
+      const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), neg2 = pack_f2(-m_new, -m_new);
+      unsigned long long sum2 = pack_f2(0.f, 0.f);
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        float p0 = fast_exp2(__uint_as_float(r[2 * i]) - m_new);
-        float p1 = fast_exp2(__uint_as_float(r[2 * i + 1]) - m_new);
-        sum += p0 + p1;                       // the softmax denominator is taken before dropout
+        float a0, a1;
+        unpack_f2(ffma2(pack_f2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), sc2, neg2), a0, a1);
+        float p0 = fast_exp2(a0);
+        float p1 = fast_exp2(a1);
+        sum2 = fadd2(sum2, pack_f2(p0, p1));          // the softmax denominator is taken before dropout
         if (DROP) {
           bool k0, k1;
           dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, k0, k1);
@@ -213,6 +221,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         pk[i] = f2_to_bf2(p0, p1);
       }
+      float sum, sum_hi;
+      unpack_f2(sum2, sum, sum_hi);
+      sum += sum_hi;
       l = l * alpha + sum;
       m = m_new;
       // the single P buffer and the O accumulator are free once PV_{j-1} has retired
@@ -311,8 +322,8 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
-  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true><<<(unsigned)grid, 192, SMEM, st>>>(mq, mk, mv, p);
-  else attn_fwd_tc_kernel<HD, false><<<(unsigned)grid, 192, SMEM, st>>>(mq, mk, mv, p);
+  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
+  else attn_fwd_tc_kernel<HD, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -356,7 +367,7 @@ struct DkvCfg {
   static constexpr int NSTG = HDIM == 64 ? 5 : 3;    // Q / dO stages
   static constexpr int T2_BYTES = BK2 * HDIM * 2;    // 16 / 32 KB  [128 x HDIM] bf16 tile
   static constexpr int QS_BYTES = QS * HDIM * 2;     // 8 / 16 KB
-  static constexpr int THREADS = 64 + NG * 128;
+  static constexpr int THREADS = 96 + NG * 128;      // TMA warp, score-MMA warp, accumulate-MMA warp, NG x 4 softmax warps
   static constexpr int SMEM = 2 * T2_BYTES + NSTG * 2 * QS_BYTES + 2 * NG * PANEL_BYTES + NSTG * LD_BYTES + 1024 + 256;
   static_assert(SMEM <= 232448, "dK/dV kernel exceeds the 227 KB shared memory of an SM");
   static_assert(2 * NG * QS + 2 * HDIM <= 512, "dK/dV kernel exceeds TMEM");
@@ -366,7 +377,7 @@ struct BwdParams {
   int B, T, H, HKV, nkt, nq64;
   DropParams drop;
   float scale, scale_log2;
-  const float* ld2;   // [B, H, nq64, 2, 64]: lse * log2e (inf beyond T) and delta (0 beyond T)
+  const float* ld2;   // [B, H, nq64, 2, 64]: -lse * log2e (-inf beyond T) and -delta (0 beyond T)
   bf16* dk;
   long long lddk;
   bf16* dv;
@@ -462,7 +473,6 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t id_s = umma_idesc_bf16(128, QS, 0, 0);     // S^T, dP^T
-      const uint32_t id_acc = umma_idesc_bf16(128, HD, 0, 1);   // dV, dK: A K-major, B MN-major
       const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
       mbar_wait(kv_full, 0);
       auto issue_s = [&](int s) {
@@ -479,10 +489,20 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           umma_bf16_ss(tmem_base + C_DPT + buf * QS, umma_desc_k128(aV + kstep<BK2>(k)), umma_desc_k128(adO + kstep<QS>(k)), id_s, k > 0);
         umma_commit(&s_full[buf]);
       };
-      auto issue_acc = [&](int s) {
+      // This thread only issues the score products; it runs as far ahead as the S^T/dP^T buffers
+      // (st_empty) and the Q/dO ring (qdo_full) allow. The accumulating products are issued by warp 2:
+      // one thread doing both spent a barrier round trip per product group and was the slowest link
+      // (the softmax warps sat on s_full for a quarter of their samples).
+      for (int s = 0; s < steps; ++s) issue_s(s);
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      const uint32_t id_acc = umma_idesc_bf16(128, HD, 0, 1);   // dV, dK: A K-major, B MN-major
+      for (int s = 0; s < steps; ++s) {
         const int stg = s % NSTG, buf = s % NG;
         const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
         const uint32_t aPt = smem_u32(sPt + buf * PANEL_BYTES), adSt = smem_u32(sdSt + buf * PANEL_BYTES);
+        mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
         mbar_wait(&ps_full[buf], (s / NG) & 1);
         tc_fence_after();
 #pragma unroll
@@ -495,12 +515,6 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                        (s > 0 || k > 0) ? 1u : 0u);
         umma_commit(&panel_free[buf]);
         umma_commit(&qdo_empty[stg]);
-      };
-      // run NG - 1 steps ahead of the accumulation so every softmax group has its S^T/dP^T waiting
-      for (int s = 0; s < NG - 1 && s < steps; ++s) issue_s(s);
-      for (int s = 0; s < steps; ++s) {
-        if (s + NG - 1 < steps) issue_s(s + NG - 1);
-        issue_acc(s);
       }
       umma_commit(acc_done);
     }
@@ -508,8 +522,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     // NG softmax groups of 4 warps take the steps round-robin (group = step % NG): each owns one of
     // the S^T/dP^T TMEM buffers and one P^T/dS^T smem panel pair, so the barrier / TMEM-load /
     // proxy-fence latencies of one group hide behind the other groups' arithmetic.
-    const int quad = warp & 3;
-    const int grp = (warp - 2) >> 2;
+    const int quad = warp & 3;                        // TMEM lane quadrant of this warp
+    const int grp = (warp - 3) >> 2;
     const int row = quad * 32 + lane;                 // key row
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int key = kv0 + row;
@@ -528,6 +542,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       if (use > 0) mbar_wait(&panel_free[buf], (use - 1) & 1);
       const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
       const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
+      const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), scl2 = pack_f2(p.scale, p.scale);
 #pragma unroll 1
       for (int hf = 0; hf < 2; ++hf) {
         uint32_t sv[32], dv[32];
@@ -542,27 +557,36 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         uint32_t pp[16], dd[16];
 #pragma unroll
         for (int i4 = 0; i4 < 8; ++i4) {
-          const float4 l4 = lds_f4(lse_s + hf * 128 + i4 * 16);
-          const float4 d4 = lds_f4(del_s + hf * 128 + i4 * 16);
-          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+          const float4 l4 = lds_f4(lse_s + hf * 128 + i4 * 16);     // -lse * log2e
+          const float4 d4 = lds_f4(del_s + hf * 128 + i4 * 16);     // -delta
+          const float nls[4] = {l4.x, l4.y, l4.z, l4.w}, nds[4] = {d4.x, d4.y, d4.z, d4.w};
           float pv[4], dsv[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int c = i4 * 4 + e;
-            float pr = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -ls[e]));
-            if (diag && key > qrow0 + hf * 32 + c) pr = 0.f;
-            float dpv = __uint_as_float(dv[c]);
-            float pdrop = pr;
-            if (DROP) {
-              const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c);
-              const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
-                                               ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
-                                           p.drop.seed, p.drop.thr16);
-              dpv = kp ? dpv * p.drop.inv_keep : 0.f;
-              pdrop = kp ? pr * p.drop.inv_keep : 0.f;
+          for (int e2 = 0; e2 < 2; ++e2) {
+            const int c = i4 * 4 + 2 * e2;
+            // packed pairs: P^T = exp2(s c - lse[q]), dS^T = P^T (dP^T - delta[q]) scale
+            float a0, a1;
+            unpack_f2(ffma2(pack_f2(__uint_as_float(sv[c]), __uint_as_float(sv[c + 1])), sc2,
+                            pack_f2(nls[2 * e2], nls[2 * e2 + 1])), a0, a1);
+            float pr[2] = {fast_exp2(a0), fast_exp2(a1)};
+            float dpv[2] = {__uint_as_float(dv[c]), __uint_as_float(dv[c + 1])};
+            float pdrop[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              if (diag && key > qrow0 + hf * 32 + c + e) pr[e] = 0.f;
+              pdrop[e] = pr[e];
+              if (DROP) {
+                const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c + e);
+                const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
+                                                 ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
+                                             p.drop.seed, p.drop.thr16);
+                dpv[e] = kp ? dpv[e] * p.drop.inv_keep : 0.f;
+                pdrop[e] = kp ? pr[e] * p.drop.inv_keep : 0.f;
+              }
+              pv[2 * e2 + e] = pdrop[e];                    // dV uses the dropped, rescaled P
             }
-            pv[e] = pdrop;                                  // dV uses the dropped, rescaled P
-            dsv[e] = pr * (dpv - ds[e]) * p.scale;
+            unpack_f2(fmul2(fmul2(pack_f2(pr[0], pr[1]), fadd2(pack_f2(dpv[0], dpv[1]), pack_f2(nds[2 * e2], nds[2 * e2 + 1]))),
+                            scl2), dsv[2 * e2], dsv[2 * e2 + 1]);
           }
           pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
           pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
@@ -641,7 +665,7 @@ struct DqParams {
 };
 
 template <int HDIM, bool DROP>
-__global__ void __launch_bounds__(192, DqCfg<HDIM>::CTAS)
+__global__ void __launch_bounds__(224, DqCfg<HDIM>::CTAS)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                       const DqParams p) {
@@ -661,7 +685,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   uint64_t* s_empty = s_full + 1;         // 1 (4 arrivals)
   uint64_t* ds_full = s_empty + 1;        // 2 (4 arrivals)
   uint64_t* dq_done = ds_full + 2;        // 1
-  uint32_t* tmem_slot = (uint32_t*)(dq_done + 1);
+  uint64_t* ds_free = dq_done + 1;        // 2: the dQ product that read this dS buffer has retired
+  uint32_t* tmem_slot = (uint32_t*)(ds_free + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int per_qt = p.B * p.H;
@@ -684,6 +709,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     mbar_init(&ds_full[0], 4);
     mbar_init(&ds_full[1], 4);
     mbar_init(dq_done, 1);
+    mbar_init(&ds_free[0], 1);
+    mbar_init(&ds_free[1], 1);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 256);
@@ -715,7 +742,6 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t id_s = umma_idesc_bf16(BQ, BKV, 0, 0);
-      const uint32_t id_dq = umma_idesc_bf16(BQ, HD, 0, 1);
       const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO);
       mbar_wait(q_full, 0);
       auto issue_s = [&](int j) {
@@ -732,12 +758,15 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           umma_bf16_ss(tmem_base + D_DP, umma_desc_k128(adO + kstep<BQ>(k)), umma_desc_k128(aV + kstep<BKV>(k)), id_s, k > 0);
         umma_commit(s_full);
       };
-      issue_s(0);
+      // score products only (throttled by s_empty: S / dP are single TMEM buffers); dQ += dS K is issued by warp 2
+      for (int j = 0; j < n_kv; ++j) issue_s(j);
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      const uint32_t id_dq = umma_idesc_bf16(BQ, HD, 0, 1);
       for (int j = 0; j < n_kv; ++j) {
-        // S/dP of the next tile go first: they only need the softmax threads to have pulled tile j
-        // out of TMEM, so they run while those threads are still forming dS_j
-        if (j + 1 < n_kv) issue_s(j + 1);
         const int s = j % DQ_NS, buf = j & 1;
+        mbar_wait(&kv_full[s], (j / DQ_NS) & 1);
         mbar_wait(&ds_full[buf], (j >> 1) & 1);
         tc_fence_after();
         const uint32_t adS = smem_u32(sdS + buf * P_BYTES), aK = smem_u32(sK + s * KV_BYTES);
@@ -746,6 +775,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           umma_bf16_ss(tmem_base + D_DQ, umma_desc_k128(adS + k * 32), umma_desc_mn128(aK + k * 2048, 8192),
                        id_dq, (j > 0 || k > 0) ? 1u : 0u);
         umma_commit(&kv_empty[s]);
+        umma_commit(&ds_free[buf]);
       }
       umma_commit(dq_done);
     }
@@ -755,8 +785,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int t = q0 + row;
     const float* ldrow = p.ld2 + (((long long)b * p.H + head) * p.nq64 + (t >> 6)) * (2 * QS) + (t & 63);
-    const float lse2 = ldrow[0];     // already * log2e, +inf for padding rows
-    const float dl = ldrow[QS];
+    const float nlse2 = ldrow[0];    // -lse * log2e, -inf for padding rows
+    const float ndl = ldrow[QS];     // -delta
+    const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), nl2 = pack_f2(nlse2, nlse2);
+    const unsigned long long nd2 = pack_f2(ndl, ndl), scl2 = pack_f2(p.scale, p.scale);
     const unsigned long long drop_row =
         (((unsigned long long)b * p.H + head) * p.T + (unsigned long long)t) * (unsigned long long)((p.T + 1) >> 1);
     for (int j = 0; j < n_kv; ++j) {
@@ -777,22 +809,28 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        float v2[2];
         bool keep[2] = {true, true};
         if (DROP)
           dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, keep[0], keep[1]);
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int c = 2 * i + e;
-          float pr = fast_exp2(fmaf(__uint_as_float(s[c]), p.scale_log2, -lse2));
-          if (diag && kv0 + c > t) pr = 0.f;
-          float dpv = __uint_as_float(d[c]);
-          if (DROP) dpv = keep[e] ? dpv * p.drop.inv_keep : 0.f;
-          v2[e] = pr * (dpv - dl) * p.scale;
+        // packed pairs: P = exp2(s c - lse), dS = P (dP - delta) scale
+        float a0, a1;
+        unpack_f2(ffma2(pack_f2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nl2), a0, a1);
+        float pr0 = fast_exp2(a0), pr1 = fast_exp2(a1);
+        if (diag) {
+          if (kv0 + 2 * i > t) pr0 = 0.f;
+          if (kv0 + 2 * i + 1 > t) pr1 = 0.f;
         }
-        pk[i] = f2_to_bf2(v2[0], v2[1]);
+        float dp0 = __uint_as_float(d[2 * i]), dp1 = __uint_as_float(d[2 * i + 1]);
+        if (DROP) {
+          dp0 = keep[0] ? dp0 * p.drop.inv_keep : 0.f;
+          dp1 = keep[1] ? dp1 * p.drop.inv_keep : 0.f;
+        }
+        float v0, v1;
+        unpack_f2(fmul2(fmul2(pack_f2(pr0, pr1), fadd2(pack_f2(dp0, dp1), nd2)), scl2), v0, v1);
+        pk[i] = f2_to_bf2(v0, v1);
       }
-      // buffer `buf` was last read by the dQ MMA of tile j-2, issued before S_j: retired once s_full fired
+      // buffer `buf` was last read by the dQ product of tile j - 2 (another warp issues those)
+      if (j >= 2) mbar_wait(&ds_free[buf], ((j >> 1) - 1) & 1);
       const uint32_t drow = smem_u32(sdS) + buf * P_BYTES + row * 128;
 #pragma unroll
       for (int c = 0; c < 8; ++c)
@@ -830,8 +868,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
 }
 
-// ld2[b, h, step, 0, j] = lse[b, h, 64*step + j] * log2e (+inf beyond T),
-// ld2[b, h, step, 1, j] = delta = sum_c dO * O (0 beyond T); HDIM/8 lanes per (token, head).
+// ld2[b, h, step, 0, j] = -lse[b, h, 64*step + j] * log2e (-inf beyond T),
+// ld2[b, h, step, 1, j] = -delta = -sum_c dO * O (0 beyond T); HDIM/8 lanes per (token, head).
 template <int HDIM>
 __global__ void __launch_bounds__(256)
 attn_delta_tc_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __restrict__ dout,
@@ -863,8 +901,8 @@ attn_delta_tc_kernel(const bf16* __restrict__ o, long long ldo, const bf16* __re
     for (int m = 1; m < LPH; m <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, m);
     if (ok && l8 == 0) {
       float* dst = ld2 + ((bb * H + head) * nq64 + (t >> 6)) * (2 * QS) + (t & 63);
-      dst[0] = real ? lse[(bb * H + head) * T + t] * LOG2E : INFINITY;
-      dst[QS] = real ? acc : 0.f;
+      dst[0] = real ? -lse[(bb * H + head) * T + t] * LOG2E : -INFINITY;     // addends of the packed FFMA / FADD
+      dst[QS] = real ? -acc : 0.f;
     }
   }
 }
@@ -923,8 +961,8 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.drop = make_drop(dropout_p, seed);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
     const long long grid = (long long)nqt * B * h;
-    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
-    else attn_bwd_dq_tc_kernel<HD, false><<<(unsigned)grid, 192, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    else attn_bwd_dq_tc_kernel<HD, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
   }
   {
