@@ -199,7 +199,7 @@ def gemm_swiglu_bwd(dy, w, u, A, ab, out=None):
     _lib.check(lib.b200_gemm_swiglu_bwd_bf16(_p(dy), lddy, _p(w), ldw, Kd, _p(u), ldu, _p(A), lda, r, _p(ab), ldab,
                                              _p(out2), ldo, M, F, _stream()), "gemm_swiglu_bwd")
     if prof is not None:
-        prof.end(start, 2.0 * M * F * (Kd + r), (M, F, Kd, r, 0, 1, 0))
+        prof.end(start, 2.0 * M * F * (Kd + r), ("swiglu_bwd_epilogue", M, F, Kd, r))
     return out
 
 
