@@ -422,11 +422,13 @@ constexpr int P_STAGE_BYTES = A_BYTES + P_BHALF_BYTES;
 constexpr int P_STAGES = RING_BYTES / P_STAGE_BYTES; // 6
 constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 + 16;
 
-// SWIGLU variant: 384 threads — two epilogue warps per TMEM lane quadrant (each takes half of the tile's
-// columns); its epilogue moves three times the bytes of a plain store and would otherwise outlast the
-// main loop of the next tile.
-template <bool SWIGLU>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SWIGLU ? 384 : 256, 1)
+// MODE 0: 256 threads, four epilogue warps. MODE 1 (SwiGLU-backward epilogue) and MODE 2 (plain epilogue, used
+// when a residual is added): 384 threads — two epilogue warps per TMEM lane quadrant, half of the tile's
+// columns each. The epilogue is one 16-byte access per thread and instruction (32 different rows per warp),
+// so it is bound by LSU transactions and load latency; with reads in it (residual, a|b) four warps outlast
+// the main loop of the next tile at K = 2048.
+template <int MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(MODE ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                          const GemmParams p) {
@@ -438,6 +440,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
 
+  constexpr bool SWIGLU = MODE == 1;
+  constexpr bool WIDE = MODE != 0;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -450,7 +454,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], SWIGLU ? 16 : 8);   // the epilogue warps of both CTAs (leader's copy is the one used)
+      mbar_init(&tempty[i], WIDE ? 16 : 8);   // the epilogue warps of both CTAs (leader's copy is the one used)
     }
     mbar_fence_init();
   }
@@ -598,7 +602,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     }
   } else if (warp >= 4) {
     const int ew = (warp - 4) & 3;                 // TMEM lane quadrant
-    const int chalf = (warp - 4) >> 2;             // SWIGLU: which half of the tile's column chunks
+    const int chalf = (warp - 4) >> 2;             // WIDE: which half of the tile's column chunks
+    const int c0 = WIDE ? chalf * (P_BN / 64) : 0, c1 = WIDE ? c0 + P_BN / 64 : P_BN / 32;
+    auto epi_sync = [] {
+      if (WIDE) asm volatile("bar.sync 1, 256;" ::: "memory");
+      else asm volatile("bar.sync 1, 128;" ::: "memory");
+    };
     int it = 0;
     for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
       int tile, kb_begin, kb_end;
@@ -624,7 +633,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         float4* mine = slot0 + (long long)sp * (256 * (P_BN / 4)) + rit;
         const uint32_t tacc = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN);
 #pragma unroll 1
-        for (int c = 0; c < P_BN / 32; ++c) {
+        for (int c = c0; c < c1; ++c) {
           uint32_t r[32];
           tmem_ld_32x32(tacc + c * 32, r);
           tmem_ld_wait();
@@ -634,18 +643,18 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
                                                          __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])));
         }
         __threadfence();
-        epi_bar_sync();
+        epi_sync();
         if (threadIdx.x == 128) {
           const int old = atomicAdd(p.tail_cnt + tt * 2 + (int)rank, 1);
           s_last = (old + 1 == p.tail_splits) ? 1 : 0;
         }
-        epi_bar_sync();
+        epi_sync();
         if (s_last) {
           __threadfence();
           ResChunk none;
           none.vec = false;
 #pragma unroll 1
-          for (int c = 0; c < P_BN / 32; ++c) {
+          for (int c = c0; c < c1; ++c) {
             uint32_t r[32];
             tmem_ld_32x32(tacc + c * 32, r);
             tmem_ld_wait();
@@ -671,7 +680,6 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         continue;
       }
       if constexpr (SWIGLU) {
-        const int c0 = chalf * (P_BN / 64), c1 = c0 + P_BN / 64;
         ABChunk nx = load_ab(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
 #pragma unroll 1
         for (int c = c0; c < c1; ++c) {
@@ -683,14 +691,14 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           swiglu_bwd_store(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
         }
       } else {
-      ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN);
+      ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
 #pragma unroll 1
-      for (int c = 0; c < P_BN / 32; ++c) {
+      for (int c = c0; c < c1; ++c) {
         uint32_t r[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32);
         tmem_ld_32x32(taddr, r);
         const ResChunk cur = rc;
-        if (c + 1 < P_BN / 32) rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
+        if (c + 1 < c1) rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
         tmem_ld_wait();
         store_chunk(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
       }
@@ -714,19 +722,24 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int work = p.tail_start + (tiles - p.tail_start) * p.tail_splits;
   int clusters = sms / 2;
   if (work < clusters) clusters = work;
+  static const int wide_env = [] { const char* e = getenv("B200_GEMM_EPI8"); return e ? atoi(e) : 0; }();   // measured neutral for residual epilogues: off unless asked for
   if (p.flags & EP_SWIGLU_BWD)
-    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<true>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
+                                    maps[1], maps[2], maps[3], p));
+  else if ((p.flags & EP_RESIDUAL) && wide_env)
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
                                     maps[1], maps[2], maps[3], p));
   else
-    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<false>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<0>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
                                     maps[1], maps[2], maps[3], p));
   b200_count_launch();
   return 0;
