@@ -373,54 +373,21 @@ int launch_bn(const CUtensorMap* maps, const GemmParams& p, int grid, cudaStream
 // Only the leader CTA issues MMAs; both CTAs run a producer, an epilogue over their own 128
 // TMEM lanes, and arrive remotely on the leader's accumulator-empty barrier.
 // ======================================================================================
-// SwiGLU backward in the epilogue of dh = dY·W3 (+ u·A3^T): for 32 columns of one row, (a | b) come from
-// the packed forward activations R [M, 2F] (b at column offset F = p.N), (da | db) go to C [M, 2F]:
+// SwiGLU backward in the epilogue of dh = dY·W3 (+ u·A3^T) (MODE 1 of the pair kernel): (a | b) come from the
+// packed forward activations R [M, 2F] (b at column offset F = p.N), (da | db) go to C [M, 2F]:
 //   s = sigmoid(a), da = dh * b * s * (1 + a (1 - s)), db = dh * a * s      (common_components.py:87,123 under autograd)
 // The separate kernel this replaces moved 10 bytes per element of [M, F]; dh never reaches memory now.
-struct ABChunk {
-  uint4 a[4], b[4];
-};
-__device__ __forceinline__ ABChunk load_ab(const GemmParams& p, long long row, bool row_ok, long long col0) {
-  ABChunk c;
-  if (row_ok && col0 + 32 <= p.N) {
-    const bf16* A = p.R + row * p.ldr + col0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      c.a[q] = ld_v4(A + q * 8);
-      c.b[q] = ld_v4(A + p.N + q * 8);
-    }
-  } else {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) c.a[q] = c.b[q] = make_uint4(0u, 0u, 0u, 0u);
-  }
-  return c;
-}
-__device__ __forceinline__ void swiglu_bwd_store(const GemmParams& p, long long row, bool row_ok, long long col0,
-                                                 const uint32_t* r, const ABChunk& ab) {
-  if (!row_ok || col0 + 32 > p.N) return;
-  bf16* C = (bf16*)p.C + row * p.ldc + col0;
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    float a[8], b[8], da[8], db[8];
-    unpack8(ab.a[q], a);
-    unpack8(ab.b[q], b);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float g = __uint_as_float(r[q * 8 + j]) * p.alpha;
-      const float sg = __fdividef(1.f, 1.f + __expf(-a[j]));
-      da[j] = g * b[j] * (sg * (1.f + a[j] * (1.f - sg)));
-      db[j] = g * (a[j] * sg);
-    }
-    st_v4(C + q * 8, pack8(da));
-    st_v4(C + p.N + q * 8, pack8(db));
-  }
-}
-
 constexpr int P_BN = 256;                       // tile N of the pair
 constexpr int P_BHALF_BYTES = (P_BN / 2) * BK * 2;   // 16 KB: this CTA's half of B
 constexpr int P_STAGE_BYTES = A_BYTES + P_BHALF_BYTES;
 constexpr int P_STAGES = RING_BYTES / P_STAGE_BYTES; // 6
-constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 + 16;
+constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 + 16 + 64;
+// MODE 1: the epilogue's (a | b) -> (da | db) tiles pass through one 32 KB staging buffer behind the ring (measured:
+// 4 ring stages + 2 or 3 buffers 260 us, 5 + 2: 243 us, 6 + 1: 233 us — the main loop needs the ring depth more)
+constexpr int P_STAGES_SWIGLU = 6;
+constexpr int P_AB_BYTES = 2 * 128 * 64 * 2;   // one [128 x 64] a tile + one b tile
+constexpr int P_AB_BUFS = 1;
+constexpr int P_SMEM_SWIGLU = P_STAGES_SWIGLU * P_STAGE_BYTES + P_AB_BUFS * P_AB_BYTES + 1024 + 256;
 
 // MODE 0: 256 threads, four epilogue warps. MODE 1 (SwiGLU-backward epilogue) and MODE 2 (plain epilogue, used
 // when a residual is added): 384 threads — two epilogue warps per TMEM lane quadrant, half of the tile's
@@ -431,30 +398,42 @@ template <int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(MODE ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                         const __grid_constant__ CUtensorMap tmAB, const __grid_constant__ CUtensorMap tmDAB,
                          const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + P_STAGES * P_STAGE_BYTES);
+  uint64_t* full = (uint64_t*)(smem + (MODE == 1 ? P_STAGES_SWIGLU * P_STAGE_BYTES + P_AB_BUFS * P_AB_BYTES
+                                                 : P_STAGES * P_STAGE_BYTES));
   uint64_t* empty = full + P_STAGES;
   uint64_t* tfull = empty + P_STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  uint64_t* in_full = tempty + 3;             // MODE 1: (a | b) staging buffers filled by TMA
+  uint64_t* out_full = in_full + P_AB_BUFS;   //         ... rewritten in place with (da | db) by the 8 epilogue warps
 
   constexpr bool SWIGLU = MODE == 1;
   constexpr bool WIDE = MODE != 0;
+  constexpr int STAGES = SWIGLU ? P_STAGES_SWIGLU : P_STAGES;
+  uint8_t* sab = smem + P_STAGES_SWIGLU * P_STAGE_BYTES;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P_STAGES; ++i) {
+    for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], WIDE ? 16 : 8);   // the epilogue warps of both CTAs (leader's copy is the one used)
+    }
+    if (SWIGLU) {
+      for (int i = 0; i < P_AB_BUFS; ++i) {
+        mbar_init(&in_full[i], 1);
+        mbar_init(&out_full[i], 8);
+      }
     }
     mbar_fence_init();
   }
@@ -531,7 +510,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             tma_load_2d_2cta(sb, mb, &full[stage], n0, kk);
             tma_load_2d_2cta(sb + 8192, mb, &full[stage], n0 + 64, kk);
           }
-          if (++stage == P_STAGES) {
+          if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
@@ -567,7 +546,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             umma_bf16_ss_2cta(d_tmem, ad, bd, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
           umma_commit_2cta(&empty[stage]);
-          if (++stage == P_STAGES) {
+          if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
@@ -576,29 +555,45 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       }
     }
   } else if (SWIGLU && warp == 3) {
-    // The epilogue's (a | b) reads are one 64-byte piece per thread and chunk: with 128 epilogue threads per
-    // SM that is ~16 KB in flight, far too little to cover HBM latency (the fused GEMM ran 40 % longer).
-    // This otherwise idle warp pulls the tile's (a | b) rows into L2 with bulk prefetches while the tile's
-    // MMAs run (issued when the previous tile's accumulator completes), so the epilogue loads hit L2.
-    int it = 0;
-    for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
-      int tile, kb_begin, kb_end;
-      unit(w, tile, kb_begin, kb_end);
-      const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
-      const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
-      if (it > 0) mbar_wait(&tfull[(it - 1) & 1], (uint32_t)(((it - 1) >> 1) & 1));
-      const long long col0 = (long long)n_blk * P_BN;
-      if (col0 + P_BN <= p.N) {
-#pragma unroll 1
-        for (int rr = lane; rr < 128; rr += 32) {
-          const long long row = (long long)m_blk * 256 + (long long)rank * 128 + rr;
-          if (row < p.M) {
-            const bf16* A = p.R + row * p.ldr + col0;
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A), "r"(P_BN * 2) : "memory");
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + p.N), "r"(P_BN * 2) : "memory");
+    // Feeds and drains the epilogue: the (a | b) tiles of the current output tile come in 64 columns at a
+    // time by TMA (swizzled staging buffers), the epilogue warps overwrite them in place with (da | db), and
+    // this thread sends those out again with TMA stores. Per-thread global accesses of one row piece each
+    // (32 rows per warp instruction) made the SM's load/store unit the bottleneck of this kernel: 303 us
+    // against 186 us for the plain GEMM, 120 us of it the stores.
+    if (lane == 0) {
+      tma_prefetch_desc(&tmAB);
+      tma_prefetch_desc(&tmDAB);
+      int n = 0;
+      int q_row[P_AB_BUFS], q_col[P_AB_BUFS];
+      auto drain = [&](int k) {               // (da | db) of group k: staged -> global
+        const int buf = k % P_AB_BUFS;
+        mbar_wait(&out_full[buf], (uint32_t)((k / P_AB_BUFS) & 1));
+        tma_store_2d(&tmDAB, sab + buf * P_AB_BYTES, q_col[buf], q_row[buf]);
+        tma_store_2d(&tmDAB, sab + buf * P_AB_BYTES + P_AB_BYTES / 2, p.N + q_col[buf], q_row[buf]);
+        tma_store_commit();
+      };
+      for (int w = cluster_id; w < num_work; w += num_clusters) {
+        int tile, kb_begin, kb_end;
+        unit(w, tile, kb_begin, kb_end);
+        const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
+        const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
+        const int row0 = m_blk * 256 + (int)rank * 128;
+        for (int g = 0; g < P_BN / 64; ++g, ++n) {
+          const int buf = n % P_AB_BUFS;
+          if (n >= P_AB_BUFS) {
+            drain(n - P_AB_BUFS);
+            tma_store_wait_read();            // the buffer may be refilled once the stores have read it
           }
+          mbar_expect_tx(&in_full[buf], P_AB_BYTES);
+          const int col = n_blk * P_BN + g * 64;
+          tma_load_2d(sab + buf * P_AB_BYTES, &tmAB, &in_full[buf], col, row0);
+          tma_load_2d(sab + buf * P_AB_BYTES + P_AB_BYTES / 2, &tmAB, &in_full[buf], p.N + col, row0);
+          q_row[buf] = row0;
+          q_col[buf] = col;
         }
       }
+      for (int k = (n >= P_AB_BUFS ? n - P_AB_BUFS : 0); k < n; ++k) drain(k);
+      tma_store_wait_all();
     }
   } else if (warp >= 4) {
     const int ew = (warp - 4) & 3;                 // TMEM lane quadrant
@@ -680,15 +675,40 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         continue;
       }
       if constexpr (SWIGLU) {
-        ABChunk nx = load_ab(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
+        // 64 columns at a time: this warp takes the half (32 columns) given by chalf; its thread's row of a and b
+        // comes out of the swizzled staging tile (16-byte piece index XOR row % 8) and da, db go back into the
+        // same places; warp 3 stores the finished tiles.
+        const int rloc = ew * 32 + lane;
 #pragma unroll 1
-        for (int c = c0; c < c1; ++c) {
+        for (int g = 0; g < P_BN / 64; ++g) {
+          const int n = it * (P_BN / 64) + g, buf = n % P_AB_BUFS;
+          const int c = 2 * g + chalf;
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
-          const ABChunk cur = nx;
-          if (c + 1 < c1) nx = load_ab(p, row, row_ok, (long long)n_blk * P_BN + (c + 1) * 32);
+          mbar_wait(&in_full[buf], (uint32_t)((n / P_AB_BUFS) & 1));
+          const uint32_t arow = smem_u32(sab) + buf * P_AB_BYTES + rloc * 128;
           tmem_ld_wait();
-          swiglu_bwd_store(p, row, row_ok, (long long)n_blk * P_BN + c * 32, r, cur);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t off = (uint32_t)(((chalf * 4 + q) ^ (rloc & 7)) << 4);
+            const float4 fa = lds_f4(arow + off), fb = lds_f4(arow + P_AB_BYTES / 2 + off);
+            float a[8], b[8], da[8], db[8];
+            unpack8(make_uint4(__float_as_uint(fa.x), __float_as_uint(fa.y), __float_as_uint(fa.z), __float_as_uint(fa.w)), a);
+            unpack8(make_uint4(__float_as_uint(fb.x), __float_as_uint(fb.y), __float_as_uint(fb.z), __float_as_uint(fb.w)), b);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float gch = __uint_as_float(r[q * 8 + j]) * p.alpha;
+              const float sg = __fdividef(1.f, 1.f + __expf(-a[j]));
+              da[j] = gch * b[j] * (sg * (1.f + a[j] * (1.f - sg)));
+              db[j] = gch * (a[j] * sg);
+            }
+            const uint4 va = pack8(da), vb = pack8(db);
+            sts_v4(arow + off, va.x, va.y, va.z, va.w);
+            sts_v4(arow + P_AB_BYTES / 2 + off, vb.x, vb.y, vb.z, vb.w);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&out_full[buf]);
         }
       } else {
       ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
@@ -723,7 +743,7 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
@@ -733,14 +753,14 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   if (work < clusters) clusters = work;
   static const int wide_env = [] { const char* e = getenv("B200_GEMM_EPI8"); return e ? atoi(e) : 0; }();   // measured neutral for residual epilogues: off unless asked for
   if (p.flags & EP_SWIGLU_BWD)
-    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
-                                    maps[1], maps[2], maps[3], p));
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
+                                    maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else if ((p.flags & EP_RESIDUAL) && wide_env)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
-                                    maps[1], maps[2], maps[3], p));
+                                    maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<0>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
-                                    maps[1], maps[2], maps[3], p));
+                                    maps[1], maps[2], maps[3], maps[4], maps[5], p));
   b200_count_launch();
   return 0;
 }
@@ -1259,7 +1279,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     }
   }
 
-  CUtensorMap maps[4];
+  CUtensorMap maps[6];
   int rc;
   Operand oa1{A1, lda1, a1_mn}, ob1{B1, ldb1, b1_mn};
   const int b_box_rows = pair ? 128 : BN;   // the pair kernel loads half of the B tile per CTA
@@ -1273,6 +1293,13 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   } else {
     maps[2] = maps[0];
     maps[3] = maps[1];
+  }
+  maps[4] = maps[0];
+  maps[5] = maps[0];
+  if (swiglu_bwd) {   // (a | b) and (da | db), both [M, 2N], move 64 columns x 128 rows at a time through TMA
+    B200_CHECK_ARG(N % P_BN == 0, "gemm: the SwiGLU-backward epilogue needs N %% %d == 0", P_BN);
+    if ((rc = b200_make_tmap_2d_bf16(&maps[4], R, (uint64_t)M, (uint64_t)(2 * N), (uint64_t)ldr, 128, 64))) return rc;
+    if ((rc = b200_make_tmap_2d_bf16(&maps[5], C, (uint64_t)M, (uint64_t)(2 * N), (uint64_t)ldc, 128, 64))) return rc;
   }
   const int work = tiles * splits;
   const int grid = work < sms ? work : sms;
@@ -1302,8 +1329,8 @@ extern "C" int b200_gemm_swiglu_bwd_bf16(const void* dY, int64_t lddy, const voi
                                          const void* U, int64_t ldu, const void* A, int64_t lda, int64_t r,
                                          const void* AB, int64_t ldab, void* dAB, int64_t lddab, int64_t M,
                                          int64_t F, void* stream) {
-  B200_CHECK_ARG(AB && dAB && M >= 256 && F >= 256 && F % 32 == 0 && ldab >= 2 * F && lddab >= 2 * F && ldab % 8 == 0 && lddab % 8 == 0,
-                 "gemm_swiglu_bwd: needs M, F >= 256, F %% 32 == 0 and packed [M, 2F] buffers with 16-B aligned rows");
+  B200_CHECK_ARG(AB && dAB && M >= 256 && F >= 256 && F % 256 == 0 && ldab >= 2 * F && lddab >= 2 * F && ldab % 8 == 0 && lddab % 8 == 0,
+                 "gemm_swiglu_bwd: needs M >= 256, F a multiple of 256 and packed [M, 2F] buffers with 16-B aligned rows");
   B200_CHECK_ARG(b200_aligned16(AB) && b200_aligned16(dAB), "gemm_swiglu_bwd: pointers must be 16-B aligned");
   return gemm_ex_impl(dY, lddy, 0, W, ldw, 1, K, U, ldu, 0, A, lda, 0, r, nullptr, AB, ldab, dAB, lddab, M, F, 0, 0, 0,
                       0, 1.0f, 0, stream, nullptr, true);

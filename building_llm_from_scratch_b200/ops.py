@@ -761,7 +761,7 @@ def _swiglu_down_bwd(ctx, grads):
         u = K.gemm_ex(dy2, _pitch_ok(B), alpha=ctx.scaling)            # s * dY B^T   [M, r]
     dab = None
     if need[0]:
-        fused = (M >= 256 and F >= 256 and F % 32 == 0 and dy2.shape[1] % 8 == 0
+        fused = (M >= 256 and F % 256 == 0 and dy2.shape[1] % 8 == 0
                  and os.environ.get("B200_SWIGLU_EPILOGUE", "1") != "0")
         if fused:
             dab = K.gemm_swiglu_bwd(dy2, weight, u, A if u is not None else None, ab2)

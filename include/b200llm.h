@@ -85,7 +85,7 @@ int b200_gemm_lora_packed_bf16(const void* X, int64_t ldx, const void* W, int64_
  *   dh = dY[M, K]·W[K, F] (+ U[M, r]·A[F, r]^T),   (da | db)[M, 2F] = SwiGLU'(a, b)·dh,   (a | b) = AB[M, 2F]
  * W = fc3.weight [K = emb_dim, F = hidden_dim] read as an MN-major operand, U = s·dY·B^T, A = fc3's LoRA A
  * (r = 0: no LoRA). dh is never written. Replaces the autograd of common_components.py:121-124
- * (fc3 input gradient, silu(fc1 x) * fc2 x). M, F >= 256, F % 32 == 0. */
+ * (fc3 input gradient, silu(fc1 x) * fc2 x). M >= 256, F a multiple of 256. */
 int b200_gemm_swiglu_bwd_bf16(const void* dY, int64_t lddy, const void* W, int64_t ldw, int64_t K,
                               const void* U, int64_t ldu, const void* A, int64_t lda, int64_t r,
                               const void* AB, int64_t ldab, void* dAB, int64_t lddab, int64_t M, int64_t F,
