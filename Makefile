@@ -18,7 +18,7 @@ $(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/common.cuh include/b200llm.h
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; exit 1)
 
 $(LIB): $(OBJS)
-	$(NVCC) -shared -o $@ $(OBJS) -lcudart
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $(OBJS) -lcudart
 
 clean:
 	rm -rf build $(LIB)
