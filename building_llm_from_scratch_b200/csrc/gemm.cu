@@ -385,15 +385,15 @@ constexpr int P_SMEM = P_STAGES * P_STAGE_BYTES + 1024 + (2 * P_STAGES + 4) * 8 
 // MODE 1: the epilogue's (a | b) -> (da | db) tiles pass through one 32 KB staging buffer behind the ring (measured:
 // 4 ring stages + 2 or 3 buffers 260 us, 5 + 2: 243 us, 6 + 1: 233 us — the main loop needs the ring depth more)
 constexpr int P_STAGES_SWIGLU = 6;
-constexpr int P_AB_BYTES = 2 * 128 * 64 * 2;   // one [128 x 64] a tile + one b tile
-constexpr int P_AB_BUFS = 1;
-constexpr int P_SMEM_SWIGLU = P_STAGES_SWIGLU * P_STAGE_BYTES + P_AB_BUFS * P_AB_BYTES + 1024 + 256;
+constexpr int P_IO_TILE = 128 * 64 * 2;        // one staged [128 rows x 64 columns] bf16 tile
+constexpr int P_IO_BYTES = 2 * P_IO_TILE;      // staging area behind the ring: MODE 1 one (a | b) buffer, MODE 2 two R buffers
+constexpr int P_SMEM_SWIGLU = P_STAGES_SWIGLU * P_STAGE_BYTES + P_IO_BYTES + 1024 + 256;
 
-// MODE 0: 256 threads, four epilogue warps. MODE 1 (SwiGLU-backward epilogue) and MODE 2 (plain epilogue, used
-// when a residual is added): 384 threads — two epilogue warps per TMEM lane quadrant, half of the tile's
-// columns each. The epilogue is one 16-byte access per thread and instruction (32 different rows per warp),
-// so it is bound by LSU transactions and load latency; with reads in it (residual, a|b) four warps outlast
-// the main loop of the next tile at K = 2048.
+// MODE 0: 256 threads, four epilogue warps, per-thread 16-byte global accesses (one row per lane). MODE 1
+// (SwiGLU-backward epilogue) and MODE 2 (residual epilogue): 384 threads — two epilogue warps per TMEM lane
+// quadrant, half of each 64-column group each — and every epilogue operand / result travels by TMA through a
+// swizzled staging area, because one-row-per-lane accesses cost 32 line transactions per warp instruction and
+// made the load/store unit the limit once the epilogue reads as well as writes.
 template <int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(MODE ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
@@ -402,18 +402,21 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
                          const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + (MODE == 1 ? P_STAGES_SWIGLU * P_STAGE_BYTES + P_AB_BUFS * P_AB_BYTES
-                                                 : P_STAGES * P_STAGE_BYTES));
+  constexpr bool SWIGLU = MODE == 1;
+  constexpr bool STAGED = MODE != 0;             // epilogue operands / results travel by TMA through smem
+  constexpr int IO_TILES = SWIGLU ? 2 : 1;       // tiles per staged group: (a | b) or the residual
+  constexpr int IO_BUFS = SWIGLU ? 1 : 2;
+  constexpr int BUF_BYTES = IO_TILES * P_IO_TILE;
+  uint64_t* full = (uint64_t*)(smem + (STAGED ? P_STAGES_SWIGLU * P_STAGE_BYTES + P_IO_BYTES : P_STAGES * P_STAGE_BYTES));
   uint64_t* empty = full + P_STAGES;
   uint64_t* tfull = empty + P_STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
-  uint64_t* in_full = tempty + 3;             // MODE 1: (a | b) staging buffers filled by TMA
-  uint64_t* out_full = in_full + P_AB_BUFS;   //         ... rewritten in place with (da | db) by the 8 epilogue warps
+  uint64_t* in_full = tempty + 3;             // staged modes: staging buffers filled by TMA
+  uint64_t* out_full = in_full + IO_BUFS;     //         ... rewritten in place with the results by the 8 epilogue warps
 
-  constexpr bool SWIGLU = MODE == 1;
   constexpr bool WIDE = MODE != 0;
-  constexpr int STAGES = SWIGLU ? P_STAGES_SWIGLU : P_STAGES;
+  constexpr int STAGES = STAGED ? P_STAGES_SWIGLU : P_STAGES;
   uint8_t* sab = smem + P_STAGES_SWIGLU * P_STAGE_BYTES;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -429,8 +432,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], WIDE ? 16 : 8);   // the epilogue warps of both CTAs (leader's copy is the one used)
     }
-    if (SWIGLU) {
-      for (int i = 0; i < P_AB_BUFS; ++i) {
+    if (STAGED) {
+      for (int i = 0; i < IO_BUFS; ++i) {
         mbar_init(&in_full[i], 1);
         mbar_init(&out_full[i], 8);
       }
@@ -554,45 +557,47 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         umma_commit_2cta(&tfull[as]);
       }
     }
-  } else if (SWIGLU && warp == 3) {
-    // Feeds and drains the epilogue: the (a | b) tiles of the current output tile come in 64 columns at a
-    // time by TMA (swizzled staging buffers), the epilogue warps overwrite them in place with (da | db), and
-    // this thread sends those out again with TMA stores. Per-thread global accesses of one row piece each
-    // (32 rows per warp instruction) made the SM's load/store unit the bottleneck of this kernel: 303 us
-    // against 186 us for the plain GEMM, 120 us of it the stores.
+  } else if (STAGED && warp == 3) {
+    // Feeds and drains the epilogue by TMA, 64 columns x 128 rows at a time, through swizzled staging buffers:
+    // MODE 1 brings in the (a | b) tiles, the epilogue warps overwrite them in place with (da | db); MODE 2
+    // brings in the residual tile, overwritten with the finished output tile; this thread stores the results.
+    // Per-thread global accesses of one row piece each (32 rows per warp instruction) made the SM's
+    // load/store unit the bottleneck of these epilogues: the SwiGLU one took 303 us against 186 us for the
+    // plain GEMM, 120 us of it the stores.
     if (lane == 0) {
       tma_prefetch_desc(&tmAB);
       tma_prefetch_desc(&tmDAB);
       int n = 0;
-      int q_row[P_AB_BUFS], q_col[P_AB_BUFS];
-      auto drain = [&](int k) {               // (da | db) of group k: staged -> global
-        const int buf = k % P_AB_BUFS;
-        mbar_wait(&out_full[buf], (uint32_t)((k / P_AB_BUFS) & 1));
-        tma_store_2d(&tmDAB, sab + buf * P_AB_BYTES, q_col[buf], q_row[buf]);
-        tma_store_2d(&tmDAB, sab + buf * P_AB_BYTES + P_AB_BYTES / 2, p.N + q_col[buf], q_row[buf]);
+      int q_row[IO_BUFS], q_col[IO_BUFS];
+      auto drain = [&](int k) {               // results of group k: staged -> global
+        const int buf = k % IO_BUFS;
+        mbar_wait(&out_full[buf], (uint32_t)((k / IO_BUFS) & 1));
+        tma_store_2d(&tmDAB, sab + buf * BUF_BYTES, q_col[buf], q_row[buf]);
+        if (IO_TILES == 2) tma_store_2d(&tmDAB, sab + buf * BUF_BYTES + P_IO_TILE, p.N + q_col[buf], q_row[buf]);
         tma_store_commit();
       };
       for (int w = cluster_id; w < num_work; w += num_clusters) {
+        if (w >= p.tail_start) continue;      // K-split tail tiles use the per-thread epilogue
         int tile, kb_begin, kb_end;
         unit(w, tile, kb_begin, kb_end);
         const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
         const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
         const int row0 = m_blk * 256 + (int)rank * 128;
         for (int g = 0; g < P_BN / 64; ++g, ++n) {
-          const int buf = n % P_AB_BUFS;
-          if (n >= P_AB_BUFS) {
-            drain(n - P_AB_BUFS);
+          const int buf = n % IO_BUFS;
+          if (n >= IO_BUFS) {
+            drain(n - IO_BUFS);
             tma_store_wait_read();            // the buffer may be refilled once the stores have read it
           }
-          mbar_expect_tx(&in_full[buf], P_AB_BYTES);
+          mbar_expect_tx(&in_full[buf], BUF_BYTES);
           const int col = n_blk * P_BN + g * 64;
-          tma_load_2d(sab + buf * P_AB_BYTES, &tmAB, &in_full[buf], col, row0);
-          tma_load_2d(sab + buf * P_AB_BYTES + P_AB_BYTES / 2, &tmAB, &in_full[buf], p.N + col, row0);
+          tma_load_2d(sab + buf * BUF_BYTES, &tmAB, &in_full[buf], col, row0);
+          if (IO_TILES == 2) tma_load_2d(sab + buf * BUF_BYTES + P_IO_TILE, &tmAB, &in_full[buf], p.N + col, row0);
           q_row[buf] = row0;
           q_col[buf] = col;
         }
       }
-      for (int k = (n >= P_AB_BUFS ? n - P_AB_BUFS : 0); k < n; ++k) drain(k);
+      for (int k = (n >= IO_BUFS ? n - IO_BUFS : 0); k < n; ++k) drain(k);
       tma_store_wait_all();
     }
   } else if (warp >= 4) {
@@ -604,6 +609,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       else asm volatile("bar.sync 1, 128;" ::: "memory");
     };
     int it = 0;
+    int nst = 0;                                   // staged 64-column groups consumed so far
     for (int w = cluster_id; w < num_work; w += num_clusters, ++it) {
       int tile, kb_begin, kb_end;
       unit(w, tile, kb_begin, kb_end);
@@ -681,17 +687,17 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         const int rloc = ew * 32 + lane;
 #pragma unroll 1
         for (int g = 0; g < P_BN / 64; ++g) {
-          const int n = it * (P_BN / 64) + g, buf = n % P_AB_BUFS;
+          const int n = nst++, buf = n % IO_BUFS;
           const int c = 2 * g + chalf;
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
-          mbar_wait(&in_full[buf], (uint32_t)((n / P_AB_BUFS) & 1));
-          const uint32_t arow = smem_u32(sab) + buf * P_AB_BYTES + rloc * 128;
+          mbar_wait(&in_full[buf], (uint32_t)((n / IO_BUFS) & 1));
+          const uint32_t arow = smem_u32(sab) + buf * BUF_BYTES + rloc * 128;
           tmem_ld_wait();
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const uint32_t off = (uint32_t)(((chalf * 4 + q) ^ (rloc & 7)) << 4);
-            const float4 fa = lds_f4(arow + off), fb = lds_f4(arow + P_AB_BYTES / 2 + off);
+            const float4 fa = lds_f4(arow + off), fb = lds_f4(arow + P_IO_TILE + off);
             float a[8], b[8], da[8], db[8];
             unpack8(make_uint4(__float_as_uint(fa.x), __float_as_uint(fa.y), __float_as_uint(fa.z), __float_as_uint(fa.w)), a);
             unpack8(make_uint4(__float_as_uint(fb.x), __float_as_uint(fb.y), __float_as_uint(fb.z), __float_as_uint(fb.w)), b);
@@ -704,7 +710,39 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             }
             const uint4 va = pack8(da), vb = pack8(db);
             sts_v4(arow + off, va.x, va.y, va.z, va.w);
-            sts_v4(arow + P_AB_BYTES / 2 + off, vb.x, vb.y, vb.z, vb.w);
+            sts_v4(arow + P_IO_TILE + off, vb.x, vb.y, vb.z, vb.w);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&out_full[buf]);
+        }
+      } else if constexpr (MODE == 2) {
+        // residual epilogue through the staging buffers: out = alpha * acc (+ bias) + R, written over R's tile
+        const int rloc = ew * 32 + lane;
+#pragma unroll 1
+        for (int g = 0; g < P_BN / 64; ++g) {
+          const int n = nst++, buf = n % IO_BUFS;
+          const int c = 2 * g + chalf;
+          const long long col0 = (long long)n_blk * P_BN + c * 32;
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + c * 32), r);
+          mbar_wait(&in_full[buf], (uint32_t)((n / IO_BUFS) & 1));
+          const uint32_t rrow = smem_u32(sab) + buf * BUF_BYTES + rloc * 128;
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t off = (uint32_t)(((chalf * 4 + q) ^ (rloc & 7)) << 4);
+            const float4 fr = lds_f4(rrow + off);
+            float res[8], v[8];
+            unpack8(make_uint4(__float_as_uint(fr.x), __float_as_uint(fr.y), __float_as_uint(fr.z), __float_as_uint(fr.w)), res);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              v[j] = __uint_as_float(r[q * 8 + j]) * p.alpha;
+              if (p.flags & EP_BIAS) v[j] += __bfloat162float(p.bias[col0 + q * 8 + j]);
+              v[j] += res[j];
+            }
+            const uint4 vo = pack8(v);
+            sts_v4(rrow + off, vo.x, vo.y, vo.z, vo.w);
           }
           fence_proxy_async_smem();
           __syncwarp();
@@ -744,19 +782,22 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
     attr_set[dev] = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int work = p.tail_start + (tiles - p.tail_start) * p.tail_splits;
   int clusters = sms / 2;
   if (work < clusters) clusters = work;
-  static const int wide_env = [] { const char* e = getenv("B200_GEMM_EPI8"); return e ? atoi(e) : 0; }();   // measured neutral for residual epilogues: off unless asked for
+  // residual epilogue through TMA staging (MODE 2): bf16 output, whole 256-column tiles, 16-byte aligned pitches
+  static const int res_tma = [] { const char* e = getenv("B200_GEMM_RES_TMA"); return e ? atoi(e) : 1; }();
+  const bool staged_res = res_tma && (p.flags & EP_RESIDUAL) && !(p.flags & (EP_GELU | EP_OUT_F32 | EP_TRANS_OUT | EP_ATOMIC)) &&
+                          p.N % P_BN == 0 && (p.ldr & 7) == 0 && (p.ldc & 7) == 0 && (((uintptr_t)p.R | (uintptr_t)p.C) & 15) == 0;
   if (p.flags & EP_SWIGLU_BWD)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
-  else if ((p.flags & EP_RESIDUAL) && wide_env)
-    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
+  else if (staged_res)
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<0>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
@@ -1296,6 +1337,12 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   }
   maps[4] = maps[0];
   maps[5] = maps[0];
+  if (pair && !swiglu_bwd && (flags & B200_GEMM_RESIDUAL) && !out_f32 && N % P_BN == 0 && ldr % 8 == 0 && ldc % 8 == 0 &&
+      b200_aligned16(R) && b200_aligned16(C)) {
+    // residual tile in, output tile out, both by TMA (MODE 2)
+    if ((rc = b200_make_tmap_2d_bf16(&maps[4], R, (uint64_t)M, (uint64_t)N, (uint64_t)ldr, 128, 64))) return rc;
+    if ((rc = b200_make_tmap_2d_bf16(&maps[5], C, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 128, 64))) return rc;
+  }
   if (swiglu_bwd) {   // (a | b) and (da | db), both [M, 2N], move 64 columns x 128 rows at a time through TMA
     B200_CHECK_ARG(N % P_BN == 0, "gemm: the SwiGLU-backward epilogue needs N %% %d == 0", P_BN);
     if ((rc = b200_make_tmap_2d_bf16(&maps[4], R, (uint64_t)M, (uint64_t)(2 * N), (uint64_t)ldr, 128, 64))) return rc;
