@@ -148,9 +148,19 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
   if (p.flags & EP_OUT_F32) {
     float* C = (float*)p.C + row * p.ldc + col0;
     if (p.flags & EP_ATOMIC) {
+      if (full_cols && (p.ldc & 3) == 0 && (((uintptr_t)C) & 15) == 0) {
+        // one REDG.F32x4 per four columns: a thread's 32 columns are contiguous, and the RED issue rate
+        // (~1 per clock per SM) is what bounds this epilogue
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < p.N) atomicAdd(&C[j], v[j]);
+        for (int q = 0; q < 8; ++q)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(C + q * 4), "f"(v[q * 4]), "f"(v[q * 4 + 1]),
+                       "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3])
+                       : "memory");
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) atomicAdd(&C[j], v[j]);
+      }
     } else if (full_cols && (p.ldc & 3) == 0) {
 #pragma unroll
       for (int q = 0; q < 8; ++q)
