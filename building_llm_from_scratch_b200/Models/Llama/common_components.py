@@ -54,6 +54,11 @@ class FeedForward(nn.Module):
         self.silu = SiLU()
 
     def forward(self, x, residual=None):
+        fused = ops.fc12_swiglu(x, self.fc1, self.fc2)       # (a | b) and h from one GEMM epilogue
+        if fused is not None:
+            out = ops.swiglu_down_module(fused[0], self.fc3, residual, h=fused[1].detach())
+            if out is not None:
+                return out
         ab = ops.linears_packed(x, [self.fc1, self.fc2])
         if ab is not None:
             fused = ops.swiglu_down_module(ab, self.fc3, residual)

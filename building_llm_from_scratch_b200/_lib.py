@@ -45,6 +45,7 @@ SIGNATURES = {
                          I64, I64, I, I, I, I, F, I, P]),
     "b200_gemm_lora_packed_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, I, C.POINTER(C.c_int64), P, I64, I64, I64, P]),
     "b200_gemm_swiglu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_workspace_bytes": (SZ, []),
     "b200_gemm_set_workspace": (I, [P, SZ]),
     "b200_gemm_grouped_bf16": (I, [I, C.POINTER(GemmProblem), P]),

@@ -35,6 +35,7 @@ enum : int {
   EP_ATOMIC = 16,
   EP_TRANS_OUT = 32,
   EP_SWIGLU_BWD = 64,   // pair kernel: the accumulator is dh; write (da | db) of SwiGLU into C, reading (a | b) from R
+  EP_SWIGLU_FWD = 128,  // pair kernel: tile = 128 columns of a | the same 128 of b; write (a | b) into C and h into R
 };
 
 struct GemmParams {
@@ -405,7 +406,7 @@ constexpr int P_SMEM_SWIGLU = P_STAGES_SWIGLU * P_STAGE_BYTES + P_IO_BYTES + 102
 // swizzled staging area, because one-row-per-lane accesses cost 32 line transactions per warp instruction and
 // made the load/store unit the limit once the epilogue reads as well as writes.
 template <int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(MODE ? 384 : 256, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((MODE == 1 || MODE == 2) ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                          const __grid_constant__ CUtensorMap tmAB, const __grid_constant__ CUtensorMap tmDAB,
@@ -413,7 +414,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   constexpr bool SWIGLU = MODE == 1;
-  constexpr bool STAGED = MODE != 0;             // epilogue operands / results travel by TMA through smem
+  constexpr bool STAGED = MODE == 1 || MODE == 2;   // epilogue operands / results travel by TMA through smem
   constexpr int IO_TILES = SWIGLU ? 2 : 1;       // tiles per staged group: (a | b) or the residual
   constexpr int IO_BUFS = SWIGLU ? 1 : 2;
   constexpr int BUF_BYTES = IO_TILES * P_IO_TILE;
@@ -425,7 +426,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   uint64_t* in_full = tempty + 3;             // staged modes: staging buffers filled by TMA
   uint64_t* out_full = in_full + IO_BUFS;     //         ... rewritten in place with the results by the 8 epilogue warps
 
-  constexpr bool WIDE = MODE != 0;
+  constexpr bool WIDE = STAGED;
   constexpr int STAGES = STAGED ? P_STAGES_SWIGLU : P_STAGES;
   uint8_t* sab = smem + P_STAGES_SWIGLU * P_STAGE_BYTES;
   const int warp = threadIdx.x >> 5;
@@ -726,6 +727,38 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           __syncwarp();
           if (lane == 0) mbar_arrive(&out_full[buf]);
         }
+      } else if constexpr (MODE == 3) {
+        // SwiGLU forward: the tile's first 128 columns are a = fc1 x, the last 128 the matching b = fc2 x (the
+        // weights were row-interleaved that way). Both are rounded to bf16 as the separate linears would, stored
+        // into the packed (a | b) buffer, and h = silu(a) * b — with the reference's bf16 roundings — goes to R.
+        const long long F = p.N >> 1;
+        const long long colf = (long long)n_blk * (P_BN / 2);
+        bf16* Cab = (bf16*)p.C + row * p.ldc + colf;
+        bf16* H = const_cast<bf16*>(p.R) + row * p.ldr + colf;
+#pragma unroll 1
+        for (int k = 0; k < P_BN / 64; ++k) {
+          uint32_t ra[32], rb[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + k * 32);
+          tmem_ld_32x32(taddr, ra);
+          tmem_ld_32x32(taddr + P_BN / 2, rb);
+          tmem_ld_wait();
+          if (row_ok && colf + k * 32 + 32 <= F) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float a[8], b[8], h[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                a[j] = bf16_round(__uint_as_float(ra[q * 8 + j]) * p.alpha);
+                b[j] = bf16_round(__uint_as_float(rb[q * 8 + j]) * p.alpha);
+                const float sg = bf16_round(__fdividef(1.f, 1.f + __expf(-a[j])));
+                h[j] = bf16_round(a[j] * sg) * b[j];
+              }
+              st_v4(Cab + k * 32 + q * 8, pack8(a));
+              st_v4(Cab + F + k * 32 + q * 8, pack8(b));
+              st_v4(H + k * 32 + q * 8, pack8(h));
+            }
+          }
+        }
       } else if constexpr (MODE == 2) {
         // residual epilogue through the staging buffers: out = alpha * acc (+ bias) + R, written over R's tile
         const int rloc = ew * 32 + lane;
@@ -793,6 +826,7 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
@@ -805,6 +839,9 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
                           p.N % P_BN == 0 && (p.ldr & 7) == 0 && (p.ldc & 7) == 0 && (((uintptr_t)p.R | (uintptr_t)p.C) & 15) == 0;
   if (p.flags & EP_SWIGLU_BWD)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
+                                    maps[1], maps[2], maps[3], maps[4], maps[5], p));
+  else if (p.flags & EP_SWIGLU_FWD)
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<3>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else if (staged_res)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
@@ -1239,7 +1276,8 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  const void* B2, int64_t ldb2, int b2_mn, int64_t K2, const void* bias,
                  const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
                  int flags, int out_f32, int accumulate, int trans_out, float alpha,
-                 int splitk, void* stream, const SegInfo* seg_info, bool swiglu_bwd = false) {
+                 int splitk, void* stream, const SegInfo* seg_info, bool swiglu_bwd = false,
+                 bool swiglu_fwd = false) {
   B200_CHECK_ARG(M > 0 && N > 0 && K1 > 0 && K2 >= 0, "gemm: bad sizes M=%lld N=%lld K1=%lld K2=%lld",
                  (long long)M, (long long)N, (long long)K1, (long long)K2);
   B200_CHECK_ARG(A1 && B1 && C, "gemm: null operand");
@@ -1277,7 +1315,10 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.ldr = ldr;
   p.C = C;
   p.ldc = ldc;
-  p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0) | (swiglu_bwd ? EP_SWIGLU_BWD : 0);
+  p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0) | (swiglu_bwd ? EP_SWIGLU_BWD : 0) |
+            (swiglu_fwd ? EP_SWIGLU_FWD : 0);
+  B200_CHECK_ARG(!swiglu_fwd || (pair && N % P_BN == 0 && R && !out_f32 && flags == 0),
+                 "gemm: the SwiGLU-forward epilogue needs the CTA-pair kernel, N %% %d == 0 and the h buffer in R", P_BN);
 
   const int sms = b200_num_sms();
   const int tiles = p.m_tiles * p.n_tiles;
@@ -1314,7 +1355,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const char* e = getenv("B200_GEMM_TAIL");
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !(e && e[0] == '0')) {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !(e && e[0] == '0')) {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1347,7 +1388,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   }
   maps[4] = maps[0];
   maps[5] = maps[0];
-  if (pair && !swiglu_bwd && (flags & B200_GEMM_RESIDUAL) && !out_f32 && N % P_BN == 0 && ldr % 8 == 0 && ldc % 8 == 0 &&
+  if (pair && !swiglu_bwd && !swiglu_fwd && (flags & B200_GEMM_RESIDUAL) && !out_f32 && N % P_BN == 0 && ldr % 8 == 0 && ldc % 8 == 0 &&
       b200_aligned16(R) && b200_aligned16(C)) {
     // residual tile in, output tile out, both by TMA (MODE 2)
     if ((rc = b200_make_tmap_2d_bf16(&maps[4], R, (uint64_t)M, (uint64_t)N, (uint64_t)ldr, 128, 64))) return rc;
@@ -1391,6 +1432,22 @@ extern "C" int b200_gemm_swiglu_bwd_bf16(const void* dY, int64_t lddy, const voi
   B200_CHECK_ARG(b200_aligned16(AB) && b200_aligned16(dAB), "gemm_swiglu_bwd: pointers must be 16-B aligned");
   return gemm_ex_impl(dY, lddy, 0, W, ldw, 1, K, U, ldu, 0, A, lda, 0, r, nullptr, AB, ldab, dAB, lddab, M, F, 0, 0, 0,
                       0, 1.0f, 0, stream, nullptr, true);
+}
+
+// (a | b) = x·[W1; W2]^T (+ LoRA) and h = silu(a) * b in one launch. Wil holds the rows of W1 and W2 interleaved in
+// blocks of 128 (tile = 128 columns of a, then the same 128 of b); T2 = [t1 | t2] (t_i = s x A_i), Bil [2r, 2F] is
+// the matching column-interleaved block matrix (rows 0..r-1: B1 in the a columns, zeros in the b columns; rows
+// r..2r-1 the other way round), so the tile's a half gets t1 B1 and its b half t2 B2.
+extern "C" int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void* Wil, int64_t ldw, int64_t K,
+                                         const void* T2, int64_t ldt, const void* Bil, int64_t ldb, int64_t r2,
+                                         void* AB, int64_t ldab, void* H, int64_t ldh, int64_t M, int64_t F,
+                                         void* stream) {
+  B200_CHECK_ARG(AB && H && M >= 256 && F >= 128 && F % 128 == 0 && ldab >= 2 * F && ldh >= F && ldab % 8 == 0 && ldh % 8 == 0,
+                 "gemm_swiglu_fwd: needs M >= 256, F a multiple of 128, a packed [M, 2F] (a | b) buffer and an [M, F] h buffer");
+  B200_CHECK_ARG(b200_aligned16(AB) && b200_aligned16(H), "gemm_swiglu_fwd: pointers must be 16-B aligned");
+  B200_CHECK_ARG(r2 >= 0 && r2 % 8 == 0 && r2 <= 128, "gemm_swiglu_fwd: 2r=%lld must be a multiple of 8 and <= 128", (long long)r2);
+  return gemm_ex_impl(X, ldx, 0, Wil, ldw, 0, K, T2, ldt, 0, Bil, ldb, 1, r2, nullptr, H, ldh, AB, ldab, M, 2 * F, 0, 0, 0,
+                      0, 1.0f, 0, stream, nullptr, false, true);
 }
 
 // Several LoRA-wrapped linears of the same input as ONE GEMM: W is the row-concatenation of the base

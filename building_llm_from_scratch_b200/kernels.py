@@ -203,6 +203,33 @@ def gemm_swiglu_bwd(dy, w, u, A, ab, out=None):
     return out
 
 
+def gemm_swiglu_fwd(x, w_il, t2, b_il, ab=None, h=None):
+    """(a | b) [M, 2F] = x [W1; W2]^T (+ LoRA), h [M, F] = silu(a) * b in one launch. w_il [2F, K]: rows of W1 / W2
+    interleaved in blocks of 128; t2 [M, 2r], b_il [2r, 2F] (see b200_gemm_swiglu_fwd_bf16) or both None."""
+    _need_cuda(x, w_il, t2, b_il, ab, h)
+    lib = _lib.load()
+    _ensure_gemm_workspace(x.device)
+    x, ldx = _rowmajor2d(x)
+    w_il, ldw = _rowmajor2d(w_il)
+    M, Kd = x.shape
+    F = w_il.shape[0] // 2
+    r2 = ldt = ldb = 0
+    if t2 is not None:
+        t2, ldt = _rowmajor2d(t2)
+        b_il, ldb = _rowmajor2d(b_il)
+        r2 = t2.shape[1]
+        assert b_il.shape == (r2, 2 * F)
+    ab = torch.empty((M, 2 * F), device=x.device, dtype=BF16) if ab is None else ab
+    h = torch.empty((M, F), device=x.device, dtype=BF16) if h is None else h
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_swiglu_fwd_bf16(_p(x), ldx, _p(w_il), ldw, Kd, _p(t2), ldt, _p(b_il), ldb, r2, _p(ab),
+                                             ab.stride(0), _p(h), h.stride(0), M, F, _stream()), "gemm_swiglu_fwd")
+    if prof is not None:
+        prof.end(start, 2.0 * M * 2 * F * (Kd + r2 // 2), (M, 2 * F, Kd, r2, 0, 0, 0))
+    return ab, h
+
+
 def gemm_grouped(problems):
     """problems: list of dicts(a, b, out, a_mn, b_mn, accumulate, trans_out, alpha) with N <= 64.
     One persistent launch for all of them (chunks of GEMM_GROUP_MAX)."""

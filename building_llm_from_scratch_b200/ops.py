@@ -493,6 +493,104 @@ def _llp_bwd(ctx, grads):
 lora_linear_packed.register_autograd(_llp_bwd, setup_context=_llp_setup)
 
 
+# fc1 | fc2 with SwiGLU in the GEMM epilogue: same packed (a | b) output and same backward as
+# lora_linear_packed, plus h = silu(a) * b straight from the accumulators (no separate 6-bytes-per-element
+# SwiGLU kernel). Needs the frozen weights interleaved in 128-row blocks (cached like the concatenation).
+_wil_cache: dict = {}
+
+
+def _interleaved_weight(weights, blk=128):
+    if len(weights) != 2 or any(w.requires_grad for w in weights) or weights[0].shape != weights[1].shape:
+        return None
+    F, Kd = weights[0].shape
+    if F % blk:
+        return None
+    key = tuple(w.data_ptr() for w in weights)
+    ver = tuple(w._version for w in weights)
+    hit = _wil_cache.get(key)
+    if hit is None or hit[0] != ver:
+        with torch.no_grad():
+            w1, w2 = (w.detach() for w in weights)
+            il = torch.stack([w1.view(F // blk, blk, Kd), w2.view(F // blk, blk, Kd)], dim=1).reshape(2 * F, Kd).contiguous()
+        hit = (ver, il)
+        _wil_cache[key] = hit
+    return hit[1]
+
+
+def _interleaved_lora_b(B1, B2, blk=128):
+    """[2r, 2F]: rows 0..r-1 = B1 in the a columns of the 128-block interleaving (zeros in the b columns), rows
+    r..2r-1 = B2 in the b columns."""
+    r, F = B1.shape
+    out = B1.new_zeros((2 * r, F // blk, 2, blk))
+    out[:r, :, 0, :] = B1.view(r, F // blk, blk)
+    out[r:, :, 1, :] = B2.view(r, F // blk, blk)
+    return out.view(2 * r, 2 * F)
+
+
+@torch.library.custom_op("b200llm::lora_fc12_swiglu", mutates_args=())
+def lora_fc12_swiglu(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor], Bs: Sequence[Tensor], scaling: float,
+                     w_cat: Optional[Tensor], w_il: Tensor) -> List[Tensor]:
+    """-> [(a | b) [.., 2F], t_cat [M, 2r], h [.., F]] for the two up projections of a SwiGLU feed-forward."""
+    x2 = _flat2d(x)
+    M = x2.shape[0]
+    F = weights[0].shape[0]
+    if len(As) > 0:
+        r = As[0].shape[1]
+        t_cat = x2.new_empty((M, 2 * r))
+        K.gemm_grouped([dict(a=x2, b=As[i], out=t_cat[:, i * r:(i + 1) * r], b_mn=True, alpha=scaling) for i in range(2)])
+        ab, h = K.gemm_swiglu_fwd(x2, w_il, t_cat, _interleaved_lora_b(Bs[0], Bs[1]))
+    else:
+        t_cat = x2.new_empty((0,))
+        ab, h = K.gemm_swiglu_fwd(x2, w_il, None, None)
+    return [ab.view(*x.shape[:-1], 2 * F), t_cat, h.view(*x.shape[:-1], F)]
+
+
+@lora_fc12_swiglu.register_fake
+def _(x, weights, As, Bs, scaling, w_cat, w_il):
+    rows = x.numel() // x.shape[-1]
+    F = weights[0].shape[0]
+    t = x.new_empty((rows, 2 * As[0].shape[1])) if len(As) > 0 else x.new_empty((0,))
+    return [x.new_empty((*x.shape[:-1], 2 * F)), t, x.new_empty((*x.shape[:-1], F))]
+
+
+def _lfs_setup(ctx, inputs, output):
+    _llp_setup(ctx, inputs[:6], output[:2])
+
+
+def _lfs_bwd(ctx, grads):
+    return _llp_bwd(ctx, grads[:2]) + (None,)
+
+
+lora_fc12_swiglu.register_autograd(_lfs_bwd, setup_context=_lfs_setup)
+
+
+def fc12_swiglu(x, fc1, fc2):
+    """(ab, h) through lora_fc12_swiglu for two bias-free up projections (both plain or both LoRA-wrapped with the
+    same rank and scaling, frozen base weights), or None when that does not apply."""
+    if os.environ.get("B200_PACKED", "1") == "0" or os.environ.get("B200_SWIGLU_FWD_EPILOGUE", "1") == "0":
+        return None
+    from .lora import LinearWithLoRA
+    mods = [fc1, fc2]
+    lora = [isinstance(m, LinearWithLoRA) for m in mods]
+    bases = [m.linear if l else m for m, l in zip(mods, lora)]
+    if any(b.bias is not None for b in bases) or lora[0] != lora[1]:
+        return None
+    rows = x.numel() // x.shape[-1]
+    weights = [b.weight for b in bases]
+    w_il = _interleaved_weight(weights)
+    if w_il is None or rows < 256:
+        return None
+    if lora[0]:
+        scal, r = fc1.lora.scaling, fc1.lora.A.shape[1]
+        if fc2.lora.scaling != scal or fc2.lora.A.shape[1] != r or r % 8 or 2 * r > 128:
+            return None
+        out = lora_fc12_swiglu(x, weights, [fc1.lora.A, fc2.lora.A], [fc1.lora.B, fc2.lora.B], scal,
+                               _packed_weight(weights), w_il)
+    else:
+        out = lora_fc12_swiglu(x, weights, [], [], 0.0, _packed_weight(weights), w_il)
+    return out[0], out[2]
+
+
 def linears_packed(x, modules):
     """Packed output of several bias-free linears (all plain or all LoRA-wrapped with one scaling and one
     rank) of the same x, or None when they cannot be fused that way."""
@@ -717,11 +815,12 @@ swiglu_packed.register_autograd(_swiglu_packed_bwd, setup_context=_swiglu_packed
 # --------------------------------------------------------------------------------------
 @torch.library.custom_op("b200llm::swiglu_down", mutates_args=())
 def swiglu_down(ab: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
-                residual: Optional[Tensor]) -> List[Tensor]:
-    """ab [.., 2F] = (fc1 x | fc2 x) -> [y = fc3(h) (+ residual), t = scaling h A, h = silu(a) * b]."""
+                residual: Optional[Tensor], h_in: Optional[Tensor]) -> List[Tensor]:
+    """ab [.., 2F] = (fc1 x | fc2 x) -> [y = fc3(h) (+ residual), t = scaling h A, h = silu(a) * b].
+    h_in: h already formed by the up projections' epilogue (lora_fc12_swiglu), else it is computed here."""
     ab2 = _flat2d(ab)
     F = ab2.shape[1] // 2
-    h = K.swiglu_fwd(ab2[:, :F], ab2[:, F:])
+    h = _flat2d(h_in) if h_in is not None else K.swiglu_fwd(ab2[:, :F], ab2[:, F:])
     res2 = _flat2d(residual) if residual is not None else None
     if A is not None:
         t = K.gemm_ex(h, A, b1_mn=True, alpha=scaling)
@@ -729,21 +828,22 @@ def swiglu_down(ab: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Ten
     else:
         t = h.new_empty((0,))
         y = K.gemm_ex(h, weight, residual=res2)
-    return [y.view(*ab.shape[:-1], weight.shape[0]), t, h]
+    # h is handed back only to be saved for backward: a fresh tensor unless it came in (outputs must not alias inputs)
+    return [y.view(*ab.shape[:-1], weight.shape[0]), t, h if h_in is None else h.new_empty((0,))]
 
 
 @swiglu_down.register_fake
-def _(ab, weight, A, B, scaling, residual):
+def _(ab, weight, A, B, scaling, residual, h_in):
     rows = ab.numel() // ab.shape[-1]
     F = ab.shape[-1] // 2
     t = ab.new_empty((rows, A.shape[1])) if A is not None else ab.new_empty((0,))
-    return [ab.new_empty((*ab.shape[:-1], weight.shape[0])), t, ab.new_empty((rows, F))]
+    return [ab.new_empty((*ab.shape[:-1], weight.shape[0])), t, ab.new_empty((rows, F) if h_in is None else (0,))]
 
 
 def _swiglu_down_setup(ctx, inputs, output):
     ctx.set_materialize_grads(False)
-    ab, weight, A, B, scaling, residual = inputs
-    ctx.save_for_backward(ab, weight, A, B, output[1], output[2])
+    ab, weight, A, B, scaling, residual, h_in = inputs
+    ctx.save_for_backward(ab, weight, A, B, output[1], output[2] if h_in is None else h_in)
     ctx.scaling = scaling
     ctx.has_res = residual is not None
 
@@ -751,8 +851,9 @@ def _swiglu_down_setup(ctx, inputs, output):
 def _swiglu_down_bwd(ctx, grads):
     dy = grads[0]
     if dy is None:
-        return (None,) * 6
+        return (None,) * 7
     ab, weight, A, B, t, h = ctx.saved_tensors
+    h = _flat2d(h)
     need = ctx.needs_input_grad
     ab2, dy2 = _flat2d(ab), _flat2d(dy)
     M, F = h.shape
@@ -777,13 +878,13 @@ def _swiglu_down_bwd(ctx, grads):
         dB = _weight_grad(dy2, t, B, trans_out=True)
     if weight.requires_grad:
         dW = _weight_grad(dy2, h, weight)
-    return dab, dW, dA, dB, None, (dy if (ctx.has_res and need[5]) else None)
+    return dab, dW, dA, dB, None, (dy if (ctx.has_res and need[5]) else None), None
 
 
 swiglu_down.register_autograd(_swiglu_down_bwd, setup_context=_swiglu_down_setup)
 
 
-def swiglu_down_module(ab, fc3, residual):
+def swiglu_down_module(ab, fc3, residual, h=None):
     """swiglu_down for a bias-free fc3 module (plain or LoRA-wrapped); None when it does not apply."""
     if os.environ.get("B200_PACKED", "1") == "0":
         return None
@@ -791,10 +892,10 @@ def swiglu_down_module(ab, fc3, residual):
     if isinstance(fc3, LinearWithLoRA):
         if fc3.linear.bias is not None:
             return None
-        return swiglu_down(ab, fc3.linear.weight, fc3.lora.A, fc3.lora.B, fc3.lora.scaling, residual)[0]
+        return swiglu_down(ab, fc3.linear.weight, fc3.lora.A, fc3.lora.B, fc3.lora.scaling, residual, h)[0]
     if getattr(fc3, "bias", None) is not None:
         return None
-    return swiglu_down(ab, fc3.weight, None, None, 0.0, residual)[0]
+    return swiglu_down(ab, fc3.weight, None, None, 0.0, residual, h)[0]
 
 
 @torch.library.custom_op("b200llm::gelu", mutates_args=())

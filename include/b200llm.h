@@ -91,6 +91,17 @@ int b200_gemm_swiglu_bwd_bf16(const void* dY, int64_t lddy, const void* W, int64
                               const void* AB, int64_t ldab, void* dAB, int64_t lddab, int64_t M, int64_t F,
                               void* stream);
 
+/* Forward of the SwiGLU feed-forward's up projections with SwiGLU in the epilogue:
+ *   (a | b)[M, 2F] = x[M, K]·[W1; W2]^T (+ LoRA),   h[M, F] = silu(a) * b  (bf16 roundings of the reference)
+ * Wil [2F, K]: rows of fc1.weight and fc2.weight interleaved in blocks of 128 (128 rows of W1, the same 128 of W2, ...);
+ * T2 [M, 2r] = [s·x·A1 | s·x·A2]; Bil [2r, 2F]: rows 0..r-1 hold B1 in the a columns of that interleaving and zeros
+ * in the b columns, rows r..2r-1 the other way round (r2 = 2r, 0: no LoRA). (a | b) is written in the plain packed
+ * layout (a in columns [0, F), b in [F, 2F)). Replaces common_components.py:121-123 (fc1, fc2, silu, product).
+ * M >= 256, F a multiple of 128. */
+int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void* Wil, int64_t ldw, int64_t K,
+                              const void* T2, int64_t ldt, const void* Bil, int64_t ldb, int64_t r2,
+                              void* AB, int64_t ldab, void* H, int64_t ldh, int64_t M, int64_t F, void* stream);
+
 /* Optional scratch for the large-GEMM kernel (one per device, caller-owned, 256-byte aligned,
  * b200_gemm_workspace_bytes() bytes, ZERO-FILLED when registered; pass NULL to unregister). With it,
  * b200_gemm_ex / b200_gemm_nt_bf16 cut the tiles of a last, at most half-filled wave along K so every

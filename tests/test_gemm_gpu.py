@@ -240,3 +240,39 @@ def test_gemm_swiglu_backward_epilogue(K, M, F, K_, r):
     dh16 = K.gemm_ex(dy, w, b1_mn=True, a2=u, b2=A) if r else K.gemm_ex(dy, w, b1_mn=True)
     da, db = K.swiglu_bwd(ab[:, :F], ab[:, F:], dh16)
     assert rel_err(got[:, :F].float(), da.float()) < 1e-2 and rel_err(got[:, F:].float(), db.float()) < 1e-2
+
+
+def _interleave_rows(w1, w2, blk=128):
+    F, Kd = w1.shape
+    return torch.stack([w1.view(F // blk, blk, Kd), w2.view(F // blk, blk, Kd)], dim=1).reshape(2 * F, Kd).contiguous()
+
+
+def _interleave_lora_b(b1, b2, blk=128):
+    r, F = b1.shape
+    out = torch.zeros(2 * r, F // blk, 2, blk, device=b1.device, dtype=b1.dtype)
+    out[:r, :, 0, :] = b1.view(r, F // blk, blk)
+    out[r:, :, 1, :] = b2.view(r, F // blk, blk)
+    return out.view(2 * r, 2 * F)
+
+
+@pytest.mark.parametrize("M,F,K_,r", [(8192, 8192, 2048, 64), (512, 384, 256, 8), (1000, 1024, 512, 0)])
+def test_gemm_swiglu_forward_epilogue(K, M, F, K_, r):
+    """(a | b) and h = silu(a) * b from one GEMM over row-interleaved fc1 / fc2 weights against the separate
+    path: two (LoRA) linears and the SwiGLU kernel (same bf16 roundings; the LoRA blocks are accumulated in one more
+    K block, so agreement is to rounding, not bit-exact)."""
+    x = rnd(M, K_, seed=1)
+    w1, w2 = rnd(F, K_, scale=0.05, seed=2), rnd(F, K_, scale=0.05, seed=3)
+    kw1 = kw2 = {}
+    t2 = bil = None
+    if r:
+        t1, t2_ = rnd(M, r, seed=4), rnd(M, r, seed=5)
+        b1, b2 = rnd(r, F, scale=0.1, seed=6), rnd(r, F, scale=0.1, seed=7)
+        kw1, kw2 = dict(a2=t1, b2=b1, b2_mn=True), dict(a2=t2_, b2=b2, b2_mn=True)
+        t2, bil = torch.cat([t1, t2_], dim=1), _interleave_lora_b(b1, b2)
+    ab, h = K.gemm_swiglu_fwd(x, _interleave_rows(w1, w2), t2, bil)
+    a_ref, b_ref = K.gemm_ex(x, w1, **kw1), K.gemm_ex(x, w2, **kw2)
+    h_ref = K.swiglu_fwd(a_ref, b_ref)
+    assert rel_err(ab[:, :F].float(), a_ref.float()) < 2e-3 and rel_err(ab[:, F:].float(), b_ref.float()) < 2e-3
+    assert rel_err(h.float(), h_ref.float()) < 1e-2
+    fa = x.float() @ w1.float().t() + (t1.float() @ b1.float() if r else 0)
+    assert rel_err(ab[:, :F].float(), fa) < BF16_TOL
