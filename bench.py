@@ -154,15 +154,15 @@ def kernel_rooflines(device, peaks):
 
 def gemm_traffic_from_profile():
     """DRAM bytes per launch of the dominant kernel (CTA-pair GEMM) from the committed ncu capture
-    (profiles/r1_gemm_traffic_2layer_step_v2.json: dram__bytes_read.sum + dram__bytes_write.sum summed over the
+    (profiles/r1_gemm_traffic_2layer_step_v3.json: dram__bytes_read.sum + dram__bytes_write.sum summed over the
     launches of a 2-block step); None if the file is absent."""
-    path = os.path.join(ROOT, "profiles", "r1_gemm_traffic_2layer_step_v2.json")
+    path = os.path.join(ROOT, "profiles", "r1_gemm_traffic_2layer_step_v3.json")
     try:
         d = json.load(open(path))
         for name, v in d.items():
             if "2cta" in name:
                 return {"dram_bytes_per_launch": v["dram_bytes"] / v["launches"], "launches": v["launches"],
-                        "tensor_active_pct": v.get("tensor_active_pct"), "source": "profiles/r1_gemm_traffic_2layer_step_v2.json"}
+                        "tensor_active_pct": v.get("tensor_active_pct"), "source": "profiles/r1_gemm_traffic_2layer_step_v3.json"}
     except Exception:
         pass
     return None
