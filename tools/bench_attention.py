@@ -1,5 +1,5 @@
 """Micro-benchmark of the attention kernels at the bench shape (not a bench value)."""
-import os, sys, math
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from building_llm_from_scratch_b200 import kernels as K

@@ -1,4 +1,4 @@
-import sys, json, torch
+import sys, torch
 import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 torch.cuda.set_device(0)
