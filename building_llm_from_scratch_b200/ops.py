@@ -15,6 +15,7 @@ from __future__ import annotations
 from typing import List, Optional, Sequence, Tuple
 
 import os
+import weakref
 
 import torch
 from torch import Tensor
@@ -368,19 +369,28 @@ def linears_of_same_input(x, modules):
 _wcat_cache: dict = {}
 
 
+def _derived_weight(cache: dict, weights, build):
+    """A tensor derived from FROZEN weights (their concatenation, an interleaving), built once and rebuilt when
+    any of them is written to (load_state_dict bumps the version counters). Entries are tied to the weight
+    OBJECTS through weak references — a freed weight's address may be handed to another tensor with the same
+    version count — and leave the cache when a weight dies, so dropped models do not pin their copies."""
+    key = tuple(id(w) for w in weights)
+    state = tuple((w.data_ptr(), w._version) for w in weights)
+    hit = cache.get(key)
+    if hit is not None and hit[0] == state and all(r() is w for r, w in zip(hit[2], weights)):
+        return hit[1]
+    with torch.no_grad():
+        out = build([w.detach() for w in weights])
+    refs = tuple(weakref.ref(w, lambda _r, k=key, c=cache: c.pop(k, None)) for w in weights)
+    cache[key] = (state, out, refs)
+    return out
+
+
 def _packed_weight(weights):
-    """cat(weights, dim=0) for FROZEN weights, built once and rebuilt when any of them is written to
-    (load_state_dict bumps the version counters); None when a weight is trainable."""
+    """cat(weights, dim=0) of frozen weights (cached); None when a weight is trainable."""
     if any(w.requires_grad for w in weights):
         return None
-    key = tuple(w.data_ptr() for w in weights)
-    ver = tuple(w._version for w in weights)
-    hit = _wcat_cache.get(key)
-    if hit is None or hit[0] != ver:
-        with torch.no_grad():
-            hit = (ver, torch.cat([w.detach() for w in weights], dim=0).contiguous())
-        _wcat_cache[key] = hit
-    return hit[1]
+    return _derived_weight(_wcat_cache, weights, lambda ws: torch.cat(ws, dim=0).contiguous())
 
 
 @torch.library.custom_op("b200llm::lora_linear_packed", mutates_args=())
@@ -505,16 +515,10 @@ def _interleaved_weight(weights, blk=128):
     F, Kd = weights[0].shape
     if F % blk:
         return None
-    key = tuple(w.data_ptr() for w in weights)
-    ver = tuple(w._version for w in weights)
-    hit = _wil_cache.get(key)
-    if hit is None or hit[0] != ver:
-        with torch.no_grad():
-            w1, w2 = (w.detach() for w in weights)
-            il = torch.stack([w1.view(F // blk, blk, Kd), w2.view(F // blk, blk, Kd)], dim=1).reshape(2 * F, Kd).contiguous()
-        hit = (ver, il)
-        _wil_cache[key] = hit
-    return hit[1]
+    return _derived_weight(
+        _wil_cache, weights,
+        lambda ws: torch.stack([ws[0].view(F // blk, blk, Kd), ws[1].view(F // blk, blk, Kd)], dim=1)
+        .reshape(2 * F, Kd).contiguous())
 
 
 def _interleaved_lora_b(B1, B2, blk=128):
