@@ -382,10 +382,24 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = _lib.launch_count()
         e0.record()
+        # D2H read of every step's loss, one step behind: the copy of step i's loss into pinned memory is enqueued
+        # right after step i, and the host reads it once step i + 1 has been enqueued, so the GPU is not left idle
+        # while the host waits (what a training loop that logs its loss does)
+        host_loss = [torch.zeros(1, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+        copied = [torch.cuda.Event(), torch.cuda.Event()]
+        losses = []
         for i in range(args.steps):
             loss = step.run(*batches[i % n_batches], n_valid=n_valid[i % n_batches])
             if read_loss:
-                last = float(loss)          # D2H read of the step's result, every step
+                host_loss[i & 1].copy_(loss.reshape(1), non_blocking=True)
+                copied[i & 1].record()
+                if i > 0:
+                    copied[(i - 1) & 1].synchronize()
+                    losses.append(float(host_loss[(i - 1) & 1]))
+        if read_loss:
+            copied[(args.steps - 1) & 1].synchronize()
+            losses.append(float(host_loss[(args.steps - 1) & 1]))
+            assert len(losses) == args.steps
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -479,7 +493,8 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(cfg, world),
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 2 * MICRO_BATCH * SEQ_LEN * 8 + 28,
-                        "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+                        "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
+                        "loss_read": "every step, async copy to pinned memory, read by the host one step behind"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "cuda_graph": step.graphs is not None, "final_loss": final_loss,
                 "ignored_target_fraction": ignored,
