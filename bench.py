@@ -204,36 +204,51 @@ class ClockSampler(threading.Thread):
 
 
 # --------------------------------------------------------------------------------------
-# CPU baseline: the oracle (port of the reference modules) on the host cores
+# CPU baseline / reference arm: the UNMODIFIED reference (baseline/_ref) through its own Trainer.train_batch
+# on the host cores. Only when that copy is missing (never on a box prepared by build()) does the oracle
+# port stand in, and the line then says kind = "port".
 # --------------------------------------------------------------------------------------
-def cpu_reference_sample(seq_len=1024):
-    """One bounded sample of the same workload on CPU: Llama-3.2-1B dims, LoRA r=64, bf16,
-    B=1 x T=seq_len, forward + CE + backward through the oracle with 1 and 3 blocks (second of two
-    runs each, the first warms the CPU kernels up); per-block and head+embedding costs are
-    separated and extrapolated to the 16-block model."""
-    from oracle import reference_ops as R
-    torch.manual_seed(123)
-    times = {}
-    for nl in (1, 3):
-        cfg = llama32_1b_cfg(seq_len, n_layers=nl)
+REF_MICRO_BATCH = 1       # bounded sample: one sequence of the workload per step (~4-7 s of CPU work per step)
+
+
+def reference_cpu_steps(warmup, steps):
+    """Time `steps` reference train_batch calls (after `warmup`) at micro-batch REF_MICRO_BATCH x SEQ_LEN, all 16
+    blocks, LoRA r=64, bf16, every row through the vocab head (the reference has no other way) -> dict."""
+    from building_llm_from_scratch_b200.datautils.synthetic import alpaca_batch
+    torch.set_num_threads(os.cpu_count() or 1)
+    cores = torch.get_num_threads()
+    gen = torch.Generator().manual_seed(1234)
+    from baseline import reference_arm as RA
+    if RA.available():
+        cfg = RA.llama32_1b_cfg(SEQ_LEN)
+        batches = [alpaca_batch(gen, REF_MICRO_BATCH, SEQ_LEN, cfg["vocab_size"]) for _ in range(4)]
+        tr = RA.build_llama_lora_trainer(cfg, LORA_RANK, LORA_ALPHA, device="cpu", lr=PEAK_LR, weight_decay=WEIGHT_DECAY)
+        secs = RA.time_steps(tr, batches, warmup, steps)
+        kind = "reference"
+        what = ("unmodified reference (baseline/_ref): Llama3Model + replace_linear_with_lora + Trainer.train_batch "
+                "(zero_grad, LR, forward, F.cross_entropy, backward, clip 1.0, AdamW)")
+    else:
+        from oracle import reference_ops as R
+        cfg = llama32_1b_cfg(SEQ_LEN)
+        batches = [alpaca_batch(gen, REF_MICRO_BATCH, SEQ_LEN, cfg["vocab_size"]) for _ in range(4)]
         sd = oracle_state(cfg, LORA_RANK)
-        x = torch.randint(0, cfg["vocab_size"], (1, seq_len))
-        y = torch.roll(x, -1, 1)
-        y[:, : seq_len // 2] = -100
-        for rep in range(2):
+        secs = []
+        for i in range(warmup + steps):
+            x, y = batches[i % len(batches)]
             t0 = time.perf_counter()
-            logits = R.llama3_forward(x, sd, cfg, LORA_ALPHA / LORA_RANK)
-            loss = R.cross_entropy(logits, y)
+            loss = R.cross_entropy(R.llama3_forward(x, sd, cfg, LORA_ALPHA / LORA_RANK), y)
             loss.backward()
-            times[nl] = time.perf_counter() - t0
-            del logits, loss
-        del sd
-    per_block = max((times[3] - times[1]) / 2, 0.02 * times[1])
-    rest = max(times[1] - per_block, 0.0)
-    full = rest + 16 * per_block
-    return dict(tokens_per_s=seq_len / full, seconds=sum(times.values()),
-                sample=f"oracle Llama-3.2-1B dims LoRA r={LORA_RANK} bf16 CPU, B=1xT={seq_len}, fwd+CE+bwd with 1 and 3 "
-                       f"blocks ({times[1]:.2f}s, {times[3]:.2f}s), extrapolated to 16 blocks + head")
+            if i >= warmup:
+                secs.append(time.perf_counter() - t0)
+            del loss
+        kind = "port"
+        what = "oracle port of the reference modules (baseline/_ref absent): forward + cross-entropy + backward, no optimizer step"
+    mean = sum(secs) / len(secs)
+    tokens = REF_MICRO_BATCH * SEQ_LEN
+    return dict(value=tokens / mean, ms_per_step=1e3 * mean, kind=kind, cores=cores, secs=secs,
+                sample=f"{what}; Llama-3.2-1B, all 16 blocks, LoRA r={LORA_RANK}, bf16, micro-batch {REF_MICRO_BATCH} x seq "
+                       f"{SEQ_LEN} Alpaca-shaped, {len(secs)} timed steps after {warmup} warm-up on {cores} host threads, "
+                       f"{mean:.2f} s/step (min {min(secs):.2f}, max {max(secs):.2f})")
 
 
 def oracle_state(cfg, rank):
@@ -264,25 +279,24 @@ def oracle_state(cfg, rank):
 
 
 def run_reference_arm(args):
+    """`--impl reference`: rank 0 alone times the reference on the host cores; the other ranks exit."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    torch.set_num_threads(os.cpu_count() or 1)
-    vals = []
-    sample = None
-    for i in range(args.warmup + args.steps):
-        r = cpu_reference_sample(seq_len=256 if i < args.warmup else 1024)
-        if i >= args.warmup:
-            vals.append(r["tokens_per_s"])
-            sample = r["sample"]
-    v = sum(vals) / len(vals)
+    r = reference_cpu_steps(max(args.warmup, 1), args.steps)
     cfg = llama32_1b_cfg()
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * MICRO_BATCH * SEQ_LEN / v, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(cfg, 1),
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
-            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    config = workload_config(cfg, 1)
+    config["workload"] += (f" -- reference arm: a bounded sample of that workload, micro-batch {REF_MICRO_BATCH} x seq {SEQ_LEN} "
+                           "per step on the host CPU")
+    config["global_batch"] = REF_MICRO_BATCH
+    config["parallelism"] = "cpu"
+    config["l2_policy"] = "n/a (host CPU)"
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": max(args.warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "step_seconds": [round(t, 3) for t in r["secs"]]}
     print(json.dumps(line), flush=True)
 
 
@@ -483,10 +497,8 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        torch.set_num_threads(os.cpu_count() or 1)
-        r = cpu_reference_sample(seq_len=2048)
-        cpu = {"value": r["tokens_per_s"], "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-               "sample": r["sample"]}
+        r = reference_cpu_steps(1, 2)       # ~20-30 s of CPU work: 1 warm-up + 2 timed reference steps
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
