@@ -166,4 +166,4 @@ class GPTModel(nn.Module):
 
     def forward_loss(self, x, targets, capacity=0):
         w, A, B, s = head_operands(self.output_head)
-        return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets, capacity)[0]
+        return ops.linear_cross_entropy(self.hidden_states(x), w, A, B, s, targets, capacity, torch.is_grad_enabled())[0]

@@ -135,4 +135,4 @@ class Llama2Model(nn.Module):
 
     def forward_loss(self, in_idx, targets, capacity=0):
         w, A, B, s = head_operands(self.out_head)
-        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity)[0]
+        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity, torch.is_grad_enabled())[0]

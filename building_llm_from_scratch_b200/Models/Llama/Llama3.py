@@ -172,4 +172,4 @@ class Llama3Model(nn.Module):
         """Fused vocab projection + cross-entropy (train.py:90-91) without a logits tensor
         handed back to Python; used by Trainer.calc_loss_batch in training mode."""
         w, A, B, s = head_operands(self.out_head)
-        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity)[0]
+        return ops.linear_cross_entropy(self.hidden_states(in_idx), w, A, B, s, targets, capacity, torch.is_grad_enabled())[0]

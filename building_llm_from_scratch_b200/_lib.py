@@ -48,6 +48,7 @@ SIGNATURES = {
     "b200_gemm_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_workspace_bytes": (SZ, []),
     "b200_gemm_set_workspace": (I, [P, SZ]),
+    "b200_gemm_set_stream_workspace": (I, [P, P, SZ]),
     "b200_gemm_grouped_bf16": (I, [I, C.POINTER(GemmProblem), P]),
     "b200_gemm_grouped_workspace_bytes": (SZ, [I, C.POINTER(GemmProblem)]),
     "b200_gemm_grouped_streamk_bf16": (I, [I, C.POINTER(GemmProblem), P, SZ, P]),
@@ -82,16 +83,17 @@ SIGNATURES = {
     "b200_transpose_bf16": (I, [P, I64, P, I64, I64, I64, F, P]),
     "b200_add_bf16": (I, [P, P, P, I64, P]),
     "b200_colsum_bf16": (I, [P, I64, P, I64, I64, P]),
-    "b200_attention_fwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, I64, I64, F, F, C.c_uint64, P]),
+    "b200_attention_fwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, I64, I64, F, F, C.c_uint64, P, P]),
     "b200_attention_dropout_mask_u8": (I, [P, I64, I64, I64, F, C.c_uint64, P]),
-    "b200_dropout_bf16": (I, [P, P, P, I64, F, C.c_uint64, P]),
+    "b200_dropout_bf16": (I, [P, P, P, I64, F, C.c_uint64, P, P]),
+    "b200_scale_bf16_dev": (I, [P, I64, P, P]),
     "b200_dropout_mask_u8": (I, [P, I64, F, C.c_uint64, P]),
     "b200_collate_i64": (I, [P, P, P, I64, I64, I64, I64, I64, P, P, P]),
     "b200_window_batch_i64": (I, [P, I64, P, I64, I64, P, P, P]),
     "b200_attention_decode_bf16": (I, [P, I64, P, P, I64, I64, P, I64, I64, I64, I64, I64, I64, F, P]),
     "b200_attention_bwd_workspace_bytes": (SZ, [I64, I64, I64, I64]),
     "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,
-                                    I64, I64, I64, I64, I64, I64, F, F, C.c_uint64, P]),
+                                    I64, I64, I64, I64, I64, I64, F, F, C.c_uint64, P, P]),
 }
 
 

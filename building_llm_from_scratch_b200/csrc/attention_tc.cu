@@ -49,7 +49,11 @@ struct DropParams {
   uint32_t thr16;
   float inv_keep;
   unsigned long long seed;
+  const unsigned long long* seed_dev;   // optional per-step offset in device memory, added to seed (graph replay)
 };
+__device__ __forceinline__ unsigned long long drop_seed(const DropParams& d) {
+  return d.seed + (d.seed_dev != nullptr ? *d.seed_dev : 0ull);
+}
 
 struct FwdParams {
   int B, T, H, HKV, nqt;
@@ -61,7 +65,8 @@ struct FwdParams {
 };
 
 template <int HDIM, bool DROP>
-__global__ void __launch_bounds__(224, FwdCfg<HDIM>::CTAS)
+// (the dropout variant needs ~30 more registers: two CTAs per SM instead of three rather than 1.3 KB of spills)
+__global__ void __launch_bounds__(224, DROP ? 2 : FwdCfg<HDIM>::CTAS)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -176,6 +181,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int row = quad * 32 + lane;
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     float m = -INFINITY, l = 0.f;
+    const unsigned long long dseed = DROP ? drop_seed(p.drop) : 0ull;
     const unsigned long long drop_row =
         (((unsigned long long)b * p.H + head) * p.T + (unsigned long long)(q0 + row)) * (unsigned long long)((p.T + 1) >> 1);
     for (int j = 0; j < n_kv; ++j) {
@@ -215,7 +221,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         sum2 = fadd2(sum2, pack_f2(p0, p1));          // the softmax denominator is taken before dropout
         if (DROP) {
           bool k0, k1;
-          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, k0, k1);
+          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), dseed, p.drop.thr16, k0, k1);
           p0 = k0 ? p0 * p.drop.inv_keep : 0.f;
           p1 = k1 ? p1 * p.drop.inv_keep : 0.f;
         }
@@ -286,8 +292,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
 }  // namespace
 
-static DropParams make_drop(float p, uint64_t seed) {
+static DropParams make_drop(float p, uint64_t seed, const uint64_t* seed_dev = nullptr) {
   DropParams d;
+  d.seed_dev = (const unsigned long long*)seed_dev;
   const float t = p * 65536.f + 0.5f;
   d.thr16 = p <= 0.f ? 0u : (t > 65535.f ? 65535u : (uint32_t)t);
   d.inv_keep = 1.f / (1.f - p);
@@ -299,7 +306,7 @@ namespace {
 template <int HD>
 int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                      void* o, int64_t ldo, float* lse, int64_t B, int64_t T, int64_t h, int64_t hkv,
-                     float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
+                     float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev, cudaStream_t st) {
   constexpr int SMEM = FwdCfg<HD>::SMEM;
   CUtensorMap mq, mk, mv;
   int rc;
@@ -318,7 +325,7 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
   p.nqt = (int)((T + BQ - 1) / BQ);
   p.scale_log2 = scale * LOG2E;
-  p.drop = make_drop(dropout_p, seed);
+  p.drop = make_drop(dropout_p, seed, seed_dev);
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
@@ -334,9 +341,9 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
 int b200_attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                           int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
                           int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed,
-                          cudaStream_t st) {
-  if (hd == 64) return attention_fwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
-  return attention_fwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, st);
+                          const uint64_t* seed_dev, cudaStream_t st) {
+  if (hd == 64) return attention_fwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
+  return attention_fwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, lse, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
 }
 
 // =====================================================================================
@@ -528,6 +535,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int key = kv0 + row;
     const int buf = grp;
+    const unsigned long long dseed = DROP ? drop_seed(p.drop) : 0ull;
     for (int s = grp; s < steps; s += NG) {
       const int stg = s % NSTG, use = s / NG;
       const int hq = s / spp;
@@ -579,7 +587,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                 const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c + e);
                 const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
                                                  ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
-                                             p.drop.seed, p.drop.thr16);
+                                             dseed, p.drop.thr16);
                 dpv[e] = kp ? dpv[e] * p.drop.inv_keep : 0.f;
                 pdrop[e] = kp ? pr[e] * p.drop.inv_keep : 0.f;
               }
@@ -791,6 +799,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const unsigned long long nd2 = pack_f2(ndl, ndl), scl2 = pack_f2(p.scale, p.scale);
     const unsigned long long drop_row =
         (((unsigned long long)b * p.H + head) * p.T + (unsigned long long)t) * (unsigned long long)((p.T + 1) >> 1);
+    const unsigned long long dseed = DROP ? drop_seed(p.drop) : 0ull;
     for (int j = 0; j < n_kv; ++j) {
       const int buf = j & 1;
       mbar_wait(s_full, j & 1);
@@ -811,7 +820,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       for (int i = 0; i < 32; ++i) {
         bool keep[2] = {true, true};
         if (DROP)
-          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), p.drop.seed, p.drop.thr16, keep[0], keep[1]);
+          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), dseed, p.drop.thr16, keep[0], keep[1]);
         // packed pairs: P = exp2(s c - lse), dS = P (dP - delta) scale
         float a0, a1;
         unpack_f2(ffma2(pack_f2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nl2), a0, a1);
@@ -920,7 +929,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
                      const void* o, int64_t ldo, const void* dout, int64_t lddo, const float* lse,
                      void* workspace, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
                      int64_t lddv, int64_t B, int64_t T, int64_t h, int64_t hkv, float scale,
-                     float dropout_p, uint64_t seed, cudaStream_t st) {
+                     float dropout_p, uint64_t seed, const uint64_t* seed_dev, cudaStream_t st) {
   constexpr int DKV_SMEM = DkvCfg<HD>::SMEM, DKV_THREADS = DkvCfg<HD>::THREADS, DQ_SMEM = DqCfg<HD>::SMEM;
   float* ld2 = (float*)workspace;   // cudaMalloc / caching-allocator memory: at least 256-B aligned
   B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
@@ -958,7 +967,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     DqParams p;
     p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv; p.nqt = nqt;
     p.scale = scale; p.scale_log2 = scale * LOG2E;
-    p.drop = make_drop(dropout_p, seed);
+    p.drop = make_drop(dropout_p, seed, seed_dev);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
     const long long grid = (long long)nqt * B * h;
     if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
@@ -973,7 +982,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
     p.nkt = nqt; p.nq64 = nq64;
     p.scale = scale; p.scale_log2 = scale * LOG2E;
-    p.drop = make_drop(dropout_p, seed);
+    p.drop = make_drop(dropout_p, seed, seed_dev);
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     const long long grid = (long long)p.nkt * B * hkv;
@@ -990,12 +999,12 @@ int b200_attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk
                           int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
                           const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                           int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, cudaStream_t st) {
+                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev, cudaStream_t st) {
   if (hd == 64)
     return attention_bwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
-                                lddv, B, T, h, hkv, scale, dropout_p, seed, st);
+                                lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
   return attention_bwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
-                               lddv, B, T, h, hkv, scale, dropout_p, seed, st);
+                               lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
 }
 
 

@@ -396,7 +396,8 @@ scatter_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ idx, b
 // same call on the upstream gradient is the backward. 6 B/elt (+2 with the residual).
 __global__ void __launch_bounds__(256)
 dropout_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res, bf16* __restrict__ y, long long n,
-               uint32_t thr16, float inv_keep, unsigned long long seed) {
+               uint32_t thr16, float inv_keep, unsigned long long seed, const unsigned long long* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev;   // per-step offset in device memory: a replayed graph draws new masks
   const long long nv = n >> 3;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
        i += (long long)gridDim.x * blockDim.x) {
@@ -431,7 +432,34 @@ dropout_mask_kernel(unsigned char* __restrict__ out, long long n, uint32_t thr16
     out[i] = dropout_keep((unsigned long long)i, seed, thr16) ? 1 : 0;
 }
 
+// x *= *scale, skipped entirely when the device scalar is exactly 1 (the gradient of a loss that .backward() was
+// called on directly): lets the fused vocab-projection backward honour a scaled loss without a host read.
+__global__ void __launch_bounds__(256)
+scale_dev_kernel(bf16* __restrict__ x, long long n, const float* __restrict__ scale) {
+  const float s = *scale;
+  if (s == 1.f) return;
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld_v4(x + i * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= s;
+    st_v4(x + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 8; k < n; ++k) x[k] = __float2bfloat16_rn(__bfloat162float(x[k]) * s);
+}
+
 }  // namespace
+
+extern "C" int b200_scale_bf16_dev(void* x, int64_t n, const float* scale_dev, void* stream) {
+  B200_CHECK_ARG(x && scale_dev && n > 0, "scale_dev: null pointer or empty");
+  B200_CHECK_ARG(b200_aligned16(x), "scale_dev: buffer must be 16-B aligned");
+  scale_dev_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>((bf16*)x, n, scale_dev);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
 
 static inline uint32_t drop_thr16(float p) {
   const float t = p * 65536.f + 0.5f;
@@ -439,12 +467,13 @@ static inline uint32_t drop_thr16(float p) {
 }
 
 extern "C" int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, uint64_t seed,
-                                 void* stream) {
+                                 const uint64_t* seed_dev, void* stream) {
   B200_CHECK_ARG(x && y && n > 0, "dropout: null pointer or empty");
   B200_CHECK_ARG(p >= 0.f && p < 1.f, "dropout: p=%f must be in [0, 1)", (double)p);
   B200_CHECK_ARG(b200_aligned16(x) && b200_aligned16(y) && (res == nullptr || b200_aligned16(res)), "dropout: pointers must be 16-B aligned");
   dropout_kernel<<<ew_grid(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, (const bf16*)res, (bf16*)y, n, drop_thr16(p), 1.f / (1.f - p), (unsigned long long)seed);
+      (const bf16*)x, (const bf16*)res, (bf16*)y, n, drop_thr16(p), 1.f / (1.f - p), (unsigned long long)seed,
+      (const unsigned long long*)seed_dev);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;

@@ -16,6 +16,7 @@
 //
 // Roofline: tensor pipe. Algorithmic FLOPs per launch = 2·M·N·(K1+K2).
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -1242,7 +1243,30 @@ struct TailWs {
   void* ptr;
   size_t bytes;
 };
+// Tail-split scratch: one default per device (b200_gemm_set_workspace) and any number of per-stream ones
+// (b200_gemm_set_stream_workspace) for hosts that run GEMMs concurrently on several streams of a device —
+// two launches sharing a scratch would mix their partial tiles.
 TailWs g_tail_ws[64] = {};
+struct StreamWs {
+  int dev;
+  void* stream;
+  TailWs ws;
+};
+std::vector<StreamWs> g_stream_ws;
+std::mutex g_ws_mu;
+
+TailWs tail_workspace_for(int dev, void* stream) {
+  std::lock_guard<std::mutex> lk(g_ws_mu);
+  for (const StreamWs& e : g_stream_ws)
+    if (e.dev == dev && e.stream == stream) return e.ws;
+  return (dev >= 0 && dev < 64) ? g_tail_ws[dev] : TailWs{nullptr, 0};
+}
+
+// environment switches (A/B measurements) are read once per process
+int env_flag(const char* name) {   // first character of the variable, 0 when unset
+  const char* e = getenv(name);
+  return e ? (int)(unsigned char)e[0] : 0;
+}
 
 bool use_pair_kernel() {
   static int v = -1;
@@ -1304,9 +1328,9 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.n_fastest = 0;
   if (pair) {
     const double a_bytes = 2.0 * (double)M * (double)(K1 + K2), b_bytes = 2.0 * (double)N * (double)(K1 + K2);
-    const char* e = getenv("B200_GEMM_ORDER");
-    if (e && e[0] == 'n') p.n_fastest = 1;
-    else if (e && e[0] == 'm') p.n_fastest = 0;
+    static const int order = env_flag("B200_GEMM_ORDER");
+    if (order == 'n') p.n_fastest = 1;
+    else if (order == 'm') p.n_fastest = 0;
     else p.n_fastest = (a_bytes > 64e6 && b_bytes < 64e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
   }
   p.alpha = alpha;
@@ -1349,13 +1373,13 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     // 3.46 waves -> 3.5 instead of 4 tile times). Needs the workspace of b200_gemm_set_workspace().
     int dev = 0;
     cudaGetDevice(&dev);
-    const TailWs tw = (dev >= 0 && dev < 64) ? g_tail_ws[dev] : TailWs{nullptr, 0};
+    const TailWs tw = tail_workspace_for(dev, stream);
     const int G = sms / 2;
     const int L = tiles % G;
-    const char* e = getenv("B200_GEMM_TAIL");
+    static const int tail_env = env_flag("B200_GEMM_TAIL");
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !(e && e[0] == '0')) {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && tail_env != '0') {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1612,7 +1636,7 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
     // Stream-K pays ~16 K blocks' worth of time for the shared-tile fix-up (RED, fence, counter, reload).
     // Replay the tile scheduler's round-robin on the host: if its busiest CTA is not clearly worse
     // than an even cut, the tiles go out whole (t = x A with K = 2048 on 64 tiles: 19 vs 23 us).
-    const char* e = getenv("B200_GEMM_STREAMK_FORCE");
+    static const int sk_env = env_flag("B200_GEMM_STREAMK_FORCE");
     long long tiles_total = 0;
     for (int i = 0; i < nprob; ++i) tiles_total += (probs[i].M + BM - 1) / BM;
     long long items = 0;
@@ -1630,7 +1654,7 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
     long long busiest = 0;
     for (long long l : load) busiest = l > busiest ? l : busiest;
     const double even = (double)units / sms;
-    const bool streamk = (e && e[0] == '1') || (!(e && e[0] == '0') && (double)busiest > 1.3 * even + 16.0);
+    const bool streamk = sk_env == '1' || (sk_env != '0' && (double)busiest > 1.3 * even + 16.0);
     if (!streamk) return b200_gemm_grouped_bf16(nprob, probs, stream);
   }
   // at least 4 K blocks per CTA: below that the fixed cost of a CTA outweighs its share of the stream
@@ -1653,7 +1677,24 @@ extern "C" int b200_gemm_set_workspace(void* workspace, size_t bytes) {
   B200_CHECK_ARG(dev >= 0 && dev < 64, "gemm_set_workspace: device index %d out of range", dev);
   B200_CHECK_ARG(workspace == nullptr || (((uintptr_t)workspace & 255) == 0 && bytes >= 4096),
                  "gemm_set_workspace: workspace must be 256-B aligned and at least 4096 bytes");
+  std::lock_guard<std::mutex> lk(g_ws_mu);
   g_tail_ws[dev] = TailWs{workspace, workspace ? bytes : 0};
+  return 0;
+}
+
+extern "C" int b200_gemm_set_stream_workspace(void* stream, void* workspace, size_t bytes) {
+  int dev = 0;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(workspace == nullptr || (((uintptr_t)workspace & 255) == 0 && bytes >= 4096),
+                 "gemm_set_stream_workspace: workspace must be 256-B aligned and at least 4096 bytes");
+  std::lock_guard<std::mutex> lk(g_ws_mu);
+  for (size_t i = 0; i < g_stream_ws.size(); ++i)
+    if (g_stream_ws[i].dev == dev && g_stream_ws[i].stream == stream) {
+      if (workspace) g_stream_ws[i].ws = TailWs{workspace, bytes};
+      else g_stream_ws.erase(g_stream_ws.begin() + (long)i);
+      return 0;
+    }
+  if (workspace) g_stream_ws.push_back(StreamWs{dev, stream, TailWs{workspace, bytes}});
   return 0;
 }
 

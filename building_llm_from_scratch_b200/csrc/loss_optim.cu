@@ -69,7 +69,8 @@ ce_row_kernel(bf16* __restrict__ logits, long long ld, const long long* __restri
     const float gs = block_sum(s, red);
     const float lse = gm + logf(gs);
     if (threadIdx.x == 0) {
-      const float lt = (tgt >= 0 && tgt < V) ? __bfloat162float(lrow[tgt]) : 0.f;
+      // a target outside [0, V) is refused: NaN poisons the mean loss (F.cross_entropy asserts on the device)
+      const float lt = (tgt >= 0 && tgt < V) ? __bfloat162float(lrow[tgt]) : __int_as_float(0x7fc00000);
       ws[2 + row] = lse - lt;
     }
     if (write_grad) {

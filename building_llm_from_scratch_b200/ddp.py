@@ -51,8 +51,7 @@ class B200DDP(nn.Module):
     def attach(self, optimizer):
         """Build the buckets over optimizer's flat gradient buffers (optim.B200AdamW layout: `_groups`
         of dict(params, offsets, g)) and subscribe to gradient-ready notifications."""
-        for h in getattr(self, "_hooks", []):
-            h.remove()
+        self.detach()
         self._opt = optimizer
         self._buckets = []
         self._bucket_of = {}
@@ -75,12 +74,27 @@ class B200DDP(nn.Module):
                     hi, members = lo, []
         self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook)
                        for grp in optimizer._groups.values() for p in grp["params"]]
+        self._subscribed = [p for grp in optimizer._groups.values() for p in grp["params"]]
         try:
             from . import ops
-            ops.set_grad_ready_callback(self._on_ready)
+            ops.register_grad_ready(self._subscribed, self._on_ready)
         except Exception:        # CPU-only unit tests drive _on_ready themselves
             pass
         return self
+
+    def detach(self):
+        """Undo attach(): remove the autograd hooks and the gradient-ready subscriptions of this wrapper."""
+        for h in getattr(self, "_hooks", []):
+            h.remove()
+        self._hooks = []
+        subs = getattr(self, "_subscribed", [])
+        if subs:
+            try:
+                from . import ops
+                ops.unregister_grad_ready(subs)
+            except Exception:
+                pass
+        self._subscribed = []
 
     def _autograd_hook(self, p):
         if not getattr(self, "_active", False) or p.grad is None:

@@ -12,6 +12,7 @@ import os
 
 import torch
 
+from . import ops
 from .ddp import B200DDP
 from .optim import B200AdamW
 from .train import Trainer
@@ -53,6 +54,9 @@ class TrainStep:
 
     # -- the two halves of a step (split where the data-parallel exchange goes) -------------
     def _fwd_bwd(self, overlap: bool = False):
+        # dropout masks are functions of (site seed, device step counter): bumping the counter inside the captured
+        # step gives every replay its own masks (GPT-2's drop_rate 0.1 at 2L+1 sites + the attention weights)
+        ops.advance_dropout_step(self.x.device)
         self.opt.zero_grad()
         if overlap:
             self.ddp.begin_backward()
@@ -112,11 +116,17 @@ class TrainStep:
             g["m"].copy_(m0)
             g["v"].copy_(v0)
         self.opt._step = saved_step
+        self._saved_step = saved_step
         if not self.use_graph:
             return
         self.graphs = self._capture_graphs()
 
     def _capture_graphs(self):
+        graphs = self._capture_graphs_impl()
+        self.opt._step = self.tr.global_step + 1   # capturing ran B200AdamW.step() in Python once: undo its count
+        return graphs
+
+    def _capture_graphs_impl(self):
         kw = {} if self.pool is None else dict(pool=self.pool)
         if self.ddp is None:
             g = torch.cuda.CUDAGraph()
@@ -185,6 +195,8 @@ class TrainStep:
         graphs = self._graphs_for(n_valid)
         tr.global_step += 1
         lr = self._refresh_hyper()
+        self.opt._step = tr.global_step + 1      # replayed steps do not pass through B200AdamW.step(): keep its
+                                                 # counter (saved in checkpoints, used by eager steps) in line
         tr.track_lrs.append(lr)
         self.x.copy_(x_src, non_blocking=True)
         self.y.copy_(y_src, non_blocking=True)

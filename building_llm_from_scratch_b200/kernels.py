@@ -552,14 +552,24 @@ def colsum(x2d, like=None):
     return out
 
 
-def dropout(x, p, seed, residual=None):
-    """(residual +) keep * x / (1 - p) with the counter-based mask of (seed, element index)."""
-    _need_cuda(x, residual)
+def dropout(x, p, seed, residual=None, seed_dev=None):
+    """(residual +) keep * x / (1 - p) with the counter-based mask of (seed + seed_dev[0], element index);
+    seed_dev: optional int64 device tensor read by the kernel when it runs (per-step offset under graph replay)."""
+    _need_cuda(x, residual, seed_dev)
     xc = x.contiguous()
     y = torch.empty_like(xc)
     rc = None if residual is None else residual.contiguous()
-    _lib.check(_lib.load().b200_dropout_bf16(_p(xc), _p(rc), _p(y), xc.numel(), float(p), int(seed), _stream()), "dropout")
+    _lib.check(_lib.load().b200_dropout_bf16(_p(xc), _p(rc), _p(y), xc.numel(), float(p), int(seed), _p(seed_dev),
+                                             _stream()), "dropout")
     return y
+
+
+def scale_dev_(x, scale):
+    """x *= scale[0] in place (scale: fp32 device scalar; the kernel returns at once when it is exactly 1)."""
+    _need_cuda(x, scale)
+    assert x.is_contiguous() and scale.dtype == torch.float32 and x.dtype == BF16
+    _lib.check(_lib.load().b200_scale_bf16_dev(_p(x), x.numel(), _p(scale), _stream()), "scale_dev")
+    return x
 
 
 def dropout_mask(n, p, seed, device="cuda"):
@@ -575,7 +585,7 @@ def attention_dropout_mask(B, H, T, p, seed, device="cuda"):
     return out
 
 
-def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None, dropout_p=0.0, seed=0):
+def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None, dropout_p=0.0, seed=0, seed_dev=None):
     """q/k/v: 2-D row-major views [B*T, *] whose first h*hd (hkv*hd) columns are the heads."""
     _need_cuda(q, k, v)
     q, ldq = _rowmajor2d(q)
@@ -584,12 +594,13 @@ def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None, dropout_p=0.0, seed=0):
     o = torch.empty((B * T, h * hd), device=q.device, dtype=BF16) if out is None else out
     lse = torch.empty((B, h, T), device=q.device, dtype=torch.float32)
     _lib.check(_lib.load().b200_attention_fwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), o.stride(0), _p(lse), B, T,
-                                                   h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p), int(seed), _stream()),
-               "attention_fwd")
+                                                   h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p), int(seed), _p(seed_dev),
+                                                   _stream()), "attention_fwd")
     return o, lse
 
 
-def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None, dropout_p=0.0, seed=0):
+def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None, dropout_p=0.0, seed=0,
+                  seed_dev=None):
     _need_cuda(q, k, v, o, do, lse)
     q, ldq = _rowmajor2d(q)
     k, ldk = _rowmajor2d(k)
@@ -606,7 +617,7 @@ def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=No
     _lib.check(lib.b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
                                            _p(ws), nbytes, _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
                                            dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p),
-                                           int(seed), _stream()), "attention_bwd")
+                                           int(seed), _p(seed_dev), _stream()), "attention_bwd")
     return dq, dk, dv
 
 

@@ -184,24 +184,42 @@ _wgrad_queue: list = []
 WGRAD_FLUSH_AT = 16
 
 
-# ddp.B200DDP subscribes here: called with the parameters whose weight-gradient GEMMs have just been
-# launched into main_grad (their gradient is final for this backward once those kernels ran)
-_grad_ready_cb = None
+# ddp.B200DDP wrappers subscribe here PER PARAMETER (several models / wrappers may live in one process): the
+# subscriber of a parameter is called with the parameters whose weight-gradient GEMMs have just been launched
+# into main_grad (their gradient is final for this backward once those kernels ran).
+_grad_ready_cbs: dict = {}      # id(parameter) -> callback
 
 
-def set_grad_ready_callback(cb):
-    global _grad_ready_cb
-    _grad_ready_cb = cb
+def register_grad_ready(params, cb) -> None:
+    for p in params:
+        _grad_ready_cbs[id(p)] = cb
+
+
+def unregister_grad_ready(params) -> None:
+    for p in params:
+        _grad_ready_cbs.pop(id(p), None)
+
+
+def _notify_ready(params) -> None:
+    if not _grad_ready_cbs:
+        return
+    by_cb: dict = {}
+    for p in params:
+        cb = _grad_ready_cbs.get(id(p))
+        if cb is not None:
+            by_cb.setdefault(id(cb), (cb, []))[1].append(p)
+    for cb, ps in by_cb.values():
+        cb(ps)
 
 
 def flush_weight_grads():
-    """Issue every queued weight-gradient GEMM (called before the optimizer / all-reduce read main_grad)."""
+    """Issue every queued weight-gradient GEMM (called before the optimizer / all-reduce read main_grad). The queue
+    is shared by everything in the process that runs on the current stream: flushing it early is always correct."""
     global _wgrad_queue
     if _wgrad_queue:
         q, _wgrad_queue = _wgrad_queue, []
         K.gemm_grouped(q)
-        if _grad_ready_cb is not None:
-            _grad_ready_cb([e["param"] for e in q])
+        _notify_ready([e["param"] for e in q])
 
 
 def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: bool = False):
@@ -220,8 +238,8 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
             K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg)
         else:
             K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=mg, accumulate=True, trans_out=trans_out)
-        if _grad_ready_cb is not None and b_mn_src.shape[1] > 64:
-            _grad_ready_cb([param])
+        if b_mn_src.shape[1] > 64:
+            _notify_ready([param])
         return None
     g32 = torch.zeros(param.shape, device=param.device, dtype=torch.float32)
     K.gemm_ex(a_mn_src, b_mn_src, a1_mn=True, b1_mn=True, out=g32, accumulate=True, trans_out=trans_out)
@@ -633,9 +651,9 @@ def attention(q: Tensor, k: Tensor, v: Tensor, cos: Optional[Tensor], sin: Optio
     if cos is not None:
         qr = K.rope(q, cos, sin, B, T, h, hd)
         kr = K.rope(k, cos, sin, B, T, hkv, hd)
-        o, lse = K.attention_fwd(qr, kr, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed)
+        o, lse = K.attention_fwd(qr, kr, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed, seed_dev=_drop_step(q, dropout_p))
         return o, lse, qr, kr
-    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd, dropout_p=dropout_p, seed=seed, seed_dev=_drop_step(q, dropout_p))
     return o, lse, q.new_empty((0,)), q.new_empty((0,))   # no rotated copies to hand back
 
 
@@ -665,7 +683,7 @@ def _attention_bwd(ctx, do, _dl, _dq, _dk):
     B, T, h, hkv, hd = ctx.dims
     v2 = v if v.stride(-1) == 1 else v.contiguous()
     dq, dk, dv = K.attention_bwd(qr, kr, v2, o, _flat2d(do), lse, B, T, h, hkv, hd, dropout_p=ctx.drop[0],
-                                 seed=ctx.drop[1])
+                                 seed=ctx.drop[1], seed_dev=_drop_step(qr, ctx.drop[0]))
     if cos is not None:
         K.rope_(dq, cos, sin, B, T, h, hd, inverse=True)
         K.rope_(dk, cos, sin, B, T, hkv, hd, inverse=True)
@@ -687,7 +705,7 @@ def attention_qkv(qkv: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: 
     else:
         qk = qkv
     o, lse = K.attention_fwd(qk[:, :nq], qk[:, nq:nq + nk], qkv[:, nq + nk:], B, T, h, hkv, hd,
-                             dropout_p=dropout_p, seed=seed)
+                             dropout_p=dropout_p, seed=seed, seed_dev=_drop_step(qkv, dropout_p))
     return o, lse, (qk if cos is not None else qkv.new_empty((0,)))
 
 
@@ -717,7 +735,7 @@ def _attention_qkv_bwd(ctx, do, _dl, _dqk):
     dqkv = qkv2.new_empty(qkv2.shape)
     K.attention_bwd(src[:, :nq], src[:, nq:nq + nk], qkv2[:, nq + nk:], o, _flat2d(do), lse, B, T, h, hkv, hd,
                     dq=dqkv[:, :nq], dk=dqkv[:, nq:nq + nk], dv=dqkv[:, nq + nk:], dropout_p=ctx.drop[0],
-                    seed=ctx.drop[1])
+                    seed=ctx.drop[1], seed_dev=_drop_step(qkv2, ctx.drop[0]))
     if cos is not None:
         K.rope_(dqkv, cos, sin, B, T, h + hkv, hd, inverse=True)      # q and k heads in one launch
     return (dqkv.view(qkv.shape),) + (None,) * 9
@@ -729,10 +747,38 @@ attention_qkv.register_autograd(_attention_qkv_bwd, setup_context=_attention_qkv
 # ======================================================================================
 # dropout (nn.Dropout sites of Models/GPT2/GPT2.py:24,81,102)
 # ======================================================================================
+# Every dropout mask is a function of (site seed + per-device step counter, element index). The site seed is a
+# host integer drawn when the op is called (new_seed()); under CUDA-graph replay it is frozen into the captured
+# kernel arguments, so the kernels also add a counter they read from DEVICE memory when they run.
+# engine.TrainStep bumps it inside the captured step (advance_dropout_step), which makes every replay draw
+# fresh masks; forward, backward and an activation-checkpoint recompute of one step all see the same value.
+_drop_steps: dict = {}
+
+
+def dropout_step_tensor(device) -> Tensor:
+    """The int64 device scalar added to every dropout seed on `device`."""
+    device = torch.device(device)
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    t = _drop_steps.get(idx)
+    if t is None:
+        t = torch.zeros(1, dtype=torch.int64, device=torch.device("cuda", idx))
+        _drop_steps[idx] = t
+    return t
+
+
+def advance_dropout_step(device) -> None:
+    """counter += 1 as a stream-ordered device operation (no host sync; capturable)."""
+    dropout_step_tensor(device).add_(1)
+
+
+def _drop_step(like: Tensor, p: float):
+    return dropout_step_tensor(like.device) if p > 0 else None
+
+
 @torch.library.custom_op("b200llm::dropout", mutates_args=())
 def dropout(x: Tensor, residual: Optional[Tensor], p: float, seed: int) -> Tensor:
-    """(residual +) keep * x / (1 - p); keep is a counter-based function of (seed, element index)."""
-    return K.dropout(x, p, seed, residual).view(x.shape)
+    """(residual +) keep * x / (1 - p); keep is a counter-based function of (seed + step counter, element index)."""
+    return K.dropout(x, p, seed, residual, seed_dev=_drop_step(x, p)).view(x.shape)
 
 
 @dropout.register_fake
@@ -746,14 +792,16 @@ def _dropout_setup(ctx, inputs, output):
 
 
 def _dropout_bwd(ctx, dy):
-    return K.dropout(dy.contiguous(), ctx.p, ctx.seed).view(dy.shape), (dy if ctx.has_res else None), None, None
+    return (K.dropout(dy.contiguous(), ctx.p, ctx.seed, seed_dev=_drop_step(dy, ctx.p)).view(dy.shape),
+            (dy if ctx.has_res else None), None, None)
 
 
 dropout.register_autograd(_dropout_bwd, setup_context=_dropout_setup)
 
 
 def new_seed() -> int:
-    """A fresh 62-bit seed from torch's CPU generator (follows torch.manual_seed; no device sync)."""
+    """A fresh 62-bit site seed from torch's CPU generator (follows torch.manual_seed and the RNG state that
+    activation checkpointing restores for its recompute; no device sync)."""
     return int(torch.randint(0, 2 ** 62, (1,)).item())
 
 
@@ -1000,13 +1048,14 @@ cross_entropy.register_autograd(_ce_bwd, setup_context=_ce_setup)
 
 @torch.library.custom_op("b200llm::linear_cross_entropy", mutates_args=())
 def linear_cross_entropy(x: Tensor, weight: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
-                         targets: Tensor, capacity: int) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+                         targets: Tensor, capacity: int, write_grad: bool = True) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """loss = CE(x W^T + scaling (x A) B, targets) -> (loss fp32 [], dlogits, t, x_rows, row_index).
 
     The logits live only in the returned work buffer, which the cross-entropy kernel overwrites in
     place with dloss/dlogits for the backward GEMMs. capacity > 0: only the rows whose target is not
     ignore_index are projected (they are the only ones that reach the loss or any gradient);
-    capacity must be >= their count (otherwise the loss comes back NaN)."""
+    capacity must be >= their count (otherwise the loss comes back NaN). write_grad=False (evaluation under
+    no_grad) skips the dlogits pass of the cross-entropy kernel."""
     x2 = _flat2d(x)
     V = weight.shape[0]
     if capacity > 0 and capacity < x2.shape[0]:
@@ -1022,12 +1071,12 @@ def linear_cross_entropy(x: Tensor, weight: Tensor, A: Optional[Tensor], B: Opti
     else:
         t = x2.new_empty((0,))
         K.gemm_ex(rows, weight, out=buf[:, :V])
-    loss = K.cross_entropy_(buf[:, :V], tg)
+    loss = K.cross_entropy_(buf[:, :V], tg, write_grad=write_grad)
     return loss.reshape(()), buf, t, (rows if idx.numel() else x2.new_empty((0,))), idx
 
 
 @linear_cross_entropy.register_fake
-def _(x, weight, A, B, scaling, targets, capacity):
+def _(x, weight, A, B, scaling, targets, capacity, write_grad=True):
     M, V = x.numel() // x.shape[-1], weight.shape[0]
     compact = 0 < capacity < M
     R = capacity if compact else M
@@ -1039,17 +1088,23 @@ def _(x, weight, A, B, scaling, targets, capacity):
 
 def _lce_setup(ctx, inputs, output):
     ctx.set_materialize_grads(False)
-    x, weight, A, B, scaling, targets, capacity = inputs
+    x, weight, A, B, scaling, targets, capacity, write_grad = inputs
     _, buf, t, rows, idx = output
     ctx.save_for_backward(x, weight, A, B, t, buf, rows, idx)
     ctx.scaling = scaling
+    ctx.write_grad = write_grad
 
 
 def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
-    """Assumes dloss == 1 (loss.backward() on the scalar loss, as train.py:112 does)."""
+    """The forward wrote dlogits for d(loss) = 1; the incoming gradient (a device scalar: 1 for loss.backward() as
+    train.py:112 does, 1/k under gradient accumulation, a loss scale) is applied to that buffer in place by a kernel
+    that returns immediately when it reads exactly 1 — so one backward per forward."""
     if dloss is None:
-        return (None,) * 7
+        return (None,) * 8
+    if not ctx.write_grad:
+        raise RuntimeError("linear_cross_entropy was run with write_grad=False (evaluation): it has no backward")
     x, weight, A, B, t, buf, rows, idx = ctx.saved_tensors
+    K.scale_dev_(buf, dloss.detach().reshape(1).to(torch.float32))
     wref, aref, bref = weight, A, B
     need = ctx.needs_input_grad
     V = weight.shape[0]
@@ -1074,7 +1129,7 @@ def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
         dB = _weight_grad(dl, t, bref, trans_out=True)
     if need[1]:
         dW = _weight_grad(dl, x2, wref)
-    return dx, dW, dA, dB, None, None, None
+    return dx, dW, dA, dB, None, None, None, None
 
 
 linear_cross_entropy.register_autograd(_lce_bwd, setup_context=_lce_setup)

@@ -37,6 +37,7 @@ class B200AdamW(torch.optim.Optimizer):
         self.zero = bool(zero) and self.world > 1
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
+        self._check_groups()
         # the reference hands every parameter to AdamW; frozen ones never get a gradient
         self._trainable = [p for g in self.param_groups for p in g["params"] if p.requires_grad]
         if not self._trainable:
@@ -81,6 +82,15 @@ class B200AdamW(torch.optim.Optimizer):
         self._partial = torch.zeros(2 * len(self._groups), device=dev, dtype=torch.float32)
         self.max_norm = None  # set by Trainer (train.py:115-120 uses 1.0)
         self.graph_safe = False
+
+    def _check_groups(self):
+        """One flat buffer per dtype is updated by one kernel launch with one set of hyper-parameters (the
+        reference builds a single group, build_components.py:258): groups that differ are refused, not ignored."""
+        g0 = self.param_groups[0]
+        for g in self.param_groups[1:]:
+            for k in ("lr", "betas", "eps", "weight_decay"):
+                if g[k] != g0[k]:
+                    raise ValueError(f"B200AdamW: param groups with different {k} ({g0[k]} vs {g[k]}) are not supported")
 
     # ------------------------------------------------------------------
     def flush_pending_grads(self):
@@ -130,6 +140,7 @@ class B200AdamW(torch.optim.Optimizer):
         from . import ops
         ops.flush_weight_grads()
         self._absorb_autograd_grads()
+        self._check_groups()
         self._step += 1
         if self.zero:
             return self._zero_step()

@@ -66,6 +66,13 @@ class Trainer:
     # train.py:88-92
     def calc_loss_batch(self, input_batch, target_batch):
         target_batch_host = target_batch if not target_batch.is_cuda else None
+        if target_batch_host is not None and isinstance(self.config, dict) and "vocab_size" in self.config:
+            # F.cross_entropy refuses class indices outside [0, V) (other than ignore_index); checked here on the
+            # host copy of the batch — targets that only exist on the device turn the loss into NaN instead
+            V = self.config["vocab_size"]
+            bad = (target_batch_host != -100) & ((target_batch_host < 0) | (target_batch_host >= V))
+            if bool(bad.any()):
+                raise IndexError(f"Target {int(target_batch_host[bad][0])} is out of bounds.")
         input_batch = input_batch.to(self.device, non_blocking=True)
         target_batch = target_batch.to(self.device, non_blocking=True)
         core = self.model.module if isinstance(self.model, B200DDP) else self.model

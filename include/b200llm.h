@@ -106,10 +106,14 @@ int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void* Wil, int64
  * b200_gemm_workspace_bytes() bytes, ZERO-FILLED when registered; pass NULL to unregister). With it,
  * b200_gemm_ex / b200_gemm_nt_bf16 cut the tiles of a last, at most half-filled wave along K so every
  * CTA pair stays busy (an 8192 x 2048 output is 256 tiles on 74 pairs); the partial sums meet in the
- * scratch, whose counters every launch leaves zero again. GEMMs that use it must not run concurrently
- * on different streams of the same device. No reference counterpart (scheduling detail of K1). */
+ * scratch, whose counters every launch leaves zero again. The device-wide scratch serves every stream
+ * that has none of its own, so GEMMs using it must not overlap on different streams of the device; a
+ * host that does run GEMMs concurrently on several streams registers one scratch per stream with
+ * b200_gemm_set_stream_workspace (same size / alignment / zero-fill rules; NULL unregisters), which
+ * makes every entry point re-entrant. No reference counterpart (scheduling detail of K1). */
 size_t b200_gemm_workspace_bytes(void);
 int b200_gemm_set_workspace(void* workspace, size_t bytes);
+int b200_gemm_set_stream_workspace(void* stream, void* workspace, size_t bytes);
 
 /* Grouped launch of up to B200_GEMM_GROUP_MAX independent skinny GEMMs (every N <= 64, one
  * operand pair each; same operand conventions as b200_gemm_ex) in ONE persistent kernel. Used
@@ -208,13 +212,20 @@ int b200_embedding_bwd_f32acc(const int64_t* idx, const void* dout, float* dtok_
 
 /* ---- K3: cross-entropy over materialised logits (train.py:91) ------------------------------
  * F.cross_entropy(logits, targets) with ignore_index = -100, reduction = mean over the
- * non-ignored rows; all rows ignored -> NaN like the reference. Overwrites `logits` in place
- * with dloss/dlogits (already divided by the valid count) when write_grad != 0.
+ * non-ignored rows; all rows ignored -> NaN like the reference. A target outside [0, V) that is
+ * not ignore_index makes the loss NaN (the reference's kernel asserts; a device-side assert would
+ * poison the context, a NaN loss is the loud, recoverable form of the same refusal). Overwrites
+ * `logits` in place with dloss/dlogits (already divided by the valid count) when write_grad != 0.
  * loss_out: 1 fp32. workspace: b200_cross_entropy_workspace_bytes(M) bytes. */
 size_t b200_cross_entropy_workspace_bytes(int64_t M);
 int b200_cross_entropy_bf16(void* logits, int64_t ld, const int64_t* targets, float* loss_out,
                             int64_t M, int64_t V, int write_grad, void* workspace,
                             size_t workspace_bytes, void* stream);
+
+/* x[0..n) *= *scale_dev (one fp32 in device memory); returns at once when it is exactly 1. The fused
+ * vocab projection writes dlogits for d(loss) = 1 during forward; this applies the incoming gradient of
+ * a scaled loss (loss / accumulation_steps, loss scaling) in backward without a host read. */
+int b200_scale_bf16_dev(void* x, int64_t n, const float* scale_dev, void* stream);
 
 /* Row compaction in front of the vocab projection: rows whose target is ignore_index (-100)
  * contribute nothing to the mean loss of train.py:91 nor to any gradient, so the projection and
@@ -292,28 +303,31 @@ int b200_colsum_bf16(const void* x, int64_t ld, float* out, int64_t M, int64_t N
 int b200_attention_fwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, void* o, int64_t ldo, float* lse, int64_t B, int64_t T,
                             int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p,
-                            uint64_t seed, void* stream);
+                            uint64_t seed, const uint64_t* seed_dev, void* stream);
 /* Backward. dq/dk/dv have the layouts of q/k/v. `workspace` is scratch of
- * b200_attention_bwd_workspace_bytes(B, T, h, hd) bytes: rowsum(dO*O) per (b, h, t) and, on the
- * tcgen05 path (hd 64), the fp32 dQ accumulator that the key-tile CTAs add into. */
+ * b200_attention_bwd_workspace_bytes(B, T, h, hd) bytes: -lse*log2(e) and -rowsum(dO*O) per
+ * (b, h, t), laid out per 64-query step. */
 size_t b200_attention_bwd_workspace_bytes(int64_t B, int64_t T, int64_t h, int64_t hd);
 int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                             int64_t ldv, const void* o, int64_t ldo, const void* dout,
                             int64_t lddo, const float* lse, void* workspace, size_t workspace_bytes,
                             void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
                             int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd, float scale,
-                            float dropout_p, uint64_t seed, void* stream);
-/* dropout_p > 0 (hd 64 only) drops attention weights after the softmax like GPT2.py:43; the mask is
- * a counter-based function of (seed, b, h, q, k), so backward must be given the forward's seed.
+                            float dropout_p, uint64_t seed, const uint64_t* seed_dev, void* stream);
+/* dropout_p > 0 drops attention weights after the softmax like GPT2.py:43; the mask is a counter-based
+ * function of (seed + *seed_dev, b, h, q, k), so backward must be given the forward's seed and seed_dev.
+ * seed_dev (may be NULL = 0) is one uint64 in device memory read by the kernels when they run: a step
+ * captured in a CUDA graph draws fresh masks on every replay if the host bumps it between replays.
  * b200_attention_dropout_mask_u8 writes that keep mask ([B, H, T, T] bytes) for tests. */
 int b200_attention_dropout_mask_u8(void* out, int64_t B, int64_t H, int64_t T, float dropout_p,
                                    uint64_t seed, void* stream);
 
 /* ---- K10: dropout (nn.Dropout, Models/GPT2/GPT2.py:24,81,102) ------------------------------
- * y = (res +) keep(i) * x / (1 - p), keep a counter-based function of (seed, i): applying the
- * same call to the upstream gradient is the backward. b200_dropout_mask_u8 dumps the mask. */
+ * y = (res +) keep(i) * x / (1 - p), keep a counter-based function of (seed + *seed_dev, i) (seed_dev:
+ * optional device uint64, see the attention note above): applying the same call to the upstream
+ * gradient is the backward. b200_dropout_mask_u8 dumps the mask of a given effective seed. */
 int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float p, uint64_t seed,
-                      void* stream);
+                      const uint64_t* seed_dev, void* stream);
 int b200_dropout_mask_u8(void* out, int64_t n, float p, uint64_t seed, void* stream);
 
 /* ---- K2 decode: one new query token per sequence against a KV cache ---------------------------

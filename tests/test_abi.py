@@ -34,7 +34,7 @@ def test_version_and_error_string(lib):
     assert rc == -1
     assert b"rmsnorm_fwd" in lib.b200_last_error()
     rc = lib.b200_attention_fwd_bf16(ctypes.c_void_p(16), 64, ctypes.c_void_p(16), 64, ctypes.c_void_p(16), 64,
-                                     ctypes.c_void_p(16), 64, ctypes.c_void_p(16), 1, 8, 1, 1, 48, 1.0, 0.0, 0, None)
+                                     ctypes.c_void_p(16), 64, ctypes.c_void_p(16), 1, 8, 1, 1, 48, 1.0, 0.0, 0, None, None)
     assert rc == -1 and b"head_dim" in lib.b200_last_error()
 
 

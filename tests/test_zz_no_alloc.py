@@ -7,8 +7,9 @@ This test drives it through the C-ABI with raw pointers and checks, on two conse
 share that array (the second one smaller, so stale slots of the first call sit right behind it),
 that loss and gradient equal what the workspace-taking entry point b200_cross_entropy_bf16
 produces on the same logits. Both run the same kernels, so the comparison is exact; the tolerance
-used is the suite's bf16 bound (2e-2 relative) all the same. It also checks that a batch beyond
-the built-in limit is refused with a readable message.
+used is the suite's bf16 bound (2e-2 relative) all the same. Loss and gradient are also held
+against the oracle's cross-entropy (autograd through the CPU restatement of train.py:91) at that
+bound. It also checks that a batch beyond the built-in limit is refused with a readable message.
 """
 import ctypes
 
@@ -60,6 +61,13 @@ def test_noalloc_cross_entropy_matches_workspace_version_twice_in_a_row():
         assert rel_err(loss, ref_loss) < BF16_TOL and torch.equal(loss, ref_loss)
         assert rel_err(grad, ref_grad) < BF16_TOL and torch.equal(grad, ref_grad)
         assert torch.all(grad[(targets == -100).cpu()] == 0)
+        # ... and against the oracle (train.py:91 restated on the CPU, gradient by autograd)
+        from oracle import reference_ops as R
+        lg = logits[:, :V].float().cpu().requires_grad_(True)
+        o_loss = R.cross_entropy(lg, targets.cpu())
+        o_loss.backward()
+        assert abs(float(loss) - float(o_loss)) <= BF16_TOL * abs(float(o_loss))
+        assert rel_err(grad, lg.grad) < BF16_TOL
 
 
 def test_noalloc_cross_entropy_refuses_oversized_batches():
