@@ -333,6 +333,42 @@ def build_trainer(cfg, device, world_size):
     return tr
 
 
+def data_parallel_selfcheck(step, dev_batches, n_valid, world):
+    """N > 1: (1) after two optimizer steps on per-rank batches the flat parameter buffers must be bit-identical on
+    every rank (checksums all-gathered); (2) the exchanged gradient must equal the mean over ranks of the local
+    gradients (the reference DDP's mean-of-means): local flat gradients are all-gathered and
+    averaged in fp32 as the expected value, then compared with what the exchange leaves in the buffer."""
+    import torch.distributed as dist
+    for i in range(2):
+        step.run(*dev_batches[i % len(dev_batches)], n_valid=n_valid[i % len(dev_batches)])
+    torch.cuda.synchronize()
+    sums = []
+    for g in step.opt._groups.values():
+        bits = g["p"].view(torch.int16).to(torch.int64)
+        w = torch.arange(bits.numel(), device=bits.device, dtype=torch.int64) % 65521 + 1
+        sums += [bits.sum(), (bits * w).sum()]
+    mine = torch.stack(sums)
+    every = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    identical = all(bool(torch.equal(e, every[0])) for e in every)
+    # gradient mean: one eager forward/backward without the exchange, then the exchange on its own
+    step.capacity = 0
+    step._fwd_bwd(False)
+    worst = 0.0
+    for flat in step.opt.flat_grads:
+        local = flat.clone()
+        parts = [torch.empty_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        expect = torch.stack(parts).mean(0)
+        del parts
+        step.ddp.reduce_gradients([flat])
+        worst = max(worst, float((flat - expect).abs().max() / expect.abs().max().clamp_min(1e-30)))
+        del expect, local
+    torch.cuda.synchronize()
+    return {"ranks_identical": identical, "grad_mean_max_rel": worst,
+            "checked": "parameter checksums after 2 steps; exchanged flat gradient vs the fp32 mean of the all-gathered local gradients"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -378,18 +414,35 @@ def main():
     n_valid = [int((y != -100).sum()) for _, y in host]        # known from the host copy of each batch
     ignored = float(sum((y == -100).float().mean() for _, y in host) / n_batches)
 
-    step = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=not args.no_graph)
-    step.compact_head = not args.full_head
-    step.capture(warmup=2)
-    for n in n_valid:
-        step.prepare(n)
+    def make_step(**kw):
+        st = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=not args.no_graph, **kw)
+        st.compact_head = not args.full_head
+        st.capture(warmup=2)
+        for n in n_valid:
+            st.prepare(n)
+        return st
+
+    step = main_step = make_step()
+
+    # ---- data-parallel self-check (N > 1), before anything is timed: numbers, not just an exit code
+    dp_check = None
+    if world > 1:
+        dp_check = data_parallel_selfcheck(step, dev, n_valid, world)
+        if not dp_check["ranks_identical"] and step.capture_collective:
+            # the single-graph form with captured collectives failed: fall back to two graphs with the
+            # exchange issued by the host between them, and check again
+            step.close()
+            step = main_step = make_step(capture_collective=False)
+            dp_check = data_parallel_selfcheck(step, dev, n_valid, world)
+            dp_check["fallback"] = "captured collectives failed the self-check; two-graph replay"
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(batches, read_loss):
+    def timed(batches, read_loss, step=None):
+        step = step or main_step
         for i in range(args.warmup):
             step.run(*batches[i % n_batches], n_valid=n_valid[i % n_batches])
         barrier()
@@ -434,6 +487,43 @@ def main():
     ms_e2e, _ = timed(host, read_loss=True)
     final_loss = float(step.loss)
 
+    # ---- secondary figures (same K steps each, outside the headline's timed region) -------------------
+    # every row through the vocab projection (no row compaction: what the headline would be without -100 targets)
+    ms_full = None
+    if step.compact_head and step.graphs is not None:
+        step.compact_head = False
+        ms_full, _ = timed(dev, read_loss=False)
+        step.compact_head = True
+    # the drop-in API itself: Trainer.train_batch, eager (no graph), host batches
+    k_eager = min(args.steps, 5)
+    for i in range(2):
+        tr.train_batch(*host[i % n_batches])
+    barrier()
+    ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ee0.record()
+    for i in range(k_eager):
+        tr.train_batch(*host[i % n_batches])
+    ee1.record()
+    barrier()
+    ms_eager = ee0.elapsed_time(ee1)
+    if world > 1:
+        t = torch.tensor([ms_eager], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_eager = float(t)
+    # what the gradient exchange costs a step: the same step with the exchange left out (ranks then diverge, so
+    # this runs last; nothing after it uses the weights)
+    comm_exposed_ms = None
+    if world > 1 and step.graphs is not None:
+        local = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=True)
+        local.ddp = None
+        local.compact_head = step.compact_head
+        local.capture(warmup=1)
+        for n in n_valid:
+            local.prepare(n)
+        ms_local, _ = timed(dev, read_loss=False, step=local)
+        comm_exposed_ms = (ms_dev - ms_local) / args.steps
+        del local
+
     tokens_step = MICRO_BATCH * SEQ_LEN * world
     value = tokens_step * args.steps / (ms_dev / 1e3)
     e2e = tokens_step * args.steps / (ms_e2e / 1e3)
@@ -446,6 +536,8 @@ def main():
         kernels.set_gemm_profile(prof)
         eager = TrainStep(tr, (MICRO_BATCH, SEQ_LEN), use_graph=False)
         eager.ddp = None                          # rank-0-only pass: no collective may be issued here
+        if getattr(tr.model, "detach", None):
+            tr.model.detach()                     # ... nor by the wrapper's gradient-ready hooks
         eager.compact_head = step.compact_head
         eager.x.copy_(dev[0][0]); eager.y.copy_(dev[0][1])
         eager._graphs_for(n_valid[0])             # same vocab-projection capacity as the timed steps
@@ -509,6 +601,13 @@ def main():
                         "loss_read": "every step, async copy to pinned memory, read by the host one step behind"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "cuda_graph": step.graphs is not None, "final_loss": final_loss,
+                "value_full_head": (tokens_step * args.steps / (ms_full / 1e3)) if ms_full else None,
+                "eager_trainer_tokens_per_s": tokens_step * k_eager / (ms_eager / 1e3),
+                "data_parallel": None if world == 1 else dict(
+                    dp_check, comm_exposed_ms=comm_exposed_ms,
+                    exchange=("bucketed NCCL all-reduce (AVG) of the flat fp32 gradient buffer, captured in the step's "
+                              "graph and overlapped with backward" if step.capture_collective else
+                              "two graphs per step, NCCL all-reduce (AVG) of the flat fp32 gradient buffer issued between them")),
                 "ignored_target_fraction": ignored,
                 "vocab_projection": ("all rows" if args.full_head else
                                      "non-ignored target rows only (exact: ignored rows reach neither the loss nor any "

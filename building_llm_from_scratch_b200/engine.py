@@ -19,7 +19,7 @@ from .train import Trainer
 
 
 class TrainStep:
-    def __init__(self, trainer: Trainer, batch_shape, use_graph: bool = True):
+    def __init__(self, trainer: Trainer, batch_shape, use_graph: bool = True, capture_collective=None):
         assert isinstance(trainer.optimizer, B200AdamW), "TrainStep drives the fused optimizer"
         self.tr = trainer
         self.opt = trainer.optimizer
@@ -36,10 +36,13 @@ class TrainStep:
         self.pool = None
         self.capacity = 0             # rows the vocab projection sees in the step being built (0 = all)
         self.compact_head = True
-        # B200_GRAPH_NCCL=1 captures the NCCL all-reduces into the graph (one launch per step, the bucket
-        # all-reduces overlap backward inside it). NCCL refuses to destroy a communicator while graphs
-        # that captured its collectives exist: call close() before destroy_process_group().
-        self.capture_collective = os.environ.get("B200_GRAPH_NCCL", "0") == "1"
+        # Data-parallel replay is ONE graph per step with the bucket all-reduces captured inside it, overlapping
+        # backward (B200_GRAPH_NCCL=0 or capture_collective=False: two graphs with the exchange issued by the host
+        # between them). NCCL refuses to destroy a communicator while graphs that captured its collectives
+        # exist: call close() before destroy_process_group().
+        if capture_collective is None:
+            capture_collective = os.environ.get("B200_GRAPH_NCCL", "1") != "0"
+        self.capture_collective = bool(capture_collective)
         # bucketed all-reduce overlapped with backward (eager steps and captured collectives); with the
         # default two-graph replay the exchange sits between the graphs and cannot overlap
         self.overlap = os.environ.get("B200_DDP_OVERLAP", "1") != "0"
@@ -195,8 +198,7 @@ class TrainStep:
         graphs = self._graphs_for(n_valid)
         tr.global_step += 1
         lr = self._refresh_hyper()
-        self.opt._step = tr.global_step + 1      # replayed steps do not pass through B200AdamW.step(): keep its
-                                                 # counter (saved in checkpoints, used by eager steps) in line
+        self.opt._step = tr.global_step          # steps taken before this one (an eager step() increments it)
         tr.track_lrs.append(lr)
         self.x.copy_(x_src, non_blocking=True)
         self.y.copy_(y_src, non_blocking=True)
@@ -208,5 +210,8 @@ class TrainStep:
             graphs[0].replay()
             self.ddp.reduce_gradients(self.opt.flat_grads)
             graphs[1].replay()
+        # replayed steps do not pass through B200AdamW.step(): keep its counter (saved in checkpoints, used for
+        # the bias corrections of later eager steps) in line with the trainer's
+        self.opt._step = tr.global_step + 1
         tr.tokens_seen += self.x.numel()
         return self.loss

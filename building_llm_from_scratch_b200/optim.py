@@ -149,13 +149,21 @@ class B200AdamW(torch.optim.Optimizer):
             scale = self.grad_norm(self.max_norm)[1:2]
         pg = self.param_groups[0]
         lr, (b1, b2), eps, wd = pg["lr"], pg["betas"], pg["eps"], pg["weight_decay"]
-        hyper = None
-        if self.graph_safe:
-            # replayable: hyper-parameters are read from device memory, refreshed by set_hyper()
-            hyper = self._hyper_dev
+        hyper = self._graph_hyper(lr)
         for g in self._groups.values():
             K.adamw_(g["p"], g["g"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
                      dev_hyper=hyper)
+
+    def _graph_hyper(self, lr):
+        """graph_safe: the kernels read (lr, bias corrections) from device memory so that a captured step can be
+        replayed with new values. Outside a capture the buffer is refreshed here from param_groups / the step
+        counter, so an eager step() (Trainer.train_batch) is never run on stale values; during a capture it is
+        left alone (TrainStep refreshes it before every replay)."""
+        if not self.graph_safe:
+            return None
+        if not torch.cuda.is_current_stream_capturing():
+            self.set_hyper(lr, max(self._step, 1))
+        return self._hyper_dev
 
     def _zero_step(self):
         """ZeRO-1 update (see the module docstring); every collective is on the current stream's
@@ -177,7 +185,7 @@ class B200AdamW(torch.optim.Optimizer):
             scale = self._norm_out[1:2]
         pg = self.param_groups[0]
         lr, (b1, b2), eps, wd = pg["lr"], pg["betas"], pg["eps"], pg["weight_decay"]
-        hyper = self._hyper_dev if self.graph_safe else None
+        hyper = self._graph_hyper(lr)
         for g in groups:
             K.adamw_(g["p_shard"], g["g_shard"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
                      dev_hyper=hyper)
@@ -186,22 +194,49 @@ class B200AdamW(torch.optim.Optimizer):
     # ---- checkpoint / resume (the reference saves the model only, train.py:231-257; a resume needs the
     # moments and the step count too) ------------------------------------------------------------------
     def state_dict(self):
-        return {"b200_adamw": 1, "step": self._step, "zero": self.zero, "world": self.world,
+        """Flat moments of the WHOLE parameter buffer + step. With ZeRO-1 every rank owns 1/world of the moments:
+        they are all-gathered here, so this is a COLLECTIVE call (every rank of the group must make it) and the
+        result is the same on every rank and independent of the sharding — a checkpoint written by rank 0 alone
+        (Trainer.save_training_state) can be resumed with any world size, with or without ZeRO."""
+        import torch.distributed as dist
+        moments = {}
+        for dt, g in self._groups.items():
+            m, v = g["m"], g["v"]
+            if self.zero:
+                fm, fv = torch.empty_like(g["p"]), torch.empty_like(g["p"])
+                dist.all_gather_into_tensor(fm, m, group=self.pg)
+                dist.all_gather_into_tensor(fv, v, group=self.pg)
+                m, v = fm, fv
+            moments[str(dt)] = {"m": m.detach().cpu(), "v": v.detach().cpu(), "numel": g["p"].numel(),
+                                "param_numel": sum(p.numel() for p in g["params"])}
+        return {"b200_adamw": 2, "step": self._step, "layout": "full", "zero": self.zero, "world": self.world,
                 "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups],
-                "moments": {str(dt): {"m": g["m"].detach().cpu(), "v": g["v"].detach().cpu(), "numel": g["p"].numel()}
-                            for dt, g in self._groups.items()}}
+                "moments": moments}
 
     def load_state_dict(self, state):
-        if not isinstance(state, dict) or state.get("b200_adamw") != 1:
+        if not isinstance(state, dict) or state.get("b200_adamw") not in (1, 2):
             raise ValueError("B200AdamW.load_state_dict: not a B200AdamW state (torch.optim.AdamW states are laid out per parameter)")
-        if bool(state["zero"]) != self.zero or (self.zero and state["world"] != self.world):
-            raise ValueError("B200AdamW.load_state_dict: ZeRO sharding of the checkpoint differs from this optimizer's")
+        if state["b200_adamw"] == 1 and state.get("zero"):
+            raise ValueError("B200AdamW.load_state_dict: version-1 ZeRO checkpoints hold only the saving rank's shard of "
+                             "the moments and cannot be resumed; re-save with this version")
         for dt, g in self._groups.items():
             src = state["moments"][str(dt)]
-            if src["numel"] != g["p"].numel() or src["m"].numel() != g["m"].numel():
+            n_par = sum(p.numel() for p in g["params"])
+            if src.get("param_numel", n_par) != n_par:
                 raise ValueError("B200AdamW.load_state_dict: flat buffer sizes differ (different set of trainable parameters)")
-            g["m"].copy_(src["m"])
-            g["v"].copy_(src["v"])
+            # the flat buffers may be padded differently (ZeRO rounds the total up to a multiple of 64 * world);
+            # the padding holds no parameter, so only the common prefix matters
+            total = g["p"].numel()
+            for key in ("m", "v"):
+                full = torch.zeros(total, dtype=g[key].dtype)
+                n = min(total, src[key].numel())
+                if n < g["offsets"][-1] + g["params"][-1].numel():
+                    raise ValueError("B200AdamW.load_state_dict: checkpoint moments are shorter than the parameters")
+                full[:n].copy_(src[key][:n])
+                if self.zero:
+                    shard = total // self.world
+                    full = full[self.rank * shard:(self.rank + 1) * shard]
+                g[key].copy_(full)
         self._step = int(state["step"])
         for pg, saved in zip(self.param_groups, state["param_groups"]):
             pg.update(saved)
