@@ -46,6 +46,8 @@ SIGNATURES = {
     "b200_gemm_lora_packed_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, I, C.POINTER(C.c_int64), P, I64, I64, I64, P]),
     "b200_gemm_swiglu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_path_counts": (I, [C.POINTER(C.c_uint64), I]),
+    "b200_gemm_set_option": (I, [I, I]),
     "b200_gemm_workspace_bytes": (SZ, []),
     "b200_gemm_set_workspace": (I, [P, SZ]),
     "b200_gemm_set_stream_workspace": (I, [P, P, SZ]),
@@ -130,6 +132,25 @@ def check(status: int, what: str = "") -> None:
     if status != 0:
         msg = load().b200_last_error().decode(errors="replace")
         raise B200Error(f"b200llm {what} failed with status {status}: {msg}")
+
+
+GEMM_PATHS = ("pair", "pair_tail_split", "single_cta", "grouped_tiles", "streamk", "packed_segments", "swiglu_fwd",
+              "swiglu_bwd")
+
+
+def gemm_path_counts() -> dict:
+    """Launch counts of the GEMM scheduling paths so far (b200_gemm_path_counts)."""
+    out = (C.c_uint64 * len(GEMM_PATHS))()
+    load().b200_gemm_path_counts(out, len(GEMM_PATHS))
+    return dict(zip(GEMM_PATHS, [int(v) for v in out]))
+
+
+GEMM_OPT_TAIL_SPLIT, GEMM_OPT_STREAMK, GEMM_OPT_N_FASTEST = 0, 1, 2
+
+
+def gemm_set_option(option: int, value: int) -> None:
+    """-1 = heuristic, 0 = off, 1 = forced (b200_gemm_set_option)."""
+    check(load().b200_gemm_set_option(option, value), "gemm_set_option")
 
 
 def launch_count() -> int:

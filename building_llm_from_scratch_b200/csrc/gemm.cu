@@ -15,6 +15,7 @@
 // shared-memory descriptor, so backward GEMMs (dX = dY·W, dW = dY^T·X) need no transposes.
 //
 // Roofline: tensor pipe. Algorithmic FLOPs per launch = 2·M·N·(K1+K2).
+#include <atomic>
 #include <cstdlib>
 #include <mutex>
 #include <vector>
@@ -1262,10 +1263,27 @@ TailWs tail_workspace_for(int dev, void* stream) {
   return (dev >= 0 && dev < 64) ? g_tail_ws[dev] : TailWs{nullptr, 0};
 }
 
-// environment switches (A/B measurements) are read once per process
-int env_flag(const char* name) {   // first character of the variable, 0 when unset
-  const char* e = getenv(name);
-  return e ? (int)(unsigned char)e[0] : 0;
+// which scheduling path each launch took (diagnostics for tests: b200_gemm_path_counts)
+enum : int { PATH_PAIR, PATH_PAIR_TAIL_SPLIT, PATH_SINGLE_CTA, PATH_GROUPED_TILES, PATH_STREAMK, PATH_PACKED_SEGMENTS,
+              PATH_SWIGLU_FWD, PATH_SWIGLU_BWD, PATH_N };
+std::atomic<uint64_t> g_path[PATH_N];
+
+// Scheduling switches for A/B measurements and tests (b200_gemm_set_option): -1 = the library's own heuristic,
+// 0 / 1 = off / forced. Their initial values come from the environment, read once per process.
+enum : int { OPT_TAIL_SPLIT, OPT_STREAMK, OPT_N_FASTEST, OPT_N };
+std::atomic<int> g_opt[OPT_N];
+std::once_flag g_opt_once;
+int gemm_option(int which) {
+  std::call_once(g_opt_once, [] {
+    auto env = [](const char* name, char on, char off) {
+      const char* e = getenv(name);
+      return !e ? -1 : (e[0] == on ? 1 : (e[0] == off ? 0 : -1));
+    };
+    g_opt[OPT_TAIL_SPLIT] = env("B200_GEMM_TAIL", '1', '0');
+    g_opt[OPT_STREAMK] = env("B200_GEMM_STREAMK_FORCE", '1', '0');
+    g_opt[OPT_N_FASTEST] = env("B200_GEMM_ORDER", 'n', 'm');
+  });
+  return g_opt[which].load();
 }
 
 bool use_pair_kernel() {
@@ -1328,9 +1346,8 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.n_fastest = 0;
   if (pair) {
     const double a_bytes = 2.0 * (double)M * (double)(K1 + K2), b_bytes = 2.0 * (double)N * (double)(K1 + K2);
-    static const int order = env_flag("B200_GEMM_ORDER");
-    if (order == 'n') p.n_fastest = 1;
-    else if (order == 'm') p.n_fastest = 0;
+    const int order = gemm_option(OPT_N_FASTEST);
+    if (order >= 0) p.n_fastest = order;
     else p.n_fastest = (a_bytes > 64e6 && b_bytes < 64e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
   }
   p.alpha = alpha;
@@ -1376,10 +1393,10 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const TailWs tw = tail_workspace_for(dev, stream);
     const int G = sms / 2;
     const int L = tiles % G;
-    static const int tail_env = env_flag("B200_GEMM_TAIL");
+    const int tail_opt = gemm_option(OPT_TAIL_SPLIT);
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && tail_env != '0') {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && tail_opt != 0) {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1426,7 +1443,15 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   const int work = tiles * splits;
   const int grid = work < sms ? work : sms;
   cudaStream_t st = (cudaStream_t)stream;
-  if (pair) return launch_2cta(maps, p, sms, st);
+  if (pair) {
+    ++g_path[PATH_PAIR];
+    if (p.tail_splits > 1) ++g_path[PATH_PAIR_TAIL_SPLIT];
+    if (seg_info && seg_info->nseg > 1) ++g_path[PATH_PACKED_SEGMENTS];
+    if (swiglu_fwd) ++g_path[PATH_SWIGLU_FWD];
+    if (swiglu_bwd) ++g_path[PATH_SWIGLU_BWD];
+    return launch_2cta(maps, p, sms, st);
+  }
+  ++g_path[PATH_SINGLE_CTA];
   switch (BN) {
     case 64: return launch_bn<64>(maps, p, grid, st);
     case 128: return launch_bn<128>(maps, p, grid, st);
@@ -1556,6 +1581,7 @@ extern "C" int b200_gemm_grouped_bf16(int nprob, const b200_gemm_problem* probs,
     attr_set[dev] = true;
   }
   const int grid = work < sms ? work : sms;
+  ++g_path[PATH_GROUPED_TILES];
   B200_CHECK_CUDA(b200_launch_pdl(gemm_grouped_kernel, dim3(grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
   b200_count_launch();
   return 0;
@@ -1636,7 +1662,7 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
     // Stream-K pays ~16 K blocks' worth of time for the shared-tile fix-up (RED, fence, counter, reload).
     // Replay the tile scheduler's round-robin on the host: if its busiest CTA is not clearly worse
     // than an even cut, the tiles go out whole (t = x A with K = 2048 on 64 tiles: 19 vs 23 us).
-    static const int sk_env = env_flag("B200_GEMM_STREAMK_FORCE");
+    const int sk_opt = gemm_option(OPT_STREAMK);
     long long tiles_total = 0;
     for (int i = 0; i < nprob; ++i) tiles_total += (probs[i].M + BM - 1) / BM;
     long long items = 0;
@@ -1654,16 +1680,30 @@ extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem
     long long busiest = 0;
     for (long long l : load) busiest = l > busiest ? l : busiest;
     const double even = (double)units / sms;
-    const bool streamk = sk_env == '1' || (sk_env != '0' && (double)busiest > 1.3 * even + 16.0);
+    const bool streamk = sk_opt == 1 || (sk_opt != 0 && (double)busiest > 1.3 * even + 16.0);
     if (!streamk) return b200_gemm_grouped_bf16(nprob, probs, stream);
   }
   // at least 4 K blocks per CTA: below that the fixed cost of a CTA outweighs its share of the stream
   long long grid = units / 4;
   if (grid > sms) grid = sms;
   if (grid < 1) grid = 1;
+  ++g_path[PATH_STREAMK];
   B200_CHECK_CUDA(b200_launch_pdl(gemm_streamk_kernel, dim3((unsigned)grid), dim3(256), G_SMEM, (cudaStream_t)stream, maps, g));
   b200_count_launch();
   return 0;
+}
+
+extern "C" int b200_gemm_set_option(int option, int value) {
+  B200_CHECK_ARG(option >= 0 && option < OPT_N && value >= -1 && value <= 1, "gemm_set_option: option %d / value %d out of range", option, value);
+  gemm_option(option);          // make sure the environment defaults are in before overriding one
+  g_opt[option] = value;
+  return 0;
+}
+
+extern "C" int b200_gemm_path_counts(uint64_t* out, int n) {
+  B200_CHECK_ARG(out && n >= 0, "gemm_path_counts: null pointer");
+  for (int i = 0; i < n; ++i) out[i] = i < PATH_N ? g_path[i].load() : 0;
+  return PATH_N;
 }
 
 extern "C" size_t b200_gemm_workspace_bytes(void) {

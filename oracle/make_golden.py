@@ -36,6 +36,7 @@ from Models.GPT2.GPT2 import MultiHeadAttention  # noqa: E402
 from Models.Llama.common_components import FeedForward, RMSNorm, compute_rope  # noqa: E402
 from Models.Llama.Llama3 import (GroupedQueryAttention, Llama3Model, SharedBuffers,  # noqa: E402
                                  precompute_rope_params)
+from Models.Llama import Llama2 as ref_llama2  # noqa: E402
 from datautils.dataloader_instruction_finetune import custom_collate_fn  # noqa: E402
 from datautils.dataset import DatasetPT  # noqa: E402
 from lora import LinearWithLoRA, replace_linear_with_lora  # noqa: E402
@@ -293,11 +294,52 @@ def gpt_modules_and_model():
     save("gpt2.pt", out)
 
 
+def llama2_modules():
+    """Llama-2 modules (Models/Llama/Llama2.py:61-190: MHA with fp32 RoPE tables, out-of-place masking, block, model)
+    in bf16, with every gradient. The driver path for Llama-2 is broken upstream, the modules are not."""
+    out = {}
+    gen = torch.Generator().manual_seed(51)
+    torch.manual_seed(123)
+    mha = ref_llama2.MultiHeadAttention(256, 256, 64, 4, dtype=torch.bfloat16)
+    xa = torch.randn(2, 40, 256, generator=gen).to(torch.bfloat16).requires_grad_(True)
+    ya = mha(xa)
+    ga = torch.randn(ya.shape, generator=gen).to(torch.bfloat16)
+    ya.backward(ga)
+    out["mha"] = dict(x=xa.detach(), sd={k: v.clone() for k, v in mha.state_dict().items() if k != "mask"},
+                      y=ya.detach(), gy=ga, dx=xa.grad.clone(), grads=grads_of(mha), n_heads=4, ctx=64)
+    cfg = dict(vocab_size=512, context_length=64, emb_dim=256, n_heads=4, n_layers=2, hidden_dim=512, dtype=torch.bfloat16)
+    blk = ref_llama2.TransformerBlock(cfg)
+    with torch.no_grad():
+        blk.norm1.weight.copy_(1 + 0.1 * torch.randn(256, generator=gen))
+        blk.norm2.weight.copy_(1 + 0.1 * torch.randn(256, generator=gen))
+    xb = torch.randn(2, 48, 256, generator=gen).to(torch.bfloat16).requires_grad_(True)
+    yb = blk(xb)
+    gb = torch.randn(yb.shape, generator=gen).to(torch.bfloat16)
+    yb.backward(gb)
+    out["block"] = dict(cfg=cfg, x=xb.detach(), sd={k: v.clone() for k, v in blk.state_dict().items() if not k.endswith("mask")},
+                        y=yb.detach(), gy=gb, dx=xb.grad.clone(), grads=grads_of(blk))
+    cfg = dict(vocab_size=256, context_length=64, emb_dim=128, n_heads=2, n_layers=2, hidden_dim=256, dtype=torch.bfloat16)
+    model = ref_llama2.Llama2Model(cfg)                  # full fine-tuning: every parameter gets a gradient
+    x = torch.randint(0, 256, (2, 64), generator=gen)
+    y = torch.roll(x, -1, dims=1)
+    y[1, :20] = -100
+    sd0 = {k: v.clone() for k, v in model.state_dict().items() if not k.endswith(".mask")}
+    logits = model(x)
+    loss = torch.nn.functional.cross_entropy(logits.flatten(0, 1), y.flatten())
+    loss.backward()
+    out["model"] = dict(cfg=cfg, sd=sd0, x=x, y=y, logits=logits.detach(), loss=loss.detach(), grads=grads_of(model))
+    save("llama2.pt", out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if len(sys.argv) > 2 and sys.argv[2] == "llama2":       # add the Llama-2 fixtures without regenerating the rest
+        llama2_modules()
+        raise SystemExit(0)
     data_pipeline()
     schedule_and_ce()
     optimizer()
     llama_modules()
     llama_model()
     gpt_modules_and_model()
+    llama2_modules()

@@ -122,12 +122,14 @@ def test_gemm_grouped_matches_individual_launches(K):
 
 
 @pytest.mark.parametrize("streamk", [True, False])
-def test_gemm_grouped_schedulers_agree_with_fp32(K, streamk, monkeypatch):
+def test_gemm_grouped_schedulers_agree_with_fp32(K, streamk, monkeypatch, request):
     """Both schedulers of the grouped launch (stream-K with shared-tile fix-up, tile-scheduled) on the
     shapes that stress the fix-up: K ranges cut across CTAs (vocab-sized K), ragged M, rank 8,
     fp32 and transposed stores; the stream-K scratch must be all zero again afterwards."""
     monkeypatch.setattr(K, "STREAMK", streamk)
-    monkeypatch.setenv("B200_GEMM_STREAMK_FORCE", "1")    # otherwise the host may pick whole tiles
+    from building_llm_from_scratch_b200 import _lib
+    _lib.gemm_set_option(_lib.GEMM_OPT_STREAMK, 1)        # otherwise the host may pick whole tiles
+    request.addfinalizer(lambda: _lib.gemm_set_option(_lib.GEMM_OPT_STREAMK, -1))
     probs, refs = [], []
     # u = s * dY B^T of a vocab projection: 3 row tiles (ragged) x 501 K blocks
     dl, Bh = rnd(300, 32064, scale=0.05, seed=60), rnd(64, 32064, scale=0.1, seed=61)
@@ -159,22 +161,27 @@ def test_gemm_grouped_schedulers_agree_with_fp32(K, streamk, monkeypatch):
 
 
 @pytest.mark.parametrize("force", ["1", ""])
-def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, monkeypatch):
+def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, request):
     """Integer-valued inputs: a single skinny product (one problem, K split over all SMs when forced,
     scheduler's own choice otherwise) is bit-exact."""
+    from building_llm_from_scratch_b200 import _lib
     if force:
-        monkeypatch.setenv("B200_GEMM_STREAMK_FORCE", force)
+        _lib.gemm_set_option(_lib.GEMM_OPT_STREAMK, 1)
+        request.addfinalizer(lambda: _lib.gemm_set_option(_lib.GEMM_OPT_STREAMK, -1))
+    before = _lib.gemm_path_counts()
     g = torch.Generator(device="cuda").manual_seed(5)
     a = torch.randint(-3, 4, (8192, 2048), generator=g, device="cuda").to(torch.bfloat16)
     b = torch.randint(-3, 4, (64, 2048), generator=g, device="cuda").to(torch.bfloat16)
     got = K.gemm_ex(a, b, alpha=0.125)
     ref = (0.125 * (a.float() @ b.float().t())).to(torch.bfloat16)
     assert torch.equal(got, ref)
+    if force:
+        assert _lib.gemm_path_counts()["streamk"] == before["streamk"] + 1
 
 
 @pytest.mark.parametrize("M,N,K_,r", [(8192, 2048, 4096, 64), (8192, 3072, 8192, 0), (8000, 2000, 4104, 8),
                                      (8192, 2048, 2048, 64)])
-def test_gemm_tail_split_wave(K, M, N, K_, r, monkeypatch):
+def test_gemm_tail_split_wave(K, M, N, K_, r, request):
     """Shapes whose last wave of 256 x 256 tiles is at most half full (256 or 384 tiles on 74 CTA pairs) and
     whose K range is deep enough to split (the last case is below the threshold and runs unsplit):
     the tail tiles are cut along K and summed through the registered workspace. Same results as with
@@ -183,14 +190,19 @@ def test_gemm_tail_split_wave(K, M, N, K_, r, monkeypatch):
     a, b = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2)
     bias, res = rnd(N, seed=3), rnd(M, N, seed=4)
     kw = dict(a2=rnd(M, r, seed=5), b2=rnd(N, r, scale=0.1, seed=6)) if r else {}
+    from building_llm_from_scratch_b200 import _lib
+    before = _lib.gemm_path_counts()
     got = K.gemm_ex(a, b, bias=bias, residual=res, **kw)
+    split = _lib.gemm_path_counts()["pair_tail_split"] - before["pair_tail_split"]
+    assert split == (1 if K_ >= 4096 else 0)               # deep K ranges are split, K = 2048 is not
     ref = a.float() @ b.float().t() + bias.float() + res.float()
     if r:
         ref = ref + kw["a2"].float() @ kw["b2"].float().t()
     assert rel_err(got.float(), ref) < BF16_TOL
-    monkeypatch.setenv("B200_GEMM_TAIL", "0")
+    _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, 0)
+    request.addfinalizer(lambda: _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, -1))
     plain = K.gemm_ex(a, b, bias=bias, residual=res, **kw)
-    monkeypatch.delenv("B200_GEMM_TAIL")
+    _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, -1)
     assert rel_err(got.float(), plain.float()) < 4e-3          # only the fp32 summation order differs
     g = torch.Generator(device="cuda").manual_seed(9)
     ai = torch.randint(-2, 3, (M, K_), generator=g, device="cuda").to(torch.bfloat16)

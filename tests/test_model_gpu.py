@@ -209,23 +209,45 @@ def test_row_compacted_vocab_projection_is_exact(golden):
     assert torch.isnan(bad)
 
 
-def test_llama2_block_matches_oracle():
-    """Llama-2 modules (MHA == GQA with kv groups == heads, theta 10 000) against the oracle."""
-    from building_llm_from_scratch_b200.Models.Llama.Llama2 import Llama2Model
-    from oracle import reference_ops as R
-    cfg = dict(vocab_size=512, context_length=128, emb_dim=256, n_heads=4, n_layers=2, hidden_dim=512,
-               dtype=torch.bfloat16)
-    torch.manual_seed(5)
-    model = Llama2Model(cfg).cuda()
-    x = torch.randint(0, 512, (2, 128), device="cuda")
-    logits = model(x)
-    sd = {k: v for k, v in model.state_dict().items() if not k.endswith("mask")}
-    ocfg = dict(cfg, n_kv_groups=cfg["n_heads"])
-    for i in range(cfg["n_layers"]):       # the reference multiplies bf16 activations by fp32 tables
-        sd[f"trf_blocks.{i}.att.cos"] = sd[f"trf_blocks.{i}.att.cos"].float()
-        sd[f"trf_blocks.{i}.att.sin"] = sd[f"trf_blocks.{i}.att.sin"].float()
-    ref = R.llama3_forward(x, sd, ocfg)
-    assert rel_err(logits.float(), ref.float()) < BF16_TOL
+def test_llama2_modules_against_reference_fixtures(golden):
+    """Llama-2 MultiHeadAttention, TransformerBlock and Llama2Model (Models/Llama/Llama2.py:61-190: fp32 RoPE tables,
+    kv groups == heads) against outputs AND gradients recorded from the reference's own modules."""
+    from building_llm_from_scratch_b200.Models.Llama import Llama2 as L2
+    g = golden("llama2.pt")
+    f = g["mha"]
+    att = L2.MultiHeadAttention(256, 256, f["ctx"], f["n_heads"], dtype=torch.bfloat16).cuda()
+    att.load_state_dict(f["sd"])
+    assert att.cos.dtype == torch.float32 and torch.equal(att.cos.cpu(), f["sd"]["cos"])
+    x = f["x"].cuda().requires_grad_(True)
+    y = att(x)
+    y.backward(f["gy"].cuda())
+    assert rel_err(y.cpu().float(), f["y"].float()) < BF16_TOL
+    assert rel_err(x.grad.cpu().float(), f["dx"].float()) < BF16_TOL
+    for k, v in f["grads"].items():
+        assert rel_err(dict(att.named_parameters())[k].grad.cpu().float(), v.float()) < BF16_TOL, k
+    f = g["block"]
+    blk = L2.TransformerBlock(f["cfg"]).cuda()
+    blk.load_state_dict(f["sd"])
+    x = f["x"].cuda().requires_grad_(True)
+    y = blk(x)
+    y.backward(f["gy"].cuda())
+    assert rel_err(y.cpu().float(), f["y"].float()) < BF16_TOL
+    assert rel_err(x.grad.cpu().float(), f["dx"].float()) < BF16_TOL
+    for k, v in f["grads"].items():
+        assert rel_err(dict(blk.named_parameters())[k].grad.cpu().float(), v.float()) < BF16_TOL, k
+    f = g["model"]
+    model = L2.Llama2Model(copy.deepcopy(f["cfg"])).cuda()
+    model.load_state_dict(f["sd"])
+    model.train()
+    logits = model(f["x"].cuda())
+    assert rel_err(logits.cpu().float(), f["logits"].float()) < BF16_TOL
+    loss = model.forward_loss(f["x"].cuda(), f["y"].cuda())
+    assert abs(float(loss) - float(f["loss"])) <= BF16_TOL * abs(float(f["loss"]))
+    loss.backward()
+    params = dict(model.named_parameters())
+    assert set(f["grads"]) == set(params)
+    for k, v in f["grads"].items():
+        assert close(params[k].grad.cpu().float(), v.float(), 5e-2, atol=1e-5), (k, rel_err(params[k].grad.cpu().float(), v.float()))
 
 
 def test_gpt2_trains_with_dropout(golden):
@@ -418,3 +440,154 @@ def test_training_state_resume(golden, tmp_path):
     # a torch.optim.AdamW state is refused rather than misread
     with pytest.raises(ValueError):
         opt2.load_state_dict({"state": {}, "param_groups": []})
+
+
+# ======================================================================================
+# Real dimensions: one block + head of the bench workload (and of the other BASELINE configs) against the
+# oracle evaluated on the GPU from the same state_dict, with the routing that only these sizes trigger.
+# ======================================================================================
+def _oracle_sd(model):
+    """state_dict of a drop-in model as leaf tensors the oracle can differentiate (LoRA A / B and any trainable
+    weight require grad; the mask buffers are not needed)."""
+    sd = {}
+    params = dict(model.named_parameters())
+    for k, v in model.state_dict().items():
+        if k.endswith("mask"):
+            continue
+        t = v.detach().clone()
+        if k in params and params[k].requires_grad:
+            t.requires_grad_(True)
+        sd[k] = t
+    return sd
+
+
+def test_llama32_1b_block_and_head_at_full_dimensions():
+    """d 2048, 32 heads / 8 kv groups, ffn 8192, V 128 256, B4 x T2048 (the bench's micro-batch), LoRA r=64 alpha=32 with perturbed B, ~60 % of
+    the targets ignored (so the row-compacted vocab projection runs): block output, input gradient, loss and all
+    16 LoRA gradients against the oracle; and the launches must have taken the packed q|k|v, SwiGLU-epilogue,
+    K-split tail and stream-K paths this shape is meant to trigger."""
+    from building_llm_from_scratch_b200 import _lib, ops
+    from building_llm_from_scratch_b200.Models.Llama import Llama3 as L
+    from building_llm_from_scratch_b200.Models.Llama.config import get_config_llama
+    from building_llm_from_scratch_b200.lora import LinearWithLoRA, head_operands, replace_linear_with_lora
+    from oracle import reference_ops as R
+    B, T, r, alpha = 4, 2048, 64, 32
+    cfg = get_config_llama("1B", "llama3_2", target_context_length=T)
+    cfg["n_layers"] = 1
+    torch.manual_seed(123)
+    L.SharedBuffers._buffers.clear()
+    with torch.device("cuda"):
+        model = L.Llama3Model(copy.deepcopy(cfg))
+    for p in model.parameters():
+        p.requires_grad = False
+    with torch.device("cuda"):
+        replace_linear_with_lora(model, rank=r, alpha=alpha, dtype=torch.bfloat16)
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    with torch.no_grad():
+        for m in model.modules():
+            if isinstance(m, LinearWithLoRA):
+                m.lora.B.copy_((torch.randn(m.lora.B.shape, generator=gen, device="cuda") * 0.02).to(torch.bfloat16))
+                m.linear.weight.copy_((torch.randn(m.linear.weight.shape, generator=gen, device="cuda") * 0.02).to(torch.bfloat16))
+    model.train()
+    sd = _oracle_sd(model)
+    x0 = (torch.randn(B, T, cfg["emb_dim"], generator=gen, device="cuda") * 0.5).to(torch.bfloat16)
+    tg = torch.randint(0, cfg["vocab_size"], (B, T), generator=gen, device="cuda")
+    tg[torch.rand(B, T, generator=gen, device="cuda") < 0.6] = -100
+    n_valid = int((tg != -100).sum())
+    capacity = (n_valid + 255) // 256 * 256
+    assert 0 < capacity < B * T
+
+    before = _lib.gemm_path_counts()
+    xa = x0.clone().requires_grad_(True)
+    y = model.trf_blocks(xa)
+    hs = model.final_norm(y).to(torch.bfloat16)
+    w, A, Bm, s = head_operands(model.out_head)
+    loss = ops.linear_cross_entropy(hs, w, A, Bm, s, tg, capacity, True)[0]
+    loss.backward()
+    ops.flush_weight_grads()
+    torch.cuda.synchronize()
+    took = {k: v - before[k] for k, v in _lib.gemm_path_counts().items()}
+    assert took["packed_segments"] >= 1, took          # q|k|v as one GEMM with per-segment LoRA blocks
+    assert took["swiglu_fwd"] == 1 and took["swiglu_bwd"] == 1, took
+    assert took["pair_tail_split"] >= 1, took          # fc3: 256 tiles on 74 CTA pairs with an 8192-deep K
+    assert took["streamk"] >= 1, took                  # u = dlogits B^T over the 128 256-wide K range
+
+    xb = x0.clone().requires_grad_(True)
+    scal = alpha / r
+    yo = R.llama3_block(xb, sd, "trf_blocks.0", cfg, scal)
+    ho = R.rmsnorm(yo, sd["final_norm.weight"]).to(torch.bfloat16)
+    lo = R.cross_entropy(R.lora_linear(ho, sd, "out_head", scal), tg)
+    lo.backward()
+    assert rel_err(y.float(), yo.float()) < BF16_TOL
+    assert abs(float(loss) - float(lo)) <= BF16_TOL * abs(float(lo))
+    assert rel_err(xa.grad.float(), xb.grad.float()) < BF16_TOL
+    n = 0
+    for k, p in model.named_parameters():
+        if p.requires_grad:
+            assert p.grad is not None and sd[k].grad is not None, k
+            assert rel_err(p.grad.float(), sd[k].grad.float()) < 5e-2, k
+            n += 1
+    assert n == 16
+
+
+def test_gpt2_1p5b_block_at_full_dimensions():
+    """One GPT2-1.5B block as BASELINE configs[3] trains it (d 1600, 25 heads, biases on out_proj / MLP, full
+    fine-tuning, B4 x T1024, dropout off for parity): output, input gradient and every weight / bias gradient
+    against the oracle. 1600 = 6.25 tiles of 256: every GEMM has an N tail, and 25 heads is not a power of two."""
+    from building_llm_from_scratch_b200.Models.GPT2 import GPT2 as G
+    from building_llm_from_scratch_b200.Models.GPT2.config import get_config_gpt2
+    from oracle import reference_ops as R
+    cfg = copy.deepcopy(get_config_gpt2("1.5B"))
+    cfg["drop_rate"] = 0.0
+    B, T = 4, 1024
+    torch.manual_seed(1)
+    with torch.device("cuda"):
+        blk = G.TransformerBlock(cfg)
+    blk = blk.to(torch.bfloat16).train()
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    with torch.no_grad():
+        for k, p in blk.named_parameters():
+            if k.endswith("bias"):
+                p.copy_((torch.randn(p.shape, generator=gen, device="cuda") * 0.1).to(torch.bfloat16))
+    sd = {"blocks.0." + k: v for k, v in _oracle_sd(blk).items()}
+    x0 = (torch.randn(B, T, cfg["emb_dim"], generator=gen, device="cuda") * 0.5).to(torch.bfloat16)
+    gy = (torch.randn(B, T, cfg["emb_dim"], generator=gen, device="cuda") * 0.1).to(torch.bfloat16)
+    xa = x0.clone().requires_grad_(True)
+    y = blk(xa)
+    y.backward(gy)
+    xb = x0.clone().requires_grad_(True)
+    yo = R.gpt2_block(xb, sd, "blocks.0", cfg)
+    yo.backward(gy)
+    assert rel_err(y.float(), yo.float()) < BF16_TOL
+    assert rel_err(xa.grad.float(), xb.grad.float()) < BF16_TOL
+    n = 0
+    for k, p in blk.named_parameters():
+        ref = sd["blocks.0." + k].grad
+        assert p.grad is not None and ref is not None, k
+        assert close(p.grad.float(), ref.float(), 5e-2, atol=2e-4), (k, rel_err(p.grad.float(), ref.float()))
+        n += 1
+    assert n == 13       # 4 attention weights + out_proj bias, 2 MLP weights + biases, 2 x (LayerNorm weight, bias)
+
+
+def test_attention_hd128_t4096_against_oracle():
+    """BASELINE configs[4]'s attention shape (Llama-3-8B: 32 heads / 8 kv groups of width 128, T 4096, B 1),
+    forward and backward against the oracle's materialised softmax(QK^T)V."""
+    from building_llm_from_scratch_b200 import kernels as K
+    from oracle import reference_ops as R
+    B, T, h, hkv, hd = 1, 4096, 32, 8, 128
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    qkv = (torch.randn(B * T, (h + 2 * hkv) * hd, generator=gen, device="cuda") * 0.5).to(torch.bfloat16)
+    q, k, v = qkv[:, :h * hd], qkv[:, h * hd:(h + hkv) * hd], qkv[:, (h + hkv) * hd:]
+    do = (torch.randn(B * T, h * hd, generator=gen, device="cuda") * 0.1).to(torch.bfloat16)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
+    dq, dk, dv = K.attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd)
+    qr, kr, vr = (t.float().clone().requires_grad_(True) for t in (q, k, v))
+    qh = qr.view(B, T, h, hd).transpose(1, 2)
+    kh = kr.view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    vh = vr.view(B, T, hkv, hd).transpose(1, 2).repeat_interleave(h // hkv, dim=1)
+    ref = R.causal_attention(qh, kh, vh).transpose(1, 2).reshape(B * T, h * hd)
+    ref.backward(do.float())
+    assert rel_err(o.float(), ref) < BF16_TOL
+    assert rel_err(dq.float(), qr.grad) < BF16_TOL
+    assert rel_err(dk.float(), kr.grad) < BF16_TOL
+    assert rel_err(dv.float(), vr.grad) < BF16_TOL
