@@ -342,15 +342,8 @@ def data_parallel_selfcheck(step, dev_batches, n_valid, world):
     for i in range(2):
         step.run(*dev_batches[i % len(dev_batches)], n_valid=n_valid[i % len(dev_batches)])
     torch.cuda.synchronize()
-    sums = []
-    for g in step.opt._groups.values():
-        bits = g["p"].view(torch.int16).to(torch.int64)
-        w = torch.arange(bits.numel(), device=bits.device, dtype=torch.int64) % 65521 + 1
-        sums += [bits.sum(), (bits * w).sum()]
-    mine = torch.stack(sums)
-    every = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(every, mine)
-    identical = all(bool(torch.equal(e, every[0])) for e in every)
+    from building_llm_from_scratch_b200.ddp import ranks_identical
+    identical = ranks_identical([g["p"] for g in step.opt._groups.values()])
     # gradient mean: one eager forward/backward without the exchange, then the exchange on its own
     step.capacity = 0
     step._fwd_bwd(False)

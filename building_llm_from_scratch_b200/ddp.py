@@ -178,3 +178,26 @@ class B200DDP(nn.Module):
                 w[1].div_(ws)
             else:
                 w.wait()
+
+
+def flat_checksum(tensors, chunk: int = 1 << 26) -> torch.Tensor:
+    """Two position-sensitive 64-bit checksums over the raw bits of bf16 / fp32 tensors (device tensor [2], no host
+    sync), computed in chunks so that a multi-GB flat buffer needs no multi-GB temporary."""
+    acc = None
+    for t in tensors:
+        bits = t.reshape(-1).view(torch.int16 if t.element_size() == 2 else torch.int32)
+        for s0 in range(0, bits.numel(), chunk):
+            b = bits[s0:s0 + chunk].to(torch.int64)
+            w = (torch.arange(s0, s0 + b.numel(), device=b.device, dtype=torch.int64) % 65521) + 1
+            part = torch.stack([b.sum(), (b * w).sum()])
+            acc = part if acc is None else acc + part
+    return acc
+
+
+def ranks_identical(tensors, group=None) -> bool:
+    """True when every rank of the group holds bit-identical copies of `tensors` (checksums all-gathered)."""
+    mine = flat_checksum(tensors)
+    world = dist.get_world_size(group)
+    every = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine, group=group)
+    return all(bool(torch.equal(e, every[0])) for e in every)

@@ -101,25 +101,24 @@ class TrainStep:
     def capture(self, warmup: int = 3):
         """Warm up eagerly on a side stream (lazy initialisation, allocator), then capture."""
         self._refresh_hyper(peek=True)
-        # warm-up steps must not move the weights or the optimizer state: snapshot and restore
-        saved = [(g["p"].clone(), g["m"].clone(), g["v"].clone()) for g in self.opt._groups.values()]
+        # Warm-up steps must not move the weights or the optimizer state. They run the real kernels with neutral
+        # hyper-parameters in the device buffer the AdamW kernel reads (lr 0, betas 1, weight decay 0: p, m and v
+        # are rewritten with their own values) — no snapshot of the parameters and moments is needed, which for a
+        # fully trained 8 B model would be 48 GB.
         saved_step = self.opt._step
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         from . import _lib
         with torch.cuda.stream(s):
+            self.opt.freeze_updates(True)
             for _ in range(warmup):
                 n0 = _lib.launch_count()
                 self._eager_step()
                 self.launches_per_step = _lib.launch_count() - n0   # b200llm kernels in one step
+            self.opt.freeze_updates(False)
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
-        for g, (p0, m0, v0) in zip(self.opt._groups.values(), saved):
-            g["p"].copy_(p0)
-            g["m"].copy_(m0)
-            g["v"].copy_(v0)
         self.opt._step = saved_step
-        self._saved_step = saved_step
         if not self.use_graph:
             return
         self.graphs = self._capture_graphs()

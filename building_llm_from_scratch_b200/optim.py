@@ -82,6 +82,7 @@ class B200AdamW(torch.optim.Optimizer):
         self._partial = torch.zeros(2 * len(self._groups), device=dev, dtype=torch.float32)
         self.max_norm = None  # set by Trainer (train.py:115-120 uses 1.0)
         self.graph_safe = False
+        self._frozen = False
 
     def _check_groups(self):
         """One flat buffer per dtype is updated by one kernel launch with one set of hyper-parameters (the
@@ -161,9 +162,21 @@ class B200AdamW(torch.optim.Optimizer):
         left alone (TrainStep refreshes it before every replay)."""
         if not self.graph_safe:
             return None
-        if not torch.cuda.is_current_stream_capturing():
+        if not torch.cuda.is_current_stream_capturing() and not self._frozen:
             self.set_hyper(lr, max(self._step, 1))
         return self._hyper_dev
+
+    def freeze_updates(self, on: bool):
+        """While on, graph_safe steps run the real kernels with neutral hyper-parameters (lr 0, beta1 = beta2 = 1,
+        weight decay 0, no bias correction): parameters and moments are rewritten with their own values. Used for
+        the warm-up steps before a CUDA-graph capture."""
+        if on and not self.graph_safe:
+            raise RuntimeError("freeze_updates needs graph_safe (hyper-parameters read from device memory)")
+        self._frozen = bool(on)
+        if on:
+            eps = self.param_groups[0]["eps"]
+            host = torch.tensor([0.0, 1.0, 1.0, eps, 0.0, 0.0, 1.0], dtype=torch.float32)
+            self._hyper_dev.copy_(host)
 
     def _zero_step(self):
         """ZeRO-1 update (see the module docstring); every collective is on the current stream's
