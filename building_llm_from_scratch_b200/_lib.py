@@ -80,6 +80,7 @@ SIGNATURES = {
     "b200_adam_hyper": (I, [P, F, F, F, F, F, I64]),
     "b200_adamw_bf16": (I, [P, P, I, P, P, I64, F, F, F, F, F, I64, P, P, P]),
     "b200_adamw_f32": (I, [P, P, P, P, I64, F, F, F, F, F, I64, P, P, P]),
+    "b200_adamw_master_f32": (I, [P, P, P, P, P, I64, F, F, F, F, F, I64, P, P, P]),
     "b200_cast_f32_to_bf16": (I, [P, P, I64, P]),
     "b200_cast_bf16_to_f32": (I, [P, P, I64, P]),
     "b200_transpose_bf16": (I, [P, I64, P, I64, I64, I64, F, P]),

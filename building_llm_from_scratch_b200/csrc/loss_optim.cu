@@ -242,6 +242,40 @@ adamw_f32_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
   }
 }
 
+// fp32 master weights (the "bf16_hybrid" policy of datautils/mixed_precision.py:24-28: parameters and optimizer
+// state in fp32, compute copy in bf16): one pass updates the master and rewrites the bf16 copy the GEMMs read.
+// 28 B/param of fp32 state traffic + 2 B/param for the copy.
+__global__ void __launch_bounds__(256)
+adamw_master_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                    float* __restrict__ v, bf16* __restrict__ p_lo, long long n, AdamConsts c0,
+                    const float* __restrict__ dev_hyper, const float* __restrict__ grad_scale) {
+  const AdamConsts c = load_consts(c0, dev_hyper);
+  const float gs = grad_scale ? grad_scale[0] : 1.f;
+  const long long nv = n >> 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 fp = *reinterpret_cast<const float4*>(p + i * 4);
+    const uint4 ug = ld_nc_v4(g + i * 4);
+    float4 fm = *reinterpret_cast<const float4*>(m + i * 4);
+    float4 fv = *reinterpret_cast<const float4*>(v + i * 4);
+    adam_update(fp.x, __uint_as_float(ug.x) * gs, fm.x, fv.x, c);
+    adam_update(fp.y, __uint_as_float(ug.y) * gs, fm.y, fv.y, c);
+    adam_update(fp.z, __uint_as_float(ug.z) * gs, fm.z, fv.z, c);
+    adam_update(fp.w, __uint_as_float(ug.w) * gs, fm.w, fv.w, c);
+    *reinterpret_cast<float4*>(p + i * 4) = fp;
+    *reinterpret_cast<float4*>(m + i * 4) = fm;
+    *reinterpret_cast<float4*>(v + i * 4) = fv;
+    *reinterpret_cast<uint2*>(p_lo + i * 4) = make_uint2(f2_to_bf2(fp.x, fp.y), f2_to_bf2(fp.z, fp.w));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long k = nv * 4; k < n; ++k) {
+      float fp = p[k], fm = m[k], fv = v[k];
+      adam_update(fp, g[k] * gs, fm, fv, c);
+      p[k] = fp; m[k] = fm; v[k] = fv;
+      p_lo[k] = __float2bfloat16_rn(fp);
+    }
+}
+
 AdamConsts make_consts(float lr, float b1, float b2, float eps, float wd, long long step) {
   AdamConsts c;
   c.lr = lr; c.b1 = b1; c.b2 = b2; c.eps = eps; c.wd = wd;
@@ -351,6 +385,19 @@ extern "C" int b200_adamw_f32(float* p, const float* g, float* m, float* v, int6
   B200_CHECK_ARG(p && g && m && v && n > 0 && (step >= 1 || dev_hyper), "adamw: null pointer, empty, or step < 1");
   adamw_f32_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(
       p, g, m, v, n, make_consts(lr, beta1, beta2, eps, weight_decay, step >= 1 ? step : 1), dev_hyper, grad_scale);
+  B200_CHECK_LAUNCH();
+  b200_count_launch();
+  return 0;
+}
+
+extern "C" int b200_adamw_master_f32(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
+                                     float lr, float beta1, float beta2, float eps, float weight_decay,
+                                     int64_t step, const float* dev_hyper, const float* grad_scale, void* stream) {
+  B200_CHECK_ARG(p && g && m && v && p_bf16 && n > 0 && (step >= 1 || dev_hyper), "adamw_master: null pointer, empty, or step < 1");
+  B200_CHECK_ARG(b200_aligned16(p) && b200_aligned16(g) && b200_aligned16(m) && b200_aligned16(v) && (((uintptr_t)p_bf16) & 7u) == 0,
+                 "adamw_master: fp32 buffers must be 16-B aligned, the bf16 copy 8-B aligned");
+  adamw_master_kernel<<<ew_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+      p, g, m, v, (bf16*)p_bf16, n, make_consts(lr, beta1, beta2, eps, weight_decay, step >= 1 ? step : 1), dev_hyper, grad_scale);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;

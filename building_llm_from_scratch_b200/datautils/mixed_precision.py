@@ -28,3 +28,12 @@ def cast_to_policy(t: torch.Tensor, policy: MixedPrecision, kind: str = "param")
     if want is None or t.dtype == want:
         return t
     return K.cast(t, want)
+
+
+def optimizer_kwargs(policy: MixedPrecision) -> dict:
+    """What a policy means for optim.B200AdamW on this path (the FSDP consumer of these objects is broken upstream,
+    SURVEY.md R6): parameters kept in fp32 while compute / reduction run in bf16 (bf16_hybrid, :24-28) = fp32 master
+    weights and fp32 moments behind the bf16 compute copy; every other policy keeps optimizer state in the parameter
+    dtype, as the reference's plain AdamW does."""
+    hybrid = policy.param_dtype == torch.float32 and policy.reduce_dtype == torch.bfloat16
+    return {"master_weights": bool(hybrid)}

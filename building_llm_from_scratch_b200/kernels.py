@@ -508,6 +508,17 @@ def adamw_(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=
     _lib.check(rc, "adamw")
 
 
+def adamw_master_(p32, g32, m32, v32, p_bf16, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.1,
+                  grad_scale=None, dev_hyper=None):
+    """AdamW on fp32 master weights (fp32 gradients and moments) that also rewrites the bf16 compute copy."""
+    _need_cuda(p32, g32, m32, v32, p_bf16, grad_scale, dev_hyper)
+    assert p32.dtype == g32.dtype == m32.dtype == v32.dtype == torch.float32 and p_bf16.dtype == BF16
+    assert p_bf16.numel() == p32.numel()
+    _lib.check(_lib.load().b200_adamw_master_f32(_p(p32), _p(g32), _p(m32), _p(v32), _p(p_bf16), p32.numel(), lr, beta1,
+                                                 beta2, eps, weight_decay, int(step), _p(dev_hyper), _p(grad_scale),
+                                                 _stream()), "adamw_master")
+
+
 def cast(x, dtype):
     _need_cuda(x)
     lib = _lib.load()

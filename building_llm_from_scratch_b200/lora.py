@@ -60,6 +60,17 @@ def replace_linear_with_lora(model: nn.Module, rank: int, alpha: float, dtype=to
             replace_linear_with_lora(module, rank, alpha, dtype)
 
 
+def activate_lora(model: nn.Module, rank: int, alpha: float, dtype=torch.float32) -> nn.Module:
+    """build_components.py:117-135 (`activate_lora(args, model, config)` there): freeze every parameter, then wrap
+    every nn.Linear; the LoRA A / B tensors are created on the device of the linear they wrap."""
+    for p in model.parameters():
+        p.requires_grad = False
+    dev = next(model.parameters()).device
+    with torch.device(dev):
+        replace_linear_with_lora(model, rank=rank, alpha=alpha, dtype=dtype)
+    return model
+
+
 def head_operands(head: nn.Module):
     """(weight, A, B, scaling) of a plain or LoRA-wrapped vocab head."""
     if isinstance(head, LinearWithLoRA):

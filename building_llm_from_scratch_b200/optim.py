@@ -28,13 +28,18 @@ def _align(n, a=64):
 
 class B200AdamW(torch.optim.Optimizer):
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, zero=False,
-                 process_group=None):
+                 process_group=None, master_weights=False):
         params = [p for p in params]
         import torch.distributed as dist
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if (zero and dist.is_initialized()) else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         self.zero = bool(zero) and self.world > 1
+        # master_weights: the bf16_hybrid policy of datautils/mixed_precision.py:24-28 — bf16 parameters keep an fp32
+        # master copy and fp32 moments; every step updates the master and rewrites the bf16 copy the GEMMs read
+        self.master_weights = bool(master_weights)
+        if self.master_weights and self.zero:
+            raise ValueError("B200AdamW: master_weights together with zero=True is not supported")
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
         self._check_groups()
@@ -69,6 +74,9 @@ class B200AdamW(torch.optim.Optimizer):
                                            p_shard=flat_p[lo:lo + shard], g_shard=torch.zeros(shard, device=dev),
                                            m=torch.zeros(shard, device=dev, dtype=dtype),
                                            v=torch.zeros(shard, device=dev, dtype=dtype))
+            elif self.master_weights and dtype == torch.bfloat16:
+                self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g, master=flat_p.float(),
+                                           m=torch.zeros(total, device=dev), v=torch.zeros(total, device=dev))
             else:
                 self._groups[dtype] = dict(params=ps, offsets=offs, p=flat_p, g=flat_g, m=torch.zeros_like(flat_p),
                                            v=torch.zeros_like(flat_p))
@@ -152,8 +160,12 @@ class B200AdamW(torch.optim.Optimizer):
         lr, (b1, b2), eps, wd = pg["lr"], pg["betas"], pg["eps"], pg["weight_decay"]
         hyper = self._graph_hyper(lr)
         for g in self._groups.values():
-            K.adamw_(g["p"], g["g"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
-                     dev_hyper=hyper)
+            if "master" in g:
+                K.adamw_master_(g["master"], g["g"], g["m"], g["v"], g["p"], self._step, lr, b1, b2, eps, wd,
+                                grad_scale=scale, dev_hyper=hyper)
+            else:
+                K.adamw_(g["p"], g["g"], g["m"], g["v"], self._step, lr, b1, b2, eps, wd, grad_scale=scale,
+                         dev_hyper=hyper)
 
     def _graph_hyper(self, lr):
         """graph_safe: the kernels read (lr, bias corrections) from device memory so that a captured step can be
@@ -222,6 +234,8 @@ class B200AdamW(torch.optim.Optimizer):
                 m, v = fm, fv
             moments[str(dt)] = {"m": m.detach().cpu(), "v": v.detach().cpu(), "numel": g["p"].numel(),
                                 "param_numel": sum(p.numel() for p in g["params"])}
+            if "master" in g:
+                moments[str(dt)]["master"] = g["master"].detach().cpu()
         return {"b200_adamw": 2, "step": self._step, "layout": "full", "zero": self.zero, "world": self.world,
                 "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups],
                 "moments": moments}
@@ -250,6 +264,12 @@ class B200AdamW(torch.optim.Optimizer):
                     shard = total // self.world
                     full = full[self.rank * shard:(self.rank + 1) * shard]
                 g[key].copy_(full)
+            if "master" in g:
+                if "master" in src:
+                    n = min(total, src["master"].numel())
+                    g["master"][:n].copy_(src["master"][:n])
+                else:                    # checkpoint written without master weights: start them from the bf16 copy
+                    g["master"].copy_(g["p"].float())
         self._step = int(state["step"])
         for pg, saved in zip(self.param_groups, state["param_groups"]):
             pg.update(saved)

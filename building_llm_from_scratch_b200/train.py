@@ -2,7 +2,9 @@
 attributes, LR schedule (train.py:100-107) and step order (zero_grad, lr, forward + CE, backward,
 clip 1.0, optimizer step; train.py:94-123). Evaluation / sampling / checkpoint orchestration is
 kept behaviour-compatible (calc_loss_loader / evaluate_model / save_checkpoint below, generate.py) but
-not separately accelerated beyond running on the same kernels.
+not separately accelerated beyond running on the same kernels; train_epoch /
+train_model / finetune_model / generate_and_print_sample follow train.py:128-229 so the reference's main.py can
+drive this class unchanged.
 """
 from __future__ import annotations
 
@@ -101,6 +103,9 @@ class Trainer:
 
     # train.py:94-126 (exceptions propagate instead of being logged and swallowed)
     def train_batch(self, input_batch, target_batch):
+        if not hasattr(self, "peak_lr"):
+            raise RuntimeError("Trainer.train_batch needs the LR schedule: call set_schedule(total_training_steps) — "
+                               "train_model / finetune_model do it, as train.py:154-156 does")
         self.optimizer.zero_grad()
         self.global_step += 1
         lr = self.lr_for_step(self.global_step)
@@ -125,6 +130,78 @@ class Trainer:
         self.tokens_seen += input_batch.numel()
         self.last_loss = loss.detach()
         return self.last_loss
+
+    # ---- orchestration around the hot loop (train.py:128-229): same cadence and return values as the reference;
+    # thin Python over train_batch / evaluate_model / generate, none of it on the timed path -------------------
+    ANTONYM_PROMPT = ("Below is an instruction that describes a task. Write a response that appropriately completes the "
+                      "request.\n\n### Instruction:\nWhat is an antonym of 'complicated'?")
+
+    def train_epoch(self, epoch_no, train_loader, val_loader, start_context="Every effort moves you"):
+        """train.py:128-151: one pass over train_loader; every eval_freq / print_sample_iter / save_ckpt_freq steps it
+        evaluates, samples and checkpoints. Errors propagate (the reference logs and swallows them)."""
+        self.model.train()
+        for input_batch, target_batch in train_loader:
+            self.train_batch(input_batch, target_batch)
+            if self.global_step % self.eval_freq == 0:
+                train_loss, val_loss = self.evaluate_model(train_loader, val_loader, self.eval_iter)
+                self.train_losses.append(train_loss)
+                self.val_losses.append(val_loss)
+                self.track_tokens_seen.append(self.tokens_seen)
+                if self.rank == 0:
+                    print(f"Epoch {epoch_no + 1} | Step {self.global_step} | Train Loss: {train_loss:.3f} | "
+                          f"Val Loss: {val_loss:.3f}")
+            if self.global_step % self.print_sample_iter == 0:
+                self.generate_and_print_sample(start_context)
+            if self.global_step % self.save_ckpt_freq == 0:
+                self.save_checkpoint(f"model_pg_{self.global_step}.pth")
+
+    def _run_epochs(self, n_epochs, read, start_context):
+        # train.py:154-156 — the schedule spans every file of every epoch
+        self.set_schedule(self.loaderObj.get_total_steps_epoch(self.data_files) * n_epochs)
+        try:
+            for epoch in range(n_epochs):
+                for file_path in self.data_files:
+                    train_loader, val_loader = self.loaderObj.create_dataloaders(read(file_path), num_workers=2)
+                    if hasattr(train_loader.sampler, "set_epoch"):
+                        train_loader.sampler.set_epoch(epoch)
+                    if start_context is None:
+                        self.train_epoch(epoch, train_loader, val_loader)
+                    else:
+                        self.train_epoch(epoch, train_loader, val_loader, start_context=start_context)
+        except KeyboardInterrupt:
+            self.save_checkpoint(f"model_pg_{self.global_step}_interrupted.pth")
+        return self.train_losses, self.val_losses, self.track_tokens_seen, self.track_lrs
+
+    def train_model(self, n_epochs):
+        """train.py:153-180: pre-training over text files (each gets the end-of-text marker appended)."""
+        def read(path):
+            with open(path, "r", encoding="utf-8") as f:
+                return f.read() + " " + self.config["eos_text"] + " "
+        return self._run_epochs(n_epochs, read, None)
+
+    def finetune_model(self, n_epochs):
+        """train.py:182-211: instruction fine-tuning over JSON files."""
+        def read(path):
+            import json
+            with open(path, "r", encoding="utf-8") as f:
+                return json.load(f)
+        return self._run_epochs(n_epochs, read, self.ANTONYM_PROMPT)
+
+    def generate_and_print_sample(self, start_context, temperature=1.0, top_k=5, memory_check=True, max_new_tokens=200):
+        """train.py:213-229: sample max_new_tokens from the model (KV-cached here) and log the text on rank 0."""
+        from .generate import generate
+        core = self.model.module if isinstance(self.model, B200DDP) else self.model
+        tok = self.loaderObj.tokenizer
+        encoded = torch.tensor(tok.encode(start_context, allowed_special={self.config["eos_text"]})).unsqueeze(0)
+        core.eval()
+        token_ids = generate(model=core, idx=encoded.to(self.device), max_new_tokens=max_new_tokens,
+                             context_size=self.config["context_length"], temperature=temperature, top_k=top_k,
+                             eos_id=self.config["eos_id"])
+        core.train()
+        decoded = tok.decode(token_ids.squeeze(0).tolist())
+        if self.rank == 0 and memory_check:
+            print("Generated Sample: " + decoded.replace(chr(10), " "))
+        return decoded
 
     # train.py:259-268
     def calc_loss_loader(self, data_loader, num_batches=None):

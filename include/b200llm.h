@@ -293,6 +293,12 @@ int b200_adamw_bf16(void* p, const void* g, int g_is_f32, void* m, void* v, int6
 int b200_adamw_f32(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
                    float beta2, float eps, float weight_decay, int64_t step, const float* dev_hyper,
                    const float* grad_scale, void* stream);
+/* fp32 master weights — the bf16_hybrid policy of datautils/mixed_precision.py:24-28 (parameters and
+ * optimizer state fp32, compute / communication copy bf16): the same update as b200_adamw_f32 on the
+ * master p (g, m, v fp32) that also rewrites p_bf16 = bf16(p), the copy the GEMMs read. */
+int b200_adamw_master_f32(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr,
+                          float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                          const float* dev_hyper, const float* grad_scale, void* stream);
 
 /* ---- K9: dtype casts (datautils/mixed_precision.py:10-35) ---------------------------------- */
 int b200_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);

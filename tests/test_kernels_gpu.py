@@ -221,6 +221,49 @@ def test_adamw_and_grad_norm_golden(K, golden, dtype):
         assert rel_err(v.cpu().float(), st["v_p"].float()) < tol
 
 
+def test_adamw_fp32_master_weights_golden(K, golden):
+    """bf16_hybrid (datautils/mixed_precision.py:24-28): fp32 master parameters and moments follow the reference's
+    fp32 AdamW + clip fixture to 1e-4, and the bf16 compute copy is exactly the rounded master."""
+    g = golden("optimizer.pt")[str(torch.float32)]
+    p = g["p0"].cuda().clone()
+    lo = p.to(torch.bfloat16)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step, ((gp, gq), st, nrm, lr) in enumerate(zip(g["grads"], g["states"], g["norms"], g["lrs"]), start=1):
+        coef = torch.clamp(1.0 / (nrm.float().cuda() + 1e-6), max=1.0).reshape(1)
+        K.adamw_master_(p, gp.cuda().float(), m, v, lo, step, lr, grad_scale=coef)
+        assert rel_err(p.cpu(), st["p"].float()) < FP32_TOL
+        assert rel_err(m.cpu(), st["m_p"].float()) < FP32_TOL
+        assert rel_err(v.cpu(), st["v_p"].float()) < FP32_TOL
+        assert torch.equal(lo, p.to(torch.bfloat16))
+
+
+def test_b200adamw_master_weights_mode():
+    """optim.B200AdamW(master_weights=True) on bf16 parameters: tiny updates that vanish in bf16 state still
+    accumulate in the fp32 master, and the parameters the model reads are the rounded master."""
+    from building_llm_from_scratch_b200.datautils.mixed_precision import bf16_hybrid_policy, bf16_policy, optimizer_kwargs
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    assert optimizer_kwargs(bf16_hybrid_policy) == {"master_weights": True}
+    assert optimizer_kwargs(bf16_policy) == {"master_weights": False}
+    torch.manual_seed(0)
+    w = torch.nn.Parameter(torch.ones(4096, device="cuda", dtype=torch.bfloat16))
+    opt = B200AdamW([w], lr=1e-5, weight_decay=0.0, **optimizer_kwargs(bf16_hybrid_policy))
+    grp = opt._groups[torch.bfloat16]
+    assert grp["master"].dtype == grp["m"].dtype == torch.float32
+    for _ in range(50):
+        opt.zero_grad()
+        w.main_grad.fill_(1.0)
+        opt.step()
+    torch.cuda.synchronize()
+    # 50 steps of -lr * sign(g): the master moved by 5e-4 although one step (1e-5) is far below bf16's 2^-8 spacing at 1
+    assert abs(float(grp["master"][0]) - (1.0 - 50e-5)) < 2e-6
+    assert torch.equal(w.data, grp["master"][:4096].to(torch.bfloat16))
+    sd = opt.state_dict()
+    opt2 = B200AdamW([torch.nn.Parameter(torch.ones(4096, device="cuda", dtype=torch.bfloat16))], lr=1e-5,
+                     weight_decay=0.0, master_weights=True)
+    opt2.load_state_dict(sd)
+    assert torch.equal(opt2._groups[torch.bfloat16]["master"], grp["master"])
+
+
 # ------------------------------------------------------------------ attention
 def ref_attention(q, k, v, B, T, h, hkv, hd):
     """oracle causal attention on [B*T, heads*hd] layouts, fp32."""
