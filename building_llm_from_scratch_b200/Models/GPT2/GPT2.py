@@ -60,7 +60,14 @@ class MultiHeadAttention(nn.Module):
         state_dict.pop(prefix + "mask", None)
         super()._load_from_state_dict(state_dict, prefix, *args)
 
-    def forward(self, x, residual=None, cache=None, layer=0):
+    def _project_out(self, ctx, residual, drop):
+        """out_proj(ctx) [+ residual], or residual + dropout(out_proj(ctx)) in one op when drop = (p, seed) is given."""
+        if drop is not None and residual is not None:
+            w, bias, A, B, s = ops.linear_operands(self.out_proj)
+            return ops.linear_dropout_residual(ctx, w, bias, A, B, s, residual, drop[0], drop[1])[0]
+        return self.out_proj(ctx, residual)
+
+    def forward(self, x, residual=None, cache=None, layer=0, drop=None):
         b, num_tokens, _ = x.shape
         if cache is not None:       # generation with a KV cache (kvcache.py); no RoPE, no dropout in eval
             from ...kvcache import attend_with_cache, packed_qkv
@@ -72,12 +79,12 @@ class MultiHeadAttention(nn.Module):
         if qkv is not None:
             ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), None, None, b, num_tokens, self.num_heads,
                                     self.num_heads, self.head_dim, p_drop, ops.new_seed() if p_drop > 0 else 0)[0]
-            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
+            return self._project_out(ctx.view(b, num_tokens, self.d_out), residual, drop)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
         ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim,
                             p_drop, ops.new_seed() if p_drop > 0 else 0)[0]
-        return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
+        return self._project_out(ctx.view(b, num_tokens, self.d_out), residual, drop)
 
 
 class FeedForward(nn.Module):
@@ -88,9 +95,21 @@ class FeedForward(nn.Module):
         self.layers = nn.Sequential(B200Linear(cfg["emb_dim"], 4 * cfg["emb_dim"]), GELU(),
                                     B200Linear(4 * cfg["emb_dim"], cfg["emb_dim"]))
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, drop=None):
+        """layers.2(gelu(layers.0 x)) [+ residual]; with drop = (p, seed): residual + dropout(...). One fused op: GELU
+        in the first GEMM's epilogue, dropout + residual in the second's, GELU backward in the input-gradient GEMM's."""
+        if x.dtype == torch.bfloat16 and x.is_cuda:
+            w1, b1, A1, B1, s1 = ops.linear_operands(self.layers[0])
+            w2, b2, A2, B2, s2 = ops.linear_operands(self.layers[2])
+            if s1 == s2 or A1 is None or A2 is None:
+                p, seed = drop if (drop is not None and residual is not None) else (0.0, 0)
+                y = ops.gelu_mlp(x, w1, b1, A1, B1, w2, b2, A2, B2, s1 if A1 is not None else s2, residual, p, seed)[0]
+                if drop is not None and residual is None:
+                    y = ops.dropout(y, None, drop[0], drop[1])
+                return y
         h = self.layers[1](self.layers[0](x))
-        return self.layers[2](h, residual)
+        y = self.layers[2](h, None if drop is not None else residual)
+        return ops.dropout(y, residual, drop[0], drop[1]) if drop is not None else y
 
 
 class TransformerBlock(nn.Module):
@@ -110,8 +129,10 @@ class TransformerBlock(nn.Module):
             x = self.att(self.norm1(x), residual=x, cache=cache, layer=layer)
             return self.ff(self.norm2(x), residual=x)
         if self.training and self.dropout.p > 0:
-            x = self.dropout(self.att(self.norm1(x)), residual=x)      # x + dropout(att(...)), GPT2.py:85
-            return self.dropout(self.ff(self.norm2(x)), residual=x)    # x + dropout(ff(...)),  GPT2.py:87
+            # x + drop_shortcut(att(...)) and x + drop_shortcut(ff(...)) (GPT2.py:85,87): dropout and the residual add
+            # run in the epilogue of out_proj / the second MLP linear
+            x = self.att(self.norm1(x), residual=x, drop=(self.dropout.p, ops.new_seed()))
+            return self.ff(self.norm2(x), residual=x, drop=(self.dropout.p, ops.new_seed()))
         x = self.att(self.norm1(x), residual=x)
         return self.ff(self.norm2(x), residual=x)
 

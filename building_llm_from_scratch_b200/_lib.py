@@ -46,6 +46,10 @@ SIGNATURES = {
     "b200_gemm_lora_packed_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, I, C.POINTER(C.c_int64), P, I64, I64, I64, P]),
     "b200_gemm_swiglu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_gelu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_gelu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_dropout_residual_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, F,
+                                            C.c_uint64, P, P]),
     "b200_gemm_path_counts": (I, [C.POINTER(C.c_uint64), I]),
     "b200_gemm_set_option": (I, [I, I]),
     "b200_gemm_workspace_bytes": (SZ, []),

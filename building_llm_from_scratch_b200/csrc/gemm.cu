@@ -38,6 +38,8 @@ enum : int {
   EP_TRANS_OUT = 32,
   EP_SWIGLU_BWD = 64,   // pair kernel: the accumulator is dh; write (da | db) of SwiGLU into C, reading (a | b) from R
   EP_SWIGLU_FWD = 128,  // pair kernel: tile = 128 columns of a | the same 128 of b; write (a | b) into C and h into R
+  EP_GELU_BWD = 256,    // pair kernel, staged epilogue: C = acc * gelu'(R) with R the saved pre-activation (GPT2.py:60 under autograd)
+  EP_DROPOUT = 512,     // pair kernel, staged epilogue: C = R + dropout(acc + bias) (GPT2.py:85,87: x + drop_shortcut(...))
 };
 
 struct GemmParams {
@@ -65,6 +67,14 @@ struct GemmParams {
   long long ldr;
   void* C;
   long long ldc;
+  bf16* Z;              // EP_GELU: also store the pre-activation here (bf16) for the backward pass
+  long long ldz;
+  // EP_DROPOUT: keep(i) is the counter-based function of (seed + *seed_dev, i = row * N + col) the stand-alone
+  // dropout kernel uses, so fused and unfused runs draw the same mask
+  uint32_t drop_thr16;
+  float drop_inv_keep;
+  unsigned long long drop_seed;
+  const unsigned long long* drop_seed_dev;
 };
 
 // barrier over the 4 epilogue warps (threads 128..255) of a CTA
@@ -72,6 +82,11 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;"
 
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+// d/dx of the erf GELU: Phi(x) + x * phi(x)
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  return cdf + x * 0.39894228040143267794f * __expf(-0.5f * x * x);
 }
 
 // Epilogue for 32 consecutive accumulator columns of one output row (one thread):
@@ -108,8 +123,26 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
       if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
   }
   if (p.flags & EP_GELU) {
+    if (p.Z != nullptr && !(p.flags & EP_TRANS_OUT)) {
+      // keep the pre-activation for backward (bf16, as the separate linear would have written it) and apply the
+      // GELU to that rounded value, like nn.GELU on the linear's bf16 output
+      if (row_ok) {
+        bf16* Zp = p.Z + row * p.ldz + col0;
+        if (full_cols && (p.ldz & 7) == 0) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          for (int q = 0; q < 4; ++q) st_v4(Zp + q * 8, pack8(&v[q * 8]));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.N) Zp[j] = __float2bfloat16_rn(v[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = gelu_erf(bf16_round(v[j]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    }
   }
   if (p.flags & EP_TRANS_OUT) {
     // C is [N, M]-shaped in memory: element (row, col) goes to C[col * ldc + row]
@@ -596,7 +629,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         const int m_blk = p.n_fastest ? tile / p.n_tiles : tile % p.m_tiles;
         const int n_blk = p.n_fastest ? tile % p.n_tiles : tile / p.m_tiles;
         const int row0 = m_blk * 256 + (int)rank * 128;
-        for (int g = 0; g < P_BN / 64; ++g, ++n) {
+        for (int g = 0; g < P_BN / 64; ++g) {
+          if (n_blk * P_BN + g * 64 >= p.N) break;     // N tail (N % 64 == 0): nothing to stage beyond it
           const int buf = n % IO_BUFS;
           if (n >= IO_BUFS) {
             drain(n - IO_BUFS);
@@ -608,6 +642,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           if (IO_TILES == 2) tma_load_2d(sab + buf * BUF_BYTES + P_IO_TILE, &tmAB, &in_full[buf], p.N + col, row0);
           q_row[buf] = row0;
           q_col[buf] = col;
+          ++n;
         }
       }
       for (int k = (n >= IO_BUFS ? n - IO_BUFS : 0); k < n; ++k) drain(k);
@@ -762,10 +797,14 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           }
         }
       } else if constexpr (MODE == 2) {
-        // residual epilogue through the staging buffers: out = alpha * acc (+ bias) + R, written over R's tile
+        // staged epilogue: out = alpha * acc (+ bias) + R  |  (alpha * acc) * gelu'(R)  |  R + dropout(alpha * acc + bias),
+        // written over R's tile
         const int rloc = ew * 32 + lane;
+        const unsigned long long drop_seed =
+            (p.flags & EP_DROPOUT) ? p.drop_seed + (p.drop_seed_dev != nullptr ? *p.drop_seed_dev : 0ull) : 0ull;
 #pragma unroll 1
         for (int g = 0; g < P_BN / 64; ++g) {
+          if (n_blk * P_BN + g * 64 >= p.N) break;
           const int n = nst++, buf = n % IO_BUFS;
           const int c = 2 * g + chalf;
           const long long col0 = (long long)n_blk * P_BN + c * 32;
@@ -784,7 +823,23 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             for (int j = 0; j < 8; ++j) {
               v[j] = __uint_as_float(r[q * 8 + j]) * p.alpha;
               if (p.flags & EP_BIAS) v[j] += __bfloat162float(p.bias[col0 + q * 8 + j]);
-              v[j] += res[j];
+            }
+            if (p.flags & EP_GELU_BWD) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] *= gelu_erf_grad(res[j]);
+            } else if (p.flags & EP_DROPOUT) {
+              const unsigned long long e0 = (unsigned long long)row * (unsigned long long)p.N + (unsigned long long)(col0 + q * 8);
+#pragma unroll
+              for (int j = 0; j < 8; j += 2) {
+                bool k0, k1;
+                dropout_keep2((e0 + j) >> 1, drop_seed, p.drop_thr16, k0, k1);
+                // the unfused path rounds the linear's output, then the dropped value, to bf16 before the add
+                v[j] = bf16_round(k0 ? bf16_round(v[j]) * p.drop_inv_keep : 0.f) + res[j];
+                v[j + 1] = bf16_round(k1 ? bf16_round(v[j + 1]) * p.drop_inv_keep : 0.f) + res[j + 1];
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] += res[j];
             }
             const uint4 vo = pack8(v);
             sts_v4(rrow + off, vo.x, vo.y, vo.z, vo.w);
@@ -837,8 +892,11 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
   if (work < clusters) clusters = work;
   // residual epilogue through TMA staging (MODE 2): bf16 output, whole 256-column tiles, 16-byte aligned pitches
   static const int res_tma = [] { const char* e = getenv("B200_GEMM_RES_TMA"); return e ? atoi(e) : 1; }();
-  const bool staged_res = res_tma && (p.flags & EP_RESIDUAL) && !(p.flags & (EP_GELU | EP_OUT_F32 | EP_TRANS_OUT | EP_ATOMIC)) &&
-                          p.N % P_BN == 0 && (p.ldr & 7) == 0 && (p.ldc & 7) == 0 && (((uintptr_t)p.R | (uintptr_t)p.C) & 15) == 0;
+  const bool fused_io = (p.flags & (EP_GELU_BWD | EP_DROPOUT)) != 0;     // these exist only in the staged epilogue
+  const bool staged_res = (res_tma || fused_io) && ((p.flags & EP_RESIDUAL) || fused_io) &&
+                          !(p.flags & (EP_GELU | EP_OUT_F32 | EP_TRANS_OUT | EP_ATOMIC)) && p.N % 64 == 0 && (p.ldr & 7) == 0 &&
+                          (p.ldc & 7) == 0 && (((uintptr_t)p.R | (uintptr_t)p.C) & 15) == 0;
+  B200_CHECK_ARG(staged_res || !fused_io, "gemm: the GELU-backward / dropout epilogues need bf16 output, N %% 64 == 0 and 16-B aligned rows");
   if (p.flags & EP_SWIGLU_BWD)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<1>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
@@ -1307,6 +1365,17 @@ int make_operand_map(CUtensorMap* map, const Operand& o, int64_t rows, int64_t K
   return b200_make_tmap_2d_bf16(map, o.ptr, (uint64_t)K, (uint64_t)rows, (uint64_t)o.ld, BK, 64);
 }
 
+// optional epilogue extras of gemm_ex_impl
+struct Extra {
+  void* Z = nullptr;          // EP_GELU: pre-activation output
+  int64_t ldz = 0;
+  bool gelu_bwd = false;      // C = acc * gelu'(R)
+  bool dropout = false;       // C = R + dropout(acc + bias)
+  float drop_p = 0.f;
+  uint64_t drop_seed = 0;
+  const uint64_t* drop_seed_dev = nullptr;
+};
+
 struct SegInfo {
   int nseg;             // output column segments (<= 4)
   int64_t start[4];     // first column of each segment (start[0] = 0), multiples of the 256-column tile
@@ -1319,7 +1388,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
                  const void* R, int64_t ldr, void* C, int64_t ldc, int64_t M, int64_t N,
                  int flags, int out_f32, int accumulate, int trans_out, float alpha,
                  int splitk, void* stream, const SegInfo* seg_info, bool swiglu_bwd = false,
-                 bool swiglu_fwd = false) {
+                 bool swiglu_fwd = false, const Extra* ex = nullptr) {
   B200_CHECK_ARG(M > 0 && N > 0 && K1 > 0 && K2 >= 0, "gemm: bad sizes M=%lld N=%lld K1=%lld K2=%lld",
                  (long long)M, (long long)N, (long long)K1, (long long)K2);
   B200_CHECK_ARG(A1 && B1 && C, "gemm: null operand");
@@ -1358,6 +1427,29 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.ldc = ldc;
   p.flags = (flags & 7) | (out_f32 ? EP_OUT_F32 : 0) | (trans_out ? EP_TRANS_OUT : 0) | (swiglu_bwd ? EP_SWIGLU_BWD : 0) |
             (swiglu_fwd ? EP_SWIGLU_FWD : 0);
+  p.Z = nullptr;
+  p.ldz = 0;
+  p.drop_thr16 = 0;
+  p.drop_inv_keep = 1.f;
+  p.drop_seed = 0;
+  p.drop_seed_dev = nullptr;
+  const bool fused_io = ex && (ex->gelu_bwd || ex->dropout);
+  if (ex) {
+    p.Z = (bf16*)ex->Z;
+    p.ldz = ex->ldz;
+    if (ex->gelu_bwd) p.flags |= EP_GELU_BWD;
+    if (ex->dropout) {
+      B200_CHECK_ARG(ex->drop_p >= 0.f && ex->drop_p < 1.f && N % 2 == 0, "gemm: dropout epilogue needs 0 <= p < 1 and an even N");
+      p.flags |= EP_DROPOUT;
+      const float t = ex->drop_p * 65536.f + 0.5f;
+      p.drop_thr16 = t > 65535.f ? 65535u : (uint32_t)t;
+      p.drop_inv_keep = 1.f / (1.f - ex->drop_p);
+      p.drop_seed = (unsigned long long)ex->drop_seed;
+      p.drop_seed_dev = (const unsigned long long*)ex->drop_seed_dev;
+    }
+    B200_CHECK_ARG(!fused_io || (pair && R && !out_f32 && N % 64 == 0 && ldr % 8 == 0 && ldc % 8 == 0 && b200_aligned16(R) && b200_aligned16(C)),
+                   "gemm: the GELU-backward / dropout epilogues need the CTA-pair kernel (M, N >= 256), bf16 output, N %% 64 == 0 and 16-B aligned rows");
+  }
   B200_CHECK_ARG(!swiglu_fwd || (pair && N % P_BN == 0 && R && !out_f32 && flags == 0),
                  "gemm: the SwiGLU-forward epilogue needs the CTA-pair kernel, N %% %d == 0 and the h buffer in R", P_BN);
 
@@ -1396,7 +1488,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const int tail_opt = gemm_option(OPT_TAIL_SPLIT);
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && tail_opt != 0) {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !fused_io && tail_opt != 0) {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1429,8 +1521,8 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   }
   maps[4] = maps[0];
   maps[5] = maps[0];
-  if (pair && !swiglu_bwd && !swiglu_fwd && (flags & B200_GEMM_RESIDUAL) && !out_f32 && N % P_BN == 0 && ldr % 8 == 0 && ldc % 8 == 0 &&
-      b200_aligned16(R) && b200_aligned16(C)) {
+  if (pair && !swiglu_bwd && !swiglu_fwd && ((flags & B200_GEMM_RESIDUAL) || fused_io) && !(flags & B200_GEMM_GELU) && !out_f32 &&
+      N % 64 == 0 && ldr % 8 == 0 && ldc % 8 == 0 && b200_aligned16(R) && b200_aligned16(C)) {
     // residual tile in, output tile out, both by TMA (MODE 2)
     if ((rc = b200_make_tmap_2d_bf16(&maps[4], R, (uint64_t)M, (uint64_t)N, (uint64_t)ldr, 128, 64))) return rc;
     if ((rc = b200_make_tmap_2d_bf16(&maps[5], C, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 128, 64))) return rc;
@@ -1497,6 +1589,50 @@ extern "C" int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void*
   B200_CHECK_ARG(r2 >= 0 && r2 % 8 == 0 && r2 <= 128, "gemm_swiglu_fwd: 2r=%lld must be a multiple of 8 and <= 128", (long long)r2);
   return gemm_ex_impl(X, ldx, 0, Wil, ldw, 0, K, T2, ldt, 0, Bil, ldb, 1, r2, nullptr, H, ldh, AB, ldab, M, 2 * F, 0, 0, 0,
                       0, 1.0f, 0, stream, nullptr, false, true);
+}
+
+// h = gelu(z), z = x W^T + bias (+ T Bl): the first linear of GPT-2's MLP with nn.GELU (GPT2.py:58-62) in the epilogue;
+// z (bf16) is kept for backward.
+extern "C" int b200_gemm_gelu_fwd_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K, const void* T,
+                                       int64_t ldt, const void* Bl, int64_t ldb, int64_t r, const void* bias, void* Z,
+                                       int64_t ldz, void* H, int64_t ldh, int64_t M, int64_t N, void* stream) {
+  B200_CHECK_ARG(Z && H && ldz >= N && ldh >= N, "gemm_gelu_fwd: null output or pitch < N");
+  Extra ex;
+  ex.Z = Z;
+  ex.ldz = ldz;
+  return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, r > 0 ? T : nullptr, ldt, 0, r > 0 ? Bl : nullptr, ldb, 1, r > 0 ? r : 0, bias,
+                      nullptr, 0, H, ldh, M, N, (bias ? B200_GEMM_BIAS : 0) | B200_GEMM_GELU, 0, 0, 0, 1.0f, 0, stream, nullptr,
+                      false, false, &ex);
+}
+
+// dZ = gelu'(Z) * (dY W + U A^T): the input gradient of GPT-2's second MLP linear with the GELU backward in the epilogue
+// (W [K, N] = layers.2.weight, read as an MN-major operand; U [M, r], A [N, r] the LoRA pair or NULL).
+extern "C" int b200_gemm_gelu_bwd_bf16(const void* dY, int64_t lddy, const void* W, int64_t ldw, int64_t K, const void* U,
+                                       int64_t ldu, const void* A, int64_t lda, int64_t r, const void* Z, int64_t ldz,
+                                       void* dZ, int64_t lddz, int64_t M, int64_t N, void* stream) {
+  B200_CHECK_ARG(Z && dZ && M >= 256 && N >= 256, "gemm_gelu_bwd: needs Z, dZ and M, N >= 256");
+  Extra ex;
+  ex.gelu_bwd = true;
+  return gemm_ex_impl(dY, lddy, 0, W, ldw, 1, K, r > 0 ? U : nullptr, ldu, 0, r > 0 ? A : nullptr, lda, 0, r > 0 ? r : 0, nullptr,
+                      Z, ldz, dZ, lddz, M, N, 0, 0, 0, 0, 1.0f, 0, stream, nullptr, false, false, &ex);
+}
+
+// Y = R + dropout(X W^T + bias (+ T Bl)): the block's residual add with drop_shortcut (GPT2.py:85,87) in the epilogue of
+// out_proj / the second MLP linear. keep(i) is the mask b200_dropout_bf16 draws for element i = row * N + col of the
+// linear's output with the same (seed, seed_dev), so backward is b200_dropout_bf16 on the incoming gradient.
+extern "C" int b200_gemm_dropout_residual_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K,
+                                               const void* T, int64_t ldt, const void* Bl, int64_t ldb, int64_t r,
+                                               const void* bias, const void* R, int64_t ldr, void* Y, int64_t ldy,
+                                               int64_t M, int64_t N, float p, uint64_t seed, const uint64_t* seed_dev,
+                                               void* stream) {
+  B200_CHECK_ARG(R && Y && M >= 256 && N >= 256, "gemm_dropout_residual: needs R, Y and M, N >= 256");
+  Extra ex;
+  ex.dropout = true;
+  ex.drop_p = p;
+  ex.drop_seed = seed;
+  ex.drop_seed_dev = seed_dev;
+  return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, r > 0 ? T : nullptr, ldt, 0, r > 0 ? Bl : nullptr, ldb, 1, r > 0 ? r : 0, bias, R,
+                      ldr, Y, ldy, M, N, bias ? B200_GEMM_BIAS : 0, 0, 0, 0, 1.0f, 0, stream, nullptr, false, false, &ex);
 }
 
 // Several LoRA-wrapped linears of the same input as ONE GEMM: W is the row-concatenation of the base

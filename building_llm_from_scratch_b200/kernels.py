@@ -230,6 +230,88 @@ def gemm_swiglu_fwd(x, w_il, t2, b_il, ab=None, h=None):
     return ab, h
 
 
+def fused_epilogue_ok(M, N):
+    """Shapes the GELU-backward / dropout-residual epilogues (staged TMA epilogue of the CTA-pair kernel) accept."""
+    return M >= 256 and N >= 256 and N % 64 == 0
+
+
+def gemm_gelu_fwd(x, w, bias, t=None, Bl=None):
+    """-> (h, z): z = x w^T + bias (+ t Bl), h = gelu(z) in one launch (z kept for the GELU's backward)."""
+    _need_cuda(x, w, bias, t, Bl)
+    lib = _lib.load()
+    _ensure_gemm_workspace(x.device)
+    x, ldx = _rowmajor2d(x)
+    w, ldw = _rowmajor2d(w)
+    M, Kd = x.shape
+    N = w.shape[0]
+    r = ldt = ldb = 0
+    if t is not None:
+        t, ldt = _rowmajor2d(t)
+        Bl, ldb = _rowmajor2d(Bl)
+        r = t.shape[1]
+    z = torch.empty((M, N), device=x.device, dtype=BF16)
+    h = torch.empty((M, N), device=x.device, dtype=BF16)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_gelu_fwd_bf16(_p(x), ldx, _p(w), ldw, Kd, _p(t), ldt, _p(Bl), ldb, r, _p(bias), _p(z), N, _p(h), N,
+                                           M, N, _stream()), "gemm_gelu_fwd")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (Kd + r), (M, N, Kd, r, 0, 0, 0))
+    return h, z
+
+
+def gemm_gelu_bwd(dy, w, z, u=None, A=None):
+    """dz = gelu'(z) * (dy w + u A^T); w [K, N] (the second MLP linear's weight), z [M, N]."""
+    _need_cuda(dy, w, z, u, A)
+    lib = _lib.load()
+    _ensure_gemm_workspace(dy.device)
+    dy, lddy = _rowmajor2d(dy)
+    w, ldw = _rowmajor2d(w)
+    z, ldz = _rowmajor2d(z)
+    M, Kd = dy.shape
+    N = w.shape[1]
+    assert w.shape[0] == Kd and z.shape == (M, N)
+    r = ldu = lda = 0
+    if u is not None:
+        u, ldu = _rowmajor2d(u)
+        A, lda = _rowmajor2d(A)
+        r = u.shape[1]
+    dz = torch.empty((M, N), device=dy.device, dtype=BF16)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_gelu_bwd_bf16(_p(dy), lddy, _p(w), ldw, Kd, _p(u), ldu, _p(A), lda, r, _p(z), ldz, _p(dz), N, M, N,
+                                           _stream()), "gemm_gelu_bwd")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (Kd + r), (M, N, Kd, r, 0, 1, 0))
+    return dz
+
+
+def gemm_dropout_residual(x, w, bias, residual, p, seed, seed_dev=None, t=None, Bl=None):
+    """y = residual + dropout(x w^T + bias (+ t Bl)) in one launch; mask = dropout()'s for the same (seed, seed_dev)."""
+    _need_cuda(x, w, bias, residual, t, Bl, seed_dev)
+    lib = _lib.load()
+    _ensure_gemm_workspace(x.device)
+    x, ldx = _rowmajor2d(x)
+    w, ldw = _rowmajor2d(w)
+    residual, ldr = _rowmajor2d(residual)
+    M, Kd = x.shape
+    N = w.shape[0]
+    r = ldt = ldb = 0
+    if t is not None:
+        t, ldt = _rowmajor2d(t)
+        Bl, ldb = _rowmajor2d(Bl)
+        r = t.shape[1]
+    y = torch.empty((M, N), device=x.device, dtype=BF16)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_dropout_residual_bf16(_p(x), ldx, _p(w), ldw, Kd, _p(t), ldt, _p(Bl), ldb, r, _p(bias), _p(residual),
+                                                   ldr, _p(y), N, M, N, float(p), int(seed), _p(seed_dev), _stream()),
+               "gemm_dropout_residual")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (Kd + r), (M, N, Kd, r, 0, 0, 0))
+    return y
+
+
 def gemm_grouped(problems):
     """problems: list of dicts(a, b, out, a_mn, b_mn, accumulate, trans_out, alpha) with N <= 64.
     One persistent launch for all of them (chunks of GEMM_GROUP_MAX)."""
@@ -308,13 +390,14 @@ def rmsnorm_fwd(x, w, eps=1e-5, res=None, bf16_steps=True):
     return (y.view_as(x), s.view_as(x)) if res is not None else y.view_as(x)
 
 
-def rmsnorm_bwd(x, w, dy, eps=1e-5, dres=None, need_dw=False):
-    _need_cuda(x, w, dy, dres)
+def rmsnorm_bwd(x, w, dy, eps=1e-5, dres=None, need_dw=False, dw_out=None):
+    """dw_out: an fp32 [d] accumulator (e.g. the weight's main_grad) the kernel adds into instead of a fresh tensor."""
+    _need_cuda(x, w, dy, dres, dw_out)
     lib = _lib.load()
     x2 = x.reshape(-1, x.shape[-1])
     M, d = x2.shape
     dx = torch.empty_like(x2)
-    dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+    dw = dw_out if dw_out is not None else (torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None)
     dy2 = dy.reshape(-1, d)
     if x.dtype == torch.float32:
         _lib.check(lib.b200_rmsnorm_bwd_f32(_p(x2), _p(w), _p(dy2), _p(dx), _p(dw), M, d, eps, _stream()), "rmsnorm_bwd_f32")
@@ -337,14 +420,18 @@ def layernorm_fwd(x, w, b, eps=1e-5):
     return y.view_as(x), mean, rstd
 
 
-def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True):
-    _need_cuda(x, w, dy)
+def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True, dw_out=None, db_out=None):
+    """dw_out / db_out: fp32 [d] accumulators (main_grad of weight / bias) the kernel adds into."""
+    _need_cuda(x, w, dy, dw_out, db_out)
     lib = _lib.load()
     x2 = x.reshape(-1, x.shape[-1])
     M, d = x2.shape
     dx = torch.empty_like(x2)
-    dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
-    db = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+    if dw_out is not None:
+        dw, db = dw_out, db_out
+    else:
+        dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
+        db = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
     _lib.check(lib.b200_layernorm_bwd_bf16(_p(x2), _p(w), _p(dy.reshape(-1, d)), _p(mean), _p(rstd), _p(dx), _p(dw),
                                            _p(db), M, d, _stream()), "layernorm_bwd")
     return dx.view_as(x), dw, db
@@ -418,12 +505,13 @@ def embedding_fwd(idx, tok_w, pos_w=None):
     return out
 
 
-def embedding_bwd(idx, dout, vocab, ctx=None):
-    _need_cuda(idx, dout)
+def embedding_bwd(idx, dout, vocab, ctx=None, dtok_out=None, dpos_out=None):
+    """dtok_out / dpos_out: fp32 accumulators ([vocab, d] / [ctx, d], e.g. main_grad) to scatter-add into."""
+    _need_cuda(idx, dout, dtok_out, dpos_out)
     B, T = idx.shape
     d = dout.shape[-1]
-    dtok = torch.zeros((vocab, d), device=dout.device, dtype=torch.float32)
-    dpos = torch.zeros((ctx, d), device=dout.device, dtype=torch.float32) if ctx else None
+    dtok = dtok_out if dtok_out is not None else torch.zeros((vocab, d), device=dout.device, dtype=torch.float32)
+    dpos = dpos_out if dpos_out is not None else (torch.zeros((ctx, d), device=dout.device, dtype=torch.float32) if ctx else None)
     _lib.check(_lib.load().b200_embedding_bwd_f32acc(_p(idx.contiguous()), _p(dout.contiguous()), _p(dtok), _p(dpos),
                                                      B * T, T, d, vocab, _stream()), "embedding_bwd")
     return dtok, dpos
@@ -551,11 +639,15 @@ def add(a, b):
     return out
 
 
-def colsum(x2d, like=None):
-    """Column sums of a [M, N] bf16 matrix (fp32 accumulate) -> [N] in like.dtype (default fp32)."""
-    _need_cuda(x2d)
+def colsum(x2d, like=None, out=None):
+    """Column sums of a [M, N] bf16 matrix (fp32 accumulate) -> [N] in like.dtype (default fp32); out: an fp32 [N]
+    accumulator to add into (returned as is)."""
+    _need_cuda(x2d, out)
     x2d, ld = _rowmajor2d(x2d)
     M, N = x2d.shape
+    if out is not None:
+        _lib.check(_lib.load().b200_colsum_bf16(_p(x2d), ld, _p(out), M, N, _stream()), "colsum")
+        return out
     out = torch.zeros(N, device=x2d.device, dtype=torch.float32)
     _lib.check(_lib.load().b200_colsum_bf16(_p(x2d), ld, _p(out), M, N, _stream()), "colsum")
     if like is not None and like.dtype == BF16:

@@ -36,6 +36,15 @@ def _pitch_ok(t: Optional[Tensor]) -> Optional[Tensor]:
     return buf[:, :t.shape[1]]
 
 
+def _main_grad(*params):
+    """The fp32 main_grad accumulators of parameters (optim.B200AdamW publishes them) when ALL of them have one, else
+    None: backward kernels that produce small gradients (norm weights, biases, embeddings) then add straight into the
+    flat gradient buffer instead of returning a tensor that autograd stores in .grad and the optimizer folds in later
+    (zero-fill + cast + copy + add per parameter: ~28 tiny launches per GPT-2 block)."""
+    gs = [getattr(p, "main_grad", None) if p is not None else None for p in params]
+    return gs if all(g is not None for g in gs) else None
+
+
 def _flat2d(x: Tensor) -> Tensor:
     x2 = x.reshape(-1, x.shape[-1])
     return x2 if x2.stride(-1) == 1 else x2.contiguous()
@@ -63,7 +72,11 @@ def _rmsnorm_setup(ctx, inputs, output):
 def _rmsnorm_bwd(ctx, dy):
     x, w = ctx.saved_tensors
     need_dw = ctx.needs_input_grad[1]
-    dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps, need_dw=need_dw)
+    mg = _main_grad(w) if need_dw else None
+    dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps, need_dw=need_dw, dw_out=mg[0] if mg else None)
+    if mg:
+        _notify_ready([w])
+        dw = None
     return dx, dw, None
 
 
@@ -90,8 +103,13 @@ class _RMSNormWithResidual(torch.autograd.Function):
         need_dw = ctx.needs_input_grad[1]
         if dy is None:
             return dres, None, None
+        mg = _main_grad(w) if need_dw else None
         dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps,
-                               dres=None if dres is None else dres.contiguous(), need_dw=need_dw)
+                               dres=None if dres is None else dres.contiguous(), need_dw=need_dw,
+                               dw_out=mg[0] if mg else None)
+        if mg:
+            _notify_ready([w])
+            dw = None
         return dx, dw, None
 
 
@@ -122,6 +140,7 @@ def _layernorm_setup(ctx, inputs, output):
     x, w, b, eps = inputs
     _, mean, rstd = output
     ctx.save_for_backward(x, w, mean, rstd)
+    ctx.bias_ref = b
 
 
 def _layernorm_bwd(ctx, dy, _dm, _dr):
@@ -129,7 +148,12 @@ def _layernorm_bwd(ctx, dy, _dm, _dr):
         return None, None, None, None
     x, w, mean, rstd = ctx.saved_tensors
     need_dw = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
-    dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_dw)
+    mg = _main_grad(w, ctx.bias_ref) if (ctx.needs_input_grad[1] and ctx.needs_input_grad[2]) else None
+    dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_dw,
+                                 dw_out=mg[0] if mg else None, db_out=mg[1] if mg else None)
+    if mg:
+        _notify_ready([w, ctx.bias_ref])
+        return dx, None, None, None
     if need_dw:
         dw, db = dw.to(w.dtype), db.to(w.dtype)
     return dx, dw, db, None
@@ -271,7 +295,12 @@ def _lora_linear_bwd(ctx, dy, _dt):
     if need[1]:
         dW = _weight_grad(dy2, x2, wref)                              # dY^T x         [out, in]
     if ctx.has_bias and need[2]:
-        dbias = K.colsum(dy2, bref)
+        mg = _main_grad(bref)
+        if mg:
+            K.colsum(dy2, out=mg[0])
+            _notify_ready([bref])
+        else:
+            dbias = K.colsum(dy2, bref)
     dres = dy if (ctx.has_res and need[6]) else None
     return dx, dW, dbias, dA, dB, None, dres
 
@@ -404,10 +433,27 @@ def _derived_weight(cache: dict, weights, build):
     return out
 
 
-def _packed_weight(weights):
-    """cat(weights, dim=0) of frozen weights (cached); None when a weight is trainable."""
-    if any(w.requires_grad for w in weights):
+def _adjacent_rows_view(weights):
+    """The [sum(out_i), in] matrix that the weights ALREADY form in memory, or None. optim.B200AdamW re-points every
+    trainable parameter into one flat buffer in registration order, so W_query / W_key / W_value (and fc1 / fc2) of a
+    block sit back to back: their row-concatenation is a zero-copy view that is always current."""
+    w0 = weights[0]
+    if any(w.dim() != 2 or not w.is_contiguous() or w.shape[1] != w0.shape[1] or w.dtype != w0.dtype for w in weights):
         return None
+    esz = w0.element_size()
+    for a, b in zip(weights[:-1], weights[1:]):
+        if b.data_ptr() != a.data_ptr() + a.numel() * esz or b.untyped_storage().data_ptr() != a.untyped_storage().data_ptr():
+            return None
+    rows = sum(w.shape[0] for w in weights)
+    return torch.empty(0, dtype=w0.dtype, device=w0.device).set_(w0.untyped_storage(), w0.storage_offset(),
+                                                               (rows, w0.shape[1]), (w0.shape[1], 1))
+
+
+def _packed_weight(weights):
+    """Row-concatenation of the weights: a cached copy for frozen weights; for trainable ones the in-place view of
+    the optimizer's flat buffer when they are adjacent there (else None)."""
+    if any(w.requires_grad for w in weights):
+        return _adjacent_rows_view([w.detach() for w in weights])
     return _derived_weight(_wcat_cache, weights, lambda ws: torch.cat(ws, dim=0).contiguous())
 
 
@@ -434,6 +480,9 @@ def lora_linear_packed(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor
             and all(B.shape[1] % 8 == 0 for B in Bs) and os.environ.get("B200_PACKED_FWD", "1") != "0"):
         # one GEMM for all members: the tile's segment picks its t block, B's sit side by side
         K.gemm_lora_packed(x2, w_cat, t_cat, torch.cat(list(Bs), dim=1), r, starts, out=y)
+        return [y.view(*x.shape[:-1], total), t_cat]
+    if w_cat is not None and len(As) == 0:
+        K.gemm_ex(x2, w_cat, out=y)           # plain linears of one input against their concatenation: one GEMM
         return [y.view(*x.shape[:-1], total), t_cat]
     off = 0
     for i, w in enumerate(weights):
@@ -508,6 +557,17 @@ def _llp_bwd(ctx, grads):
     dWs = [None] * n
     dAs = [None] * n if ctx.lora else []
     dBs = [None] * n if ctx.lora else []
+    if not ctx.lora and all(w.requires_grad and getattr(w, "_b200_grad_fresh", False) for w in weights):
+        # full fine-tuning: the members' main_grad accumulators are adjacent in the flat gradient buffer exactly like
+        # the weights, so dW of the whole group is one store-mode GEMM dY_packed^T x
+        mgs = _main_grad(*weights)
+        mg_cat = _adjacent_rows_view(mgs) if mgs else None
+        if mg_cat is not None:
+            K.gemm_ex(dy, x2, a1_mn=True, b1_mn=True, out=mg_cat)
+            for w in weights:
+                w._b200_grad_fresh = False
+            _notify_ready(list(weights))
+            return dx, dWs, dAs, dBs, None, None
     for i in range(n):
         if ctx.lora and need_a and As[i].requires_grad:
             dAs[i] = _weight_grad(x2, u_cat[:, i * r:(i + 1) * r], As[i])
@@ -637,6 +697,169 @@ def linears_packed(x, modules):
 
 def linear(x, weight, bias=None, residual=None):
     return lora_linear(x, weight, bias, None, None, 0.0, residual)[0]
+
+
+# --------------------------------------------------------------------------------------
+# GPT-2 block fusions (Models/GPT2/GPT2.py:58-62, 83-88)
+#   linear_dropout_residual:  residual + dropout(linear(x))          -- `x + drop_shortcut(att(...))`, :85
+#   gelu_mlp:                 residual + dropout(W2 gelu(W1 x + b1) + b2)   -- `x + drop_shortcut(ff(...))`, :87
+# Forward: GELU and dropout + residual run in GEMM epilogues. Backward: the GELU's derivative runs in the epilogue of the
+# second linear's input-gradient GEMM; the dropout mask is re-drawn on the incoming gradient by the stand-alone kernel
+# (that masked gradient is an operand of three GEMMs, so it has to exist).
+# --------------------------------------------------------------------------------------
+def _linear_fwd(x2, weight, bias, A, B, scaling, residual=None, drop=None):
+    """y = [residual +] [dropout](x W^T + bias + s (x A) B) -> (y, t); drop = (p, seed) or None."""
+    t = K.gemm_ex(x2, A, b1_mn=True, alpha=scaling) if A is not None else None
+    Bp = _pitch_ok(B) if A is not None else None
+    if drop is not None and drop[0] > 0:
+        if K.fused_epilogue_ok(x2.shape[0], weight.shape[0]) and residual is not None:
+            y = K.gemm_dropout_residual(x2, weight, bias, residual, drop[0], drop[1], _drop_step(x2, drop[0]), t, Bp)
+        else:
+            y = K.gemm_ex(x2, weight, a2=t, b2=Bp, b2_mn=True, bias=bias)
+            y = K.dropout(y, drop[0], drop[1], residual, seed_dev=_drop_step(x2, drop[0]))
+    else:
+        y = K.gemm_ex(x2, weight, a2=t, b2=Bp, b2_mn=True, bias=bias, residual=residual)
+    return y, t
+
+
+def _linear_bwd(dy2, x2, weight, bias, A, B, t, scaling, need_x, dx_fn=None):
+    """Gradients of y = x W^T + bias + s (x A) B given dy: -> (dx or None, dW, dbias, dA, dB). dx_fn(dy2, weight, u, A)
+    replaces the plain input-gradient GEMM (an epilogue-fused variant)."""
+    dx = dW = dbias = dA = dB = None
+    u = None
+    lora_live = A is not None and (need_x or A.requires_grad)
+    if lora_live:
+        u = K.gemm_ex(dy2, _pitch_ok(B), alpha=scaling)                   # s * dY B^T   [M, r]
+    if need_x:
+        if dx_fn is not None:
+            dx = dx_fn(dy2, weight, u, A if u is not None else None)
+        elif u is not None:
+            dx = K.gemm_ex(dy2, weight, b1_mn=True, a2=u, b2=A)
+        else:
+            dx = K.gemm_ex(dy2, weight, b1_mn=True)
+    if A is not None and A.requires_grad:
+        dA = _weight_grad(x2, u, A)
+    if B is not None and B.requires_grad:
+        dB = _weight_grad(dy2, t, B, trans_out=True)
+    if weight.requires_grad:
+        dW = _weight_grad(dy2, x2, weight)
+    if bias is not None and bias.requires_grad:
+        mg = _main_grad(bias)
+        if mg:
+            K.colsum(dy2, out=mg[0])
+            _notify_ready([bias])
+        else:
+            dbias = K.colsum(dy2, bias)
+    return dx, dW, dbias, dA, dB
+
+
+@torch.library.custom_op("b200llm::linear_dropout_residual", mutates_args=())
+def linear_dropout_residual(x: Tensor, weight: Tensor, bias: Optional[Tensor], A: Optional[Tensor], B: Optional[Tensor],
+                            scaling: float, residual: Tensor, p: float, seed: int) -> Tuple[Tensor, Tensor]:
+    """-> (residual + dropout(x W^T + bias + s (x A) B), t = s x A)."""
+    x2 = _flat2d(x)
+    y, t = _linear_fwd(x2, weight, bias, A, B, scaling, _flat2d(residual), (p, seed))
+    return y.view(*x.shape[:-1], weight.shape[0]), (t if t is not None else x2.new_empty((0,)))
+
+
+@linear_dropout_residual.register_fake
+def _(x, weight, bias, A, B, scaling, residual, p, seed):
+    rows = x.numel() // x.shape[-1]
+    t = x.new_empty((rows, A.shape[1])) if A is not None else x.new_empty((0,))
+    return x.new_empty((*x.shape[:-1], weight.shape[0])), t
+
+
+def _ldr_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    x, weight, bias, A, B, scaling, residual, p, seed = inputs
+    ctx.save_for_backward(x, weight, A, B, output[1])
+    ctx.bias_ref = bias
+    ctx.scaling, ctx.p, ctx.seed = scaling, p, seed
+
+
+def _ldr_bwd(ctx, dy, _dt):
+    if dy is None:
+        return (None,) * 9
+    x, weight, A, B, t = ctx.saved_tensors
+    need = ctx.needs_input_grad
+    dy2 = _flat2d(dy)
+    dym = K.dropout(dy2, ctx.p, ctx.seed, seed_dev=_drop_step(dy2, ctx.p)) if ctx.p > 0 else dy2
+    dx, dW, dbias, dA, dB = _linear_bwd(dym, _flat2d(x), weight, ctx.bias_ref, A, B, t, ctx.scaling, need[0])
+    return (None if dx is None else dx.view(x.shape)), dW, dbias, dA, dB, None, (dy if need[6] else None), None, None
+
+
+linear_dropout_residual.register_autograd(_ldr_bwd, setup_context=_ldr_setup)
+
+
+@torch.library.custom_op("b200llm::gelu_mlp", mutates_args=())
+def gelu_mlp(x: Tensor, w1: Tensor, b1: Optional[Tensor], A1: Optional[Tensor], B1: Optional[Tensor], w2: Tensor,
+             b2: Optional[Tensor], A2: Optional[Tensor], B2: Optional[Tensor], scaling: float, residual: Optional[Tensor],
+             p: float, seed: int) -> List[Tensor]:
+    """[residual + dropout_p](W2 gelu(W1 x + b1) + b2), LoRA pairs optional -> [y, z, h, t1, t2] (z: pre-activation,
+    h = gelu(z), t_i = s (input of linear i) A_i; all but y only saved for backward)."""
+    x2 = _flat2d(x)
+    M = x2.shape[0]
+    t1 = K.gemm_ex(x2, A1, b1_mn=True, alpha=scaling) if A1 is not None else None
+    if M >= 256 and w1.shape[0] >= 256:
+        h, z = K.gemm_gelu_fwd(x2, w1, b1, t1, _pitch_ok(B1) if A1 is not None else None)
+    else:
+        z = K.gemm_ex(x2, w1, a2=t1, b2=_pitch_ok(B1) if A1 is not None else None, b2_mn=True, bias=b1)
+        h = K.gelu_fwd(z)
+    res2 = _flat2d(residual) if residual is not None else None
+    y, t2 = _linear_fwd(h, w2, b2, A2, B2, scaling, res2, (p, seed) if p > 0 else None)
+    e = x2.new_empty((0,))
+    return [y.view(*x.shape[:-1], w2.shape[0]), z, h, t1 if t1 is not None else e, t2 if t2 is not None else e]
+
+
+@gelu_mlp.register_fake
+def _(x, w1, b1, A1, B1, w2, b2, A2, B2, scaling, residual, p, seed):
+    rows = x.numel() // x.shape[-1]
+    e = x.new_empty((0,))
+    return [x.new_empty((*x.shape[:-1], w2.shape[0])), x.new_empty((rows, w1.shape[0])), x.new_empty((rows, w1.shape[0])),
+            x.new_empty((rows, A1.shape[1])) if A1 is not None else e,
+            x.new_empty((rows, A2.shape[1])) if A2 is not None else e]
+
+
+def _gelu_mlp_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    x, w1, b1, A1, B1, w2, b2, A2, B2, scaling, residual, p, seed = inputs
+    ctx.save_for_backward(x, w1, A1, B1, w2, A2, B2, *output[1:])
+    ctx.biases = (b1, b2)
+    ctx.scaling, ctx.p, ctx.seed = scaling, p, seed
+    ctx.has_res = residual is not None
+
+
+def _gelu_mlp_bwd(ctx, grads):
+    dy = grads[0]
+    if dy is None:
+        return (None,) * 13
+    x, w1, A1, B1, w2, A2, B2, z, h, t1, t2 = ctx.saved_tensors
+    b1, b2 = ctx.biases
+    need = ctx.needs_input_grad
+    x2, dy2 = _flat2d(x), _flat2d(dy)
+    dym = K.dropout(dy2, ctx.p, ctx.seed, seed_dev=_drop_step(dy2, ctx.p)) if ctx.p > 0 else dy2
+    M, F = z.shape
+
+    def dz_fn(g, w, u, A):
+        if K.fused_epilogue_ok(M, F):
+            return K.gemm_gelu_bwd(g, w, z, u, A)          # dz = gelu'(z) * (g W2 + u A2^T), one launch
+        dh = K.gemm_ex(g, w, b1_mn=True, a2=u, b2=A) if u is not None else K.gemm_ex(g, w, b1_mn=True)
+        return K.gelu_bwd(z, dh)
+    dz, dW2, db2, dA2, dB2 = _linear_bwd(dym, h, w2, b2, A2, B2, t2, ctx.scaling, True, dx_fn=dz_fn)
+    dx, dW1, db1, dA1, dB1 = _linear_bwd(dz, x2, w1, b1, A1, B1, t1, ctx.scaling, need[0])
+    return ((None if dx is None else dx.view(x.shape)), dW1, db1, dA1, dB1, dW2, db2, dA2, dB2, None,
+            (dy if (ctx.has_res and need[10]) else None), None, None)
+
+
+gelu_mlp.register_autograd(_gelu_mlp_bwd, setup_context=_gelu_mlp_setup)
+
+
+def linear_operands(mod):
+    """(weight, bias, A, B, scaling) of a B200Linear or a LinearWithLoRA."""
+    from .lora import LinearWithLoRA
+    if isinstance(mod, LinearWithLoRA):
+        return mod.linear.weight, mod.linear.bias, mod.lora.A, mod.lora.B, mod.lora.scaling
+    return mod.weight, mod.bias, None, None, 0.0
 
 
 # ======================================================================================
@@ -988,6 +1211,7 @@ def _(idx, tok_w, pos_w):
 def _embedding_setup(ctx, inputs, output):
     idx, tok_w, pos_w = inputs
     ctx.save_for_backward(idx)
+    ctx.weights = (tok_w, pos_w)
     ctx.vocab = tok_w.shape[0]
     ctx.ctx_len = None if pos_w is None else pos_w.shape[0]
     ctx.dtype = tok_w.dtype
@@ -996,6 +1220,14 @@ def _embedding_setup(ctx, inputs, output):
 def _embedding_bwd(ctx, dout):
     (idx,) = ctx.saved_tensors
     if not (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]):
+        return None, None, None
+    tok_w, pos_w = ctx.weights
+    both = ctx.needs_input_grad[1] and (pos_w is None or ctx.needs_input_grad[2])
+    mg = _main_grad(tok_w, *([pos_w] if pos_w is not None else [])) if both else None
+    if mg:      # scatter-add straight into the flat fp32 gradient buffer (no [V, d] zero-fill, cast, copy, add)
+        K.embedding_bwd(idx, dout.contiguous(), ctx.vocab, ctx.ctx_len, dtok_out=mg[0],
+                        dpos_out=mg[1] if pos_w is not None else None)
+        _notify_ready([tok_w] + ([pos_w] if pos_w is not None else []))
         return None, None, None
     dtok, dpos = K.embedding_bwd(idx, dout.contiguous(), ctx.vocab, ctx.ctx_len)
     dtok = K.cast(dtok, ctx.dtype) if ctx.dtype == BF16 else dtok

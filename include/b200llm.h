@@ -102,6 +102,27 @@ int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void* Wil, int64
                               const void* T2, int64_t ldt, const void* Bil, int64_t ldb, int64_t r2,
                               void* AB, int64_t ldab, void* H, int64_t ldh, int64_t M, int64_t F, void* stream);
 
+/* GPT-2 MLP and residual fusions (Models/GPT2/GPT2.py:58-62, 83-88); all need M, N >= 256 (CTA-pair kernel), bf16.
+ * b200_gemm_gelu_fwd_bf16:  Z = X W^T + bias (+ T Bl), H = gelu(Z) (erf form, nn.GELU()), both written by the epilogue
+ *                           (Z is what autograd saves for the GELU's backward).
+ * b200_gemm_gelu_bwd_bf16:  dZ = gelu'(Z) * (dY W + U A^T): the input gradient of the MLP's second linear with the GELU
+ *                           backward in the epilogue (W [K, N] row-major = layers.2.weight; N % 64 == 0).
+ * b200_gemm_dropout_residual_bf16: Y = R + dropout(X W^T + bias (+ T Bl)), the `x + drop_shortcut(...)` of GPT2.py:85,87;
+ *                           the mask of element i = row * N + col is the one b200_dropout_bf16 draws for (seed, seed_dev)
+ *                           (N % 64 == 0).
+ * T [M, r] = s X A and Bl [r, N] are the LoRA pair (lora.py:26) or NULL with r = 0; U [M, r] = s dY Bl^T, A [N, r]. */
+int b200_gemm_gelu_fwd_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K, const void* T,
+                            int64_t ldt, const void* Bl, int64_t ldb, int64_t r, const void* bias, void* Z,
+                            int64_t ldz, void* H, int64_t ldh, int64_t M, int64_t N, void* stream);
+int b200_gemm_gelu_bwd_bf16(const void* dY, int64_t lddy, const void* W, int64_t ldw, int64_t K, const void* U,
+                            int64_t ldu, const void* A, int64_t lda, int64_t r, const void* Z, int64_t ldz,
+                            void* dZ, int64_t lddz, int64_t M, int64_t N, void* stream);
+int b200_gemm_dropout_residual_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K,
+                                    const void* T, int64_t ldt, const void* Bl, int64_t ldb, int64_t r,
+                                    const void* bias, const void* R, int64_t ldr, void* Y, int64_t ldy,
+                                    int64_t M, int64_t N, float p, uint64_t seed, const uint64_t* seed_dev,
+                                    void* stream);
+
 /* Optional scratch for the large-GEMM kernel (one per device, caller-owned, 256-byte aligned,
  * b200_gemm_workspace_bytes() bytes, ZERO-FILLED when registered; pass NULL to unregister). With it,
  * b200_gemm_ex / b200_gemm_nt_bf16 cut the tiles of a last, at most half-filled wave along K so every

@@ -288,3 +288,58 @@ def test_gemm_swiglu_forward_epilogue(K, M, F, K_, r):
     assert rel_err(h.float(), h_ref.float()) < 1e-2
     fa = x.float() @ w1.float().t() + (t1.float() @ b1.float() if r else 0)
     assert rel_err(ab[:, :F].float(), fa) < BF16_TOL
+
+
+# ------------------------------------------------------------------ GPT-2 epilogue fusions
+def _gelu(x):
+    return 0.5 * x * (1.0 + torch.erf(x / 2 ** 0.5))
+
+
+def _gelu_grad(x):
+    return 0.5 * (1.0 + torch.erf(x / 2 ** 0.5)) + x * torch.exp(-0.5 * x * x) / (2 * torch.pi) ** 0.5
+
+
+@pytest.mark.parametrize("M,N,K_,r", [(4096, 6400, 1600, 0), (512, 5120, 1280, 8), (300, 320, 64, 0)])
+def test_gemm_gelu_forward_epilogue(K, M, N, K_, r):
+    """z = x W^T + b (+ t B) and h = gelu(z) from one launch (Models/GPT2/GPT2.py:58-62); h is the GELU of the bf16 z."""
+    x, w, b = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2), rnd(N, seed=3)
+    t, Bl = (rnd(M, r, seed=4), rnd(r, N, scale=0.1, seed=5)) if r else (None, None)
+    h, z = K.gemm_gelu_fwd(x, w, b, t, Bl)
+    ref = x.float() @ w.float().t() + b.float()
+    if r:
+        ref = ref + t.float() @ Bl.float()
+    assert rel_err(z.float(), ref) < BF16_TOL
+    assert rel_err(h.float(), _gelu(z.float())) < 4e-3        # exact up to the final bf16 rounding
+    assert rel_err(h.float(), _gelu(ref)) < BF16_TOL
+
+
+@pytest.mark.parametrize("M,N,K_,r", [(4096, 6400, 1600, 0), (512, 5120, 1280, 8), (384, 1600, 256, 0)])
+def test_gemm_gelu_backward_epilogue(K, M, N, K_, r):
+    """dz = gelu'(z) * (dy W + u A^T) in the epilogue of the input-gradient GEMM; N = 1600 / 6400 have a partly
+    filled last 256-column tile."""
+    dy, w, z = rnd(M, K_, scale=0.1, seed=1), rnd(K_, N, scale=0.05, seed=2), rnd(M, N, scale=1.5, seed=3)
+    u, A = (rnd(M, r, seed=4), rnd(N, r, scale=0.1, seed=5)) if r else (None, None)
+    dz = K.gemm_gelu_bwd(dy, w, z, u, A)
+    dh = dy.float() @ w.float()
+    if r:
+        dh = dh + u.float() @ A.float().t()
+    assert rel_err(dz.float(), dh * _gelu_grad(z.float())) < BF16_TOL
+    assert rel_err(dz.float(), K.gelu_bwd(z, dh.to(torch.bfloat16)).float()) < BF16_TOL
+
+
+@pytest.mark.parametrize("M,N,K_,r", [(4096, 1600, 1600, 0), (4096, 1600, 6400, 0), (512, 1280, 1280, 8)])
+def test_gemm_dropout_residual_epilogue_draws_the_standalone_mask(K, M, N, K_, r):
+    """y = res + dropout(x W^T + b): the fused epilogue and the GEMM followed by the dropout kernel agree bit for bit
+    (same counter-based mask, same bf16 roundings), also with a device-side seed offset; about p of the linear's
+    outputs are dropped."""
+    p, seed = 0.1, 1234567
+    x, w, b, res = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2), rnd(N, seed=3), rnd(M, N, seed=4)
+    t, Bl = (rnd(M, r, seed=5), rnd(r, N, scale=0.1, seed=6)) if r else (None, None)
+    lin = K.gemm_ex(x, w, a2=t, b2=Bl, b2_mn=True, bias=b)
+    for off in (None, torch.tensor([77], device="cuda", dtype=torch.int64)):
+        fused = K.gemm_dropout_residual(x, w, b, res, p, seed, off, t, Bl)
+        plain = K.dropout(lin, p, seed, res, seed_dev=off)
+        assert torch.equal(fused, plain)
+        dropped = (fused.float() == res.float()).float().mean()
+        assert abs(float(dropped) - p) < 0.01
+    assert not torch.equal(fused, K.gemm_dropout_residual(x, w, b, res, p, seed, None, t, Bl))     # the offset matters

@@ -591,3 +591,79 @@ def test_attention_hd128_t4096_against_oracle():
     assert rel_err(dq.float(), qr.grad) < BF16_TOL
     assert rel_err(dk.float(), kr.grad) < BF16_TOL
     assert rel_err(dv.float(), vr.grad) < BF16_TOL
+
+
+def _mk(shape, gen, scale=1.0, grad=True):
+    t = (torch.randn(*shape, generator=gen, device="cuda") * scale).to(torch.bfloat16)
+    return t.requires_grad_(True) if grad else t
+
+
+@pytest.mark.parametrize("lora", [False, True])
+def test_gpt2_fused_block_ops_match_their_compositions(lora):
+    """ops.linear_dropout_residual and ops.gelu_mlp (GELU / dropout + residual / GELU-backward in GEMM epilogues) against
+    the same computation from separate ops (linear, gelu, dropout with the same seeds) at GPT2-774M's MLP shape:
+    outputs and every gradient."""
+    from building_llm_from_scratch_b200 import ops
+    gen = torch.Generator(device="cuda").manual_seed(17)
+    M, d, F, r, s, p = 1024, 1280, 5120, 8, 2.0, 0.1
+    x0, res0 = _mk((M, d), gen, 0.5), _mk((M, d), gen, 0.5)
+    ws = dict(w1=_mk((F, d), gen, 0.03), b1=_mk((F,), gen, 0.1), w2=_mk((d, F), gen, 0.03), b2=_mk((d,), gen, 0.1))
+    if lora:
+        ws.update(A1=_mk((d, r), gen, 0.1), B1=_mk((r, F), gen, 0.1), A2=_mk((F, r), gen, 0.1), B2=_mk((r, d), gen, 0.1))
+    else:
+        ws.update(A1=None, B1=None, A2=None, B2=None)
+    gy = _mk((M, d), gen, 0.1, grad=False)
+
+    def run(fused):
+        leaves = {k: (v.detach().clone().requires_grad_(True) if v is not None else None) for k, v in ws.items()}
+        x, res = x0.detach().clone().requires_grad_(True), res0.detach().clone().requires_grad_(True)
+        L = leaves
+        if fused:
+            y = ops.gelu_mlp(x, L["w1"], L["b1"], L["A1"], L["B1"], L["w2"], L["b2"], L["A2"], L["B2"], s, res, p, 99)[0]
+            y2 = ops.linear_dropout_residual(y, L["w2"][:, :d].contiguous().detach(), None, None, None, 0.0, res, p, 7)[0]
+        else:
+            z = ops.lora_linear(x, L["w1"], L["b1"], L["A1"], L["B1"], s, None)[0]
+            h = ops.gelu(z)
+            o = ops.lora_linear(h, L["w2"], L["b2"], L["A2"], L["B2"], s, None)[0]
+            y = ops.dropout(o, res, p, 99)
+            o2 = ops.lora_linear(y, L["w2"][:, :d].contiguous().detach(), None, None, None, 0.0, None)[0]
+            y2 = ops.dropout(o2, res, p, 7)
+        y2.backward(gy)
+        grads = {k: v.grad for k, v in L.items() if v is not None}
+        grads.update(x=x.grad, res=res.grad)
+        return y2.detach(), grads
+    yf, gf = run(True)
+    yu, gu = run(False)
+    assert rel_err(yf.float(), yu.float()) < 4e-3
+    for k in gu:
+        assert gf[k] is not None, k
+        assert close(gf[k].float(), gu[k].float(), BF16_TOL, atol=1e-5), (k, rel_err(gf[k].float(), gu[k].float()))
+
+
+def test_gpt2_dropout_masks_change_between_graph_replays(golden):
+    """drop_rate 0.1 under CUDA-graph replay: the site seeds are frozen into the captured kernel arguments, the
+    per-step counter the kernels read from device memory is not — the same batch replayed twice sees two different
+    masks (different losses), and the counter advances once per step."""
+    from building_llm_from_scratch_b200 import ops
+    from building_llm_from_scratch_b200.Models.GPT2.GPT2 import GPTModel
+    from building_llm_from_scratch_b200.engine import TrainStep
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    from building_llm_from_scratch_b200.train import Trainer
+    cfg = dict(vocab_size=512, context_length=128, emb_dim=256, n_heads=4, n_layers=2, drop_rate=0.1, qkv_bias=False)
+    torch.manual_seed(0)
+    model = GPTModel(cfg).cuda().to(torch.bfloat16).train()
+    opt = B200AdamW(model.parameters(), lr=0.0, weight_decay=0.0)          # lr 0: only the masks can change the loss
+    tr = Trainer(model, opt, cfg, [], None, "/tmp", device="cuda")
+    tr.set_schedule(100, peak_lr=0.0)
+    tr.initial_lr = tr.min_lr = 0.0
+    tr.lr_increment = 0.0
+    step = TrainStep(tr, (4, 128), use_graph=True)
+    step.compact_head = False
+    step.capture(warmup=1)
+    x = torch.randint(0, 512, (4, 128), device="cuda")
+    y = torch.roll(x, -1, 1)
+    c0 = int(ops.dropout_step_tensor("cuda"))
+    losses = [float(step.run(x, y).clone()) for _ in range(4)]
+    assert int(ops.dropout_step_tensor("cuda")) == c0 + 4
+    assert len(set(losses)) == 4, losses
+    assert max(losses) - min(losses) < 0.5
