@@ -46,6 +46,8 @@ SIGNATURES = {
     "b200_gemm_lora_packed_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, I, C.POINTER(C.c_int64), P, I64, I64, I64, P]),
     "b200_gemm_swiglu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_swiglu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
+    "b200_gemm_qkv_rope_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, I, C.POINTER(C.c_int64), P, P, I64, I64, I64, P,
+                                    I64, I64, I64, P]),
     "b200_gemm_gelu_fwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_gelu_bwd_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, I64, P, I64, I64, I64, P]),
     "b200_gemm_dropout_residual_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, F,
@@ -99,6 +101,8 @@ SIGNATURES = {
     "b200_window_batch_i64": (I, [P, I64, P, I64, I64, P, P, P]),
     "b200_attention_decode_bf16": (I, [P, I64, P, P, I64, I64, P, I64, I64, I64, I64, I64, I64, F, P]),
     "b200_attention_bwd_workspace_bytes": (SZ, [I64, I64, I64, I64]),
+    "b200_attention_bwd_rope_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,
+                                         I64, I64, I64, I64, I64, I64, F, P, P, P]),
     "b200_attention_bwd_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,
                                     I64, I64, I64, I64, I64, I64, F, F, C.c_uint64, P, P]),
 }

@@ -23,7 +23,7 @@ int b200_attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk
                           const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                           int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
                           int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
-                          cudaStream_t st);
+                          const void* rope_cos, const void* rope_sin, cudaStream_t st);
 
 namespace {
 
@@ -67,6 +67,26 @@ extern "C" size_t b200_attention_bwd_workspace_bytes(int64_t B, int64_t T, int64
   return b200_attention_bwd_tc_workspace(B, T, h);
 }
 
+namespace {
+int attention_bwd_entry(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                        const void* o, int64_t ldo, const void* dout, int64_t lddo, const float* lse, void* workspace,
+                        size_t workspace_bytes, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                        int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd, float scale, float dropout_p,
+                        uint64_t seed, const uint64_t* seed_dev, const void* rope_cos, const void* rope_sin, void* stream) {
+  const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
+  int rc = check_common(q, k, v, B, T, h, hkv, hd, lds, 8);
+  if (rc) return rc;
+  B200_CHECK_ARG(o && dout && lse && workspace && dq && dk && dv, "attention_bwd: null pointer");
+  B200_CHECK_ARG(workspace_bytes >= b200_attention_bwd_workspace_bytes(B, T, h, hd), "attention_bwd: workspace too small");
+  B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
+  B200_CHECK_ARG((rope_cos == nullptr) == (rope_sin == nullptr) && b200_aligned16(rope_cos) && b200_aligned16(rope_sin),
+                 "attention_bwd: the RoPE tables come as a 16-B aligned pair");
+  return b200_attention_bwd_tc(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
+                               lddv, B, T, h, hkv, hd, scale, dropout_p, seed, seed_dev, rope_cos, rope_sin,
+                               (cudaStream_t)stream);
+}
+}  // namespace
+
 extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk,
                                        const void* v, int64_t ldv, const void* o, int64_t ldo,
                                        const void* dout, int64_t lddo, const float* lse,
@@ -74,14 +94,24 @@ extern "C" int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k
                                        int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
                                        int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd,
                                        float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev, void* stream) {
-  const int64_t lds[8] = {ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv};
-  int rc = check_common(q, k, v, B, T, h, hkv, hd, lds, 8);
-  if (rc) return rc;
-  B200_CHECK_ARG(o && dout && lse && workspace && dq && dk && dv, "attention_bwd: null pointer");
-  B200_CHECK_ARG(workspace_bytes >= b200_attention_bwd_workspace_bytes(B, T, h, hd), "attention_bwd: workspace too small");
-  B200_CHECK_ARG(dropout_p >= 0.f && dropout_p < 1.f, "attention: dropout_p=%f must be in [0, 1)", (double)dropout_p);
-  return b200_attention_bwd_tc(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
-                               lddv, B, T, h, hkv, hd, scale, dropout_p, seed, seed_dev, (cudaStream_t)stream);
+  return attention_bwd_entry(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, workspace_bytes, dq, lddq, dk,
+                             lddk, dv, lddv, B, T, h, hkv, hd, scale, dropout_p, seed, seed_dev, nullptr, nullptr, stream);
+}
+
+// Backward for q / k that were rotated (RoPE) BEFORE the attention kernels saw them — by the q|k|v projection's
+// epilogue (b200_gemm_qkv_rope_bf16): dq and dk come out already multiplied by the transposed rotation, i.e. as the
+// gradients of the un-rotated projections, so no separate inverse-RoPE pass runs. cos / sin: [>= T, hd] bf16 tables
+// whose two column halves are equal (precompute_rope_params builds them as cat([angles, angles])).
+extern "C" int b200_attention_bwd_rope_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk,
+                                            const void* v, int64_t ldv, const void* o, int64_t ldo,
+                                            const void* dout, int64_t lddo, const float* lse,
+                                            void* workspace, size_t workspace_bytes, void* dq,
+                                            int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                                            int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd,
+                                            float scale, const void* cos, const void* sin, void* stream) {
+  B200_CHECK_ARG(cos && sin, "attention_bwd_rope: null RoPE tables");
+  return attention_bwd_entry(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, workspace_bytes, dq, lddq, dk,
+                             lddk, dv, lddv, B, T, h, hkv, hd, scale, 0.f, 0, nullptr, cos, sin, stream);
 }
 
 // ======================================================================================

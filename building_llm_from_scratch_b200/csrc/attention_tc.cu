@@ -389,7 +389,28 @@ struct BwdParams {
   long long lddk;
   bf16* dv;
   long long lddv;
+  const bf16* rope_cos;   // non-null: K was rotated before the kernel (RoPE fused into the projection's epilogue), so dK
+  const bf16* rope_sin;   // leaves through the transposed rotation; tables [>= T, HD] bf16 with equal halves
 };
+
+// Gradient of rotate-half RoPE (the transpose of the rotation): for the chunk pair (first half a, second half b) of a
+// head and this row's table entries, dx1 = a cos + b sin, dx2 = b cos - a sin (compute_rope under autograd,
+// Models/Llama/common_components.py:24-35; the two table halves are equal).
+__device__ __forceinline__ void rope_inverse_pair(uint32_t* a, uint32_t* b, const bf16* __restrict__ cosr,
+                                                  const bf16* __restrict__ sinr) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float c[8], s[8];
+    unpack8(ld_v4(cosr + q * 8), c);
+    unpack8(ld_v4(sinr + q * 8), s);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x1 = __uint_as_float(a[q * 8 + j]), x2 = __uint_as_float(b[q * 8 + j]);
+      a[q * 8 + j] = __float_as_uint(x1 * c[j] + x2 * s[j]);
+      b[q * 8 + j] = __float_as_uint(x2 * c[j] - x1 * s[j]);
+    }
+  }
+}
 
 template <int HDIM, bool DROP>
 __global__ void __launch_bounds__(DkvCfg<HDIM>::THREADS, 1)
@@ -615,28 +636,37 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    // epilogue: the groups share the 32-column chunks of dV and dK of their key row round-robin
+    // epilogue: the groups share the work of their key row round-robin. Unit u < HD/64 = the chunk pair
+    // (u, u + HD/64) of dV and of dK (first / second half of the head: what the RoPE gradient combines).
+    constexpr int HC = HD / 64;
 #pragma unroll 1
-    for (int c32 = grp; c32 < HD / 32; c32 += NG) {
-    bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD + c32 * 32;
-    bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD + c32 * 32;
-    uint32_t a[32], c2[32];
-    tmem_ld_32x32(tlane + C_DV + c32 * 32, a);
-    tmem_ld_32x32(tlane + C_DK + c32 * 32, c2);
-    tmem_ld_wait();
-    if (key < p.T) {
+    for (int e = grp; e < 2 * HC; e += NG) {
+      bf16* dkrow = p.dk + (long long)(row_base + key) * p.lddk + (long long)kvh * HD;
+      bf16* dvrow = p.dv + (long long)(row_base + key) * p.lddv + (long long)kvh * HD;
+      const int which = e / HC, u = e % HC;              // which = 0: dV, 1: dK
+      {
+        uint32_t a[32], c2[32];
+        const uint32_t col = which ? C_DK : C_DV;
+        tmem_ld_32x32(tlane + col + u * 32, a);
+        tmem_ld_32x32(tlane + col + (u + HC) * 32, c2);
+        tmem_ld_wait();
+        if (key < p.T) {
+          if (which && p.rope_cos != nullptr)
+            rope_inverse_pair(a, c2, p.rope_cos + (long long)key * HD + u * 32, p.rope_sin + (long long)key * HD + u * 32);
+          bf16* dst = which ? dkrow : dvrow;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float f[8], g[8];
+          for (int c = 0; c < 4; ++c) {
+            float f[8], g[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          f[i] = __uint_as_float(a[c * 8 + i]);
-          g[i] = __uint_as_float(c2[c * 8 + i]);
+            for (int i = 0; i < 8; ++i) {
+              f[i] = __uint_as_float(a[c * 8 + i]);
+              g[i] = __uint_as_float(c2[c * 8 + i]);
+            }
+            st_v4(dst + u * 32 + c * 8, pack8(f));
+            st_v4(dst + (u + HC) * 32 + c * 8, pack8(g));
+          }
         }
-        st_v4(dvrow + c * 8, pack8(f));
-        st_v4(dkrow + c * 8, pack8(g));
       }
-    }
     }
   }
 
@@ -670,6 +700,8 @@ struct DqParams {
   int nq64;
   bf16* dq;
   long long lddq;
+  const bf16* rope_cos;   // see BwdParams
+  const bf16* rope_sin;
 };
 
 template <int HDIM, bool DROP>
@@ -852,18 +884,26 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     mbar_wait(dq_done, 0);
     tc_fence_after();
     bf16* orow = p.dq + (long long)(row_base + t) * p.lddq + (long long)head * HD;
-#pragma unroll
-    for (int h2 = 0; h2 < HD / 32; ++h2) {
-      uint32_t o[32];
-      tmem_ld_32x32(tlane + D_DQ + h2 * 32, o);
+    constexpr int HC = HD / 64;          // chunk u and chunk u + HC: first / second half of the head
+#pragma unroll 1
+    for (int u = 0; u < HC; ++u) {
+      uint32_t o[32], o2[32];
+      tmem_ld_32x32(tlane + D_DQ + u * 32, o);
+      tmem_ld_32x32(tlane + D_DQ + (u + HC) * 32, o2);
       tmem_ld_wait();
       if (t < p.T) {
+        if (p.rope_cos != nullptr)      // Q was rotated in the projection's epilogue: dQ leaves through the transposed rotation
+          rope_inverse_pair(o, o2, p.rope_cos + (long long)t * HD + u * 32, p.rope_sin + (long long)t * HD + u * 32);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          float f[8];
+          float f[8], g[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(o[c * 8 + i]);
-          st_v4(orow + h2 * 32 + c * 8, pack8(f));
+          for (int i = 0; i < 8; ++i) {
+            f[i] = __uint_as_float(o[c * 8 + i]);
+            g[i] = __uint_as_float(o2[c * 8 + i]);
+          }
+          st_v4(orow + u * 32 + c * 8, pack8(f));
+          st_v4(orow + (u + HC) * 32 + c * 8, pack8(g));
         }
       }
     }
@@ -929,7 +969,8 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
                      const void* o, int64_t ldo, const void* dout, int64_t lddo, const float* lse,
                      void* workspace, void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv,
                      int64_t lddv, int64_t B, int64_t T, int64_t h, int64_t hkv, float scale,
-                     float dropout_p, uint64_t seed, const uint64_t* seed_dev, cudaStream_t st) {
+                     float dropout_p, uint64_t seed, const uint64_t* seed_dev, const void* rope_cos, const void* rope_sin,
+                     cudaStream_t st) {
   constexpr int DKV_SMEM = DkvCfg<HD>::SMEM, DKV_THREADS = DkvCfg<HD>::THREADS, DQ_SMEM = DqCfg<HD>::SMEM;
   float* ld2 = (float*)workspace;   // cudaMalloc / caching-allocator memory: at least 256-B aligned
   B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
@@ -969,6 +1010,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.scale = scale; p.scale_log2 = scale * LOG2E;
     p.drop = make_drop(dropout_p, seed, seed_dev);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
+    p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
     const long long grid = (long long)nqt * B * h;
     if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     else attn_bwd_dq_tc_kernel<HD, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
@@ -985,6 +1027,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.drop = make_drop(dropout_p, seed, seed_dev);
     p.ld2 = ld2;
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
+    p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
     const long long grid = (long long)p.nkt * B * hkv;
     if (p.drop.thr16) attn_bwd_dkv_tc_kernel<HD, true><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     else attn_bwd_dkv_tc_kernel<HD, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
@@ -999,12 +1042,13 @@ int b200_attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk
                           int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
                           const float* lse, void* workspace, void* dq, int64_t lddq, void* dk,
                           int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
-                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev, cudaStream_t st) {
+                          int64_t hkv, int64_t hd, float scale, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
+                          const void* rope_cos, const void* rope_sin, cudaStream_t st) {
   if (hd == 64)
     return attention_bwd_tc<64>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
-                                lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
+                                lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, rope_cos, rope_sin, st);
   return attention_bwd_tc<128>(q, ldq, k, ldk, v, ldv, o, ldo, dout, lddo, lse, workspace, dq, lddq, dk, lddk, dv,
-                               lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, st);
+                               lddv, B, T, h, hkv, scale, dropout_p, seed, seed_dev, rope_cos, rope_sin, st);
 }
 
 

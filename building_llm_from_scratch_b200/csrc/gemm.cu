@@ -40,6 +40,7 @@ enum : int {
   EP_SWIGLU_FWD = 128,  // pair kernel: tile = 128 columns of a | the same 128 of b; write (a | b) into C and h into R
   EP_GELU_BWD = 256,    // pair kernel, staged epilogue: C = acc * gelu'(R) with R the saved pre-activation (GPT2.py:60 under autograd)
   EP_DROPOUT = 512,     // pair kernel, staged epilogue: C = R + dropout(acc + bias) (GPT2.py:85,87: x + drop_shortcut(...))
+  EP_ROPE = 1024,       // pair kernel, per-thread epilogue: rotate-half RoPE on the output columns < rope_cols (q | k heads)
 };
 
 struct GemmParams {
@@ -75,6 +76,11 @@ struct GemmParams {
   float drop_inv_keep;
   unsigned long long drop_seed;
   const unsigned long long* drop_seed_dev;
+  // EP_ROPE (compute_rope, Models/Llama/common_components.py:6-35, applied to the q | k heads of a packed q|k|v
+  // projection): row m is position m % rope_T; tables [>= rope_T, rope_hd] bf16 whose two halves are equal
+  const bf16* rope_cos;
+  const bf16* rope_sin;
+  int rope_T, rope_hd, rope_cols;
 };
 
 // barrier over the 4 epilogue warps (threads 128..255) of a CTA
@@ -94,10 +100,32 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
 // Residual values for one 32-column chunk, fetched one chunk ahead of their use so the L2 latency of
 // the residual read does not serialise with the TMEM load / convert / store of every chunk (short-K
 // GEMMs with a residual epilogue were epilogue-bound: 23 % tensor-pipe activity at K = 512).
+// rotate-half RoPE on one (first-half, second-half) pair of 32-column accumulator chunks of a head, with the
+// reference's bf16 roundings (the linear's output, each product and the sum are bf16 there):
+//   o1 = x1 cos - x2 sin,  o2 = x2 cos + x1 sin     (cos / sin: this row's 32 table entries for these columns)
+__device__ __forceinline__ void rope_chunk_pair(uint32_t* r1, uint32_t* r2, const bf16* __restrict__ cosr,
+                                                const bf16* __restrict__ sinr, float alpha) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float c[8], s[8];
+    unpack8(ld_v4(cosr + q * 8), c);
+    unpack8(ld_v4(sinr + q * 8), s);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x1 = bf16_round(__uint_as_float(r1[q * 8 + j]) * alpha);
+      const float x2 = bf16_round(__uint_as_float(r2[q * 8 + j]) * alpha);
+      r1[q * 8 + j] = __float_as_uint(bf16_round(x1 * c[j]) + bf16_round(-x2 * s[j]));
+      r2[q * 8 + j] = __float_as_uint(bf16_round(x2 * c[j]) + bf16_round(x1 * s[j]));
+    }
+  }
+}
+
 struct ResChunk {
   uint4 v[4];
   bool vec;   // v[] holds the 32 residual values (fast path)
 };
+__device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, bool row_ok, long long col0,
+                                            const uint32_t* r, const struct ResChunk& rc);
 __device__ __forceinline__ ResChunk load_residual(const GemmParams& p, long long row, bool row_ok, long long col0) {
   ResChunk rc;
   rc.vec = false;
@@ -111,12 +139,12 @@ __device__ __forceinline__ ResChunk load_residual(const GemmParams& p, long long
 }
 
 __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, bool row_ok,
-                                            long long col0, const uint32_t* r, const ResChunk& rc) {
+                                            long long col0, const uint32_t* r, const ResChunk& rc, const float alpha) {
   if (col0 >= p.N) return;
   const bool full_cols = col0 + 32 <= p.N;
   float v[32];
 #pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
   if (p.flags & EP_BIAS) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
@@ -217,6 +245,11 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
         if (col0 + j < p.N) C[j] = __float2bfloat16_rn(v[j]);
     }
   }
+}
+
+__device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, bool row_ok, long long col0,
+                                            const uint32_t* r, const ResChunk& rc) {
+  store_chunk(p, row, row_ok, col0, r, rc, p.alpha);
 }
 
 template <int BN>
@@ -848,6 +881,36 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           __syncwarp();
           if (lane == 0) mbar_arrive(&out_full[buf]);
         }
+      } else if ((p.flags & EP_ROPE) && (long long)n_blk * P_BN < p.rope_cols) {
+        // q | k tile of a packed q|k|v projection: RoPE in the epilogue (alpha is folded in here, so the stores below
+        // are told alpha = 1). A head is rope_hd / 32 chunks; its halves are hc chunks apart.
+        const int hc = p.rope_hd >> 6;                       // chunks per half head: 1 (hd 64) or 2 (hd 128)
+        const long long t = row_ok ? row % p.rope_T : 0;
+        ResChunk none;
+        none.vec = false;
+#pragma unroll 1
+        for (int c = c0; c < c1; c += 2 * hc) {
+#pragma unroll 1
+          for (int k = 0; k < hc; ++k) {
+            uint32_t r1[32], r2[32];
+            const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * P_BN + (c + k) * 32);
+            tmem_ld_32x32(taddr, r1);
+            tmem_ld_32x32(taddr + hc * 32, r2);
+            tmem_ld_wait();
+            const long long col1 = (long long)n_blk * P_BN + (c + k) * 32;
+            if (col1 < p.rope_cols)
+              rope_chunk_pair(r1, r2, p.rope_cos + t * p.rope_hd + k * 32, p.rope_sin + t * p.rope_hd + k * 32, p.alpha);
+            else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                r1[j] = __float_as_uint(__uint_as_float(r1[j]) * p.alpha);
+                r2[j] = __float_as_uint(__uint_as_float(r2[j]) * p.alpha);
+              }
+            }
+            store_chunk(p, row, row_ok, col1, r1, none, 1.f);
+            store_chunk(p, row, row_ok, col1 + hc * 32, r2, none, 1.f);
+          }
+        }
       } else {
       ResChunk rc = load_residual(p, row, row_ok, (long long)n_blk * P_BN + c0 * 32);
 #pragma unroll 1
@@ -1374,6 +1437,9 @@ struct Extra {
   float drop_p = 0.f;
   uint64_t drop_seed = 0;
   const uint64_t* drop_seed_dev = nullptr;
+  const void* rope_cos = nullptr;   // EP_ROPE on the output columns < rope_cols
+  const void* rope_sin = nullptr;
+  int64_t rope_T = 0, rope_hd = 0, rope_cols = 0;
 };
 
 struct SegInfo {
@@ -1433,6 +1499,20 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
   p.drop_inv_keep = 1.f;
   p.drop_seed = 0;
   p.drop_seed_dev = nullptr;
+  p.rope_cos = p.rope_sin = nullptr;
+  p.rope_T = p.rope_hd = p.rope_cols = 0;
+  if (ex && ex->rope_cos) {
+    B200_CHECK_ARG(pair && ex->rope_sin && (ex->rope_hd == 64 || ex->rope_hd == 128) && ex->rope_T > 0 && ex->rope_cols > 0 &&
+                       ex->rope_cols % ex->rope_hd == 0 && ex->rope_cols <= N && !out_f32 && (flags & 7) == 0 && ldc % 8 == 0,
+                   "gemm: the RoPE epilogue needs the CTA-pair kernel, head_dim 64 or 128, whole heads, bf16 output, no bias / GELU / residual");
+    B200_CHECK_ARG(b200_aligned16(ex->rope_cos) && b200_aligned16(ex->rope_sin), "gemm: RoPE tables must be 16-B aligned");
+    p.flags |= EP_ROPE;
+    p.rope_cos = (const bf16*)ex->rope_cos;
+    p.rope_sin = (const bf16*)ex->rope_sin;
+    p.rope_T = (int)ex->rope_T;
+    p.rope_hd = (int)ex->rope_hd;
+    p.rope_cols = (int)ex->rope_cols;
+  }
   const bool fused_io = ex && (ex->gelu_bwd || ex->dropout);
   if (ex) {
     p.Z = (bf16*)ex->Z;
@@ -1488,7 +1568,7 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const int tail_opt = gemm_option(OPT_TAIL_SPLIT);
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !fused_io && tail_opt != 0) {
+    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !fused_io && !(p.flags & EP_ROPE) && tail_opt != 0) {
       int s = G / L;
       if (s > total_kb / 32) s = total_kb / 32;
       if (s > 4) s = 4;
@@ -1655,6 +1735,40 @@ extern "C" int b200_gemm_lora_packed_bf16(const void* X, int64_t ldx, const void
   B200_CHECK_ARG(M >= 256 && N >= 256, "gemm_lora_packed: needs M, N >= 256");
   return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, T, ldt, 0, Bcat, ldb, 1, r, nullptr, nullptr, 0, C, ldc, M, N, 0, 0, 0,
                       0, 1.0f, 0, stream, &si);
+}
+
+// The packed q | k | v projection of an attention block (b200_gemm_lora_packed_bf16) with compute_rope
+// (Models/Llama/common_components.py:6-35, called at Llama3.py:140-141) applied to the q and k heads — the first rope_cols
+// output columns — in the epilogue: row m is position m % seq_len, cos / sin are [>= seq_len, head_dim] bf16 tables
+// whose two column halves are equal. T / Bcat may be NULL with r = 0 (plain linears).
+extern "C" int b200_gemm_qkv_rope_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K,
+                                       const void* T, int64_t ldt, const void* Bcat, int64_t ldb, int64_t r,
+                                       int nseg, const int64_t* seg_start, const void* cos, const void* sin,
+                                       int64_t seq_len, int64_t head_dim, int64_t rope_cols, void* C, int64_t ldc,
+                                       int64_t M, int64_t N, void* stream) {
+  B200_CHECK_ARG(cos && sin, "gemm_qkv_rope: null RoPE tables");
+  B200_CHECK_ARG(M >= 256 && N >= 256, "gemm_qkv_rope: needs M, N >= 256");
+  Extra ex;
+  ex.rope_cos = cos;
+  ex.rope_sin = sin;
+  ex.rope_T = seq_len;
+  ex.rope_hd = head_dim;
+  ex.rope_cols = rope_cols;
+  if (r <= 0)
+    return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, nullptr, 0, 0, nullptr, 0, 0, 0, nullptr, nullptr, 0, C, ldc, M, N, 0, 0, 0, 0,
+                        1.0f, 0, stream, nullptr, false, false, &ex);
+  B200_CHECK_ARG(nseg >= 1 && nseg <= 4 && seg_start && seg_start[0] == 0, "gemm_qkv_rope: 1..4 segments, the first starting at column 0");
+  B200_CHECK_ARG(r <= 64 && r % 8 == 0, "gemm_qkv_rope: rank %lld must be a multiple of 8 and <= 64", (long long)r);
+  SegInfo si;
+  si.nseg = nseg;
+  si.a2_stride = r;
+  for (int i = 0; i < nseg; ++i) {
+    B200_CHECK_ARG(seg_start[i] % P_BN == 0 && seg_start[i] < N && (i == 0 || seg_start[i] > seg_start[i - 1]),
+                   "gemm_qkv_rope: segment starts must be increasing multiples of %d below N", P_BN);
+    si.start[i] = seg_start[i];
+  }
+  return gemm_ex_impl(X, ldx, 0, W, ldw, 0, K, T, ldt, 0, Bcat, ldb, 1, r, nullptr, nullptr, 0, C, ldc, M, N, 0, 0, 0, 0, 1.0f,
+                      0, stream, &si, false, false, &ex);
 }
 
 namespace {

@@ -174,6 +174,37 @@ def gemm_lora_packed(x, w_cat, t_cat, b_cat, r, seg_starts, out=None):
     return out
 
 
+def gemm_qkv_rope(x, w_cat, t_cat, b_cat, r, seg_starts, cos, sin, T, hd, rope_cols, out=None):
+    """The packed q|k|v projection (gemm_lora_packed; t_cat / b_cat None for plain linears) with RoPE applied to the
+    first rope_cols output columns in the epilogue; row m is position m % T."""
+    _need_cuda(x, w_cat, t_cat, b_cat, cos, sin, out)
+    lib = _lib.load()
+    _ensure_gemm_workspace(x.device)
+    x, ldx = _rowmajor2d(x)
+    w_cat, ldw = _rowmajor2d(w_cat)
+    M, Kd = x.shape
+    N = w_cat.shape[0]
+    ldt = ldb = 0
+    if t_cat is not None:
+        t_cat, ldt = _rowmajor2d(t_cat)
+        b_cat, ldb = _rowmajor2d(b_cat)
+        assert b_cat.shape == (r, N) and t_cat.shape == (M, r * len(seg_starts))
+    else:
+        r = 0
+    assert cos.dtype == BF16 and sin.dtype == BF16 and cos.shape[1] == hd and cos.shape[0] >= T and cos.is_contiguous() and sin.is_contiguous()
+    if out is None:
+        out = torch.empty((M, N), device=x.device, dtype=BF16)
+    out2, ldc = _rowmajor2d(out)
+    segs = (_lib.C.c_int64 * len(seg_starts))(*seg_starts)
+    prof = _gemm_profile
+    start = prof.begin() if prof is not None else None
+    _lib.check(lib.b200_gemm_qkv_rope_bf16(_p(x), ldx, _p(w_cat), ldw, Kd, _p(t_cat), ldt, _p(b_cat), ldb, r, len(seg_starts), segs,
+                                           _p(cos), _p(sin), T, hd, rope_cols, _p(out2), ldc, M, N, _stream()), "gemm_qkv_rope")
+    if prof is not None:
+        prof.end(start, 2.0 * M * N * (Kd + r), (M, N, Kd, r, 0, 0, 0))
+    return out
+
+
 def gemm_swiglu_bwd(dy, w, u, A, ab, out=None):
     """(da | db) [M, 2F] = SwiGLU'(a, b) * (dy w + u A^T) with (a | b) = ab [M, 2F]; w [K, F] (fc3.weight), u [M, r]
     and A [F, r] or both None."""
@@ -703,7 +734,9 @@ def attention_fwd(q, k, v, B, T, h, hkv, hd, out=None, dropout_p=0.0, seed=0, se
 
 
 def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=None, dropout_p=0.0, seed=0,
-                  seed_dev=None):
+                  seed_dev=None, rope=None):
+    """rope = (cos, sin): q / k were rotated before the attention kernels (projection epilogue); dq / dk then come out
+    multiplied by the transposed rotation (gradients of the un-rotated projections)."""
     _need_cuda(q, k, v, o, do, lse)
     q, ldq = _rowmajor2d(q)
     k, ldk = _rowmajor2d(k)
@@ -717,6 +750,15 @@ def attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, dq=None, dk=None, dv=No
     lib = _lib.load()
     nbytes = lib.b200_attention_bwd_workspace_bytes(B, T, h, hd)
     ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    if rope is not None:
+        assert dropout_p == 0.0
+        cos, sin = rope
+        assert cos.dtype == BF16 and cos.is_contiguous() and sin.is_contiguous() and cos.shape[1] == hd and cos.shape[0] >= T
+        _lib.check(lib.b200_attention_bwd_rope_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
+                                                    _p(ws), nbytes, _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
+                                                    dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), _p(cos), _p(sin),
+                                                    _stream()), "attention_bwd_rope")
+        return dq, dk, dv
     _lib.check(lib.b200_attention_bwd_bf16(_p(q), ldq, _p(k), ldk, _p(v), ldv, _p(o), ldo, _p(do), lddo, _p(lse),
                                            _p(ws), nbytes, _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv),
                                            dv.stride(0), B, T, h, hkv, hd, 1.0 / math.sqrt(hd), float(dropout_p),

@@ -807,17 +807,17 @@ def gelu_mlp(x: Tensor, w1: Tensor, b1: Optional[Tensor], A1: Optional[Tensor], 
         h = K.gelu_fwd(z)
     res2 = _flat2d(residual) if residual is not None else None
     y, t2 = _linear_fwd(h, w2, b2, A2, B2, scaling, res2, (p, seed) if p > 0 else None)
-    e = x2.new_empty((0,))
-    return [y.view(*x.shape[:-1], w2.shape[0]), z, h, t1 if t1 is not None else e, t2 if t2 is not None else e]
+    # (outputs of a custom op may not alias each other: two separate empties)
+    return [y.view(*x.shape[:-1], w2.shape[0]), z, h, t1 if t1 is not None else x2.new_empty((0,)),
+            t2 if t2 is not None else x2.new_empty((0,))]
 
 
 @gelu_mlp.register_fake
 def _(x, w1, b1, A1, B1, w2, b2, A2, B2, scaling, residual, p, seed):
     rows = x.numel() // x.shape[-1]
-    e = x.new_empty((0,))
     return [x.new_empty((*x.shape[:-1], w2.shape[0])), x.new_empty((rows, w1.shape[0])), x.new_empty((rows, w1.shape[0])),
-            x.new_empty((rows, A1.shape[1])) if A1 is not None else e,
-            x.new_empty((rows, A2.shape[1])) if A2 is not None else e]
+            x.new_empty((rows, A1.shape[1])) if A1 is not None else x.new_empty((0,)),
+            x.new_empty((rows, A2.shape[1])) if A2 is not None else x.new_empty((0,))]
 
 
 def _gelu_mlp_setup(ctx, inputs, output):

@@ -102,6 +102,16 @@ int b200_gemm_swiglu_fwd_bf16(const void* X, int64_t ldx, const void* Wil, int64
                               const void* T2, int64_t ldt, const void* Bil, int64_t ldb, int64_t r2,
                               void* AB, int64_t ldab, void* H, int64_t ldh, int64_t M, int64_t F, void* stream);
 
+/* The packed q | k | v projection (b200_gemm_lora_packed_bf16; T / Bcat NULL and r = 0 for plain linears) with
+ * compute_rope (Models/Llama/common_components.py:6-35 at Llama3.py:140-141) applied to the first rope_cols output
+ * columns (the q and k heads) in the epilogue, with the reference's bf16 roundings: row m is position m % seq_len;
+ * cos / sin are [>= seq_len, head_dim] bf16 tables whose two column halves are equal (precompute_rope_params builds
+ * them as cat([angles, angles])); head_dim 64 or 128. Pair it with b200_attention_bwd_rope_bf16 in backward. */
+int b200_gemm_qkv_rope_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, int64_t K, const void* T,
+                            int64_t ldt, const void* Bcat, int64_t ldb, int64_t r, int nseg, const int64_t* seg_start,
+                            const void* cos, const void* sin, int64_t seq_len, int64_t head_dim, int64_t rope_cols,
+                            void* C, int64_t ldc, int64_t M, int64_t N, void* stream);
+
 /* GPT-2 MLP and residual fusions (Models/GPT2/GPT2.py:58-62, 83-88); all need M, N >= 256 (CTA-pair kernel), bf16.
  * b200_gemm_gelu_fwd_bf16:  Z = X W^T + bias (+ T Bl), H = gelu(Z) (erf form, nn.GELU()), both written by the epilogue
  *                           (Z is what autograd saves for the GELU's backward).
@@ -352,6 +362,14 @@ int b200_attention_bwd_bf16(const void* q, int64_t ldq, const void* k, int64_t l
                             void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv,
                             int64_t B, int64_t T, int64_t h, int64_t hkv, int64_t hd, float scale,
                             float dropout_p, uint64_t seed, const uint64_t* seed_dev, void* stream);
+/* Backward for q / k that were rotated by the projection's epilogue (b200_gemm_qkv_rope_bf16): dq / dk leave through
+ * the transposed rotation, i.e. as gradients of the UN-rotated projections (compute_rope under autograd), so no
+ * separate inverse-RoPE pass over dq | dk runs. No dropout on this path (Llama has none). */
+int b200_attention_bwd_rope_bf16(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                                 int64_t ldv, const void* o, int64_t ldo, const void* dout, int64_t lddo,
+                                 const float* lse, void* workspace, size_t workspace_bytes, void* dq, int64_t lddq,
+                                 void* dk, int64_t lddk, void* dv, int64_t lddv, int64_t B, int64_t T, int64_t h,
+                                 int64_t hkv, int64_t hd, float scale, const void* cos, const void* sin, void* stream);
 /* dropout_p > 0 drops attention weights after the softmax like GPT2.py:43; the mask is a counter-based
  * function of (seed + *seed_dev, b, h, q, k), so backward must be given the forward's seed and seed_dev.
  * seed_dev (may be NULL = 0) is one uint64 in device memory read by the kernels when they run: a step
