@@ -91,6 +91,10 @@ class GroupedQueryAttention(nn.Module):
             ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), cos, sin, cache, layer,
                                     b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)
             return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
+        ctx = ops.qkv_rope_attention(x, [self.W_query, self.W_key, self.W_value], cos, sin, b, num_tokens, self.num_heads,
+                                     self.num_kv_groups, self.head_dim)
+        if ctx is not None:     # projection + RoPE (GEMM epilogue) + attention as one op
+            return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         qkv = ops.linears_packed(x, [self.W_query, self.W_key, self.W_value])
         if qkv is not None:     # one packed projection: RoPE and the backward dX GEMM run once over q|k|v
             ctx = ops.attention_qkv(qkv.view(b * num_tokens, -1), cos, sin, b, num_tokens, self.num_heads,

@@ -86,12 +86,21 @@ struct GemmParams {
 // barrier over the 4 epilogue warps (threads 128..255) of a CTA
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
+// erf by Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far inside bf16's 2^-9): one reciprocal, one exponential and
+// six FMAs instead of erff's ~35 instructions — the GELU epilogue of a K = 1600 GEMM is otherwise longer than its main loop.
+__device__ __forceinline__ float erf_as(float x) {
+  const float ax = fabsf(x);
+  const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+  const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
+  const float e = 1.f - poly * __expf(-ax * ax);
+  return copysignf(e, x);
+}
 __device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+  return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752440f));
 }
 // d/dx of the erf GELU: Phi(x) + x * phi(x)
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  const float cdf = 0.5f * (1.0f + erf_as(x * 0.70710678118654752440f));
   return cdf + x * 0.39894228040143267794f * __expf(-0.5f * x * x);
 }
 
@@ -474,7 +483,7 @@ constexpr int P_SMEM_SWIGLU = P_STAGES_SWIGLU * P_STAGE_BYTES + P_IO_BYTES + 102
 // swizzled staging area, because one-row-per-lane accesses cost 32 line transactions per warp instruction and
 // made the load/store unit the limit once the epilogue reads as well as writes.
 template <int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((MODE == 1 || MODE == 2) ? 384 : 256, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((MODE == 1 || MODE == 2 || MODE == 4) ? 384 : 256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                          const __grid_constant__ CUtensorMap tmAB, const __grid_constant__ CUtensorMap tmDAB,
@@ -494,7 +503,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   uint64_t* in_full = tempty + 3;             // staged modes: staging buffers filled by TMA
   uint64_t* out_full = in_full + IO_BUFS;     //         ... rewritten in place with the results by the 8 epilogue warps
 
-  constexpr bool WIDE = STAGED;
+  // MODE 4 = MODE 0's per-thread epilogue on eight epilogue warps (two per TMEM lane quadrant, half of the tile's columns
+  // each): for epilogues that are arithmetic-heavy (GELU) or write two outputs
+  constexpr bool WIDE = STAGED || MODE == 4;
   constexpr int STAGES = STAGED ? P_STAGES_SWIGLU : P_STAGES;
   uint8_t* sab = smem + P_STAGES_SWIGLU * P_STAGE_BYTES;
   const int warp = threadIdx.x >> 5;
@@ -947,6 +958,7 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_SWIGLU));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set[dev] = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
@@ -968,6 +980,9 @@ int launch_2cta(const CUtensorMap* maps, const GemmParams& p, int sms, cudaStrea
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else if (staged_res)
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<2>, dim3(2 * clusters), dim3(384), P_SMEM_SWIGLU, st, maps[0],
+                                    maps[1], maps[2], maps[3], maps[4], maps[5], p));
+  else if (p.flags & EP_GELU)
+    B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<4>, dim3(2 * clusters), dim3(384), P_SMEM, st, maps[0],
                                     maps[1], maps[2], maps[3], maps[4], maps[5], p));
   else
     B200_CHECK_CUDA(b200_launch_pdl(gemm_tcgen05_2cta_kernel<0>, dim3(2 * clusters), dim3(256), P_SMEM, st, maps[0],

@@ -485,7 +485,7 @@ extern "C" int b200_rmsnorm_bwd_bf16(const void* x, const float* w, const void* 
   B200_CHECK_ARG(d % 8 == 0 && d > 0 && d <= 16384, "rmsnorm_bwd: d=%lld must be a multiple of 8 and <= 16384", (long long)d);
   cudaStream_t st = (cudaStream_t)stream;
   int grid = grid_for_rows_wpr(M, d);
-  if (dw && grid > 2 * b200_num_sms()) grid = 2 * b200_num_sms();   // fat CTAs: column partials span many rows
+  if (dw && grid > b200_num_sms()) grid = b200_num_sms();   // fat CTAs: column partials span many rows
 #define BWD_ARGS (const bf16*)x, w, (const bf16*)dy, (const bf16*)dres_in, (bf16*)dx, dw, M, (int)d, eps
 #define CALL(NV, WPR)                                                                                   \
   do {                                                                                                  \
@@ -549,8 +549,8 @@ extern "C" int b200_layernorm_bwd_bf16(const void* x, const void* w, const void*
   int grid = grid_for_rows(M);
   B200_CHECK_ARG((dw == nullptr) == (db == nullptr), "layernorm_bwd: dw and db must be given together");
   if (dw) {
-    // weight gradients: every warp keeps its column partials over MANY rows (2 CTAs per SM), see the kernel
-    const int fat = 2 * b200_num_sms();
+    // weight gradients: every warp keeps its column partials over MANY rows (one CTA per SM), see the kernel
+    const int fat = b200_num_sms();
     if (grid > fat) grid = fat;
     B200_CHECK_ARG(d <= 4096, "layernorm_bwd: weight gradient supported for d <= 4096");
     const int nv = (int)((d / 8 + 31) / 32);

@@ -581,6 +581,129 @@ def _llp_bwd(ctx, grads):
 lora_linear_packed.register_autograd(_llp_bwd, setup_context=_llp_setup)
 
 
+# --------------------------------------------------------------------------------------
+# q | k | v projection + RoPE + causal attention as ONE op (Models/Llama/Llama3.py:135-153): compute_rope runs in the
+# epilogue of the packed projection GEMM and its transpose in the epilogues of the attention-backward kernels, so neither
+# the rotation (one 4-bytes-per-element pass over q | k) nor its gradient (another) exists as a kernel.
+# --------------------------------------------------------------------------------------
+_rope_ok_cache: dict = {}
+
+
+def rope_tables_fusable(cos: Tensor, sin: Tensor) -> bool:
+    """The fused rotation reads one half of each table row for both halves of a head: allowed when the two column halves
+    are equal — which precompute_rope_params guarantees (angles = cat([a, a])); checked once per table."""
+    key = (cos.data_ptr(), sin.data_ptr(), cos._version, sin._version, tuple(cos.shape))
+    hit = _rope_ok_cache.get(key)
+    if hit is None:
+        half = cos.shape[1] // 2
+        hit = bool(cos.dtype == BF16 and sin.dtype == BF16 and cos.is_contiguous() and sin.is_contiguous()
+                   and torch.equal(cos[:, :half], cos[:, half:]) and torch.equal(sin[:, :half], sin[:, half:]))
+        if len(_rope_ok_cache) > 64:
+            _rope_ok_cache.clear()
+        _rope_ok_cache[key] = hit
+    return hit
+
+
+@torch.library.custom_op("b200llm::lora_qkv_rope_attention", mutates_args=())
+def lora_qkv_rope_attention(x: Tensor, weights: Sequence[Tensor], As: Sequence[Tensor], Bs: Sequence[Tensor], scaling: float,
+                            w_cat: Tensor, cos: Tensor, sin: Tensor, B: int, T: int, h: int, hkv: int,
+                            hd: int) -> List[Tensor]:
+    """-> [o [B*T, h*hd], qkv_rot [B*T, (h + 2 hkv) hd] (q, k rotated), lse, t_cat]."""
+    x2 = _flat2d(x)
+    M = x2.shape[0]
+    n = len(weights)
+    starts = [0]
+    for w in weights[:-1]:
+        starts.append(starts[-1] + w.shape[0])
+    if len(As) > 0:
+        r = As[0].shape[1]
+        t_cat = x2.new_empty((M, n * r))
+        K.gemm_grouped([dict(a=x2, b=As[i], out=t_cat[:, i * r:(i + 1) * r], b_mn=True, alpha=scaling) for i in range(n)])
+        qkv = K.gemm_qkv_rope(x2, w_cat, t_cat, torch.cat(list(Bs), dim=1), r, starts, cos, sin, T, hd, (h + hkv) * hd)
+    else:
+        t_cat = x2.new_empty((0,))
+        qkv = K.gemm_qkv_rope(x2, w_cat, None, None, 0, starts, cos, sin, T, hd, (h + hkv) * hd)
+    nq, nk = h * hd, hkv * hd
+    o, lse = K.attention_fwd(qkv[:, :nq], qkv[:, nq:nq + nk], qkv[:, nq + nk:], B, T, h, hkv, hd)
+    return [o, qkv, lse, t_cat]
+
+
+@lora_qkv_rope_attention.register_fake
+def _(x, weights, As, Bs, scaling, w_cat, cos, sin, B, T, h, hkv, hd):
+    rows = x.numel() // x.shape[-1]
+    t = x.new_empty((rows, len(As) * As[0].shape[1])) if len(As) > 0 else x.new_empty((0,))
+    return [x.new_empty((rows, h * hd)), x.new_empty((rows, (h + 2 * hkv) * hd)),
+            x.new_empty((B, h, T), dtype=torch.float32), t]
+
+
+def _lqra_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    x, weights, As, Bs, scaling, w_cat, cos, sin, B, T, h, hkv, hd = inputs
+    o, qkv, lse, t_cat = output
+    ctx.n, ctx.lora, ctx.scaling, ctx.has_cat = len(weights), len(As) > 0, scaling, True
+    ctx.dims = (B, T, h, hkv, hd)
+    # layout expected by _llp_bwd: x, weights, As, Bs, t_cat, w_cat — then this op's own tensors
+    ctx.save_for_backward(x, *weights, *As, *Bs, t_cat, w_cat, qkv, o, lse, cos, sin)
+
+
+def _lqra_bwd(ctx, grads):
+    do = grads[0]
+    n = ctx.n
+    n_in = 13
+    if do is None:
+        return (None, [None] * n, [None] * (n if ctx.lora else 0), [None] * (n if ctx.lora else 0)) + (None,) * (n_in - 4)
+    saved = ctx.saved_tensors
+    qkv, o, lse, cos, sin = saved[-5:]
+    B, T, h, hkv, hd = ctx.dims
+    nq, nk = h * hd, hkv * hd
+    dqkv = qkv.new_empty(qkv.shape)
+    # dq / dk come out of the attention-backward epilogues already multiplied by the transposed rotation
+    K.attention_bwd(qkv[:, :nq], qkv[:, nq:nq + nk], qkv[:, nq + nk:], o, _flat2d(do), lse, B, T, h, hkv, hd,
+                    dq=dqkv[:, :nq], dk=dqkv[:, nq:nq + nk], dv=dqkv[:, nq + nk:], rope=(cos, sin))
+    out = _llp_bwd(_BwdView(ctx, saved[:-5]), [dqkv.view(*saved[0].shape[:-1], dqkv.shape[-1]), None])
+    return out + (None,) * (n_in - len(out))
+
+
+class _BwdView:
+    """ctx stand-in handing _llp_bwd the packed-projection part of another op's saved tensors."""
+
+    def __init__(self, ctx, saved):
+        self.n, self.lora, self.scaling, self.has_cat = ctx.n, ctx.lora, ctx.scaling, ctx.has_cat
+        self.saved_tensors = saved
+        self.needs_input_grad = ctx.needs_input_grad
+
+
+lora_qkv_rope_attention.register_autograd(_lqra_bwd, setup_context=_lqra_setup)
+
+
+def qkv_rope_attention(x, modules, cos, sin, B, T, h, hkv, hd):
+    """Context vectors [B*T, h*hd] of causal attention over RoPE'd q, k from the three projection modules of x, through
+    lora_qkv_rope_attention; None when the fused form does not apply (caller falls back to separate ops)."""
+    if os.environ.get("B200_PACKED", "1") == "0" or os.environ.get("B200_ROPE_EPILOGUE", "1") == "0":
+        return None
+    from .lora import LinearWithLoRA
+    lora = [isinstance(m, LinearWithLoRA) for m in modules]
+    bases = [m.linear if l else m for m, l in zip(modules, lora)]
+    if any(b.bias is not None for b in bases) or (any(lora) and not all(lora)) or hd not in (64, 128):
+        return None
+    weights = [b.weight for b in bases]
+    rows = x.numel() // x.shape[-1]
+    if rows < 256 or any(w.shape[0] % 256 for w in weights) or x.dtype != BF16 or not rope_tables_fusable(cos, sin):
+        return None
+    w_cat = _packed_weight(weights)
+    if w_cat is None:
+        return None
+    if all(lora):
+        scal, r = modules[0].lora.scaling, modules[0].lora.A.shape[1]
+        if any(m.lora.scaling != scal or m.lora.A.shape[1] != r for m in modules) or r % 8 or r > 64:
+            return None
+        if any(m.lora.B.shape[1] % 8 for m in modules):
+            return None
+        return lora_qkv_rope_attention(x, weights, [m.lora.A for m in modules], [m.lora.B for m in modules], scal, w_cat,
+                                       cos, sin, B, T, h, hkv, hd)[0]
+    return lora_qkv_rope_attention(x, weights, [], [], 0.0, w_cat, cos, sin, B, T, h, hkv, hd)[0]
+
+
 # fc1 | fc2 with SwiGLU in the GEMM epilogue: same packed (a | b) output and same backward as
 # lora_linear_packed, plus h = silu(a) * b straight from the accumulators (no separate 6-bytes-per-element
 # SwiGLU kernel). Needs the frozen weights interleaved in 128-row blocks (cached like the concatenation).

@@ -343,3 +343,53 @@ def test_gemm_dropout_residual_epilogue_draws_the_standalone_mask(K, M, N, K_, r
         dropped = (fused.float() == res.float()).float().mean()
         assert abs(float(dropped) - p) < 0.01
     assert not torch.equal(fused, K.gemm_dropout_residual(x, w, b, res, p, seed, None, t, Bl))     # the offset matters
+
+
+# ------------------------------------------------------------------ RoPE in the q|k|v projection's epilogue
+def _rope_tables(T, hd, base=7812.5):
+    inv = 1.0 / (base ** (torch.arange(0, hd, 2).float() / hd))
+    ang = torch.arange(T)[:, None] * inv[None, :]
+    ang = torch.cat([ang, ang], dim=1)
+    return torch.cos(ang).to(torch.bfloat16).cuda(), torch.sin(ang).to(torch.bfloat16).cuda()
+
+
+@pytest.mark.parametrize("B,T,h,hkv,hd,d,r", [(4, 2048, 32, 8, 64, 2048, 64), (2, 512, 8, 4, 128, 1024, 0), (1, 300, 4, 4, 64, 256, 8)])
+def test_gemm_qkv_rope_epilogue_equals_projection_then_rope_kernel(K, B, T, h, hkv, hd, d, r):
+    """compute_rope (common_components.py:6-35) in the epilogue of the packed q|k|v GEMM: bit-identical to the packed GEMM
+    followed by the stand-alone rotation kernel (same bf16 roundings); the v columns are untouched."""
+    M = B * T
+    outs = (h * hd, hkv * hd, hkv * hd)
+    x = rnd(M, d, seed=1)
+    w_cat = rnd(sum(outs), d, scale=0.05, seed=2)
+    cos, sin = _rope_tables(T, hd)
+    starts = [0, outs[0], outs[0] + outs[1]]
+    if r:
+        t_cat, b_cat = rnd(M, 3 * r, seed=3), rnd(r, sum(outs), scale=0.1, seed=4)
+        plain = K.gemm_lora_packed(x, w_cat, t_cat, b_cat, r, starts)
+        fused = K.gemm_qkv_rope(x, w_cat, t_cat, b_cat, r, starts, cos, sin, T, hd, (h + hkv) * hd)
+    else:
+        plain = K.gemm_ex(x, w_cat)
+        fused = K.gemm_qkv_rope(x, w_cat, None, None, 0, starts, cos, sin, T, hd, (h + hkv) * hd)
+    ref = plain.clone()
+    K.rope_(ref, cos, sin, B, T, h + hkv, hd)
+    assert torch.equal(fused, ref)
+    assert not torch.equal(fused[:, :outs[0]], plain[:, :outs[0]])
+
+
+@pytest.mark.parametrize("B,T,h,hkv,hd", [(2, 512, 8, 2, 64), (1, 640, 4, 2, 128)])
+def test_attention_backward_with_rope_transpose_in_the_epilogues(K, B, T, h, hkv, hd):
+    """b200_attention_bwd_rope_bf16 = attention backward followed by the inverse rotation of dq | dk (compute_rope under
+    autograd); the fused form rotates the fp32 accumulators, so it is compared at a few bf16 ulps."""
+    qkv = rnd(B * T, (h + 2 * hkv) * hd, seed=1)
+    nq, nk = h * hd, hkv * hd
+    q, k, v = qkv[:, :nq], qkv[:, nq:nq + nk], qkv[:, nq + nk:]
+    do = rnd(B * T, nq, scale=0.1, seed=2)
+    cos, sin = _rope_tables(T, hd)
+    o, lse = K.attention_fwd(q, k, v, B, T, h, hkv, hd)
+    dq, dk, dv = K.attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd)
+    K.rope_(dq, cos, sin, B, T, h, hd, inverse=True)
+    K.rope_(dk, cos, sin, B, T, hkv, hd, inverse=True)
+    fq, fk, fv = K.attention_bwd(q, k, v, o, do, lse, B, T, h, hkv, hd, rope=(cos, sin))
+    assert torch.equal(fv, dv)
+    assert rel_err(fq.float(), dq.float()) < 6e-3
+    assert rel_err(fk.float(), dk.float()) < 6e-3
