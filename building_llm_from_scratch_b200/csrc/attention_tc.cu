@@ -13,6 +13,8 @@
 // columns, two CTAs), so one CTA's softmax overlaps the others' MMAs and barrier / TMEM-load latencies. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
 //
 // Roofline: tensor pipe / MUFU (head_dim 64: 8192 exp2 per 128x64 tile vs 256 MMA cycles).
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace {
@@ -20,6 +22,7 @@ namespace {
 constexpr int BQ = 128, BKV = 64, NS = 2;
 constexpr int P_BYTES = BQ * BKV * 2;    // 16 KB
 constexpr float LOG2E = 1.4426950408889634f;
+constexpr float RESCALE_SLACK = 8.f;     // forward softmax: tolerated growth of the row maximum before O is rescaled
 
 template <int HDIM>
 struct FwdCfg {
@@ -206,7 +209,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       float mx = -INFINITY;
 #pragma unroll
       for (int i = 0; i < 32; ++i) mx = fmax3(mx, __uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
-      const float m_new = fmaxf(m, mx * p.scale_log2);
+      // The running maximum only has to bound the exponents, not equal the true maximum: while the new tile raises it
+      // by less than RESCALE_SLACK (log2 units) the old reference is kept — p = exp2(s - m) then stays below
+      // 2^RESCALE_SLACK, well inside fp32 / bf16 range — and O and l need no rescaling (alpha = 1). With the exact
+      // maximum 82 % of the iterations paid a TMEM load / multiply / store round trip over O on the critical path.
+      const float m_cand = fmaxf(m, mx * p.scale_log2);
+      const float m_new = (m_cand - m > RESCALE_SLACK) ? m_cand : m;     // first tile: m = -inf -> takes m_cand
       const float alpha = fast_exp2(m - m_new);
       // p = exp2(s * scale - m_new): one packed FFMA and one packed FADD per column pair
       const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), neg2 = pack_f2(-m_new, -m_new);
@@ -572,63 +580,71 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
       const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
       const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), scl2 = pack_f2(p.scale, p.scale);
-#pragma unroll 1
-      for (int hf = 0; hf < 2; ++hf) {
-        uint32_t sv[32], dv[32];
-        tmem_ld_32x32(tlane + C_ST + buf * QS + hf * 32, sv);
-        tmem_ld_32x32(tlane + C_DPT + buf * QS + hf * 32, dv);
-        tmem_ld_wait();
-        if (hf == 1) {   // both halves are in registers: the MMA issuer may overwrite this TMEM buffer
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&st_empty[buf]);
-        }
-        uint32_t pp[16], dd[16];
-#pragma unroll
-        for (int i4 = 0; i4 < 8; ++i4) {
-          const float4 l4 = lds_f4(lse_s + hf * 128 + i4 * 16);     // -lse * log2e
-          const float4 d4 = lds_f4(del_s + hf * 128 + i4 * 16);     // -delta
-          const float nls[4] = {l4.x, l4.y, l4.z, l4.w}, nds[4] = {d4.x, d4.y, d4.z, d4.w};
-          float pv[4], dsv[4];
-#pragma unroll
-          for (int e2 = 0; e2 < 2; ++e2) {
-            const int c = i4 * 4 + 2 * e2;
-            // packed pairs: P^T = exp2(s c - lse[q]), dS^T = P^T (dP^T - delta[q]) scale
-            float a0, a1;
-            unpack_f2(ffma2(pack_f2(__uint_as_float(sv[c]), __uint_as_float(sv[c + 1])), sc2,
-                            pack_f2(nls[2 * e2], nls[2 * e2 + 1])), a0, a1);
-            float pr[2] = {fast_exp2(a0), fast_exp2(a1)};
-            float dpv[2] = {__uint_as_float(dv[c]), __uint_as_float(dv[c + 1])};
-            float pdrop[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              if (diag && key > qrow0 + hf * 32 + c + e) pr[e] = 0.f;
-              pdrop[e] = pr[e];
-              if (DROP) {
-                const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c + e);
-                const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
-                                                 ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
-                                             dseed, p.drop.thr16);
-                dpv[e] = kp ? dpv[e] * p.drop.inv_keep : 0.f;
-                pdrop[e] = kp ? pr[e] * p.drop.inv_keep : 0.f;
-              }
-              pv[2 * e2 + e] = pdrop[e];                    // dV uses the dropped, rescaled P
-            }
-            unpack_f2(fmul2(fmul2(pack_f2(pr[0], pr[1]), fadd2(pack_f2(dpv[0], dpv[1]), pack_f2(nds[2 * e2], nds[2 * e2 + 1]))),
-                            scl2), dsv[2 * e2], dsv[2 * e2 + 1]);
+      // Two copies of the step body, chosen per step: only the steps on the diagonal (two per head) carry the causal
+      // compare / select per element; a single body with `if (diag && ...)` still computed every index and comparison
+      // on every step — a third of its instructions.
+      auto half_steps = [&](auto masked) {
+        constexpr bool MASK = decltype(masked)::value;
+  #pragma unroll 1
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t sv[32], dv[32];
+          tmem_ld_32x32(tlane + C_ST + buf * QS + hf * 32, sv);
+          tmem_ld_32x32(tlane + C_DPT + buf * QS + hf * 32, dv);
+          tmem_ld_wait();
+          if (hf == 1) {   // both halves are in registers: the MMA issuer may overwrite this TMEM buffer
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&st_empty[buf]);
           }
-          pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
-          pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
-          dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
-          dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
+          uint32_t pp[16], dd[16];
+  #pragma unroll
+          for (int i4 = 0; i4 < 8; ++i4) {
+            const float4 l4 = lds_f4(lse_s + hf * 128 + i4 * 16);     // -lse * log2e
+            const float4 d4 = lds_f4(del_s + hf * 128 + i4 * 16);     // -delta
+            const float nls[4] = {l4.x, l4.y, l4.z, l4.w}, nds[4] = {d4.x, d4.y, d4.z, d4.w};
+            float pv[4], dsv[4];
+  #pragma unroll
+            for (int e2 = 0; e2 < 2; ++e2) {
+              const int c = i4 * 4 + 2 * e2;
+              // packed pairs: P^T = exp2(s c - lse[q]), dS^T = P^T (dP^T - delta[q]) scale
+              float a0, a1;
+              unpack_f2(ffma2(pack_f2(__uint_as_float(sv[c]), __uint_as_float(sv[c + 1])), sc2,
+                              pack_f2(nls[2 * e2], nls[2 * e2 + 1])), a0, a1);
+              float pr[2] = {fast_exp2(a0), fast_exp2(a1)};
+              float dpv[2] = {__uint_as_float(dv[c]), __uint_as_float(dv[c + 1])};
+              float pdrop[2];
+  #pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                if (MASK && key > qrow0 + hf * 32 + c + e) pr[e] = 0.f;
+                pdrop[e] = pr[e];
+                if (DROP) {
+                  const unsigned long long qg = (unsigned long long)(qrow0 + hf * 32 + c + e);
+                  const bool kp = dropout_keep((((drop_bh * p.T + qg) * (unsigned long long)((p.T + 1) >> 1)) << 1) +
+                                                   ((unsigned long long)(key >> 1) << 1) + (unsigned long long)(key & 1),
+                                               dseed, p.drop.thr16);
+                  dpv[e] = kp ? dpv[e] * p.drop.inv_keep : 0.f;
+                  pdrop[e] = kp ? pr[e] * p.drop.inv_keep : 0.f;
+                }
+                pv[2 * e2 + e] = pdrop[e];                    // dV uses the dropped, rescaled P
+              }
+              unpack_f2(fmul2(fmul2(pack_f2(pr[0], pr[1]), fadd2(pack_f2(dpv[0], dpv[1]), pack_f2(nds[2 * e2], nds[2 * e2 + 1]))),
+                              scl2), dsv[2 * e2], dsv[2 * e2 + 1]);
+            }
+            pp[i4 * 2] = f2_to_bf2(pv[0], pv[1]);
+            pp[i4 * 2 + 1] = f2_to_bf2(pv[2], pv[3]);
+            dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
+            dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
+          }
+  #pragma unroll
+          for (int t4 = 0; t4 < 4; ++t4) {
+            const int ch = (hf * 4 + t4) ^ (row & 7);
+            sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
+            sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+          }
         }
-#pragma unroll
-        for (int t4 = 0; t4 < 4; ++t4) {
-          const int ch = (hf * 4 + t4) ^ (row & 7);
-          sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
-          sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
-        }
-      }
+      };
+      if (diag) half_steps(std::true_type{});
+      else half_steps(std::false_type{});
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
@@ -836,39 +852,52 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       const int buf = j & 1;
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      uint32_t s[64], d[64];
-      tmem_ld_32x32(tlane + D_S, s);
-      tmem_ld_32x32(tlane + D_S + 32, s + 32);
-      tmem_ld_32x32(tlane + D_DP, d);
-      tmem_ld_32x32(tlane + D_DP + 32, d + 32);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_empty);
       const int kv0 = j * BKV;
-      const bool diag = kv0 + BKV - 1 > q0 + quad * 32;
+      const bool diag = kv0 + BKV - 1 > q0 + quad * 32;      // warp-uniform
       uint32_t pk[32];
+      // 32 key columns at a time (S and dP halves: 64 live registers instead of 128, no spills at two CTAs per SM).
+      // Two copies of the element loop, chosen per tile: only the (few) tiles on the diagonal carry the causal
+      // compare / select per element. As one loop with `if (diag && ...)` the compiler predicated the selects but
+      // still computed every column index and comparison on every tile — a third of the loop's instructions.
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        bool keep[2] = {true, true};
-        if (DROP)
-          dropout_keep2(drop_row + (unsigned long long)((kv0 >> 1) + i), dseed, p.drop.thr16, keep[0], keep[1]);
-        // packed pairs: P = exp2(s c - lse), dS = P (dP - delta) scale
-        float a0, a1;
-        unpack_f2(ffma2(pack_f2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nl2), a0, a1);
-        float pr0 = fast_exp2(a0), pr1 = fast_exp2(a1);
-        if (diag) {
-          if (kv0 + 2 * i > t) pr0 = 0.f;
-          if (kv0 + 2 * i + 1 > t) pr1 = 0.f;
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t s[32], d[32];
+        tmem_ld_32x32(tlane + D_S + hf * 32, s);
+        tmem_ld_32x32(tlane + D_DP + hf * 32, d);
+        tmem_ld_wait();
+        if (hf == 1) {       // S and dP are in registers: the score MMAs of the next tile may overwrite them
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(s_empty);
         }
-        float dp0 = __uint_as_float(d[2 * i]), dp1 = __uint_as_float(d[2 * i + 1]);
-        if (DROP) {
-          dp0 = keep[0] ? dp0 * p.drop.inv_keep : 0.f;
-          dp1 = keep[1] ? dp1 * p.drop.inv_keep : 0.f;
-        }
-        float v0, v1;
-        unpack_f2(fmul2(fmul2(pack_f2(pr0, pr1), fadd2(pack_f2(dp0, dp1), nd2)), scl2), v0, v1);
-        pk[i] = f2_to_bf2(v0, v1);
+        auto elements = [&](auto masked) {
+          constexpr bool MASK = decltype(masked)::value;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int col = kv0 + hf * 32 + 2 * i;
+            bool keep[2] = {true, true};
+            if (DROP)
+              dropout_keep2(drop_row + (unsigned long long)(col >> 1), dseed, p.drop.thr16, keep[0], keep[1]);
+            // packed pairs: P = exp2(s c - lse), dS = P (dP - delta) scale
+            float a0, a1;
+            unpack_f2(ffma2(pack_f2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nl2), a0, a1);
+            float pr0 = fast_exp2(a0), pr1 = fast_exp2(a1);
+            if (MASK) {
+              if (col > t) pr0 = 0.f;
+              if (col + 1 > t) pr1 = 0.f;
+            }
+            float dp0 = __uint_as_float(d[2 * i]), dp1 = __uint_as_float(d[2 * i + 1]);
+            if (DROP) {
+              dp0 = keep[0] ? dp0 * p.drop.inv_keep : 0.f;
+              dp1 = keep[1] ? dp1 * p.drop.inv_keep : 0.f;
+            }
+            float v0, v1;
+            unpack_f2(fmul2(fmul2(pack_f2(pr0, pr1), fadd2(pack_f2(dp0, dp1), nd2)), scl2), v0, v1);
+            pk[hf * 16 + i] = f2_to_bf2(v0, v1);
+          }
+        };
+        if (diag) elements(std::true_type{});
+        else elements(std::false_type{});
       }
       // buffer `buf` was last read by the dQ product of tile j - 2 (another warp issues those)
       if (j >= 2) mbar_wait(&ds_free[buf], ((j >> 1) - 1) & 1);
