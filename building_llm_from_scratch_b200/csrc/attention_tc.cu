@@ -28,7 +28,13 @@ template <int HDIM>
 struct FwdCfg {
   static constexpr int Q_BYTES = BQ * HDIM * 2;     // 16 / 32 KB
   static constexpr int KV_BYTES = BKV * HDIM * 2;   // 8 / 16 KB
-  static constexpr int SMEM = Q_BYTES + NS * 2 * KV_BYTES + P_BYTES + 1024 + 256;
+  // K tiles are released as soon as their score product has retired (they are not needed for P V), V tiles after
+  // P V: separate rings, K one stage deeper where shared memory allows (head_dim 64: 73 KB, still three CTAs per SM).
+  // With one shared two-stage ring the score issuer spun on k_full: a K tile could only be requested once the P V
+  // product two tiles back had retired, one softmax (~500 clk) ahead of its use against ~1 us of load latency.
+  static constexpr int NSK = HDIM == 64 ? 3 : 2;
+  static constexpr int NSV = 2;
+  static constexpr int SMEM = Q_BYTES + (NSK + NSV) * KV_BYTES + P_BYTES + 1024 + 256;
   static constexpr uint32_t TMEM_COLS = HDIM == 64 ? 128 : 256;   // S [0,64)  O [64, 64 + HDIM)
   static constexpr int CTAS = HDIM == 64 ? 3 : 2;
 };
@@ -77,16 +83,18 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   constexpr int HD = HDIM;
   constexpr int Q_BYTES = FwdCfg<HDIM>::Q_BYTES, KV_BYTES = FwdCfg<HDIM>::KV_BYTES;
   constexpr uint32_t TMEM_COLS = FwdCfg<HDIM>::TMEM_COLS;
+  constexpr int NSK = FwdCfg<HDIM>::NSK, NSV = FwdCfg<HDIM>::NSV;
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + Q_BYTES;
-  uint8_t* sV = sK + NS * KV_BYTES;
-  uint8_t* sP = sV + NS * KV_BYTES;
+  uint8_t* sV = sK + NSK * KV_BYTES;
+  uint8_t* sP = sV + NSV * KV_BYTES;
   uint64_t* bars = (uint64_t*)(sP + P_BYTES);
   uint64_t* q_full = bars;            // 1
-  uint64_t* k_full = bars + 1;        // NS
-  uint64_t* v_full = k_full + NS;     // NS
-  uint64_t* kv_empty = v_full + NS;   // NS
-  uint64_t* s_full = kv_empty + NS;   // 1
+  uint64_t* k_full = bars + 1;        // NSK
+  uint64_t* v_full = k_full + NSK;    // NSV
+  uint64_t* k_empty = v_full + NSV;   // NSK
+  uint64_t* v_empty = k_empty + NSK;  // NSV
+  uint64_t* s_full = v_empty + NSV;   // 1
   uint64_t* s_empty = s_full + 1;     // 1 (4 arrivals)
   uint64_t* p_full = s_empty + 1;     // 1 (4 arrivals)
   uint64_t* o_done = p_full + 1;      // 1
@@ -105,10 +113,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
-    for (int i = 0; i < NS; ++i) {
+    for (int i = 0; i < NSK; ++i) {
       mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+    }
+    for (int i = 0; i < NSV; ++i) {
       mbar_init(&v_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
     }
     mbar_init(s_full, 1);
     mbar_init(s_empty, 4);
@@ -132,12 +143,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_expect_tx(q_full, Q_BYTES);
       tma_load_tile<HD>(sQ, &tmQ, q_full, head * HD, row_base + q0, BQ);
       for (int j = 0; j < n_kv; ++j) {
-        const int s = j % NS;
-        mbar_wait(&kv_empty[s], ((j / NS) & 1) ^ 1);
-        mbar_expect_tx(&k_full[s], KV_BYTES);
-        tma_load_tile<HD>(sK + s * KV_BYTES, &tmK, &k_full[s], kvh * HD, row_base + j * BKV, BKV);
-        mbar_expect_tx(&v_full[s], KV_BYTES);
-        tma_load_tile<HD>(sV + s * KV_BYTES, &tmV, &v_full[s], kvh * HD, row_base + j * BKV, BKV);
+        const int sk = j % NSK, sv = j % NSV;
+        mbar_wait(&k_empty[sk], ((j / NSK) & 1) ^ 1);
+        mbar_expect_tx(&k_full[sk], KV_BYTES);
+        tma_load_tile<HD>(sK + sk * KV_BYTES, &tmK, &k_full[sk], kvh * HD, row_base + j * BKV, BKV);
+        mbar_wait(&v_empty[sv], ((j / NSV) & 1) ^ 1);
+        mbar_expect_tx(&v_full[sv], KV_BYTES);
+        tma_load_tile<HD>(sV + sv * KV_BYTES, &tmV, &v_full[sv], kvh * HD, row_base + j * BKV, BKV);
       }
     }
   } else if (warp == 1) {
@@ -146,14 +158,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t aQ = smem_u32(sQ);
       mbar_wait(q_full, 0);
       auto issue_s = [&](int j) {
-        const int s = j % NS;
-        mbar_wait(&k_full[s], (j / NS) & 1);
+        const int s = j % NSK;
+        mbar_wait(&k_full[s], (j / NSK) & 1);
         if (j > 0) mbar_wait(s_empty, (j - 1) & 1);     // softmax threads hold S_{j-1} in registers
         tc_fence_after();
         const uint32_t aK = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
           umma_bf16_ss(tmem_base, umma_desc_k128(aQ + kstep<BQ>(k)), umma_desc_k128(aK + kstep<BKV>(k)), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&k_empty[s]);                       // the K tile is free once S_j has been formed
         umma_commit(s_full);
       };
       // score products only; P V is issued by warp 2 (one thread doing both was the slowest link of the
@@ -164,8 +177,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (lane == 0) {
       const uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, 0, 1);
       for (int j = 0; j < n_kv; ++j) {
-        const int s = j % NS;
-        mbar_wait(&v_full[s], (j / NS) & 1);
+        const int s = j % NSV;
+        mbar_wait(&v_full[s], (j / NSV) & 1);
         mbar_wait(p_full, j & 1);
         tc_fence_after();
         const uint32_t aP = smem_u32(sP);
@@ -174,7 +187,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         for (int k = 0; k < BKV / 16; ++k)
           umma_bf16_ss(tmem_base + 64, umma_desc_k128(aP + k * 32), umma_desc_mn128(aV + k * 2048, 8192),
                        idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
-        umma_commit(&kv_empty[s]);
+        umma_commit(&v_empty[s]);
         umma_commit(o_done);
       }
     }
@@ -576,7 +589,10 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const bool diag = qrow0 < kv0 + BK2;
       const uint32_t lse_s = smem_u32(sLd) + stg * LD_BYTES;
       const uint32_t del_s = lse_s + QS * 4;
-      if (use > 0) mbar_wait(&panel_free[buf], (use - 1) & 1);
+      // (the wait for this group's P^T / dS^T panels to be free — the accumulate MMAs of step s - NG have retired — sits
+      // right before the first store into them, not here: the exponentials and products of this step do not need the
+      // panels, and with the wait up front each group idled through its own MMAs' issue-to-retire latency; the spin on
+      // panel_free was the most executed instruction of the kernel)
       const uint32_t prow = smem_u32(sPt) + buf * PANEL_BYTES + row * 128;
       const uint32_t drow = smem_u32(sdSt) + buf * PANEL_BYTES + row * 128;
       const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), scl2 = pack_f2(p.scale, p.scale);
@@ -635,7 +651,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
             dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
           }
-  #pragma unroll
+            if (hf == 0 && use > 0) mbar_wait(&panel_free[buf], (use - 1) & 1);
+#pragma unroll
           for (int t4 = 0; t4 < 4; ++t4) {
             const int ch = (hf * 4 + t4) ^ (row & 7);
             sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
