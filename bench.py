@@ -333,6 +333,15 @@ def build_trainer(cfg, device, world_size):
     return tr
 
 
+def nccl_options(dist):
+    """High-priority NCCL streams: the bucket all-reduces overlap backward, whose persistent GEMM kernels fill every SM;
+    with default priority the collective's CTAs queue behind each newly launched GEMM and most of the exchange ends up
+    after backward. B200_NCCL_HIGH_PRIORITY=0 restores the default."""
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = os.environ.get("B200_NCCL_HIGH_PRIORITY", "1") != "0"
+    return opts
+
+
 def data_parallel_selfcheck(step, dev_batches, n_valid, world):
     """N > 1: (1) after two optimizer steps on per-rank batches the flat parameter buffers must be bit-identical on
     every rank (checksums all-gathered); (2) the exchanged gradient must equal the mean over ranks of the local
@@ -390,7 +399,7 @@ def main():
     device = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
+        dist.init_process_group("nccl", device_id=device, pg_options=nccl_options(dist))
 
     from building_llm_from_scratch_b200 import _lib, kernels
     from building_llm_from_scratch_b200.datautils.synthetic import alpaca_batch

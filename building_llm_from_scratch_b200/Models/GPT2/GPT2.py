@@ -82,8 +82,8 @@ class MultiHeadAttention(nn.Module):
             return self._project_out(ctx.view(b, num_tokens, self.d_out), residual, drop)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
-        ctx = ops.attention(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim,
-                            p_drop, ops.new_seed() if p_drop > 0 else 0)[0]
+        ctx = ops.attend(q, k, v, None, None, b, num_tokens, self.num_heads, self.num_heads, self.head_dim,
+                         p_drop, ops.new_seed() if p_drop > 0 else 0)
         return self._project_out(ctx.view(b, num_tokens, self.d_out), residual, drop)
 
 

@@ -61,7 +61,7 @@ class MultiHeadAttention(nn.Module):
 
     def forward(self, x, residual=None, cache=None, layer=0):
         b, num_tokens, _ = x.shape
-        cos, sin = self._tables()
+        cos, sin = (self.cos, self.sin) if x.dtype == torch.float32 else self._tables()
         if cache is not None:       # generation with a KV cache (kvcache.py)
             from ...kvcache import attend_with_cache, packed_qkv
             ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), cos, sin, cache, layer,
@@ -78,7 +78,7 @@ class MultiHeadAttention(nn.Module):
             return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
-        ctx = ops.attention(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)[0]
+        ctx = ops.attend(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_heads, self.head_dim)
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 
 

@@ -84,8 +84,11 @@ class GroupedQueryAttention(nn.Module):
 
     def forward(self, x, residual=None, cache=None, layer=0):
         b, num_tokens, _ = x.shape
-        cos = self.cos if self.cos.dtype == torch.bfloat16 else self.cos.to(torch.bfloat16)
-        sin = self.sin if self.sin.dtype == torch.bfloat16 else self.sin.to(torch.bfloat16)
+        if x.dtype == torch.float32:      # fp32 parity mode: fp32 tables, plain-fp32 kernels
+            cos, sin = self.cos.float(), self.sin.float()
+        else:
+            cos = self.cos if self.cos.dtype == torch.bfloat16 else self.cos.to(torch.bfloat16)
+            sin = self.sin if self.sin.dtype == torch.bfloat16 else self.sin.to(torch.bfloat16)
         if cache is not None:       # generation with a KV cache (kvcache.py)
             from ...kvcache import attend_with_cache, packed_qkv
             ctx = attend_with_cache(packed_qkv(x, [self.W_query, self.W_key, self.W_value]), cos, sin, cache, layer,
@@ -102,7 +105,7 @@ class GroupedQueryAttention(nn.Module):
             return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
         q, k, v = (t.view(b * num_tokens, -1)
                    for t in ops.linears_of_same_input(x, [self.W_query, self.W_key, self.W_value]))
-        ctx = ops.attention(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)[0]
+        ctx = ops.attend(q, k, v, cos, sin, b, num_tokens, self.num_heads, self.num_kv_groups, self.head_dim)
         return self.out_proj(ctx.view(b, num_tokens, self.d_out), residual)
 
 

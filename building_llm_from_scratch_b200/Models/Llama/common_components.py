@@ -13,6 +13,10 @@ def compute_rope(x, cos, sin):
     """common_components.py:6-35. x: [B, H, T, hd] -> rotated copy (stand-alone form; inside the
     attention module RoPE is applied by the fused attention op on the [B*T, H*hd] layout)."""
     B, H, T, hd = x.shape
+    if x.dtype == torch.float32:      # fp32 parity mode
+        from ... import f32
+        flat = x.transpose(1, 2).reshape(B * T, H * hd).contiguous()
+        return f32.rope(flat, cos, sin, T, H, hd).view(B, T, H, hd).transpose(1, 2)
     flat = x.transpose(1, 2).reshape(B * T, H * hd).contiguous()
     out = K.rope(flat, cos.to(torch.bfloat16), sin.to(torch.bfloat16), B, T, H, hd)
     return out.view(B, T, H, hd).transpose(1, 2).to(dtype=x.dtype)

@@ -99,6 +99,18 @@ SIGNATURES = {
     "b200_dropout_mask_u8": (I, [P, I64, F, C.c_uint64, P]),
     "b200_collate_i64": (I, [P, P, P, I64, I64, I64, I64, I64, P, P, P]),
     "b200_window_batch_i64": (I, [P, I64, P, I64, I64, P, P, P]),
+    "b200_gemm_f32": (I, [P, I64, I64, I64, P, I64, I64, I64, P, P, I64, I64, I64, I64, I64, I64, I64, F, F, P]),
+    "b200_softmax_causal_f32": (I, [P, I64, I64, F, P]),
+    "b200_softmax_bwd_f32": (I, [P, P, I64, I64, F, P]),
+    "b200_layernorm_fwd_f32": (I, [P, P, P, P, P, P, I64, I64, F, P]),
+    "b200_layernorm_bwd_f32": (I, [P, P, P, P, P, P, P, P, I64, I64, P]),
+    "b200_elementwise_f32": (I, [P, P, P, I64, I, P]),
+    "b200_swiglu_bwd_f32": (I, [P, P, P, P, P, I64, P]),
+    "b200_rope_f32": (I, [P, P, P, P, I64, I64, I64, I64, I, P]),
+    "b200_cross_entropy_f32_workspace_bytes": (SZ, [I64]),
+    "b200_cross_entropy_f32": (I, [P, I64, P, P, I64, I64, I, P, SZ, P]),
+    "b200_embedding_fwd_f32": (I, [P, P, P, P, I64, I64, I64, P]),
+    "b200_embedding_bwd_f32": (I, [P, P, P, P, I64, I64, I64, P]),
     "b200_attention_decode_bf16": (I, [P, I64, P, P, I64, I64, P, I64, I64, I64, I64, I64, I64, F, P]),
     "b200_attention_bwd_workspace_bytes": (SZ, [I64, I64, I64, I64]),
     "b200_attention_bwd_rope_bf16": (I, [P, I64, P, I64, P, I64, P, I64, P, I64, P, P, SZ, P, I64, P, I64, P,

@@ -439,6 +439,9 @@ def rmsnorm_bwd(x, w, dy, eps=1e-5, dres=None, need_dw=False, dw_out=None):
 
 
 def layernorm_fwd(x, w, b, eps=1e-5):
+    if x.dtype == torch.float32:
+        from . import f32
+        return f32.layernorm_fwd(x, w, b, eps)
     _need_cuda(x, w, b)
     lib = _lib.load()
     x2 = x.reshape(-1, x.shape[-1])
@@ -453,6 +456,9 @@ def layernorm_fwd(x, w, b, eps=1e-5):
 
 def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True, dw_out=None, db_out=None):
     """dw_out / db_out: fp32 [d] accumulators (main_grad of weight / bias) the kernel adds into."""
+    if x.dtype == torch.float32:
+        from . import f32
+        return f32.layernorm_bwd(x, w, dy, mean, rstd, need_dw, dw_out, db_out)
     _need_cuda(x, w, dy, dw_out, db_out)
     lib = _lib.load()
     x2 = x.reshape(-1, x.shape[-1])
@@ -495,6 +501,9 @@ def swiglu_bwd(a, b, dh, da=None, db=None):
 
 
 def gelu_fwd(x):
+    if x.dtype == torch.float32:
+        from . import f32
+        return f32.gelu_fwd(x)
     _need_cuda(x)
     y = torch.empty_like(x)
     _lib.check(_lib.load().b200_gelu_fwd_bf16(_p(x), _p(y), x.numel(), _stream()), "gelu_fwd")
@@ -502,6 +511,9 @@ def gelu_fwd(x):
 
 
 def gelu_bwd(x, dy):
+    if x.dtype == torch.float32:
+        from . import f32
+        return f32.gelu_bwd(x, dy)
     _need_cuda(x, dy)
     dx = torch.empty_like(x)
     _lib.check(_lib.load().b200_gelu_bwd_bf16(_p(x), _p(dy), _p(dx), x.numel(), _stream()), "gelu_bwd")
@@ -527,6 +539,9 @@ def rope_(x2d, cos, sin, B, T, nheads, hd, inverse=False, bf16_steps=True):
 
 
 def embedding_fwd(idx, tok_w, pos_w=None):
+    if tok_w.dtype == torch.float32:
+        from . import f32
+        return f32.embedding_fwd(idx, tok_w, pos_w)
     _need_cuda(idx, tok_w, pos_w)
     B, T = idx.shape
     d = tok_w.shape[1]
@@ -538,6 +553,9 @@ def embedding_fwd(idx, tok_w, pos_w=None):
 
 def embedding_bwd(idx, dout, vocab, ctx=None, dtok_out=None, dpos_out=None):
     """dtok_out / dpos_out: fp32 accumulators ([vocab, d] / [ctx, d], e.g. main_grad) to scatter-add into."""
+    if dout.dtype == torch.float32:
+        from . import f32
+        return f32.embedding_bwd(idx, dout, vocab, ctx, dtok_out, dpos_out)
     _need_cuda(idx, dout, dtok_out, dpos_out)
     B, T = idx.shape
     d = dout.shape[-1]

@@ -20,9 +20,11 @@ import weakref
 import torch
 from torch import Tensor
 
+from . import f32 as K32
 from . import kernels as K
 
 BF16 = torch.bfloat16
+F32 = torch.float32      # fp32 parity mode: ops handed float32 activations run the plain-fp32 kernels (f32.py)
 
 
 def _pitch_ok(t: Optional[Tensor]) -> Optional[Tensor]:
@@ -172,6 +174,9 @@ def lora_linear(x: Tensor, weight: Tensor, bias: Optional[Tensor], A: Optional[T
     x2 = _flat2d(x)
     out_f = weight.shape[0]
     res2 = None if residual is None else _flat2d(residual)
+    if x.dtype == F32:
+        y, t = K32.linear_fwd(x2, weight, bias, A, B, scaling, res2)
+        return y.view(*x.shape[:-1], out_f), (t if t is not None else x2.new_empty((0,)))
     if A is not None:
         # A [in, r] and B [r, out] are read as MN-major operands: no transposes are materialised
         t = K.gemm_ex(x2, A, b1_mn=True, alpha=scaling)
@@ -278,6 +283,10 @@ def _lora_linear_bwd(ctx, dy, _dt):
     need = ctx.needs_input_grad
     x2 = _flat2d(x)
     dy2 = _flat2d(dy)
+    if dy2.dtype == F32:
+        dx, dW, dbias, dA, dB = K32.linear_bwd(dy2.contiguous(), x2, weight, ctx.bias_ref, A, B, t, ctx.scaling, need[0])
+        return ((None if dx is None else dx.view(x.shape)), dW, dbias, dA, dB, None,
+                (dy if (ctx.has_res and need[6]) else None))
     dx = dW = dbias = dA = dB = None
     u = None
     if A is not None and (need[0] or need[3]):
@@ -393,7 +402,7 @@ def linears_of_same_input(x, modules):
     from .lora import LinearWithLoRA
     lora = [isinstance(m, LinearWithLoRA) for m in modules]
     bases = [m.linear if l else m for m, l in zip(modules, lora)]
-    if any(b.bias is not None for b in bases) or (any(lora) and not all(lora)):
+    if x.dtype != BF16 or any(b.bias is not None for b in bases) or (any(lora) and not all(lora)):
         return [m(x) for m in modules]
     n = len(modules)
     if all(lora):
@@ -772,7 +781,7 @@ lora_fc12_swiglu.register_autograd(_lfs_bwd, setup_context=_lfs_setup)
 def fc12_swiglu(x, fc1, fc2):
     """(ab, h) through lora_fc12_swiglu for two bias-free up projections (both plain or both LoRA-wrapped with the
     same rank and scaling, frozen base weights), or None when that does not apply."""
-    if os.environ.get("B200_PACKED", "1") == "0" or os.environ.get("B200_SWIGLU_FWD_EPILOGUE", "1") == "0":
+    if x.dtype != BF16 or os.environ.get("B200_PACKED", "1") == "0" or os.environ.get("B200_SWIGLU_FWD_EPILOGUE", "1") == "0":
         return None
     from .lora import LinearWithLoRA
     mods = [fc1, fc2]
@@ -799,7 +808,7 @@ def fc12_swiglu(x, fc1, fc2):
 def linears_packed(x, modules):
     """Packed output of several bias-free linears (all plain or all LoRA-wrapped with one scaling and one
     rank) of the same x, or None when they cannot be fused that way."""
-    if os.environ.get("B200_PACKED", "1") == "0":
+    if x.dtype != BF16 or os.environ.get("B200_PACKED", "1") == "0":
         return None
     from .lora import LinearWithLoRA
     lora = [isinstance(m, LinearWithLoRA) for m in modules]
@@ -1039,6 +1048,63 @@ def _attention_bwd(ctx, do, _dl, _dq, _dk):
 attention.register_autograd(_attention_bwd, setup_context=_attention_setup)
 
 
+# fp32 parity mode: the same attention with materialised scores in plain fp32 (f32.py); P is saved for backward
+@torch.library.custom_op("b200llm::attention_f32", mutates_args=())
+def attention_f32(q: Tensor, k: Tensor, v: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: int, T: int, h: int,
+                  hkv: int, hd: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """float32 q [B*T, h*hd], k / v [B*T, hkv*hd] -> (o, P [B, h, T, T], q_rot, k_rot)."""
+    if cos is not None:
+        qr, kr = K32.rope(q, cos, sin, T, h, hd), K32.rope(k, cos, sin, T, hkv, hd)
+    else:
+        qr, kr = q.contiguous(), k.contiguous()
+    o, P = K32.attention_fwd(qr, kr, v, B, T, h, hkv, hd)
+    if cos is None:
+        return o, P, q.new_empty((0,)), q.new_empty((0,))
+    return o, P, qr, kr
+
+
+@attention_f32.register_fake
+def _(q, k, v, cos, sin, B, T, h, hkv, hd):
+    o, P = q.new_empty((B * T, h * hd)), q.new_empty((B, h, T, T))
+    if cos is None:
+        return o, P, q.new_empty((0,)), q.new_empty((0,))
+    return o, P, q.new_empty((B * T, h * hd)), q.new_empty((B * T, hkv * hd))
+
+
+def _attention_f32_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)
+    q, k, v, cos, sin, B, T, h, hkv, hd = inputs
+    o, P, qr, kr = output
+    if cos is None:
+        qr, kr = q, k
+    ctx.save_for_backward(qr, kr, v, P, cos, sin)
+    ctx.dims = (B, T, h, hkv, hd)
+
+
+def _attention_f32_bwd(ctx, do, _dp, _dq, _dk):
+    if do is None:
+        return (None,) * 10
+    qr, kr, v, P, cos, sin = ctx.saved_tensors
+    B, T, h, hkv, hd = ctx.dims
+    dq, dk, dv = K32.attention_bwd(qr, kr, v, P, _flat2d(do), B, T, h, hkv, hd)
+    if cos is not None:
+        dq, dk = K32.rope(dq, cos, sin, T, h, hd, inverse=True), K32.rope(dk, cos, sin, T, hkv, hd, inverse=True)
+    return (dq, dk, dv) + (None,) * 7
+
+
+attention_f32.register_autograd(_attention_f32_bwd, setup_context=_attention_f32_setup)
+
+
+def attend(q, k, v, cos, sin, B, T, h, hkv, hd, dropout_p=0.0, seed=0):
+    """Context vectors [B*T, h*hd] of causal attention over q / k (rotated when cos / sin are given) and v: the
+    tcgen05 kernels for bf16, the plain-fp32 path for float32 (parity mode; no dropout there)."""
+    if q.dtype == F32:
+        if dropout_p > 0:
+            raise RuntimeError("the fp32 parity mode runs with drop_rate = 0 (SURVEY.md H5)")
+        return attention_f32(q, k, v, cos, sin, B, T, h, hkv, hd)[0]
+    return attention(q, k, v, cos, sin, B, T, h, hkv, hd, dropout_p, seed)[0]
+
+
 @torch.library.custom_op("b200llm::attention_qkv", mutates_args=())
 def attention_qkv(qkv: Tensor, cos: Optional[Tensor], sin: Optional[Tensor], B: int, T: int, h: int, hkv: int,
                   hd: int, dropout_p: float = 0.0, seed: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
@@ -1124,6 +1190,8 @@ def _drop_step(like: Tensor, p: float):
 @torch.library.custom_op("b200llm::dropout", mutates_args=())
 def dropout(x: Tensor, residual: Optional[Tensor], p: float, seed: int) -> Tensor:
     """(residual +) keep * x / (1 - p); keep is a counter-based function of (seed + step counter, element index)."""
+    if x.dtype != BF16:
+        raise RuntimeError("b200llm dropout is a bf16 kernel: the fp32 parity mode runs with drop_rate = 0 (SURVEY.md H5)")
     return K.dropout(x, p, seed, residual, seed_dev=_drop_step(x, p)).view(x.shape)
 
 
@@ -1156,6 +1224,8 @@ def new_seed() -> int:
 # ======================================================================================
 @torch.library.custom_op("b200llm::swiglu", mutates_args=())
 def swiglu(a: Tensor, b: Tensor) -> Tensor:
+    if a.dtype == F32:
+        return K32.swiglu_fwd(a, b)
     return K.swiglu_fwd(_flat2d(a), _flat2d(b)).view(a.shape)
 
 
@@ -1170,6 +1240,9 @@ def _swiglu_setup(ctx, inputs, output):
 
 def _swiglu_bwd(ctx, dh):
     a, b = ctx.saved_tensors
+    if a.dtype == F32:
+        da, db = K32.swiglu_bwd(a, b, dh)
+        return da.view(a.shape), db.view(b.shape)
     da, db = K.swiglu_bwd(_flat2d(a), _flat2d(b), dh.contiguous())
     return da.view(a.shape), db.view(b.shape)
 
@@ -1284,7 +1357,7 @@ swiglu_down.register_autograd(_swiglu_down_bwd, setup_context=_swiglu_down_setup
 
 def swiglu_down_module(ab, fc3, residual, h=None):
     """swiglu_down for a bias-free fc3 module (plain or LoRA-wrapped); None when it does not apply."""
-    if os.environ.get("B200_PACKED", "1") == "0":
+    if ab.dtype != BF16 or os.environ.get("B200_PACKED", "1") == "0":
         return None
     from .lora import LinearWithLoRA
     if isinstance(fc3, LinearWithLoRA):
@@ -1371,9 +1444,9 @@ def cross_entropy(logits: Tensor, targets: Tensor) -> Tuple[Tensor, Tensor]:
     V = logits.shape[-1]
     M = logits.numel() // V
     ld = (V + 7) // 8 * 8
-    buf = torch.empty((M, ld), device=logits.device, dtype=BF16)
+    buf = torch.empty((M, ld), device=logits.device, dtype=logits.dtype)
     buf[:, :V].copy_(logits.reshape(M, V))
-    loss = K.cross_entropy_(buf[:, :V], targets)
+    loss = (K32 if logits.dtype == F32 else K).cross_entropy_(buf[:, :V], targets)
     return loss.reshape(()), buf
 
 
@@ -1413,6 +1486,16 @@ def linear_cross_entropy(x: Tensor, weight: Tensor, A: Optional[Tensor], B: Opti
     no_grad) skips the dlogits pass of the cross-entropy kernel."""
     x2 = _flat2d(x)
     V = weight.shape[0]
+    if x.dtype == F32:          # parity mode: every row, fp32 logits in the work buffer
+        M, ld = x2.shape[0], (V + 7) // 8 * 8
+        buf = torch.empty((M, ld), device=x.device, dtype=F32)
+        K32.gemm(x2, weight, out=buf[:, :V])
+        t = x2.new_empty((0,))
+        if A is not None:
+            t = K32.gemm(x2, A.t(), alpha=scaling)
+            K32.gemm(t, B.t(), out=buf[:, :V], beta=1.0)
+        loss = K32.cross_entropy_(buf[:, :V], targets, write_grad=write_grad)
+        return loss.reshape(()), buf, t, x2.new_empty((0,)), x2.new_empty((0,), dtype=torch.int32)
     if capacity > 0 and capacity < x2.shape[0]:
         rows, tg, idx = K.compact_gather(x2, targets, capacity)
     else:
@@ -1459,6 +1542,12 @@ def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
     if not ctx.write_grad:
         raise RuntimeError("linear_cross_entropy was run with write_grad=False (evaluation): it has no backward")
     x, weight, A, B, t, buf, rows, idx = ctx.saved_tensors
+    if buf.dtype == F32:
+        V = weight.shape[0]
+        dl = K32.scale_by_device_scalar(buf, dloss.detach().to(F32))[:, :V]
+        dx, dW, _, dA, dB = K32.linear_bwd(dl, _flat2d(x), weight, None, A, B, t if A is not None else None, ctx.scaling,
+                                           ctx.needs_input_grad[0])
+        return (None if dx is None else dx.view(x.shape)), dW, dA, dB, None, None, None, None
     K.scale_dev_(buf, dloss.detach().reshape(1).to(torch.float32))
     wref, aref, bref = weight, A, B
     need = ctx.needs_input_grad

@@ -386,6 +386,36 @@ int b200_dropout_bf16(const void* x, const void* res, void* y, int64_t n, float 
                       const uint64_t* seed_dev, void* stream);
 int b200_dropout_mask_u8(void* out, int64_t n, float p, uint64_t seed, void* stream);
 
+/* ---- fp32 parity mode (csrc/fp32.cu) ------------------------------------------------------------------------
+ * The same operators in plain fp32 (FFMA accumulation, no tensor cores) so that the fp32 tolerance class of the
+ * north star — 1e-4 relative per op — can be checked on the GPU: the reference's GPT-2 modules are fp32 as written
+ * (Models/GPT2/GPT2.py:20-23,59-61) and its Llama sub-modules accept dtype=float32. Correctness mode, not tuned.
+ * b200_gemm_f32: C[b][m,n] = alpha * sum_k A[b][m,k] B[b][n,k] (+ bias[n]) (+ beta C[b][m,n]); every matrix is given by
+ * (pointer, batch stride, row stride, column stride) in elements, so transposes and head slices are views.
+ * b200_softmax_causal_f32: rows of [.., T, T] scores: softmax over k <= q of S * scale, zeros beyond (GPT2.py:38-42,
+ * Llama3.py:148-152); b200_softmax_bwd_f32: dS = P (dP - sum_k dP P) scale in place over dP.
+ * b200_elementwise_f32 op: 0 y = gelu(a) (erf), 1 y = b gelu'(a), 2 y = a + b, 3 y = silu(a) b, 4 y = a * b[0]. */
+int b200_gemm_f32(const float* A, int64_t a_bs, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_bs, int64_t b_rs,
+                  int64_t b_cs, const float* bias, float* C, int64_t c_bs, int64_t c_rs, int64_t c_cs, int64_t batch,
+                  int64_t M, int64_t N, int64_t K, float alpha, float beta, void* stream);
+int b200_softmax_causal_f32(float* S, int64_t rows, int64_t T, float scale, void* stream);
+int b200_softmax_bwd_f32(const float* P, float* dP, int64_t rows, int64_t T, float scale, void* stream);
+int b200_layernorm_fwd_f32(const float* x, const float* w, const float* b, float* y, float* mean, float* rstd, int64_t M,
+                           int64_t d, float eps, void* stream);
+int b200_layernorm_bwd_f32(const float* x, const float* w, const float* dy, const float* mean, const float* rstd, float* dx,
+                           float* dw, float* db, int64_t M, int64_t d, void* stream);
+int b200_elementwise_f32(const float* a, const float* b, float* y, int64_t n, int op, void* stream);
+int b200_swiglu_bwd_f32(const float* a, const float* b, const float* dh, float* da, float* db, int64_t n, void* stream);
+int b200_rope_f32(const float* x, float* y, const float* cos, const float* sin, int64_t rows, int64_t T, int64_t nheads,
+                  int64_t hd, int inverse, void* stream);
+size_t b200_cross_entropy_f32_workspace_bytes(int64_t M);
+int b200_cross_entropy_f32(float* logits, int64_t ld, const int64_t* targets, float* loss_out, int64_t M, int64_t V,
+                           int write_grad, void* workspace, size_t workspace_bytes, void* stream);
+int b200_embedding_fwd_f32(const int64_t* idx, const float* tok_w, const float* pos_w, float* out, int64_t M, int64_t T,
+                           int64_t d, void* stream);
+int b200_embedding_bwd_f32(const int64_t* idx, const float* dout, float* dtok_w, float* dpos_w, int64_t M, int64_t T,
+                           int64_t d, void* stream);
+
 /* ---- K2 decode: one new query token per sequence against a KV cache ---------------------------
  * o[b, head, :] = softmax(q[b, head, :]·K[b, 0..T, kv(head), :]^T * scale)·V[b, 0..T, kv(head), :]
  * q, o: [B, h*hd] (row pitches ldq, ldo); k_cache, v_cache: [B, t_max, hkv*hd] bf16 with row pitch ldc

@@ -95,7 +95,9 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        opts = dist.ProcessGroupNCCL.Options()       # see bench.nccl_options
+        opts.is_high_priority_stream = os.environ.get("B200_NCCL_HIGH_PRIORITY", "1") != "0"
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
 
     from building_llm_from_scratch_b200 import _lib
     from building_llm_from_scratch_b200.datautils.synthetic import gutenberg_batch
