@@ -39,6 +39,7 @@ SIGNATURES = {
     "b200_version": (I, []),
     "b200_init": (I, [I]),
     "b200_last_error": (C.c_char_p, []),
+    "b200_set_sm_limit": (I, [I]),
     "b200_launch_count": (C.c_uint64, []),
     "b200_gemm_nt_bf16": (I, [P, I64, P, I64, I64, P, I64, P, I64, I64, P, P, I64, P, I64, I64, I64, I, P]),
     "b200_gemm_ex": (I, [P, I64, I, P, I64, I, I64, P, I64, I, P, I64, I, I64, P, P, I64, P, I64,

@@ -40,6 +40,11 @@ static int ensure_driver() {
   return 0;
 }
 
+// SMs the persistent kernels size their grids for. b200_set_sm_limit() lowers it below the device's count so that a
+// few SMs stay free for the CTAs of a concurrent kernel — the NCCL all-reduce of a data-parallel step, which a grid
+// of one persistent CTA per SM otherwise cannot overlap with (0 = no limit).
+static std::atomic<int> g_sm_limit{0};
+
 int b200_num_sms() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
@@ -49,7 +54,14 @@ int b200_num_sms() {
       n = 148;
     g_sms[dev] = n;
   }
-  return g_sms[dev];
+  const int lim = g_sm_limit.load();
+  return (lim > 0 && lim < g_sms[dev]) ? lim : g_sms[dev];
+}
+
+extern "C" int b200_set_sm_limit(int sms) {
+  if (sms < 0 || (sms > 0 && sms < 8) || (sms & 1)) return b200_set_error(B200_ERR_ARG, "set_sm_limit: %d must be 0 or an even count >= 8", sms);
+  g_sm_limit = sms;
+  return 0;
 }
 
 int b200_make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,

@@ -37,6 +37,11 @@ extern "C" {
 int b200_version(void);
 /* Binds driver entry points and caches device properties; optional (done lazily otherwise). */
 int b200_init(int device);
+/* SMs the persistent kernels (GEMMs, element-wise grids) size their launches for: 0 = every SM (default), else an
+ * even count >= 8 below the device's. A data-parallel step with a large gradient exchange (full fine-tuning: the
+ * DDP all-reduce of build_components.py:176 moves every gradient) sets it a few SMs below 148 so that NCCL's CTAs
+ * find room while backward runs — a grid of one persistent CTA per SM cannot overlap with another kernel. */
+int b200_set_sm_limit(int sms);
 /* Thread-local text of the last error returned on this thread. */
 const char* b200_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */

@@ -85,6 +85,7 @@ def main():
     ap.add_argument("--eager", action="store_true", help="no CUDA graph")
     ap.add_argument("--zero", action="store_true", help="ZeRO-1 optimizer-state sharding (--use_zero_opt)")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
+    ap.add_argument("--sm-limit", type=int, default=0, help="SMs the persistent kernels may fill (0 = all): leaves room for NCCL")
     args = ap.parse_args()
 
     import torch.distributed as dist
@@ -106,6 +107,8 @@ def main():
     from building_llm_from_scratch_b200.optim import B200AdamW
     from building_llm_from_scratch_b200.train import Trainer
     _lib.check(_lib.load().b200_init(local_rank), "init")
+    if args.sm_limit:
+        _lib.check(_lib.load().b200_set_sm_limit(args.sm_limit), "set_sm_limit")
     model, cfg, T, what = build_config(args.config, dev, args.layers, args.drop)
     n_train = sum(p.numel() for p in model.parameters() if p.requires_grad)
     fpt = algorithmic_flops_per_token(model, T, cfg["emb_dim"], cfg["n_layers"])
@@ -168,7 +171,7 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "tokens_per_s": tok_s,
             "algorithmic_gflops_per_token": fpt / 1e9,
             "frac_of_burst_bf16_peak_per_gpu": tok_s / world * fpt / 1e12 / burst, "burst_peak_tflops": burst,
-            "ranks_identical": identical, "comm_exposed_ms": comm_exposed,
+            "ranks_identical": identical, "comm_exposed_ms": comm_exposed, "sm_limit": args.sm_limit,
             "allreduce_bytes_per_step": None if world == 1 else 4 * sum(g["g"].numel() for g in opt._groups.values()),
             "losses": [round(l, 4) for l in losses], "b200llm_launches_per_step": step.launches_per_step,
             "b200llm_launches_total": _lib.launch_count() - n0,
