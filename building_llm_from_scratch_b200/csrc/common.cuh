@@ -221,6 +221,19 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (M rows = TMEM lanes, K bf16 elements packed two per 32-bit
+// column, K-major) is read from tensor memory instead of shared memory.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // arrive on an mbarrier once all previously issued MMAs of this thread retire
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile(
@@ -403,6 +416,15 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
   return r;
+}
+// 256-bit global store (sm_100: STG.E.ENL2.256): two uint4 = 16 bf16 to a 32-byte aligned address — a whole 32-byte
+// sector per thread and instruction. Epilogues whose lanes each write their own row issue one sector write per lane
+// either way; with 16-byte stores every sector took two instructions and arrived at L2 in halves.
+__device__ __forceinline__ void st_v8(void* p, uint4 a, uint4 b) {
+  asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(p), "l"(((unsigned long long)a.y << 32) | a.x),
+               "l"(((unsigned long long)a.w << 32) | a.z), "l"(((unsigned long long)b.y << 32) | b.x),
+               "l"(((unsigned long long)b.w << 32) | b.z)
+               : "memory");
 }
 __device__ __forceinline__ uint4 ld_v4(const void* p) { return *reinterpret_cast<const uint4*>(p); }
 __device__ __forceinline__ void st_v4(void* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }

@@ -165,7 +165,10 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
       // GELU to that rounded value, like nn.GELU on the linear's bf16 output
       if (row_ok) {
         bf16* Zp = p.Z + row * p.ldz + col0;
-        if (full_cols && (p.ldz & 7) == 0) {
+        if (full_cols && (p.ldz & 15) == 0 && (((uintptr_t)p.Z) & 31) == 0) {
+          st_v8(Zp, pack8(&v[0]), pack8(&v[8]));
+          st_v8(Zp + 16, pack8(&v[16]), pack8(&v[24]));
+        } else if (full_cols && (p.ldz & 7) == 0) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) st_v4(Zp + q * 8, pack8(&v[q * 8]));
         } else {
@@ -245,7 +248,10 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, long long row, 
     }
   } else {
     bf16* C = (bf16*)p.C + row * p.ldc + col0;
-    if (full_cols && (p.ldc & 7) == 0) {
+    if (full_cols && (p.ldc & 15) == 0 && (((uintptr_t)p.C) & 31) == 0) {
+      st_v8(C, pack8(&v[0]), pack8(&v[8]));
+      st_v8(C + 16, pack8(&v[16]), pack8(&v[24]));
+    } else if (full_cols && (p.ldc & 7) == 0) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) st_v4(C + q * 8, pack8(&v[q * 8]));
     } else {
@@ -824,19 +830,35 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           tmem_ld_32x32(taddr + P_BN / 2, rb);
           tmem_ld_wait();
           if (row_ok && colf + k * 32 + 32 <= F) {
+            const bool wide = ((p.ldc | p.ldr | F) & 15) == 0 && ((((uintptr_t)p.C) | ((uintptr_t)p.R)) & 31) == 0;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              float a[8], b[8], h[8];
+            for (int q2 = 0; q2 < 2; ++q2) {
+              uint4 pa[2], pb[2], ph[2];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                a[j] = bf16_round(__uint_as_float(ra[q * 8 + j]) * p.alpha);
-                b[j] = bf16_round(__uint_as_float(rb[q * 8 + j]) * p.alpha);
-                const float sg = bf16_round(__fdividef(1.f, 1.f + __expf(-a[j])));
-                h[j] = bf16_round(a[j] * sg) * b[j];
+              for (int qq = 0; qq < 2; ++qq) {
+                const int q = q2 * 2 + qq;
+                float a[8], b[8], h[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  a[j] = bf16_round(__uint_as_float(ra[q * 8 + j]) * p.alpha);
+                  b[j] = bf16_round(__uint_as_float(rb[q * 8 + j]) * p.alpha);
+                  const float sg = bf16_round(__fdividef(1.f, 1.f + __expf(-a[j])));
+                  h[j] = bf16_round(a[j] * sg) * b[j];
+                }
+                pa[qq] = pack8(a);
+                pb[qq] = pack8(b);
+                ph[qq] = pack8(h);
               }
-              st_v4(Cab + k * 32 + q * 8, pack8(a));
-              st_v4(Cab + F + k * 32 + q * 8, pack8(b));
-              st_v4(H + k * 32 + q * 8, pack8(h));
+              const int c = k * 32 + q2 * 16;
+              if (wide) {                       // 32-byte stores: a whole sector per lane and instruction
+                st_v8(Cab + c, pa[0], pa[1]);
+                st_v8(Cab + F + c, pb[0], pb[1]);
+                st_v8(H + c, ph[0], ph[1]);
+              } else {
+                st_v4(Cab + c, pa[0]); st_v4(Cab + c + 8, pa[1]);
+                st_v4(Cab + F + c, pb[0]); st_v4(Cab + F + c + 8, pb[1]);
+                st_v4(H + c, ph[0]); st_v4(H + c + 8, ph[1]);
+              }
             }
           }
         }
