@@ -13,6 +13,7 @@
 // columns, two CTAs), so one CTA's softmax overlaps the others' MMAs and barrier / TMEM-load latencies. Causality is a predicate on the diagonal tiles; fully masked tiles are never loaded.
 //
 // Roofline: tensor pipe / MUFU (head_dim 64: 8192 exp2 per 128x64 tile vs 256 MMA cycles).
+#include <cstdlib>
 #include <type_traits>
 
 #include "common.cuh"
@@ -73,16 +74,20 @@ struct FwdParams {
   float* lse;
 };
 
-template <int HDIM, bool DROP>
+// PT: P (the bf16 softmax weights) goes to tensor memory and feeds O += P V as the MMA's A operand from there, instead
+// of a swizzled shared-memory tile: 16 KB of stores and 16 KB of operand reads less per tile on a kernel whose MMAs
+// are bound by shared-memory bandwidth. Costs 32 more TMEM columns: 256 per CTA, two CTAs per SM.
+template <int HDIM, bool DROP, bool PT>
 // (the dropout variant needs ~30 more registers: two CTAs per SM instead of three rather than 1.3 KB of spills)
-__global__ void __launch_bounds__(224, DROP ? 2 : FwdCfg<HDIM>::CTAS)
+__global__ void __launch_bounds__(224, (DROP || PT) ? 2 : FwdCfg<HDIM>::CTAS)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   constexpr int HD = HDIM;
   constexpr int Q_BYTES = FwdCfg<HDIM>::Q_BYTES, KV_BYTES = FwdCfg<HDIM>::KV_BYTES;
-  constexpr uint32_t TMEM_COLS = FwdCfg<HDIM>::TMEM_COLS;
+  constexpr uint32_t TMEM_COLS = PT ? 256 : FwdCfg<HDIM>::TMEM_COLS;
+  constexpr uint32_t P_COL = 64 + HDIM;     // PT: P [128 lanes x 64 keys] bf16 = 32 columns behind S (64) and O (HDIM)
   constexpr int NSK = FwdCfg<HDIM>::NSK, NSV = FwdCfg<HDIM>::NSV;
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + Q_BYTES;
@@ -184,9 +189,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const uint32_t aP = smem_u32(sP);
         const uint32_t aV = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16_ss(tmem_base + 64, umma_desc_k128(aP + k * 32), umma_desc_mn128(aV + k * 2048, 8192),
-                       idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < BKV / 16; ++k) {
+          if (PT)      // A = 16 keys of P from tensor memory: 8 columns per k step
+            umma_bf16_ts(tmem_base + 64, tmem_base + P_COL + k * 8, umma_desc_mn128(aV + k * 2048, 8192), idesc_pv,
+                         (j > 0 || k > 0) ? 1u : 0u);
+          else
+            umma_bf16_ss(tmem_base + 64, umma_desc_k128(aP + k * 32), umma_desc_mn128(aV + k * 2048, 8192),
+                         idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+        }
         umma_commit(&v_empty[s]);
         umma_commit(o_done);
       }
@@ -258,12 +268,18 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(o_done, (j - 1) & 1);
         tc_fence_after();
       }
-      // P row -> smem, K-major 128B-swizzled (16-byte chunk index XOR row % 8)
-      const uint32_t prow = smem_u32(sP) + row * 128;
+      if (PT) {
+        // P row -> tensor memory: this thread's lane, 32 columns of two bf16 each (keys 2c, 2c + 1 in column c)
+        tmem_st_32x32(tlane + P_COL, pk);
+        tmem_st_wait();
+      } else {
+        // P row -> smem, K-major 128B-swizzled (16-byte chunk index XOR row % 8)
+        const uint32_t prow = smem_u32(sP) + row * 128;
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        sts_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-      fence_proxy_async_smem();
+        for (int c = 0; c < 8; ++c)
+          sts_v4(prow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+        fence_proxy_async_smem();
+      }
       if (j > 0 && !__all_sync(0xffffffffu, alpha == 1.f)) {
         uint32_t o[32];
 #pragma unroll
@@ -338,10 +354,15 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<HD, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set[dev & 63] = true;
   }
+  // measured (B200): P through TMEM pays at head_dim 128 (218 -> 202 us at B1 T4096; both variants run two CTAs per SM)
+  // and costs at head_dim 64 (130 -> 136 us: it gives up the third CTA per SM); B200_ATTN_P_TMEM=0/1 overrides
+  static const int p_tmem_env = [] { const char* e = getenv("B200_ATTN_P_TMEM"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
+  const bool p_tmem = p_tmem_env >= 0 ? p_tmem_env == 1 : HD == 128;
   FwdParams p;
   p.B = (int)B; p.T = (int)T; p.H = (int)h; p.HKV = (int)hkv;
   p.nqt = (int)((T + BQ - 1) / BQ);
@@ -350,8 +371,9 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
-  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
-  else attn_fwd_tc_kernel<HD, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
+  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
+  else if (p_tmem) attn_fwd_tc_kernel<HD, false, true><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
+  else attn_fwd_tc_kernel<HD, false, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -433,7 +455,11 @@ __device__ __forceinline__ void rope_inverse_pair(uint32_t* a, uint32_t* b, cons
   }
 }
 
-template <int HDIM, bool DROP>
+// DT: P^T and dS^T go to tensor memory — over the S^T / dP^T columns their softmax group has just read — and feed the
+// accumulating products as A operands from there, instead of swizzled shared-memory panels (32 KB of stores and 32 KB
+// of operand reads less per step; the kernel is bound by shared-memory bandwidth). The score issuer then has to wait
+// for the accumulating products of the buffer's previous step (panel_free) before it overwrites the columns.
+template <int HDIM, bool DROP, bool DT>
 __global__ void __launch_bounds__(DkvCfg<HDIM>::THREADS, 1)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                        const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
@@ -528,7 +554,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const int stg = s % NSTG, buf = s % NG, use = s / NG;
         const uint32_t aQ = smem_u32(sQ + stg * QS_BYTES), adO = smem_u32(sdO + stg * QS_BYTES);
         mbar_wait(&qdo_full[stg], (s / NSTG) & 1);
-        if (use > 0) mbar_wait(&st_empty[buf], (use - 1) & 1);
+        if (use > 0) mbar_wait(DT ? &panel_free[buf] : &st_empty[buf], (use - 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -555,13 +581,23 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         mbar_wait(&ps_full[buf], (s / NG) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < QS / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DV, umma_desc_k128(aPt + k * 32), umma_desc_mn128(adO + k * 2048, 8192), id_acc,
-                       (s > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < QS / 16; ++k) {
+          if (DT)
+            umma_bf16_ts(tmem_base + C_DV, tmem_base + C_ST + buf * QS + k * 8, umma_desc_mn128(adO + k * 2048, 8192), id_acc,
+                         (s > 0 || k > 0) ? 1u : 0u);
+          else
+            umma_bf16_ss(tmem_base + C_DV, umma_desc_k128(aPt + k * 32), umma_desc_mn128(adO + k * 2048, 8192), id_acc,
+                         (s > 0 || k > 0) ? 1u : 0u);
+        }
 #pragma unroll
-        for (int k = 0; k < QS / 16; ++k)
-          umma_bf16_ss(tmem_base + C_DK, umma_desc_k128(adSt + k * 32), umma_desc_mn128(aQ + k * 2048, 8192), id_acc,
-                       (s > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < QS / 16; ++k) {
+          if (DT)
+            umma_bf16_ts(tmem_base + C_DK, tmem_base + C_DPT + buf * QS + k * 8, umma_desc_mn128(aQ + k * 2048, 8192), id_acc,
+                         (s > 0 || k > 0) ? 1u : 0u);
+          else
+            umma_bf16_ss(tmem_base + C_DK, umma_desc_k128(adSt + k * 32), umma_desc_mn128(aQ + k * 2048, 8192), id_acc,
+                         (s > 0 || k > 0) ? 1u : 0u);
+        }
         umma_commit(&panel_free[buf]);
         umma_commit(&qdo_empty[stg]);
       }
@@ -651,18 +687,26 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             dd[i4 * 2] = f2_to_bf2(dsv[0], dsv[1]);
             dd[i4 * 2 + 1] = f2_to_bf2(dsv[2], dsv[3]);
           }
+            if (DT) {
+            // this thread's key row: 32 query columns of this half = 16 packed columns, over the S^T / dP^T columns
+            // already in registers (half 1 of S^T / dP^T sits in columns 32..63 and is untouched by half 0's write)
+            tmem_st_32x16(tlane + C_ST + buf * QS + hf * 16, pp);
+            tmem_st_32x16(tlane + C_DPT + buf * QS + hf * 16, dd);
+          } else {
             if (hf == 0 && use > 0) mbar_wait(&panel_free[buf], (use - 1) & 1);
 #pragma unroll
-          for (int t4 = 0; t4 < 4; ++t4) {
-            const int ch = (hf * 4 + t4) ^ (row & 7);
-            sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
-            sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+            for (int t4 = 0; t4 < 4; ++t4) {
+              const int ch = (hf * 4 + t4) ^ (row & 7);
+              sts_v4(prow + (ch << 4), pp[4 * t4], pp[4 * t4 + 1], pp[4 * t4 + 2], pp[4 * t4 + 3]);
+              sts_v4(drow + (ch << 4), dd[4 * t4], dd[4 * t4 + 1], dd[4 * t4 + 2], dd[4 * t4 + 3]);
+            }
           }
         }
       };
       if (diag) half_steps(std::true_type{});
       else half_steps(std::false_type{});
-      fence_proxy_async_smem();
+      if (DT) tmem_st_wait();
+      else fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ps_full[buf]);
@@ -737,7 +781,9 @@ struct DqParams {
   const bf16* rope_sin;
 };
 
-template <int HDIM, bool DROP>
+// DT: dS goes to tensor memory (two 32-column buffers) and feeds dQ += dS K as the MMA's A operand from there instead
+// of two swizzled shared-memory tiles (see attn_fwd_tc_kernel's PT): 256 TMEM columns at head_dim 64, 512 at 128.
+template <int HDIM, bool DROP, bool DT>
 __global__ void __launch_bounds__(224, DqCfg<HDIM>::CTAS)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
@@ -786,7 +832,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     mbar_init(&ds_free[1], 1);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  constexpr uint32_t DQ_TMEM = (DT && HDIM == 128) ? 512 : 256;
+  if (warp == 1) tmem_alloc(tmem_slot, DQ_TMEM);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmdO);
@@ -797,7 +844,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  constexpr uint32_t D_S = 0, D_DP = 64, D_DQ = 128;
+  constexpr uint32_t D_S = 0, D_DP = 64, D_DQ = 128, D_DS = 128 + HDIM;    // D_DS: DT only, 2 x 32 columns
 
   if (warp == 0) {
     if (lane == 0) {
@@ -844,9 +891,14 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         tc_fence_after();
         const uint32_t adS = smem_u32(sdS + buf * P_BYTES), aK = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16_ss(tmem_base + D_DQ, umma_desc_k128(adS + k * 32), umma_desc_mn128(aK + k * 2048, 8192),
-                       id_dq, (j > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < BKV / 16; ++k) {
+          if (DT)
+            umma_bf16_ts(tmem_base + D_DQ, tmem_base + D_DS + buf * 32 + k * 8, umma_desc_mn128(aK + k * 2048, 8192), id_dq,
+                         (j > 0 || k > 0) ? 1u : 0u);
+          else
+            umma_bf16_ss(tmem_base + D_DQ, umma_desc_k128(adS + k * 32), umma_desc_mn128(aK + k * 2048, 8192),
+                         id_dq, (j > 0 || k > 0) ? 1u : 0u);
+        }
         umma_commit(&kv_empty[s]);
         umma_commit(&ds_free[buf]);
       }
@@ -918,11 +970,17 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       }
       // buffer `buf` was last read by the dQ product of tile j - 2 (another warp issues those)
       if (j >= 2) mbar_wait(&ds_free[buf], ((j >> 1) - 1) & 1);
-      const uint32_t drow = smem_u32(sdS) + buf * P_BYTES + row * 128;
+      if (DT) {      // dS row -> this thread's TMEM lane: keys 2c, 2c + 1 in column c of the buffer
+        tc_fence_after();
+        tmem_st_32x32(tlane + D_DS + buf * 32, pk);
+        tmem_st_wait();
+      } else {
+        const uint32_t drow = smem_u32(sdS) + buf * P_BYTES + row * 128;
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        sts_v4(drow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-      fence_proxy_async_smem();
+        for (int c = 0; c < 8; ++c)
+          sts_v4(drow + ((c ^ (row & 7)) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+        fence_proxy_async_smem();
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[buf]);
@@ -959,7 +1017,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, DQ_TMEM);
   }
 }
 
@@ -1043,10 +1101,12 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<HD, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DKV_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<HD, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM));
     attr_set[dev & 63] = true;
   }
   const int nqt = (int)((T + BK2 - 1) / BK2);
@@ -1058,8 +1118,11 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
     p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
     const long long grid = (long long)nqt * B * h;
-    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
-    else attn_bwd_dq_tc_kernel<HD, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    // dS through TMEM: 10 us (hd 64, B4 T2048) / 19 us (hd 128, B1 T4096) faster; B200_ATTN_DS_TMEM=0 restores the panels
+    static const bool ds_tmem = [] { const char* e = getenv("B200_ATTN_DS_TMEM"); return !(e && e[0] == '0'); }();
+    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    else if (ds_tmem) attn_bwd_dq_tc_kernel<HD, false, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    else attn_bwd_dq_tc_kernel<HD, false, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
     B200_CHECK_LAUNCH();
   }
   {
@@ -1075,8 +1138,11 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.dk = (bf16*)dk; p.lddk = lddk; p.dv = (bf16*)dv; p.lddv = lddv;
     p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
     const long long grid = (long long)p.nkt * B * hkv;
-    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<HD, true><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
-    else attn_bwd_dkv_tc_kernel<HD, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    // P^T / dS^T through TMEM: 14 us faster at hd 64 (B4 T2048); B200_ATTN_DKV_TMEM=0 restores the shared-memory panels
+    static const bool pt_tmem = [] { const char* e = getenv("B200_ATTN_DKV_TMEM"); return !(e && e[0] == '0'); }();
+    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<HD, true, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    else if (pt_tmem) attn_bwd_dkv_tc_kernel<HD, false, true><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    else attn_bwd_dkv_tc_kernel<HD, false, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(3);
