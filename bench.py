@@ -154,17 +154,18 @@ def kernel_rooflines(device, peaks):
 
 def gemm_traffic_from_profile():
     """DRAM bytes per launch of the dominant kernel (CTA-pair GEMM) from the committed ncu capture
-    (profiles/r1_gemm_traffic_2layer_step_v3.json: dram__bytes_read.sum + dram__bytes_write.sum summed over the
-    launches of a 2-block step); None if the file is absent."""
-    path = os.path.join(ROOT, "profiles", "r1_gemm_traffic_2layer_step_v3.json")
-    try:
-        d = json.load(open(path))
-        for name, v in d.items():
-            if "2cta" in name:
-                return {"dram_bytes_per_launch": v["dram_bytes"] / v["launches"], "launches": v["launches"],
-                        "tensor_active_pct": v.get("tensor_active_pct"), "source": "profiles/r1_gemm_traffic_2layer_step_v3.json"}
-    except Exception:
-        pass
+    (profiles/r2_gemm_traffic_2layer_step.json, made by tools/ncu_launch_summary.py from one ncu pass over a 2-block
+    step: dram__bytes_read.sum + dram__bytes_write.sum summed over the kernel's launches; the round-1 file when that one
+    is absent); None if neither exists."""
+    for rel in ("profiles/r2_gemm_traffic_2layer_step.json", "profiles/r1_gemm_traffic_2layer_step_v3.json"):
+        try:
+            d = json.load(open(os.path.join(ROOT, rel)))
+            for name, v in d.items():
+                if "2cta" in name and "<0>" in name:
+                    return {"dram_bytes_per_launch": v["dram_bytes"] / v["launches"], "launches": v["launches"],
+                            "tensor_active_pct": v.get("tensor_active_pct"), "source": rel}
+        except Exception:
+            continue
     return None
 
 
