@@ -132,6 +132,25 @@ def kernel_rooflines(device, peaks):
     tg = torch.randint(0, V, (rows_ce,), device=device)
     hbm("cross-entropy fwd+bwd in place [4096x128256] (6 B/logit)", 6 * rows_ce * V, lambda: K.cross_entropy_(logits, tg))
     del logits
+    # rank-64 LoRA products (gemm_grouped / gemm_streamk): bytes of the streamed activations, read once
+    A3 = [bf(d, 64) for _ in range(3)]
+    t3 = [torch.empty(M, 64, device=device, dtype=torch.bfloat16) for _ in range(3)]
+    hbm("rank-64 product t = x A for q|k|v [3 x 8192x64x2048, x shared] (x read once: 2 B/elt)", 2 * M * d,
+        lambda: K.gemm_grouped([dict(a=x, b=A3[i], out=t3[i], b_mn=True) for i in range(3)]))
+    hbm("rank-64 product t = x A, one projection [8192x64x2048]", 2 * M * d,
+        lambda: K.gemm_grouped([dict(a=x, b=A3[0], out=t3[0], b_mn=True)]))
+    hF, AF = bf(M, F), bf(F, 64)
+    hbm("rank-64 product t = h A for fc3 [8192x64x8192]", 2 * M * F,
+        lambda: K.gemm_grouped([dict(a=hF, b=AF, out=t3[0], b_mn=True)]))
+    wg, wg_bytes = [], 0
+    for d_in, d_out in [(d, d), (d, 512), (d, 512), (d, d), (d, F), (d, F), (F, d)]:
+        xi, u, dy, t = (hF if d_in == F else x), bf(M, 64), (hF if d_out == F else bf(M, d_out)), bf(M, 64)
+        wg.append(dict(a=xi, b=u, out=torch.zeros(d_in, 64, device=device), a_mn=True, b_mn=True, accumulate=True))
+        wg.append(dict(a=dy, b=t, out=torch.zeros(64, d_out, device=device), a_mn=True, b_mn=True, accumulate=True, trans_out=True))
+        wg_bytes += 2 * M * (d_in + d_out)
+    hbm("rank-64 weight gradients dA, dB of one block [14 problems, one launch] (x and dY read once)", wg_bytes,
+        lambda: K.gemm_grouped(wg))
+    del hF, AF, wg, A3, t3
     n = 53_428_224
     p_, g_, m_, v_ = (torch.zeros(n, device=device, dtype=torch.bfloat16), torch.zeros(n, device=device),
                       torch.zeros(n, device=device, dtype=torch.bfloat16), torch.zeros(n, device=device, dtype=torch.bfloat16))
@@ -554,26 +573,33 @@ def main():
         # line below: its time is not pure tensor work
         by_shape = prof.by_shape()
         fused = {k: v for k, v in by_shape.items() if isinstance(k[0], str) and k[0].startswith("swiglu")}
-        plain = {k: v for k, v in by_shape.items() if k not in fused}
+        # the rank-64 LoRA products run in other kernels (gemm_grouped / gemm_streamk) and are HBM-bound streams:
+        # they are rows of other_kernels (bytes / time against the copy bandwidth), not part of the tensor roofline
+        skinny = {k: v for k, v in by_shape.items() if isinstance(k[0], str) and k[0] == "grouped"}
+        plain = {k: v for k, v in by_shape.items() if k not in fused and k not in skinny}
         flops = sum(v[2] for v in plain.values())
         ms_gemm = sum(v[1] for v in plain.values())
         n_gemm = sum(v[0] for v in plain.values())
         fused_flops = sum(v[2] for v in fused.values())
         fused_ms = sum(v[1] for v in fused.values())
         fused_n = sum(v[0] for v in fused.values())
+        skinny_flops = sum(v[2] for v in skinny.values())
         fpt = flops_per_token(cfg, LORA_RANK, SEQ_LEN)
-        roof = {"bound": "tensor", "kernel": "gemm_tcgen05 kernels (every launch of one step except the SwiGLU-epilogue variant, listed under other_kernels)",
+        roof = {"bound": "tensor", "kernel": "gemm_tcgen05_2cta_kernel (every launch of one step: projections, LoRA K extensions, residual / RoPE / SwiGLU-forward epilogues; the SwiGLU-backward-epilogue launches are listed under other_kernels)",
                 "achieved": flops / (ms_gemm * 1e-3) / 1e12, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": flops / (ms_gemm * 1e-3) / 1e12 / peaks["tf_sustained"], "traffic": None,
                 "peak_source": f"{peaks['src']} (sustained; burst {peaks['tf_burst']})",
                 "gemm_launches_per_step": n_gemm, "gemm_ms_per_step": ms_gemm,
                 "gemm_share_of_step": (ms_gemm + fused_ms) / (ms_dev / args.steps),
+                "rank_r_products": {"launches_per_step": sum(v[0] for v in skinny.values()),
+                                    "gflop_per_step": sum(v[2] for v in skinny.values()) / 1e9,
+                                    "note": "gemm_grouped / gemm_streamk launches (t = xA, u = dY B^T, dA, dB): HBM-bound, see other_kernels"},
                 "step_frac_of_burst_peak": value / world * fpt / 1e12 / peaks["tf_burst"],
                 "algorithmic_gflops_per_token": fpt / 1e9,
                 # FLOPs the kernels really executed (LoRA K-padding included, ignored-target rows of the
                 # vocab projection excluded when it is row-compacted) + causal attention
-                "executed_gflops_per_token": ((flops + fused_flops) / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e9,
-                "step_frac_of_burst_peak_executed": value / world * ((flops + fused_flops) / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e12 / peaks["tf_burst"]}
+                "executed_gflops_per_token": ((flops + fused_flops + skinny_flops) / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e9,
+                "step_frac_of_burst_peak_executed": value / world * ((flops + fused_flops + skinny_flops) / (MICRO_BATCH * SEQ_LEN) + attn_flops_per_token(cfg, SEQ_LEN)) / 1e12 / peaks["tf_burst"]}
         roof["other_kernels"] = kernel_rooflines(device, peaks)
         if fused_n:
             tf = fused_flops / (fused_ms * 1e-3) / 1e12

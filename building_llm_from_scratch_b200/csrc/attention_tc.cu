@@ -247,8 +247,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (int i = 0; i < 32; ++i) {
         float a0, a1;
         unpack_f2(ffma2(pack_f2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), sc2, neg2), a0, a1);
-        float p0 = fast_exp2(a0);
-        float p1 = fast_exp2(a1);
+        float p0, p1;
+        if (((HDIM == 128 ? B200_ATTN_POLY_FWD_HD128 : B200_ATTN_POLY_FWD) >> (i & 7)) & 1) {
+          exp2_poly_pair(a0, a1, p0, p1);
+        } else {
+          p0 = fast_exp2(a0);
+          p1 = fast_exp2(a1);
+        }
         sum2 = fadd2(sum2, pack_f2(p0, p1));          // the softmax denominator is taken before dropout
         if (DROP) {
           bool k0, k1;
@@ -662,7 +667,13 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
               float a0, a1;
               unpack_f2(ffma2(pack_f2(__uint_as_float(sv[c]), __uint_as_float(sv[c + 1])), sc2,
                               pack_f2(nls[2 * e2], nls[2 * e2 + 1])), a0, a1);
-              float pr[2] = {fast_exp2(a0), fast_exp2(a1)};
+              float pr[2];
+              if ((B200_ATTN_POLY_DKV >> ((i4 * 2 + e2) & 7)) & 1) {
+                exp2_poly_pair(a0, a1, pr[0], pr[1]);
+              } else {
+                pr[0] = fast_exp2(a0);
+                pr[1] = fast_exp2(a1);
+              }
               float dpv[2] = {__uint_as_float(dv[c]), __uint_as_float(dv[c + 1])};
               float pdrop[2];
   #pragma unroll
@@ -950,7 +961,13 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             // packed pairs: P = exp2(s c - lse), dS = P (dP - delta) scale
             float a0, a1;
             unpack_f2(ffma2(pack_f2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nl2), a0, a1);
-            float pr0 = fast_exp2(a0), pr1 = fast_exp2(a1);
+            float pr0, pr1;
+            if ((B200_ATTN_POLY_DQ >> (i & 7)) & 1) {
+              exp2_poly_pair(a0, a1, pr0, pr1);
+            } else {
+              pr0 = fast_exp2(a0);
+              pr1 = fast_exp2(a1);
+            }
             if (MASK) {
               if (col > t) pr0 = 0.f;
               if (col + 1 > t) pr1 = 0.f;

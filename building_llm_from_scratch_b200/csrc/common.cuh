@@ -159,6 +159,49 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// 2^x for a pair of arguments on the FMA pipe instead of the MUFU (whose 16 results / clk / SM bound the attention
+// kernels at head_dim 64): x = n + f with n = round(x) taken from the low mantissa bits of x + 1.5 * 2^23, |f| <= 0.5,
+// 2^f by a degree-3 minimax polynomial (relative error 7.5e-5, far below the bf16 rounding the result gets), n added to
+// the exponent field. Arguments below -126 (masked scores) give ~2^-126.
+__device__ __forceinline__ unsigned long long pack_f2(float a, float b);
+__device__ __forceinline__ void unpack_f2(unsigned long long v, float& a, float& b);
+__device__ __forceinline__ unsigned long long ffma2(unsigned long long a, unsigned long long b, unsigned long long c);
+__device__ __forceinline__ unsigned long long fadd2(unsigned long long a, unsigned long long b);
+__device__ __forceinline__ void exp2_poly_pair(float a0, float a1, float& p0, float& p1) {
+  constexpr float MAGIC = 12582912.f;
+  a0 = fmaxf(a0, -126.f);
+  a1 = fmaxf(a1, -126.f);
+  const unsigned long long x2 = pack_f2(a0, a1);
+  const unsigned long long t2 = fadd2(x2, pack_f2(MAGIC, MAGIC));
+  const unsigned long long r2 = fadd2(t2, pack_f2(-MAGIC, -MAGIC));
+  const unsigned long long f2 = ffma2(r2, pack_f2(-1.f, -1.f), x2);
+  unsigned long long q2 = ffma2(f2, pack_f2(0.055171407759189606f, 0.055171407759189606f), pack_f2(0.24261075258255005f, 0.24261075258255005f));
+  q2 = ffma2(q2, f2, pack_f2(0.6932609677314758f, 0.6932609677314758f));
+  q2 = ffma2(q2, f2, pack_f2(0.9999281167984009f, 0.9999281167984009f));
+  float q0, q1, t0, t1;
+  unpack_f2(q2, q0, q1);
+  unpack_f2(t2, t0, t1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
+// Which column pairs of every 8 take the polynomial (bit i of the mask = pair i mod 8), per kernel; 0 = all on the MUFU.
+// Measured (B4 T2048 h32 kv8 hd64 / B1 T4096 h32 kv8 hd128, masks 0x24, 0x4A, 0x55 in all three kernels): at head_dim 64
+// every pattern is slower (forward 129 -> 137 / 137 / 145 us, backward 333 -> 345 / 347 / 353 us: those kernels are bound by
+// issue slots and barrier round trips, not by the MUFU, and the polynomial costs 11 issue slots per pair against 3); at
+// head_dim 128 the forward gains (203 -> 197 / 194 / 197 us), the backward does not. Hence the defaults.
+#ifndef B200_ATTN_POLY_FWD
+#define B200_ATTN_POLY_FWD 0x00
+#endif
+#ifndef B200_ATTN_POLY_FWD_HD128
+#define B200_ATTN_POLY_FWD_HD128 0x4A
+#endif
+#ifndef B200_ATTN_POLY_DQ
+#define B200_ATTN_POLY_DQ 0x00
+#endif
+#ifndef B200_ATTN_POLY_DKV
+#define B200_ATTN_POLY_DKV 0x00
+#endif
+
 // Blackwell packed fp32 pairs (FFMA2 / FADD2 / FMUL2) and the 3-input maximum (FMNMX3): half the issue
 // slots of the scalar forms in the softmax loops, which are issue-bound rather than MUFU-bound.
 __device__ __forceinline__ unsigned long long pack_f2(float a, float b) {
