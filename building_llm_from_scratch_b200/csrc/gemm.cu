@@ -1520,7 +1520,9 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const double a_bytes = 2.0 * (double)M * (double)(K1 + K2), b_bytes = 2.0 * (double)N * (double)(K1 + K2);
     const int order = gemm_option(OPT_N_FASTEST);
     if (order >= 0) p.n_fastest = order;
-    else p.n_fastest = (a_bytes > 64e6 && b_bytes < 64e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
+    // (B up to ~3/4 of the 126 MB L2: the fc1|fc2 input-gradient GEMM has B = 67.6 MB against A = 270 MB and read
+    // 1176 MB from DRAM per launch with M fastest, 3.5x its operands)
+    else p.n_fastest = (a_bytes > 64e6 && b_bytes < 96e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
   }
   p.alpha = alpha;
   p.bias = (const bf16*)bias;
@@ -1605,13 +1607,22 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     const int tail_opt = gemm_option(OPT_TAIL_SPLIT);
     // parking and re-reading the partial tiles costs about as much as 16 K blocks of MMA time: measured
     // 65 -> 69 us at K = 2048 (a loss) but 202 -> 189 us at K = 8192, so only deep K ranges are split
-    if (tw.ptr && tiles > G && L > 0 && 2 * L <= G && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !fused_io && !(p.flags & EP_ROPE) && tail_opt != 0) {
-      int s = G / L;
-      if (s > total_kb / 32) s = total_kb / 32;
-      if (s > 4) s = 4;
+    if (tw.ptr && tiles > G && L > 0 && total_kb >= 64 && !swiglu_bwd && !swiglu_fwd && !fused_io && !(p.flags & EP_ROPE) && tail_opt != 0) {
+      // s K ranges per tail tile make L * s units: the tail takes ceil(L s / G) / s tile times; every split also pays
+      // the fix-up (~24 K blocks' worth). L = 38 (vocab-projection input gradient at 3584 rows: 112 tiles) gains nothing
+      // from s = 2 (76 units on 74 pairs) but s = 3 gives two rounds of thirds: 2.0 -> 1.67 tile times.
       const size_t cnt_bytes = 4096;   // fixed: the counters of one launch must never be another launch's slot bytes
       const size_t slot_bytes = (size_t)256 * P_BN * sizeof(float);
-      while (s >= 2 && cnt_bytes + (size_t)L * s * slot_bytes > tw.bytes) --s;
+      int s = 1;
+      double best = 1.0;
+      for (int c = 2; c <= 4 && c <= total_kb / 32; ++c) {
+        if (cnt_bytes + (size_t)L * c * slot_bytes > tw.bytes || (size_t)L * 2 * sizeof(int) > cnt_bytes) break;
+        const double cost = (double)((L * c + G - 1) / G) / c + 24.0 / total_kb;
+        if (cost < best - 0.05) {
+          best = cost;
+          s = c;
+        }
+      }
       if (s >= 2) {
         p.tail_start = tiles - L;
         p.tail_splits = s;
@@ -1994,8 +2005,8 @@ extern "C" int b200_gemm_path_counts(uint64_t* out, int n) {
 }
 
 extern "C" size_t b200_gemm_workspace_bytes(void) {
-  // one 256 x 256 fp32 slot per (tail tile, K split): at most 74 CTA pairs' worth, + the counters
-  return (size_t)74 * 256 * P_BN * sizeof(float) + 4096;
+  // one 256 x 256 fp32 slot per (tail tile, K split): up to two rounds of 74 CTA pairs' worth, + the counters
+  return (size_t)2 * 74 * 256 * P_BN * sizeof(float) + 4096;
 }
 
 extern "C" int b200_gemm_set_workspace(void* workspace, size_t bytes) {

@@ -180,10 +180,11 @@ def test_skinny_gemm_ex_routes_through_streamk_exactly(K, force, request):
 
 
 @pytest.mark.parametrize("M,N,K_,r", [(8192, 2048, 4096, 64), (8192, 3072, 8192, 0), (8000, 2000, 4104, 8),
-                                     (8192, 2048, 2048, 64)])
+                                     (8192, 2048, 2048, 64), (3584, 2048, 8192, 0)])
 def test_gemm_tail_split_wave(K, M, N, K_, r, request):
     """Shapes whose last wave of 256 x 256 tiles is at most half full (256 or 384 tiles on 74 CTA pairs) and
-    whose K range is deep enough to split (the last case is below the threshold and runs unsplit):
+    whose K range is deep enough to split (the K = 2048 case is below the threshold and runs unsplit), and one whose
+    last wave is just over half full (112 tiles: 38 tail tiles go out as 114 thirds in two rounds):
     the tail tiles are cut along K and summed through the registered workspace. Same results as with
     tail splitting off (bias + residual + LoRA K extension in the epilogue of the fix-up), exact for
     integer-valued inputs, arrival counters zero afterwards."""
@@ -328,14 +329,18 @@ def test_gemm_gelu_backward_epilogue(K, M, N, K_, r):
 
 
 @pytest.mark.parametrize("M,N,K_,r", [(4096, 1600, 1600, 0), (4096, 1600, 6400, 0), (512, 1280, 1280, 8)])
-def test_gemm_dropout_residual_epilogue_draws_the_standalone_mask(K, M, N, K_, r):
+def test_gemm_dropout_residual_epilogue_draws_the_standalone_mask(K, M, N, K_, r, request):
     """y = res + dropout(x W^T + b): the fused epilogue and the GEMM followed by the dropout kernel agree bit for bit
     (same counter-based mask, same bf16 roundings), also with a device-side seed offset; about p of the linear's
     outputs are dropped."""
     p, seed = 0.1, 1234567
     x, w, b, res = rnd(M, K_, seed=1), rnd(N, K_, scale=0.05, seed=2), rnd(N, seed=3), rnd(M, N, seed=4)
     t, Bl = (rnd(M, r, seed=5), rnd(r, N, scale=0.1, seed=6)) if r else (None, None)
+    from building_llm_from_scratch_b200 import _lib
+    _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, 0)        # the fused epilogue never K-splits its tail wave; a split
+    request.addfinalizer(lambda: _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, -1))   # changes the fp32 summation order
     lin = K.gemm_ex(x, w, a2=t, b2=Bl, b2_mn=True, bias=b)
+    _lib.gemm_set_option(_lib.GEMM_OPT_TAIL_SPLIT, -1)
     for off in (None, torch.tensor([77], device="cuda", dtype=torch.int64)):
         fused = K.gemm_dropout_residual(x, w, b, res, p, seed, off, t, Bl)
         plain = K.dropout(lin, p, seed, res, seed_dev=off)

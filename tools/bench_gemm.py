@@ -38,6 +38,15 @@ for (N, Kd, b_mn, r) in [(2048, 2048, 0, 64), (8192, 2048, 0, 64), (2048, 8192, 
     fl = 2.0 * M * N * (Kd + r)
     print(f"{tag} M={M} N={N} K={Kd}+{r} b_mn={b_mn}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TF/s")
 
+# the two input-gradient GEMMs with the most DRAM traffic per launch: fc1|fc2 (K = 16384) and the vocab projection
+for (Mx, N, Kd, r) in [(8192, 2048, 16384, 128), (3584, 2048, 128256, 64), (3072, 2048, 128256, 64)]:
+    a, b = rnd(Mx, Kd), rnd(Kd, N)
+    out = torch.empty(Mx, N, device="cuda", dtype=torch.bfloat16)
+    a2, b2 = rnd(Mx, r), rnd(N, r)
+    ms = timeit(lambda: K.gemm_ex(a, b, b1_mn=True, out=out, a2=a2, b2=b2))
+    print(f"{tag} dX GEMM M={Mx} N={N} K={Kd}+{r} b_mn=1: {ms*1e3:8.1f} us  {2.0*Mx*N*(Kd+r)/ms/1e9:7.1f} TF/s")
+    del a, b
+
 # short-K GEMMs with a residual epilogue (the dX chain of the k / v projections) and o-proj
 for (N, Kd) in [(2048, 512), (2048, 2048)]:
     a, b = rnd(M, Kd), rnd(Kd, N)
