@@ -790,6 +790,11 @@ struct DqParams {
   long long lddq;
   const bf16* rope_cos;   // see BwdParams
   const bf16* rope_sin;
+  // DT kernels only, lse != nullptr: no attn_delta_tc_kernel ran — this kernel forms -lse * log2e and -delta = -sum dO * O
+  // for its own query rows (the O tile comes in next to Q and dO, into the shared memory the dS panels do not use) and
+  // writes them to ld2_out for the dK/dV kernel that follows
+  const float* lse;
+  float* ld2_out;
 };
 
 // DT: dS goes to tensor memory (two 32-column buffers) and feeds dQ += dS K as the MMA's A operand from there instead
@@ -798,7 +803,7 @@ template <int HDIM, bool DROP, bool DT>
 __global__ void __launch_bounds__(224, DqCfg<HDIM>::CTAS)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                      const DqParams p) {
+                      const __grid_constant__ CUtensorMap tmO, const DqParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   constexpr int HD = HDIM, Q_BYTES = DqCfg<HDIM>::Q_BYTES, KV_BYTES = DqCfg<HDIM>::KV_BYTES;
@@ -859,9 +864,11 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(q_full, 2 * Q_BYTES);
+      const bool fold = DT && p.lse != nullptr;
+      mbar_expect_tx(q_full, (fold ? 3 : 2) * Q_BYTES);
       tma_load_tile<HD>(sQ, &tmQ, q_full, head * HD, row_base + q0, BQ);
       tma_load_tile<HD>(sdO, &tmdO, q_full, head * HD, row_base + q0, BQ);
+      if (fold) tma_load_tile<HD>(sdS, &tmO, q_full, head * HD, row_base + q0, BQ);
       for (int j = 0; j < n_kv; ++j) {
         const int s = j % DQ_NS;
         mbar_wait(&kv_empty[s], ((j / DQ_NS) & 1) ^ 1);
@@ -920,9 +927,36 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const int row = quad * 32 + lane;
     const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
     const int t = q0 + row;
-    const float* ldrow = p.ld2 + (((long long)b * p.H + head) * p.nq64 + (t >> 6)) * (2 * QS) + (t & 63);
-    const float nlse2 = ldrow[0];    // -lse * log2e, -inf for padding rows
-    const float ndl = ldrow[QS];     // -delta
+    const long long ldoff = (((long long)b * p.H + head) * p.nq64 + (t >> 6)) * (2 * QS) + (t & 63);
+    float nlse2, ndl;                // -lse * log2e (-inf for padding rows), -delta
+    if (DT && p.lse != nullptr) {
+      mbar_wait(q_full, 0);
+      float acc = 0.f;
+#pragma unroll
+      for (int pnl = 0; pnl < HD / 64; ++pnl) {
+        const uint32_t off = (uint32_t)(pnl * BQ * 128 + row * 128);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint32_t o16 = off + (uint32_t)((c ^ (row & 7)) << 4);
+          const float4 fg = lds_f4(smem_u32(sdO) + o16), fo = lds_f4(smem_u32(sdS) + o16);
+          float g[8], a[8];
+          unpack8(make_uint4(__float_as_uint(fg.x), __float_as_uint(fg.y), __float_as_uint(fg.z), __float_as_uint(fg.w)), g);
+          unpack8(make_uint4(__float_as_uint(fo.x), __float_as_uint(fo.y), __float_as_uint(fo.z), __float_as_uint(fo.w)), a);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc += a[i] * g[i];
+        }
+      }
+      const bool real = t < p.T;
+      nlse2 = real ? -p.lse[((long long)b * p.H + head) * p.T + t] * LOG2E : -INFINITY;
+      ndl = real ? -acc : 0.f;
+      if ((t >> 6) < p.nq64) {
+        p.ld2_out[ldoff] = nlse2;
+        p.ld2_out[ldoff + QS] = ndl;
+      }
+    } else {
+      nlse2 = p.ld2[ldoff];
+      ndl = p.ld2[ldoff + QS];
+    }
     const unsigned long long sc2 = pack_f2(p.scale_log2, p.scale_log2), nl2 = pack_f2(nlse2, nlse2);
     const unsigned long long nd2 = pack_f2(ndl, ndl), scl2 = pack_f2(p.scale, p.scale);
     const unsigned long long drop_row =
@@ -1097,7 +1131,13 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   B200_CHECK_ARG((((uintptr_t)ld2) & 15u) == 0, "attention_bwd: workspace must be 16-B aligned");
   const long long rows = B * T;
   const int nq64 = (int)((T + QS - 1) / QS);
-  {
+  // dS through TMEM: 10 us (hd 64, B4 T2048) / 19 us (hd 128, B1 T4096) faster; B200_ATTN_DS_TMEM=0 restores the panels
+  static const bool ds_tmem = [] { const char* e = getenv("B200_ATTN_DS_TMEM"); return !(e && e[0] == '0'); }();
+  // ... and leaves the dS panels' shared memory free for the O tile: the dQ kernel forms lse2 / delta itself
+  // (B200_ATTN_DELTA_FOLD=0 keeps the separate pass; the dropout variant always uses it)
+  static const bool delta_fold = [] { const char* e = getenv("B200_ATTN_DELTA_FOLD"); return !(e && e[0] == '0'); }();
+  const bool fold = ds_tmem && delta_fold && dropout_p <= 0.f;
+  if (!fold) {
     const long long total = B * nq64 * QS * h;
     long long blocks = (total + 31) / 32;
     const long long cap = (long long)b200_num_sms() * 16;
@@ -1106,8 +1146,9 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     B200_CHECK_LAUNCH();
   }
   // every map has a 64-column box: a [rows x HD] tile is fetched as HD/64 panels
-  CUtensorMap mq, mdo, mk, mv, mk64, mv64;
+  CUtensorMap mq, mdo, mk, mv, mk64, mv64, mo;
   int rc;
+  if ((rc = b200_make_tmap_2d_bf16(&mo, o, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldo, BK2, 64))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mq, q, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)ldq, BK2, 64))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mdo, dout, (uint64_t)rows, (uint64_t)(h * HD), (uint64_t)lddo, BK2, 64))) return rc;
   if ((rc = b200_make_tmap_2d_bf16(&mk, k, (uint64_t)rows, (uint64_t)(hkv * HD), (uint64_t)ldk, BK2, 64))) return rc;
@@ -1134,12 +1175,11 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.drop = make_drop(dropout_p, seed, seed_dev);
     p.ld2 = ld2; p.nq64 = nq64; p.dq = (bf16*)dq; p.lddq = lddq;
     p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
+    p.lse = fold ? lse : nullptr; p.ld2_out = ld2;
     const long long grid = (long long)nqt * B * h;
-    // dS through TMEM: 10 us (hd 64, B4 T2048) / 19 us (hd 128, B1 T4096) faster; B200_ATTN_DS_TMEM=0 restores the panels
-    static const bool ds_tmem = [] { const char* e = getenv("B200_ATTN_DS_TMEM"); return !(e && e[0] == '0'); }();
-    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
-    else if (ds_tmem) attn_bwd_dq_tc_kernel<HD, false, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
-    else attn_bwd_dq_tc_kernel<HD, false, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, p);
+    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
+    else if (ds_tmem) attn_bwd_dq_tc_kernel<HD, false, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
+    else attn_bwd_dq_tc_kernel<HD, false, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
     B200_CHECK_LAUNCH();
   }
   {
@@ -1162,7 +1202,7 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     else attn_bwd_dkv_tc_kernel<HD, false, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
     B200_CHECK_LAUNCH();
   }
-  b200_count_launch(3);
+  b200_count_launch(fold ? 2 : 3);
   return 0;
 }
 }  // namespace
