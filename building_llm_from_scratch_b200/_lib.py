@@ -157,7 +157,7 @@ def check(status: int, what: str = "") -> None:
 
 
 GEMM_PATHS = ("pair", "pair_tail_split", "single_cta", "grouped_tiles", "streamk", "packed_segments", "swiglu_fwd",
-              "swiglu_bwd")
+              "swiglu_bwd", "skinny_pair")
 
 
 def gemm_path_counts() -> dict:
@@ -167,7 +167,7 @@ def gemm_path_counts() -> dict:
     return dict(zip(GEMM_PATHS, [int(v) for v in out]))
 
 
-GEMM_OPT_TAIL_SPLIT, GEMM_OPT_STREAMK, GEMM_OPT_N_FASTEST = 0, 1, 2
+GEMM_OPT_TAIL_SPLIT, GEMM_OPT_STREAMK, GEMM_OPT_N_FASTEST, GEMM_OPT_SKINNY_PAIR = 0, 1, 2, 3
 
 
 def gemm_set_option(option: int, value: int) -> None:

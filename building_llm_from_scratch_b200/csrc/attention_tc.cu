@@ -142,6 +142,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // barriers, TMEM and descriptors are set up: the rest waits for the previous kernel's results
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -376,9 +378,9 @@ int attention_fwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
   p.o = (bf16*)o; p.ldo = ldo; p.lse = lse;
   const long long grid = (long long)p.nqt * B * h;
   B200_CHECK_ARG(grid < (1ll << 31), "attention: grid too large");
-  if (p.drop.thr16) attn_fwd_tc_kernel<HD, true, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
-  else if (p_tmem) attn_fwd_tc_kernel<HD, false, true><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
-  else attn_fwd_tc_kernel<HD, false, false><<<(unsigned)grid, 224, SMEM, st>>>(mq, mk, mv, p);
+  if (p.drop.thr16) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_fwd_tc_kernel<HD, true, false>, dim3((unsigned)grid), dim3(224), SMEM, st, mq, mk, mv, p));
+  else if (p_tmem) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_fwd_tc_kernel<HD, false, true>, dim3((unsigned)grid), dim3(224), SMEM, st, mq, mk, mv, p));
+  else B200_CHECK_CUDA(b200_launch_pdl_wide(attn_fwd_tc_kernel<HD, false, false>, dim3((unsigned)grid), dim3(224), SMEM, st, mq, mk, mv, p));
   B200_CHECK_LAUNCH();
   b200_count_launch();
   return 0;
@@ -528,6 +530,8 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // barriers, TMEM and descriptors are set up: the rest waits for the previous kernel's results
+  pdl_wait();
   constexpr uint32_t C_ST = 0, C_DPT = NG * QS, C_DV = 2 * NG * QS, C_DK = 2 * NG * QS + HD;   // 512 columns for NG = 3
 
   if (warp == 0) {
@@ -860,6 +864,8 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // barriers, TMEM and descriptors are set up: the rest waits for the previous kernel's results
+  pdl_wait();
   constexpr uint32_t D_S = 0, D_DP = 64, D_DQ = 128, D_DS = 128 + HDIM;    // D_DS: DT only, 2 x 32 columns
 
   if (warp == 0) {
@@ -1177,9 +1183,9 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
     p.lse = fold ? lse : nullptr; p.ld2_out = ld2;
     const long long grid = (long long)nqt * B * h;
-    if (p.drop.thr16) attn_bwd_dq_tc_kernel<HD, true, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
-    else if (ds_tmem) attn_bwd_dq_tc_kernel<HD, false, true><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
-    else attn_bwd_dq_tc_kernel<HD, false, false><<<(unsigned)grid, 224, DQ_SMEM, st>>>(mq, mdo, mk64, mv64, mo, p);
+    if (p.drop.thr16) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dq_tc_kernel<HD, true, false>, dim3((unsigned)grid), dim3(224), DQ_SMEM, st, mq, mdo, mk64, mv64, mo, p));
+    else if (ds_tmem) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dq_tc_kernel<HD, false, true>, dim3((unsigned)grid), dim3(224), DQ_SMEM, st, mq, mdo, mk64, mv64, mo, p));
+    else B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dq_tc_kernel<HD, false, false>, dim3((unsigned)grid), dim3(224), DQ_SMEM, st, mq, mdo, mk64, mv64, mo, p));
     B200_CHECK_LAUNCH();
   }
   {
@@ -1197,9 +1203,9 @@ int attention_bwd_tc(const void* q, int64_t ldq, const void* k, int64_t ldk, con
     const long long grid = (long long)p.nkt * B * hkv;
     // P^T / dS^T through TMEM: 14 us faster at hd 64 (B4 T2048); B200_ATTN_DKV_TMEM=0 restores the shared-memory panels
     static const bool pt_tmem = [] { const char* e = getenv("B200_ATTN_DKV_TMEM"); return !(e && e[0] == '0'); }();
-    if (p.drop.thr16) attn_bwd_dkv_tc_kernel<HD, true, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
-    else if (pt_tmem) attn_bwd_dkv_tc_kernel<HD, false, true><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
-    else attn_bwd_dkv_tc_kernel<HD, false, false><<<(unsigned)grid, DKV_THREADS, DKV_SMEM, st>>>(mq64, mdo64, mk, mv, p);
+    if (p.drop.thr16) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dkv_tc_kernel<HD, true, false>, dim3((unsigned)grid), dim3(DKV_THREADS), DKV_SMEM, st, mq64, mdo64, mk, mv, p));
+    else if (pt_tmem) B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dkv_tc_kernel<HD, false, true>, dim3((unsigned)grid), dim3(DKV_THREADS), DKV_SMEM, st, mq64, mdo64, mk, mv, p));
+    else B200_CHECK_CUDA(b200_launch_pdl_wide(attn_bwd_dkv_tc_kernel<HD, false, false>, dim3((unsigned)grid), dim3(DKV_THREADS), DKV_SMEM, st, mq64, mdo64, mk, mv, p));
     B200_CHECK_LAUNCH();
   }
   b200_count_launch(fold ? 2 : 3);

@@ -4,6 +4,7 @@
 // (cp.async.bulk.tensor), tcgen05 (alloc / mma / commit / ld / fences) plus the
 // 128-bit vector load/store and reduction helpers used by the bandwidth kernels.
 #pragma once
+#include <cstdlib>
 
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -55,6 +56,19 @@ inline cudaError_t b200_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 blo
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+// The same for the kernels around the GEMMs (attention, norms): B200_PDL_WIDE=0 launches them the plain way (A/B runs).
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch_pdl_wide(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                        cudaStream_t st, Args&&... args) {
+  static const bool on = [] { const char* e = getenv("B200_PDL_WIDE"); return !(e && e[0] == '0'); }();
+  if (on) return b200_launch_pdl(kernel, grid, block, smem, st, std::forward<Args>(args)...);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 #endif

@@ -1187,6 +1187,219 @@ gemm_grouped_kernel(const __grid_constant__ GroupedMaps maps, const __grid_const
 }
 
 // ======================================================================================
+// Skinny problems on a CTA pair per 128-row tile: the two CTAs of a cluster each stream HALF of the K range into their
+// own TMEM accumulator and exchange fp32 partial sums through distributed shared memory (rows 0..63 are finished by
+// CTA 0, rows 64..127 by CTA 1). A skinny launch is bound by how fast one SM takes TMA data (~77 GB/s measured, L2
+// hits or not): M = 8192 gives only 64 tiles, so the tile-scheduled kernel streams 768 KB per CTA on 64 of 148 SMs;
+// stream-K spreads it over all SMs but pays ~5 us for the fix-up through global memory (RED, fence, counter, reload).
+// Here 128 CTAs stream 384 KB each and the fix-up is a 16 KB DSMEM write plus one cluster barrier.
+// Up to SP_NB problems that share the A operand (q | k | v, fc1 | fc2 projections of the same x) are ONE work item:
+// A is loaded once per K block, every B has its own 64-column accumulator.
+// ======================================================================================
+constexpr int SP_NB = 3;
+constexpr int SP_RING_BYTES = 176 * 1024;
+struct PairSkinnyParams {
+  int ngroups;
+  int tile_end[GROUP_MAX];     // exclusive prefix sums of the groups' 128-row tiles
+  int first[GROUP_MAX];        // first problem of the group
+  int nb[GROUP_MAX];           // problems in the group (same A, M, K)
+  GemmParams p[GROUP_MAX];
+};
+template <int NB>
+struct PairSkinnyCfg {
+  static constexpr int STAGE_BYTES = A_BYTES + NB * G_B_BYTES;
+  static constexpr int STAGES = SP_RING_BYTES / STAGE_BYTES;          // 7 / 5 / 4
+  static constexpr int PART_BYTES = NB * 64 * G_BN * 4;               // 64 rows x 64 columns fp32 per B
+  static constexpr int SMEM = STAGES * STAGE_BYTES + PART_BYTES + 1024 + (2 * STAGES + 2) * 8 + 16;
+  static constexpr uint32_t TMEM_COLS = NB == 1 ? 64 : (NB == 2 ? 128 : 256);
+};
+
+__device__ __forceinline__ void st_cluster_f4(uint32_t local_saddr, uint32_t rank, float a, float b, float c, float d) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.v4.f32 [ra], {%2, %3, %4, %5};\n\t"
+      "}" ::"r"(local_saddr),
+      "r"(rank), "f"(a), "f"(b), "f"(c), "f"(d)
+      : "memory");
+}
+
+template <int NB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+gemm_skinny_pair_kernel(const __grid_constant__ GroupedMaps maps, const __grid_constant__ PairSkinnyParams g) {
+  using Cfg = PairSkinnyCfg<NB>;
+  constexpr int STAGES = Cfg::STAGES, STAGE_BYTES = Cfg::STAGE_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* part = smem + STAGES * STAGE_BYTES;                  // [NB][16 column quads][64 rows] float4
+  uint64_t* full = (uint64_t*)(part + Cfg::PART_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(tfull + 2);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(tfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  cluster_sync_all();            // also: the peer CTA is running before anything is written into its shared memory
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  // work item of this cluster
+  const int cid = (int)(blockIdx.x >> 1);
+  int gi = 0, begin = 0;
+  while (gi < g.ngroups - 1 && cid >= g.tile_end[gi]) {
+    begin = g.tile_end[gi];
+    ++gi;
+  }
+  const int m_blk = cid - begin;
+  const int first = g.first[gi], nb = g.nb[gi];
+  const GemmParams& p0 = g.p[first];
+  const int kb_begin = (int)((long long)rank * p0.kb1 / 2);
+  const int kb_end = (int)((long long)(rank + 1) * p0.kb1 / 2);
+  const bool has = kb_end > kb_begin;                            // K = 64: CTA 0 has nothing to add
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], (uint32_t)(A_BYTES + nb * G_B_BYTES));
+        uint8_t* sa = smem + stage * STAGE_BYTES;
+        const int kk = kb * BK;
+        if (!p0.a1_mn) {
+          tma_load_2d(sa, &maps.a[first], &full[stage], kk, m_blk * BM);
+        } else {
+          tma_load_2d(sa, &maps.a[first], &full[stage], m_blk * BM, kk);
+          tma_load_2d(sa + 8192, &maps.a[first], &full[stage], m_blk * BM + 64, kk);
+        }
+        for (int i = 0; i < nb; ++i) {
+          uint8_t* sb = sa + A_BYTES + i * G_B_BYTES;
+          if (!g.p[first + i].b1_mn) tma_load_2d(sb, &maps.b[first + i], &full[stage], kk, 0);
+          else tma_load_2d(sb, &maps.b[first + i], &full[stage], 0, kk);
+        }
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+        for (int i = 0; i < nb; ++i) {
+          const uint32_t sb = sa + A_BYTES + i * G_B_BYTES;
+          const int b_mn = g.p[first + i].b1_mn;
+          const uint32_t idesc = umma_idesc_bf16(BM, G_BN, (uint32_t)p0.a1_mn, (uint32_t)b_mn);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = p0.a1_mn ? umma_desc_mn128(sa + k * 2048, 8192) : umma_desc_k128(sa + k * 32);
+            const uint64_t bd = b_mn ? umma_desc_mn128(sb + k * 2048, 8192) : umma_desc_k128(sb + k * 32);
+            umma_bf16_ss(tmem_base + (uint32_t)(i * G_BN), ad, bd, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty[stage]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (has) umma_commit(tfull);
+      else mbar_arrive(tfull);
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // rows [64 r, 64 r + 64) of the tile are finished by CTA r: the other two epilogue warps send their partial sums
+    const int ew = warp - 4;
+    const uint32_t owner = (uint32_t)(ew >> 1);
+    mbar_wait(tfull, 0);
+    tc_fence_after();
+    if (owner != rank) {
+      const int rl = (ew & 1) * 32 + lane;                       // row inside the owner's 64
+      for (int i = 0; i < nb; ++i) {
+#pragma unroll 1
+        for (int c = 0; c < G_BN / 32; ++c) {
+          uint32_t r[32];
+          if (has) {
+            tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(i * G_BN + c * 32), r);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = 0u;
+          }
+          const uint32_t dst = smem_u32(part) + (uint32_t)(((i * 16 + c * 8) * 64 + rl) * 16);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            st_cluster_f4(dst + (uint32_t)(q * 64 * 16), owner, __uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                          __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+        }
+      }
+    }
+  }
+  __syncwarp();
+  cluster_sync_all();            // the partial sums of both CTAs are in place (release / acquire at cluster scope)
+  if (warp >= 4) {
+    const int ew = warp - 4;
+    if ((uint32_t)(ew >> 1) == rank) {
+      const int rl = (ew & 1) * 32 + lane;
+      const long long row = (long long)m_blk * BM + ew * 32 + lane;
+      for (int i = 0; i < nb; ++i) {
+        const GemmParams& p = g.p[first + i];
+        const bool row_ok = row < p.M;
+#pragma unroll 1
+        for (int c = 0; c < G_BN / 32; ++c) {
+          uint32_t r[32];
+          if (has) {
+            tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(i * G_BN + c * 32), r);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = 0u;
+          }
+          const uint32_t src = smem_u32(part) + (uint32_t)(((i * 16 + c * 8) * 64 + rl) * 16);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 v = lds_f4(src + (uint32_t)(q * 64 * 16));
+            r[4 * q] = __float_as_uint(__uint_as_float(r[4 * q]) + v.x);
+            r[4 * q + 1] = __float_as_uint(__uint_as_float(r[4 * q + 1]) + v.y);
+            r[4 * q + 2] = __float_as_uint(__uint_as_float(r[4 * q + 2]) + v.z);
+            r[4 * q + 3] = __float_as_uint(__uint_as_float(r[4 * q + 3]) + v.w);
+          }
+          ResChunk none;
+          none.vec = false;
+          store_chunk(p, row, row_ok, (long long)c * 32, r, none);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ======================================================================================
 // Stream-K form of the grouped launch. The skinny problems are HBM-bound streams over an
 // activation (t = x A, u = dY B^T, dA = x^T u, dB = t^T dY: N <= 64, K up to 128 K), so what matters is
 // that all 148 SMs stream the same number of bytes. The (problem, 128-row tile, 64-wide K block)
@@ -1423,12 +1636,12 @@ TailWs tail_workspace_for(int dev, void* stream) {
 
 // which scheduling path each launch took (diagnostics for tests: b200_gemm_path_counts)
 enum : int { PATH_PAIR, PATH_PAIR_TAIL_SPLIT, PATH_SINGLE_CTA, PATH_GROUPED_TILES, PATH_STREAMK, PATH_PACKED_SEGMENTS,
-              PATH_SWIGLU_FWD, PATH_SWIGLU_BWD, PATH_N };
+              PATH_SWIGLU_FWD, PATH_SWIGLU_BWD, PATH_SKINNY_PAIR, PATH_N };
 std::atomic<uint64_t> g_path[PATH_N];
 
 // Scheduling switches for A/B measurements and tests (b200_gemm_set_option): -1 = the library's own heuristic,
 // 0 / 1 = off / forced. Their initial values come from the environment, read once per process.
-enum : int { OPT_TAIL_SPLIT, OPT_STREAMK, OPT_N_FASTEST, OPT_N };
+enum : int { OPT_TAIL_SPLIT, OPT_STREAMK, OPT_N_FASTEST, OPT_SKINNY_PAIR, OPT_N };
 std::atomic<int> g_opt[OPT_N];
 std::once_flag g_opt_once;
 int gemm_option(int which) {
@@ -1440,6 +1653,7 @@ int gemm_option(int which) {
     g_opt[OPT_TAIL_SPLIT] = env("B200_GEMM_TAIL", '1', '0');
     g_opt[OPT_STREAMK] = env("B200_GEMM_STREAMK_FORCE", '1', '0');
     g_opt[OPT_N_FASTEST] = env("B200_GEMM_ORDER", 'n', 'm');
+    g_opt[OPT_SKINNY_PAIR] = env("B200_GEMM_SKINNY_PAIR", '1', '0');
   });
   return g_opt[which].load();
 }
@@ -1904,9 +2118,94 @@ extern "C" size_t b200_gemm_grouped_workspace_bytes(int nprob, const b200_gemm_p
   return (size_t)(n_cnt * 4 + n_floats * 4);
 }
 
+namespace {
+template <int NB>
+int launch_skinny_pair(const GroupedMaps& maps, const PairSkinnyParams& g, int clusters, cudaStream_t st) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_skinny_pair_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, PairSkinnyCfg<NB>::SMEM));
+    attr_set[dev] = true;
+  }
+  B200_CHECK_CUDA(b200_launch_pdl(gemm_skinny_pair_kernel<NB>, dim3(2 * clusters), dim3(256), PairSkinnyCfg<NB>::SMEM, st, maps, g));
+  return 0;
+}
+
+// The group on CTA pairs (gemm_skinny_pair_kernel) when that fits: nothing accumulates into its output, K is at
+// least two blocks and not so deep that 148 stream-K CTAs do better, and the tiles fill most of the machine as pairs.
+// *launched = 0: not applicable, the caller goes on with stream-K / tile scheduling.
+int try_skinny_pair(int nprob, const b200_gemm_problem* probs, void* stream, int* launched) {
+  *launched = 0;
+  if (gemm_option(OPT_SKINNY_PAIR) == 0 || gemm_option(OPT_STREAMK) == 1) return 0;     // switched off, or stream-K forced
+  const int sms = b200_num_sms();
+  long long tiles = 0;
+  for (int i = 0; i < nprob; ++i) {
+    const b200_gemm_problem& q = probs[i];
+    if (!q.A || !q.B || !q.C || q.M <= 0 || q.N <= 0 || q.K <= 0 || q.N > G_BN || q.accumulate) return 0;
+    if (q.K < 2 * BK || q.K > 8192) return 0;
+  }
+  PairSkinnyParams g;
+  GroupedMaps maps;
+  int ng = 0, nbmax = 1;
+  for (int i = 0; i < nprob;) {
+    int nb = 1;
+    while (i + nb < nprob && nb < SP_NB && probs[i + nb].A == probs[i].A && probs[i + nb].lda == probs[i].lda &&
+           probs[i + nb].a_mn == probs[i].a_mn && probs[i + nb].M == probs[i].M && probs[i + nb].K == probs[i].K)
+      ++nb;
+    g.first[ng] = i;
+    g.nb[ng] = nb;
+    tiles += (probs[i].M + BM - 1) / BM;
+    g.tile_end[ng] = (int)tiles;
+    if (nb > nbmax) nbmax = nb;
+    ++ng;
+    i += nb;
+  }
+  // pairs of CTAs: at least ~2/3 of the SMs busy, at most a few rounds
+  if (2 * tiles < (2 * sms) / 3 || tiles > 4LL * sms) return 0;
+  g.ngroups = ng;
+  for (int i = ng; i < GROUP_MAX; ++i) {
+    g.tile_end[i] = (int)tiles;
+    g.first[i] = 0;
+    g.nb[i] = 0;
+  }
+  for (int i = 0; i < nprob; ++i) {
+    const b200_gemm_problem& q = probs[i];
+    B200_CHECK_ARG(!(q.accumulate && !q.out_f32), "gemm_grouped: accumulate needs fp32 output (problem %d)", i);
+    GemmParams& p = g.p[i];
+    p.M = (int)q.M; p.N = (int)q.N;
+    p.kb1 = (int)((q.K + BK - 1) / BK); p.kb2 = 0;
+    p.a1_mn = q.a_mn; p.b1_mn = q.b_mn; p.a2_mn = p.b2_mn = 0;
+    p.m_tiles = (int)((q.M + BM - 1) / BM); p.n_tiles = 1; p.n_fastest = 0;
+    p.tail_start = p.m_tiles; p.tail_splits = 1; p.tail_ws = nullptr; p.tail_cnt = nullptr; p.splits = 1;
+    p.alpha = q.alpha; p.bias = nullptr; p.R = nullptr; p.ldr = 0;
+    p.C = q.C; p.ldc = q.ldc;
+    p.flags = (q.out_f32 ? EP_OUT_F32 : 0) | (q.trans_out ? EP_TRANS_OUT : 0);
+    Operand oa{q.A, q.lda, q.a_mn}, ob{q.B, q.ldb, q.b_mn};
+    int rc;
+    if ((rc = make_operand_map(&maps.a[i], oa, q.M, q.K, BM))) return rc;
+    if ((rc = make_operand_map(&maps.b[i], ob, q.N, q.K, G_BN))) return rc;
+  }
+  int rc;
+  if (nbmax == 1) rc = launch_skinny_pair<1>(maps, g, (int)tiles, (cudaStream_t)stream);
+  else if (nbmax == 2) rc = launch_skinny_pair<2>(maps, g, (int)tiles, (cudaStream_t)stream);
+  else rc = launch_skinny_pair<3>(maps, g, (int)tiles, (cudaStream_t)stream);
+  if (rc) return rc;
+  ++g_path[PATH_SKINNY_PAIR];
+  b200_count_launch();
+  *launched = 1;
+  return 0;
+}
+}  // namespace
+
 extern "C" int b200_gemm_grouped_streamk_bf16(int nprob, const b200_gemm_problem* probs, void* workspace,
                                               size_t workspace_bytes, void* stream) {
   B200_CHECK_ARG(nprob >= 1 && nprob <= GROUP_MAX && probs, "gemm_grouped_streamk: nprob=%d must be in [1, %d]", nprob, GROUP_MAX);
+  {
+    int launched = 0;
+    const int rc = try_skinny_pair(nprob, probs, stream, &launched);
+    if (rc || launched) return rc;
+  }
   StreamKParams g;
   GroupedMaps maps;
   g.nprob = nprob;

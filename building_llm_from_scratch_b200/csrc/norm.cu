@@ -62,6 +62,8 @@ rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
                    const float* __restrict__ w, bf16* __restrict__ sum_out, bf16* __restrict__ y,
                    long long M, int d, float eps) {
   __shared__ float red[WARPS][2];
+  pdl_launch_dependents();                  // see gemm.cu: the next kernel's prologue may overlap this grid's tail
+  pdl_wait();
   constexpr int RPB = WARPS / WPR;          // rows per CTA pass
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int col0 = (warp % WPR) * (NV * 32) + lane;   // first vector of this lane
@@ -131,6 +133,8 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
                    const bf16* __restrict__ dy, const bf16* __restrict__ dres, bf16* __restrict__ dx,
                    float* __restrict__ dw, long long M, int d, float eps) {
   __shared__ float red[WARPS][2];
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int RPB = WARPS / WPR;
   constexpr bool KEEP_G = !HAS_DW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -463,11 +467,11 @@ extern "C" int b200_rmsnorm_fwd_bf16(const void* x, const void* res, const float
 #define CALL(NV, WPR)                                                                                    \
   do {                                                                                                   \
     if (res != nullptr) {                                                                                \
-      if (bf16_steps) rmsnorm_fwd_kernel<NV, WPR, true, true><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);   \
-      else rmsnorm_fwd_kernel<NV, WPR, true, false><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);             \
+      if (bf16_steps) b200_launch_pdl_wide(rmsnorm_fwd_kernel<NV, WPR, true, true>, dim3(grid), dim3(WARPS * 32), 0, st, FWD_ARGS);   \
+      else b200_launch_pdl_wide(rmsnorm_fwd_kernel<NV, WPR, true, false>, dim3(grid), dim3(WARPS * 32), 0, st, FWD_ARGS);             \
     } else {                                                                                             \
-      if (bf16_steps) rmsnorm_fwd_kernel<NV, WPR, false, true><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);  \
-      else rmsnorm_fwd_kernel<NV, WPR, false, false><<<grid, WARPS * 32, 0, st>>>(FWD_ARGS);            \
+      if (bf16_steps) b200_launch_pdl_wide(rmsnorm_fwd_kernel<NV, WPR, false, true>, dim3(grid), dim3(WARPS * 32), 0, st, FWD_ARGS);  \
+      else b200_launch_pdl_wide(rmsnorm_fwd_kernel<NV, WPR, false, false>, dim3(grid), dim3(WARPS * 32), 0, st, FWD_ARGS);            \
     }                                                                                                    \
   } while (0)
   DISPATCH_ROW(d, CALL);
@@ -490,11 +494,11 @@ extern "C" int b200_rmsnorm_bwd_bf16(const void* x, const float* w, const void* 
 #define CALL(NV, WPR)                                                                                   \
   do {                                                                                                  \
     if (dw) {                                                                                           \
-      if (dres_in) rmsnorm_bwd_kernel<NV, WPR, true, true><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);     \
-      else rmsnorm_bwd_kernel<NV, WPR, true, false><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);            \
+      if (dres_in) b200_launch_pdl_wide(rmsnorm_bwd_kernel<NV, WPR, true, true>, dim3(grid), dim3(WARPS * 32), 0, st, BWD_ARGS);     \
+      else b200_launch_pdl_wide(rmsnorm_bwd_kernel<NV, WPR, true, false>, dim3(grid), dim3(WARPS * 32), 0, st, BWD_ARGS);            \
     } else {                                                                                            \
-      if (dres_in) rmsnorm_bwd_kernel<NV, WPR, false, true><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);    \
-      else rmsnorm_bwd_kernel<NV, WPR, false, false><<<grid, WARPS * 32, 0, st>>>(BWD_ARGS);           \
+      if (dres_in) b200_launch_pdl_wide(rmsnorm_bwd_kernel<NV, WPR, false, true>, dim3(grid), dim3(WARPS * 32), 0, st, BWD_ARGS);    \
+      else b200_launch_pdl_wide(rmsnorm_bwd_kernel<NV, WPR, false, false>, dim3(grid), dim3(WARPS * 32), 0, st, BWD_ARGS);           \
     }                                                                                                   \
   } while (0)
   DISPATCH_ROW(d, CALL);

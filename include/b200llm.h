@@ -149,14 +149,16 @@ int b200_gemm_dropout_residual_bf16(const void* X, int64_t ldx, const void* W, i
  * makes every entry point re-entrant. No reference counterpart (scheduling detail of K1). */
 /* Diagnostics (no reference counterpart): launches so far by scheduling path, out[0..n): [0] CTA-pair kernel,
  * [1] of those with a K-split tail wave, [2] single-CTA kernel, [3] grouped tile-scheduled, [4] grouped stream-K,
- * [5] packed LoRA segments, [6] SwiGLU-forward epilogue, [7] SwiGLU-backward epilogue. Returns the number of paths. */
+ * [5] packed LoRA segments, [6] SwiGLU-forward epilogue, [7] SwiGLU-backward epilogue, [8] grouped skinny GEMMs on
+ * K-splitting CTA pairs. Returns the number of paths. */
 int b200_gemm_path_counts(uint64_t* out, int n);
 /* Scheduling switches for A/B measurements and tests (no reference counterpart). value: -1 = the library's own
  * heuristic (default), 0 = off, 1 = forced. Initial values come from B200_GEMM_TAIL (0/1), B200_GEMM_STREAMK_FORCE
- * (0/1) and B200_GEMM_ORDER (m/n), read once per process. */
+ * (0/1), B200_GEMM_ORDER (m/n) and B200_GEMM_SKINNY_PAIR (0/1), read once per process. */
 #define B200_GEMM_OPT_TAIL_SPLIT 0  /* K-split of a partly filled last wave (CTA-pair kernel) */
 #define B200_GEMM_OPT_STREAMK 1     /* stream-K scheduling of the grouped skinny GEMM */
 #define B200_GEMM_OPT_N_FASTEST 2   /* tile walk order of the CTA-pair kernel: 1 = N tiles of an M row back to back */
+#define B200_GEMM_OPT_SKINNY_PAIR 3 /* grouped skinny GEMMs on CTA pairs that split K and reduce through distributed shared memory */
 int b200_gemm_set_option(int option, int value);
 size_t b200_gemm_workspace_bytes(void);
 int b200_gemm_set_workspace(void* workspace, size_t bytes);

@@ -213,6 +213,44 @@ def test_gemm_tail_split_wave(K, M, N, K_, r, request):
     assert int(torch.count_nonzero(K._gemm_ws[torch.cuda.current_device()][:4096])) == 0    # arrival counters
 
 
+@pytest.mark.parametrize("M,Ks,N,share,a_mn", [(8192, (2048,), 64, False, False), (8192, (2048, 2048, 2048), 64, True, False),
+                                               (8192, (2048, 2048), 64, True, False), (8192, (2048, 512, 512), 64, False, False),
+                                               (8192, (8192,), 64, False, False), (8000, (2000,), 8, False, False),
+                                               (8192, (128,), 64, False, False), (8192, (4096, 4096), 64, False, True)])
+def test_gemm_grouped_on_k_splitting_cta_pairs(K, M, Ks, N, share, a_mn, request):
+    """Non-accumulating skinny groups that fill the machine as CTA pairs (rank-64 LoRA products of the bench shapes: t = x A for
+    q | k | v sharing x, u = dY B of three different dY, K = 8192, ragged M / K / N, MN-major A): each pair splits K and
+    exchanges partial sums through distributed shared memory. Same results as stream-K / tile scheduling up to the fp32
+    summation order, fp32 and transposed outputs included."""
+    from building_llm_from_scratch_b200 import _lib
+    probs, refs = [], []
+    x_shared = rnd(M, Ks[0], seed=1)
+    for i, K_ in enumerate(Ks):
+        a = x_shared if share else rnd(M, K_, seed=10 + i)
+        b = rnd(K_, N, scale=0.05, seed=20 + i)                       # stored [K, N]: b_mn
+        a_arg = a.t().contiguous() if a_mn else a
+        out_dtype = torch.float32 if i == 1 else torch.bfloat16
+        trans = i == 2
+        out = torch.empty((N, M) if trans else (M, N), device="cuda", dtype=out_dtype)
+        probs.append(dict(a=a_arg, b=b, out=out, a_mn=a_mn, b_mn=True, alpha=0.5, trans_out=trans))
+        refs.append(0.5 * (a.float() @ b.float()))
+    before = _lib.gemm_path_counts()["skinny_pair"]
+    K.gemm_grouped(probs)
+    assert _lib.gemm_path_counts()["skinny_pair"] == before + 1
+    got = [(pr["out"].t() if pr["trans_out"] else pr["out"]).float().clone() for pr in probs]
+    for gt, ref in zip(got, refs):
+        assert rel_err(gt, ref) < BF16_TOL
+    _lib.gemm_set_option(_lib.GEMM_OPT_SKINNY_PAIR, 0)
+    request.addfinalizer(lambda: _lib.gemm_set_option(_lib.GEMM_OPT_SKINNY_PAIR, -1))
+    for pr in probs:
+        pr["out"].zero_()
+    K.gemm_grouped(probs)
+    assert _lib.gemm_path_counts()["skinny_pair"] == before + 1
+    for gt, pr in zip(got, probs):
+        other = (pr["out"].t() if pr["trans_out"] else pr["out"]).float()
+        assert rel_err(gt, other) < 4e-3
+
+
 @pytest.mark.parametrize("M,outs,K_,r", [(8192, (2048, 512, 512), 2048, 64), (1024, (768, 256), 512, 8),
                                         (300, (256, 256, 256, 512), 128, 16)])
 def test_gemm_lora_packed_segments(K, M, outs, K_, r):

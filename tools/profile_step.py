@@ -58,11 +58,15 @@ def main():
         rows = [dict(shape=list(k), launches=v[0], ms=v[1], tflops=v[2] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0)
                 for k, v in sorted(prof.by_shape().items(), key=lambda kv: -kv[1][1])]
         json.dump(rows, open(args.shapes, "w"), indent=1)
+    from building_llm_from_scratch_b200 import _lib
+    before = _lib.gemm_path_counts()
     torch.cuda.profiler.start()
     step._eager_step()
     torch.cuda.synchronize()
     torch.cuda.profiler.stop()
+    after = _lib.gemm_path_counts()
     print("profiled one step, loss", float(step.loss))
+    print("GEMM launches by scheduling path:", {k: after[k] - before[k] for k in after if after[k] != before[k]})
 
 
 if __name__ == "__main__":
