@@ -1736,6 +1736,8 @@ int gemm_ex_impl(const void* A1, int64_t lda1, int a1_mn, const void* B1, int64_
     if (order >= 0) p.n_fastest = order;
     // (B up to ~3/4 of the 126 MB L2: the fc1|fc2 input-gradient GEMM has B = 67.6 MB against A = 270 MB and read
     // 1176 MB from DRAM per launch with M fastest, 3.5x its operands)
+    // When neither fits (vocab projection's input gradient: A = dlogits 919 MB, B = W 525 MB) N fastest measured worse:
+    // 3565 MB of DRAM reads per launch against 2479 MB with M fastest.
     else p.n_fastest = (a_bytes > 64e6 && b_bytes < 96e6 && a_bytes > 2.0 * b_bytes) ? 1 : 0;
   }
   p.alpha = alpha;
