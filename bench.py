@@ -346,7 +346,8 @@ def build_trainer(cfg, device, world_size):
         replace_linear_with_lora(model, rank=LORA_RANK, alpha=LORA_ALPHA, dtype=cfg["dtype"])
     model.train()
     if world_size > 1:
-        model = B200DDP(model)
+        # bucket size of the gradient exchange (MB of fp32 gradients per all-reduce); B200_DDP_BUCKET_MB for A/B runs
+        model = B200DDP(model, bucket_mb=float(os.environ.get("B200_DDP_BUCKET_MB", "64")))
     opt = B200AdamW(model.parameters(), lr=PEAK_LR, weight_decay=WEIGHT_DECAY)
     tr = Trainer(model, opt, cfg, [], None, "/tmp", device=device)
     tr.set_schedule(total_training_steps=100_000)
