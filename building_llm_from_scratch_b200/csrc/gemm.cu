@@ -2163,8 +2163,12 @@ int try_skinny_pair(int nprob, const b200_gemm_problem* probs, void* stream, int
     ++ng;
     i += nb;
   }
-  // pairs of CTAs: at least ~2/3 of the SMs busy, at most a few rounds
-  if (2 * tiles < (2 * sms) / 3 || tiles > 4LL * sms) return 0;
+  // pairs of CTAs: at least ~2/3 of the SMs busy (fewer tiles with a deep K range do better cut into 148 stream-K
+  // ranges; with a short K range — GPT-2's M = 4096, K = 1280: 32 tiles x 20 K blocks — the pair still halves what the
+  // tile-scheduled kernel streams per CTA and stream-K's fix-up costs more than the whole problem), at most a few rounds
+  long long kb_max = 0;
+  for (int i = 0; i < nprob; ++i) kb_max = std::max<long long>(kb_max, (probs[i].K + BK - 1) / BK);
+  if ((2 * tiles < (2 * sms) / 3 && !(tiles >= 8 && kb_max <= 48)) || tiles > 4LL * sms) return 0;
   g.ngroups = ng;
   for (int i = ng; i < GROUP_MAX; ++i) {
     g.tile_end[i] = (int)tiles;

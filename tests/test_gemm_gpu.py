@@ -216,7 +216,8 @@ def test_gemm_tail_split_wave(K, M, N, K_, r, request):
 @pytest.mark.parametrize("M,Ks,N,share,a_mn", [(8192, (2048,), 64, False, False), (8192, (2048, 2048, 2048), 64, True, False),
                                                (8192, (2048, 2048), 64, True, False), (8192, (2048, 512, 512), 64, False, False),
                                                (8192, (8192,), 64, False, False), (8000, (2000,), 8, False, False),
-                                               (8192, (128,), 64, False, False), (8192, (4096, 4096), 64, False, True)])
+                                               (8192, (128,), 64, False, False), (8192, (4096, 4096), 64, False, True),
+                                               (4096, (1280, 1280), 8, True, False)])
 def test_gemm_grouped_on_k_splitting_cta_pairs(K, M, Ks, N, share, a_mn, request):
     """Non-accumulating skinny groups that fill the machine as CTA pairs (rank-64 LoRA products of the bench shapes: t = x A for
     q | k | v sharing x, u = dY B of three different dY, K = 8192, ragged M / K / N, MN-major A): each pair splits K and
