@@ -154,6 +154,9 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
       const int idx = col0 + 32 * i;
       vx[i] = ld_row_v4(x + row * d + idx * 8, rok && idx < nvec);
       vg[i] = ld_row_v4(dy + row * d + idx * 8, rok && idx < nvec);
+      // the residual-stream gradient is only needed after the row reduction and there are no registers left to hold it
+      // until then: ask for it now, into L2, so that the loads after the barrier do not start a second DRAM round trip
+      if (DRES && rok && idx < nvec) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + row * d + idx * 8));
     }
     float ss = 0.f, dot = 0.f;   // sum x^2, sum dy*w*x
 #pragma unroll
