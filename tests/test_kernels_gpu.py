@@ -156,6 +156,21 @@ def test_rope_golden_and_layout(K, golden):
     assert torch.equal(qkv[:, (h + kv) * hd:], orig[:, (h + kv) * hd:])
 
 
+@pytest.mark.parametrize("M,N,ld", [(4096, 1600, 1600), (4096, 6400, 6400), (300, 264, 272), (1000, 50257, 50264), (77, 8, 8),
+                                    (5000, 2048, 6144)])
+def test_colsum_bias_gradient(K, M, N, ld):
+    """out[n] (+)= sum_m x[m, n] (the bias gradient of nn.Linear): tiled kernel for 16-byte rows, first form otherwise
+    (N = 50257); accumulates into an existing fp32 buffer; column slices of a wider buffer."""
+    buf = rnd(M, ld, seed=1)
+    x = buf[:, :N]
+    ref = x.float().sum(0)
+    got = K.colsum(x)
+    assert got.dtype == torch.float32 and rel_err(got, ref) < 1e-5
+    acc = torch.full((N,), 2.0, device="cuda")
+    K.colsum(x, out=acc)
+    assert rel_err(acc, ref + 2.0) < 1e-5
+
+
 def test_embedding_and_casts(K):
     V, d, B, T = 1000, 256, 3, 37
     w, pw = rnd(V, d, seed=1), rnd(64, d, seed=2)

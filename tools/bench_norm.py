@@ -35,3 +35,8 @@ ms = timeit(lambda: K.rmsnorm_bwd(x, w, dy))
 print(f"rmsnorm_bwd [8192x2048] (6 B/elt): {ms*1e3:6.1f} us  {6*M*d/ms/1e6:6.0f} GB/s")
 ms = timeit(lambda: K.rmsnorm_fwd(x, w, res=dres))
 print(f"rmsnorm_fwd + residual [8192x2048] (8 B/elt): {ms*1e3:6.1f} us  {8*M*d/ms/1e6:6.0f} GB/s")
+for N in (1600, 6400):
+    dyb = bf(4096, N)
+    acc = torch.zeros(N, device=dev)
+    ms = timeit(lambda: K.colsum(dyb, out=acc))
+    print(f"colsum (bias gradient) [4096x{N}] (2 B/elt): {ms*1e3:6.1f} us  {2*4096*N/ms/1e6:6.0f} GB/s")
