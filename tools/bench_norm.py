@@ -40,3 +40,11 @@ for N in (1600, 6400):
     acc = torch.zeros(N, device=dev)
     ms = timeit(lambda: K.colsum(dyb, out=acc))
     print(f"colsum (bias gradient) [4096x{N}] (2 B/elt): {ms*1e3:6.1f} us  {2*4096*N/ms/1e6:6.0f} GB/s")
+xl, dyl, wl, bl = bf(4096, 1600), bf(4096, 1600), bf(1600), bf(1600)
+_, mean, rstd = K.layernorm_fwd(xl, wl, bl)
+ms = timeit(lambda: K.layernorm_bwd(xl, wl, dyl, mean, rstd, need_dw=True))
+print(f"layernorm_bwd with dw, db [4096x1600] (6 B/elt): {ms*1e3:6.1f} us  {6*4096*1600/ms/1e6:6.0f} GB/s")
+ms = timeit(lambda: K.layernorm_bwd(xl, wl, dyl, mean, rstd, need_dw=False))
+print(f"layernorm_bwd dx only [4096x1600] (6 B/elt): {ms*1e3:6.1f} us  {6*4096*1600/ms/1e6:6.0f} GB/s")
+ms = timeit(lambda: K.layernorm_fwd(xl, wl, bl))
+print(f"layernorm_fwd [4096x1600] (4 B/elt): {ms*1e3:6.1f} us  {4*4096*1600/ms/1e6:6.0f} GB/s")
