@@ -2,7 +2,7 @@
 # Pass R: final 1-GPU validation: full GPU suite, smoke(), bench (default flags, with the CPU reference leg), reference arm,
 # the other configs, launch list with DRAM bytes.
 set -u
-O=gpurun_out/r
+O=gpurun_out/r2
 mkdir -p $O
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest.log 2>&1; echo "pytest rc=$?" >> $O/status.txt
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" >> $O/status.txt
