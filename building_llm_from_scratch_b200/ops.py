@@ -38,6 +38,12 @@ def _pitch_ok(t: Optional[Tensor]) -> Optional[Tensor]:
     return buf[:, :t.shape[1]]
 
 
+# Saved tensors are not always the Parameter objects: under torch.utils.checkpoint (use_reentrant=False) the backward of
+# a recomputed segment gets DETACHED copies of whatever forward saved — same storage, no Python attributes. main_grad,
+# _b200_grad_fresh and the gradient-ready subscriptions live on the Parameter, so every setup_context keeps the
+# parameters it was called with (`ctx.p_*`) and backward looks attributes up on those; a LoRA / full-finetune block
+# under activation checkpointing otherwise fell off the main_grad path (zero-filled fp32 temporaries, split-K atomics,
+# cast, .grad, a second add: 7 weights x 4 extra launches and weight-gradient GEMMs at 2/3 of their speed per block).
 def _main_grad(*params):
     """The fp32 main_grad accumulators of parameters (optim.B200AdamW publishes them) when ALL of them have one, else
     None: backward kernels that produce small gradients (norm weights, biases, embeddings) then add straight into the
@@ -69,10 +75,12 @@ def _rmsnorm_setup(ctx, inputs, output):
     x, w, eps = inputs
     ctx.save_for_backward(x, w)
     ctx.eps = eps
+    ctx.p_w = w
 
 
 def _rmsnorm_bwd(ctx, dy):
     x, w = ctx.saved_tensors
+    w = ctx.p_w
     need_dw = ctx.needs_input_grad[1]
     mg = _main_grad(w) if need_dw else None
     dx, dw = K.rmsnorm_bwd(x.contiguous(), w, dy.contiguous(), ctx.eps, need_dw=need_dw, dw_out=mg[0] if mg else None)
@@ -96,12 +104,14 @@ class _RMSNormWithResidual(torch.autograd.Function):
         y = K.rmsnorm_fwd(x.contiguous(), weight, eps)
         ctx.save_for_backward(x, weight)
         ctx.eps = eps
+        ctx.p_w = weight
         ctx.set_materialize_grads(False)
         return y, x.view_as(x)
 
     @staticmethod
     def backward(ctx, dy, dres):
         x, w = ctx.saved_tensors
+        w = ctx.p_w
         need_dw = ctx.needs_input_grad[1]
         if dy is None:
             return dres, None, None
@@ -143,12 +153,14 @@ def _layernorm_setup(ctx, inputs, output):
     _, mean, rstd = output
     ctx.save_for_backward(x, w, mean, rstd)
     ctx.bias_ref = b
+    ctx.p_w = w
 
 
 def _layernorm_bwd(ctx, dy, _dm, _dr):
     if dy is None:
         return None, None, None, None
     x, w, mean, rstd = ctx.saved_tensors
+    w = ctx.p_w
     need_dw = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
     mg = _main_grad(w, ctx.bias_ref) if (ctx.needs_input_grad[1] and ctx.needs_input_grad[2]) else None
     dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_dw,
@@ -204,6 +216,7 @@ def _lora_linear_setup(ctx, inputs, output):
     ctx.has_bias = bias is not None
     ctx.has_res = residual is not None
     ctx.bias_ref = bias
+    ctx.p_w, ctx.p_A, ctx.p_B = weight, A, B
 
 
 # Weight-gradient GEMMs into main_grad accumulators are off the critical path of backward: they are
@@ -278,8 +291,8 @@ def _weight_grad(a_mn_src: Tensor, b_mn_src: Tensor, param: Tensor, trans_out: b
 def _lora_linear_bwd(ctx, dy, _dt):
     if dy is None:
         return (None,) * 7
-    x, weight, A, B, t = ctx.saved_tensors   # saved tensors are the Parameter objects themselves
-    wref, bref, aref, bbref = weight, ctx.bias_ref, A, B
+    x, weight, A, B, t = ctx.saved_tensors
+    wref, bref, aref, bbref = ctx.p_w, ctx.bias_ref, ctx.p_A, ctx.p_B     # the Parameters (see _main_grad)
     need = ctx.needs_input_grad
     x2 = _flat2d(x)
     dy2 = _flat2d(dy)
@@ -351,6 +364,7 @@ def _llm_setup(ctx, inputs, output):
     n = len(weights)
     ctx.n, ctx.lora = n, len(As) > 0
     ctx.scaling = scaling
+    ctx.p_weights, ctx.p_As, ctx.p_Bs = list(weights), list(As), list(Bs)
     ctx.save_for_backward(x, *weights, *As, *Bs, *output[n:])
 
 
@@ -358,9 +372,7 @@ def _llm_bwd(ctx, grads):
     n = ctx.n
     saved = ctx.saved_tensors
     x = saved[0]
-    weights = saved[1:1 + n]
-    As = saved[1 + n:1 + 2 * n] if ctx.lora else ()
-    Bs = saved[1 + 2 * n:1 + 3 * n] if ctx.lora else ()
+    weights, As, Bs = ctx.p_weights, ctx.p_As, ctx.p_Bs          # the Parameters themselves (see _main_grad)
     ts = saved[1 + 3 * n:1 + 4 * n] if ctx.lora else ()
     dys = [None if g is None else _flat2d(g) for g in grads[:n]]
     live = [i for i in range(n) if dys[i] is not None]
@@ -517,6 +529,7 @@ def _llp_setup(ctx, inputs, output):
     x, weights, As, Bs, scaling, w_cat = inputs
     ctx.n, ctx.lora, ctx.scaling = len(weights), len(As) > 0, scaling
     ctx.has_cat = w_cat is not None
+    ctx.p_weights, ctx.p_As, ctx.p_Bs = list(weights), list(As), list(Bs)
     ctx.save_for_backward(x, *weights, *As, *Bs, output[1], *([w_cat] if w_cat is not None else []))
 
 
@@ -524,9 +537,7 @@ def _llp_bwd(ctx, grads):
     n = ctx.n
     saved = ctx.saved_tensors
     x = saved[0]
-    weights = saved[1:1 + n]
-    As = saved[1 + n:1 + 2 * n] if ctx.lora else ()
-    Bs = saved[1 + 2 * n:1 + 3 * n] if ctx.lora else ()
+    weights, As, Bs = ctx.p_weights, ctx.p_As, ctx.p_Bs          # the Parameters themselves (see _main_grad)
     pos = 1 + (3 * n if ctx.lora else n)
     t_cat = saved[pos]
     w_cat = saved[pos + 1] if ctx.has_cat else None
@@ -651,6 +662,7 @@ def _lqra_setup(ctx, inputs, output):
     o, qkv, lse, t_cat = output
     ctx.n, ctx.lora, ctx.scaling, ctx.has_cat = len(weights), len(As) > 0, scaling, True
     ctx.dims = (B, T, h, hkv, hd)
+    ctx.p_weights, ctx.p_As, ctx.p_Bs = list(weights), list(As), list(Bs)
     # layout expected by _llp_bwd: x, weights, As, Bs, t_cat, w_cat — then this op's own tensors
     ctx.save_for_backward(x, *weights, *As, *Bs, t_cat, w_cat, qkv, o, lse, cos, sin)
 
@@ -678,6 +690,7 @@ class _BwdView:
 
     def __init__(self, ctx, saved):
         self.n, self.lora, self.scaling, self.has_cat = ctx.n, ctx.lora, ctx.scaling, ctx.has_cat
+        self.p_weights, self.p_As, self.p_Bs = ctx.p_weights, ctx.p_As, ctx.p_Bs
         self.saved_tensors = saved
         self.needs_input_grad = ctx.needs_input_grad
 
@@ -906,6 +919,7 @@ def _ldr_setup(ctx, inputs, output):
     x, weight, bias, A, B, scaling, residual, p, seed = inputs
     ctx.save_for_backward(x, weight, A, B, output[1])
     ctx.bias_ref = bias
+    ctx.p_w, ctx.p_A, ctx.p_B = weight, A, B
     ctx.scaling, ctx.p, ctx.seed = scaling, p, seed
 
 
@@ -913,6 +927,7 @@ def _ldr_bwd(ctx, dy, _dt):
     if dy is None:
         return (None,) * 9
     x, weight, A, B, t = ctx.saved_tensors
+    weight, A, B = ctx.p_w, ctx.p_A, ctx.p_B                     # the Parameters themselves (see _main_grad)
     need = ctx.needs_input_grad
     dy2 = _flat2d(dy)
     dym = K.dropout(dy2, ctx.p, ctx.seed, seed_dev=_drop_step(dy2, ctx.p)) if ctx.p > 0 else dy2
@@ -957,6 +972,7 @@ def _gelu_mlp_setup(ctx, inputs, output):
     x, w1, b1, A1, B1, w2, b2, A2, B2, scaling, residual, p, seed = inputs
     ctx.save_for_backward(x, w1, A1, B1, w2, A2, B2, *output[1:])
     ctx.biases = (b1, b2)
+    ctx.p_lin = (w1, A1, B1, w2, A2, B2)
     ctx.scaling, ctx.p, ctx.seed = scaling, p, seed
     ctx.has_res = residual is not None
 
@@ -966,6 +982,7 @@ def _gelu_mlp_bwd(ctx, grads):
     if dy is None:
         return (None,) * 13
     x, w1, A1, B1, w2, A2, B2, z, h, t1, t2 = ctx.saved_tensors
+    w1, A1, B1, w2, A2, B2 = ctx.p_lin                           # the Parameters themselves (see _main_grad)
     b1, b2 = ctx.biases
     need = ctx.needs_input_grad
     x2, dy2 = _flat2d(x), _flat2d(dy)
@@ -1317,6 +1334,7 @@ def _swiglu_down_setup(ctx, inputs, output):
     ctx.save_for_backward(ab, weight, A, B, output[1], output[2] if h_in is None else h_in)
     ctx.scaling = scaling
     ctx.has_res = residual is not None
+    ctx.p_w, ctx.p_A, ctx.p_B = weight, A, B
 
 
 def _swiglu_down_bwd(ctx, grads):
@@ -1324,6 +1342,7 @@ def _swiglu_down_bwd(ctx, grads):
     if dy is None:
         return (None,) * 7
     ab, weight, A, B, t, h = ctx.saved_tensors
+    weight, A, B = ctx.p_w, ctx.p_A, ctx.p_B                     # the Parameters themselves (see _main_grad)
     h = _flat2d(h)
     need = ctx.needs_input_grad
     ab2, dy2 = _flat2d(ab), _flat2d(dy)
@@ -1531,6 +1550,7 @@ def _lce_setup(ctx, inputs, output):
     ctx.save_for_backward(x, weight, A, B, t, buf, rows, idx)
     ctx.scaling = scaling
     ctx.write_grad = write_grad
+    ctx.p_w, ctx.p_A, ctx.p_B = weight, A, B
 
 
 def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
@@ -1549,7 +1569,7 @@ def _lce_bwd(ctx, dloss, _dbuf, _dt, _dr, _di):
                                            ctx.needs_input_grad[0])
         return (None if dx is None else dx.view(x.shape)), dW, dA, dB, None, None, None, None
     K.scale_dev_(buf, dloss.detach().reshape(1).to(torch.float32))
-    wref, aref, bref = weight, A, B
+    wref, aref, bref = ctx.p_w, ctx.p_A, ctx.p_B                 # the Parameters themselves (see _main_grad)
     need = ctx.needs_input_grad
     V = weight.shape[0]
     dl = buf[:, :V]

@@ -179,6 +179,42 @@ def test_activation_checkpointing_matches_plain(golden):
             assert close(p.grad.float(), plain[k].float(), 1e-3, atol=1e-6), k
 
 
+@pytest.mark.parametrize("lora", [True, False])
+def test_activation_checkpointing_keeps_the_main_grad_path(golden, lora):
+    """Under torch.utils.checkpoint (use_reentrant=False) backward receives DETACHED copies of the saved weights — no
+    main_grad, no gradient-ready subscription. The ops keep the Parameters they were called with, so a checkpointed
+    block still accumulates straight into the optimizer's flat fp32 buffer: nothing comes back as .grad, the flat
+    gradients equal the un-checkpointed run's, and every parameter is reported ready (what B200DDP's overlap needs)."""
+    from building_llm_from_scratch_b200 import ops
+    from building_llm_from_scratch_b200.optim import B200AdamW
+    g = golden("llama_model.pt")
+    model, _ = build_llama(g, False)
+    if not lora:                                       # full fine-tuning of the same modules
+        for p in model.parameters():
+            p.requires_grad = p.dtype == torch.bfloat16
+    opt = B200AdamW(model.parameters(), lr=5e-4, weight_decay=0.1)
+    x, y = g["x"].cuda(), g["y"].cuda()
+
+    def run(ckpt):
+        model.use_actv_ckpt = ckpt
+        opt.zero_grad()
+        seen = []
+        ops.register_grad_ready(opt._trainable, lambda ps: seen.extend(id(q) for q in ps))
+        model.forward_loss(x, y).backward()
+        ops.flush_weight_grads()
+        ops.unregister_grad_ready(opt._trainable)
+        stray = [k for k, p in model.named_parameters() if p.grad is not None]
+        return [gr.clone() for gr in opt.flat_grads], set(seen), stray
+
+    plain, seen_plain, stray_plain = run(False)
+    ck, seen_ck, stray_ck = run(True)
+    assert stray_plain == [] and stray_ck == [], (stray_plain, stray_ck)
+    want = {id(p) for p in opt._trainable}
+    assert seen_plain == want and seen_ck == want
+    for a, b in zip(plain, ck):
+        assert float(a.abs().max()) > 0 and close(b, a, 1e-3, atol=1e-6)
+
+
 def test_ops_reject_cpu_tensors():
     from building_llm_from_scratch_b200 import ops
     with pytest.raises(RuntimeError, match="no CPU fallback"):
