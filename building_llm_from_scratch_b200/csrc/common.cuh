@@ -456,12 +456,21 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
 // One 32-bit hash of (seed, element index) per PAIR of elements; each 16-bit half is compared with
 // thr16 = round(p * 65536): keep iff half >= thr16. Stateless, so the backward kernels regenerate
 // exactly the mask the forward kernels used (nothing is stored).
+// One 64-bit multiply folds the (pair index, seed) into 32 bits, a two-multiply 32-bit finisher mixes them: ~14
+// integer instructions per pair. (The first version ran the whole splitmix64 finisher — two 64-bit multiplies and three
+// 64-bit xor-shifts, ~28 instructions — per call, and the attention dK/dV kernel needs one call per ELEMENT because its
+// threads walk down a column of the mask: the dropout variants of the attention kernels ran 2.5x slower than the plain
+// ones.) The seed-only part is loop-invariant and hoisted by the compiler.
 __host__ __device__ __forceinline__ uint32_t dropout_hash(unsigned long long pair_index, unsigned long long seed) {
-  unsigned long long z = pair_index + seed * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z = z ^ (z >> 31);
-  return (uint32_t)(z >> 16);
+  const unsigned long long sk = (seed ^ (seed >> 29)) * 0xBF58476D1CE4E5B9ull + 0x632BE59BD9B4E019ull;
+  const unsigned long long z = (pair_index ^ sk) * 0x9E3779B97F4A7C15ull;
+  uint32_t x = (uint32_t)(z >> 32) ^ (uint32_t)z;
+  x ^= x >> 15;
+  x *= 0x2C1B3C6Du;
+  x ^= x >> 12;
+  x *= 0x297A2D39u;
+  x ^= x >> 15;
+  return x;
 }
 // keep flags of elements 2*pair_index and 2*pair_index+1
 __host__ __device__ __forceinline__ void dropout_keep2(unsigned long long pair_index, unsigned long long seed,
