@@ -20,7 +20,7 @@
 
 namespace {
 
-constexpr int BQ = 128, BKV = 64, NS = 2;
+constexpr int BQ = 128, BKV = 64;
 constexpr int P_BYTES = BQ * BKV * 2;    // 16 KB
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float RESCALE_SLACK = 8.f;     // forward softmax: tolerated growth of the row maximum before O is rescaled

@@ -664,7 +664,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       tma_prefetch_desc(&tmAB);
       tma_prefetch_desc(&tmDAB);
       int n = 0;
-      int q_row[IO_BUFS], q_col[IO_BUFS];
+      int q_row[IO_BUFS] = {}, q_col[IO_BUFS] = {};
       auto drain = [&](int k) {               // results of group k: staged -> global
         const int buf = k % IO_BUFS;
         mbar_wait(&out_full[buf], (uint32_t)((k / IO_BUFS) & 1));
