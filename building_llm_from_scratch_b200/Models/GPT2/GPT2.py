@@ -128,13 +128,19 @@ class TransformerBlock(nn.Module):
         if cache is not None:
             x = self.att(self.norm1(x), residual=x, cache=cache, layer=layer)
             return self.ff(self.norm2(x), residual=x)
+        # the norm hands x on as the residual stream: its backward kernel adds the shortcut's gradient while it writes dx
+        n1, n2 = self.norm1, self.norm2
         if self.training and self.dropout.p > 0:
             # x + drop_shortcut(att(...)) and x + drop_shortcut(ff(...)) (GPT2.py:85,87): dropout and the residual add
             # run in the epilogue of out_proj / the second MLP linear
-            x = self.att(self.norm1(x), residual=x, drop=(self.dropout.p, ops.new_seed()))
-            return self.ff(self.norm2(x), residual=x, drop=(self.dropout.p, ops.new_seed()))
-        x = self.att(self.norm1(x), residual=x)
-        return self.ff(self.norm2(x), residual=x)
+            h, res = ops.layernorm_with_residual(x, n1.weight, n1.bias, n1.eps)
+            x = self.att(h, residual=res, drop=(self.dropout.p, ops.new_seed()))
+            h, res = ops.layernorm_with_residual(x, n2.weight, n2.bias, n2.eps)
+            return self.ff(h, residual=res, drop=(self.dropout.p, ops.new_seed()))
+        h, res = ops.layernorm_with_residual(x, n1.weight, n1.bias, n1.eps)
+        x = self.att(h, residual=res)
+        h, res = ops.layernorm_with_residual(x, n2.weight, n2.bias, n2.eps)
+        return self.ff(h, residual=res)
 
 
 class GPTModel(nn.Module):

@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200_rmsnorm_bwd_f32": (I, [P, P, P, P, P, I64, I64, F, P]),
     "b200_layernorm_fwd_bf16": (I, [P, P, P, P, P, P, I64, I64, F, P]),
     "b200_layernorm_bwd_bf16": (I, [P, P, P, P, P, P, P, P, I64, I64, P]),
+    "b200_layernorm_bwd_res_bf16": (I, [P, P, P, P, P, P, P, P, P, I64, I64, P]),
     "b200_swiglu_fwd_bf16": (I, [P, I64, P, I64, P, I64, I64, I, P]),
     "b200_swiglu_bwd_bf16": (I, [P, I64, P, I64, P, P, I64, P, I64, I64, I64, P]),
     "b200_gelu_fwd_bf16": (I, [P, P, I64, P]),

@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(WARPS * 32)
 layernorm_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                      const bf16* __restrict__ dy, const float* __restrict__ mean,
                      const float* __restrict__ rstd, bf16* __restrict__ dx, float* __restrict__ dw,
-                     float* __restrict__ db, long long M, int d) {
+                     float* __restrict__ db, long long M, int d, const bf16* __restrict__ dres) {
   const int lane = threadIdx.x & 31;
   const long long warp0 = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * WARPS;
@@ -356,6 +356,9 @@ layernorm_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
       if (idx < nvec) {
         vx[i] = ld_nc_v4(x + row * d + idx * 8);
         vg[i] = ld_nc_v4(dy + row * d + idx * 8);
+        // gradient of the residual stream (x also feeds the block's residual add): added while dx is written, asked
+        // for now so that it is in L2 by then (see rmsnorm_bwd_kernel)
+        if (dres != nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + row * d + idx * 8));
         float f[8], g[8], ww[8];
         unpack8(vx[i], f);
         unpack8(vg[i], g);
@@ -386,6 +389,12 @@ layernorm_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
             dwacc[i * 8 + j] += g[j] * xn;
             dbacc[i * 8 + j] += g[j];
           }
+        }
+        if (dres != nullptr) {
+          float e[8];
+          unpack8(ld_nc_v4(dres + row * d + idx * 8), e);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += e[j];
         }
         st_v4(dx + row * d + idx * 8, pack8(o));
       }
@@ -607,9 +616,18 @@ extern "C" int b200_layernorm_fwd_bf16(const void* x, const void* w, const void*
   return 0;
 }
 
+extern "C" int b200_layernorm_bwd_res_bf16(const void* x, const void* w, const void* dy, const void* dres,
+                                           const float* mean, const float* rstd, void* dx, float* dw,
+                                           float* db, int64_t M, int64_t d, void* stream);
 extern "C" int b200_layernorm_bwd_bf16(const void* x, const void* w, const void* dy,
                                        const float* mean, const float* rstd, void* dx, float* dw,
                                        float* db, int64_t M, int64_t d, void* stream) {
+  return b200_layernorm_bwd_res_bf16(x, w, dy, nullptr, mean, rstd, dx, dw, db, M, d, stream);
+}
+
+extern "C" int b200_layernorm_bwd_res_bf16(const void* x, const void* w, const void* dy, const void* dres,
+                                           const float* mean, const float* rstd, void* dx, float* dw,
+                                           float* db, int64_t M, int64_t d, void* stream) {
   B200_CHECK_ARG(x && w && dy && mean && rstd && dx && M > 0, "layernorm_bwd: null pointer or empty");
   B200_CHECK_ARG(d % 8 == 0 && d > 0 && d <= 16384, "layernorm_bwd: d=%lld must be a multiple of 8 and <= 16384", (long long)d);
   cudaStream_t st = (cudaStream_t)stream;
@@ -618,7 +636,7 @@ extern "C" int b200_layernorm_bwd_bf16(const void* x, const void* w, const void*
   static const bool split_dw = [] { const char* e = getenv("B200_LN_SPLIT_DW"); return !(e && e[0] == '0'); }();
   if (dw && split_dw && b200_aligned16(x) && b200_aligned16(dy)) {
     // dx by the light kernel (no column partials in registers), dw / db by a tiled pass of their own
-#define CALL(NV) layernorm_bwd_kernel<NV, false><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, nullptr, nullptr, M, (int)d)
+#define CALL(NV) layernorm_bwd_kernel<NV, false><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, nullptr, nullptr, M, (int)d, (const bf16*)dres)
     DISPATCH_MAXV(d, CALL);
 #undef CALL
     B200_CHECK_LAUNCH();
@@ -639,11 +657,11 @@ extern "C" int b200_layernorm_bwd_bf16(const void* x, const void* w, const void*
     if (grid > fat) grid = fat;
     B200_CHECK_ARG(d <= 4096, "layernorm_bwd: weight gradient supported for d <= 4096");
     const int nv = (int)((d / 8 + 31) / 32);
-#define CALLW(NV) layernorm_bwd_kernel<NV, true><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, dw, db, M, (int)d)
+#define CALLW(NV) layernorm_bwd_kernel<NV, true><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, dw, db, M, (int)d, (const bf16*)dres)
     if (nv <= 4) { CALLW(4); } else if (nv <= 8) { CALLW(8); } else { CALLW(16); }
 #undef CALLW
   } else {
-#define CALL(NV) layernorm_bwd_kernel<NV, false><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, nullptr, nullptr, M, (int)d)
+#define CALL(NV) layernorm_bwd_kernel<NV, false><<<grid, WARPS * 32, 0, st>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, nullptr, nullptr, M, (int)d, (const bf16*)dres)
     DISPATCH_MAXV(d, CALL);
 #undef CALL
   }

@@ -454,12 +454,14 @@ def layernorm_fwd(x, w, b, eps=1e-5):
     return y.view_as(x), mean, rstd
 
 
-def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True, dw_out=None, db_out=None):
-    """dw_out / db_out: fp32 [d] accumulators (main_grad of weight / bias) the kernel adds into."""
+def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True, dw_out=None, db_out=None, dres=None):
+    """dw_out / db_out: fp32 [d] accumulators (main_grad of weight / bias) the kernel adds into; dres: gradient of the
+    residual stream, added to dx as it is written."""
     if x.dtype == torch.float32:
         from . import f32
-        return f32.layernorm_bwd(x, w, dy, mean, rstd, need_dw, dw_out, db_out)
-    _need_cuda(x, w, dy, dw_out, db_out)
+        dx, dw, db = f32.layernorm_bwd(x, w, dy, mean, rstd, need_dw, dw_out, db_out)
+        return (dx if dres is None else dx + dres), dw, db
+    _need_cuda(x, w, dy, dw_out, db_out, dres)
     lib = _lib.load()
     x2 = x.reshape(-1, x.shape[-1])
     M, d = x2.shape
@@ -469,8 +471,9 @@ def layernorm_bwd(x, w, dy, mean, rstd, need_dw=True, dw_out=None, db_out=None):
     else:
         dw = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
         db = torch.zeros(d, device=x.device, dtype=torch.float32) if need_dw else None
-    _lib.check(lib.b200_layernorm_bwd_bf16(_p(x2), _p(w), _p(dy.reshape(-1, d)), _p(mean), _p(rstd), _p(dx), _p(dw),
-                                           _p(db), M, d, _stream()), "layernorm_bwd")
+    _lib.check(lib.b200_layernorm_bwd_res_bf16(_p(x2), _p(w), _p(dy.reshape(-1, d)),
+                                               _p(dres.reshape(-1, d)) if dres is not None else None, _p(mean), _p(rstd),
+                                               _p(dx), _p(dw), _p(db), M, d, _stream()), "layernorm_bwd")
     return dx.view_as(x), dw, db
 
 

@@ -135,6 +135,44 @@ def rmsnorm_with_residual(x, weight, eps):
 # ======================================================================================
 # LayerNorm (nn.LayerNorm in Models/GPT2/GPT2.py:79-80,105)
 # ======================================================================================
+class _LayerNormWithResidual(torch.autograd.Function):
+    """y = layernorm(x) and x itself handed on as the residual stream (GPT2.py:83-87: x feeds the norm and the shortcut
+    add): the norm's backward kernel adds the residual-stream gradient while it writes dx, like _RMSNormWithResidual."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        y, mean, rstd = K.layernorm_fwd(x.contiguous(), weight, bias, eps)
+        ctx.save_for_backward(x, mean, rstd)
+        ctx.p_w, ctx.p_b = weight, bias
+        ctx.set_materialize_grads(False)
+        return y, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, dres):
+        x, mean, rstd = ctx.saved_tensors
+        w, b = ctx.p_w, ctx.p_b
+        if dy is None:
+            return dres, None, None, None
+        need_w, need_b = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        mg = _main_grad(w, b) if (need_w and need_b) else None
+        dx, dw, db = K.layernorm_bwd(x.contiguous(), w, dy.contiguous(), mean, rstd, need_dw=need_w or need_b,
+                                     dw_out=mg[0] if mg else None, db_out=mg[1] if mg else None,
+                                     dres=None if dres is None else dres.contiguous())
+        if mg:
+            _notify_ready([w, b])
+            return dx, None, None, None
+        if need_w or need_b:
+            dw, db = dw.to(w.dtype), db.to(w.dtype)
+        return dx, (dw if need_w else None), (db if need_b else None), None
+
+
+def layernorm_with_residual(x, weight, bias, eps):
+    """-> (layernorm(x), x as residual stream); see _LayerNormWithResidual."""
+    if x.dtype != BF16:
+        return layernorm(x, weight, bias, eps)[0], x
+    return _LayerNormWithResidual.apply(x, weight, bias, eps)
+
+
 @torch.library.custom_op("b200llm::layernorm", mutates_args=())
 def layernorm(x: Tensor, weight: Tensor, bias: Tensor, eps: float) -> Tuple[Tensor, Tensor, Tensor]:
     return K.layernorm_fwd(x.contiguous(), weight, bias, eps)

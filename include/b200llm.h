@@ -225,6 +225,12 @@ int b200_layernorm_fwd_bf16(const void* x, const void* w, const void* b, void* y
 int b200_layernorm_bwd_bf16(const void* x, const void* w, const void* dy, const float* mean,
                             const float* rstd, void* dx, float* dw, float* db, int64_t M,
                             int64_t d, void* stream);
+/* The same with the gradient of the residual stream added to dx as it is written (x feeds both the norm and the
+ * block's residual add, GPT2.py:83-87: autograd would sum the two contributions with a separate add kernel); dres may be
+ * NULL. */
+int b200_layernorm_bwd_res_bf16(const void* x, const void* w, const void* dy, const void* dres, const float* mean,
+                                const float* rstd, void* dx, float* dw, float* db, int64_t M, int64_t d,
+                                void* stream);
 
 /* ---- K5: SwiGLU gate (Models/Llama/common_components.py:78-88,121-123) --------------------
  * h = silu(a) * b; a, b [M,F] with row pitches lda, ldb (they may be the two halves of one

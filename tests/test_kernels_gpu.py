@@ -104,6 +104,13 @@ def test_layernorm(K, M, d):
     dx, dw, db = K.layernorm_bwd(x, w, gy, mean, rstd)
     assert rel_err(dx.float(), xr.grad) < BF16_TOL
     assert rel_err(dw, wr.grad) < BF16_TOL and rel_err(db, br.grad) < BF16_TOL
+    # the residual-stream gradient added while dx is written (with and without the dw / db pass)
+    dres = rnd(M, d, seed=5)
+    for need_dw in (True, False):
+        dx2, dw2, db2 = K.layernorm_bwd(x, w, gy, mean, rstd, need_dw=need_dw, dres=dres)
+        assert rel_err(dx2.float(), xr.grad + dres.float()) < BF16_TOL
+        if need_dw:
+            assert torch.equal(dw2, dw) and torch.equal(db2, db) or rel_err(dw2, dw) < 1e-5
 
 
 def test_gelu(K):
